@@ -1,0 +1,317 @@
+#!/usr/bin/env python
+"""bench.py - transcript tokens/s of preprocess+chunk (BASELINE.json metric) on N B200s.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--config 3] [--scale 1.0]
+  python bench.py --impl reference ...     # the reference-equivalent CPU path (oracle port) on host cores
+
+One step = one pass of the whole hot path (trc_preprocess + trc_chunk) over one batch of synthetic
+transcripts.  `value` is measured with the inputs already resident in HBM; `e2e` is the same metric
+through the C ABI with pinned HOST buffers (H2D of the inputs and D2H of every result array inside the
+timed region).  One process per GPU; documents shard across ranks with no collective,
+so torch.distributed is only used for the barrier and the max-over-ranks of the device times.
+"""
+import argparse, json, os, subprocess, sys, threading, time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "transcript tokens/sec preprocess+chunk"
+UNIT = "tokens/s"
+OUT_ARRAYS = [("K2R", "<i4"), ("COFF", "<i8"), ("CLEAN", "u1"), ("GSTART", "<i4"), ("POFF", "<i8"), ("GTS", "u1"),
+              ("GTOK", "<i8"), ("ITEM_GROUP", "<i4"), ("ITEM_SUB", "<i4"), ("ITEM_TOK", "<i4"), ("ITEM_LEN", "<i8"),
+              ("ITEM_DST", "<i8"), ("SUBS", None), ("CHUNKS", None), ("SPK_LIST", "<i4"), ("TWC", "u1"), ("DOC_ERR", "<i4"),
+              ("GDOC_OFF", "<i8"), ("CDOC_OFF", "<i8")]
+
+
+def workload(args, rank):
+    from llm_map_reduce_summarizer_b200 import synth
+    b, mt, desc = synth.config(args.config, args.scale)
+    if rank:
+        # weak scaling: every rank gets its own shard of the same shape (different seed)
+        saved = synth.BASE_SEED
+        synth.BASE_SEED = saved + 1000 * rank
+        try:
+            b, mt, desc = synth.config(args.config, args.scale)
+        finally:
+            synth.BASE_SEED = saved
+    return b, mt, desc
+
+
+def algorithmic_bytes(c):
+    """compulsory traffic of the whole path, each byte once."""
+    return c["b_raw"] + 28 * c["n_seg"] + c["b_clean"] + c["b_twc"] + 40 * c["n_groups"] + 64 * c["n_chunks"]
+
+
+KERNEL_BYTES = {  # algorithmic bytes of one launch of the named kernel
+    "k_count_units": lambda c: c["b_clean"] + 16 * c["n_kept"] + 8 * c["n_kept"],
+    "k_clean_count": lambda c: c["b_raw"] + 8 * c["n_seg"] + 16 * c["n_seg"],
+    "k_clean_write": lambda c: c["b_raw"] + c["b_clean"] + 12 * c["n_kept"],
+    "k_emit_chunk_pieces": lambda c: c["b_clean"] + c["b_twc"] + 24 * c["n_kept"],
+    "k_emit_merged": lambda c: c["b_clean"] + c["b_merged"] + 24 * c["n_kept"],
+    "k_clean_tok_fused": lambda c: c["b_raw"] + c["b_clean"] + 28 * c["n_seg"],
+}
+
+
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.rows, self.p = [], None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                       "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append(line.strip().split(", "))
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+                for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[2:6]):
+                    if v.strip() == "Active":
+                        reasons.add(name)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def oracle_docs(args_tuple):
+    """Worker: reference-equivalent CPU path (oracle) on a list of documents; returns tokens."""
+    docs, mts = args_tuple
+    from oracle import chunker as OC, preprocess as OP
+    tok = 0
+    for segs, mt in zip(docs, mts):
+        proc = OP.preprocess(segs)
+        ch = OC.ChunkerOracle(int(mt)).chunk(proc)
+        tok += sum(c["token_count"] for c in ch)
+    return tok
+
+
+def cpu_sample(b, mt, max_docs, max_bytes):
+    from llm_map_reduce_summarizer_b200 import synth
+    docs, mts, nbytes = [], [], 0
+    for x in range(min(b.n_doc, max_docs)):
+        docs.append(synth.doc_to_segments(b, x))
+        mts.append(int(mt[x]))
+        nbytes += int(b.seg_off[b.doc_off[x + 1]] - b.seg_off[b.doc_off[x]])
+        if nbytes >= max_bytes:
+            break
+    return docs, mts, nbytes
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation is pure Python + tiktoken's Rust CoreBPE;
+    /root/reference does not exist on the GPU box, so this arm times the oracle port of it (same Python
+    control flow, the same real CoreBPE, Punkt restated) on all host cores, one process per core."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import multiprocessing as mp
+    b, mt, desc = workload(args, 0)
+    cores = os.cpu_count() or 1
+    docs, mts, nbytes = cpu_sample(b, mt, 100000, args.cpu_sample_mb * 1e6)
+    parts = [(docs[i::cores], mts[i::cores]) for i in range(cores)] if len(docs) >= cores else [(docs, mts)]
+    used = len(parts)
+    ctx = mp.get_context("fork")
+    with ctx.Pool(used) as pool:
+        for _ in range(args.warmup):
+            pool.map(oracle_docs, parts)
+        t0 = time.perf_counter()
+        tok = 0
+        for _ in range(args.steps):
+            tok = sum(pool.map(oracle_docs, parts))
+        dt = time.perf_counter() - t0
+    val = tok * args.steps / dt
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "config %d: %s" % (args.config, desc), "scale": args.scale},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": used, "kind": "port",
+                             "sample": "%d documents / %.1f MB of the workload per step, oracle port (Python + tiktoken CoreBPE), "
+                                       "one process per core" % (len(docs), nbytes / 1e6)},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--config", type=int, default=3)
+    ap.add_argument("--scale", type=float, default=1.0)
+    ap.add_argument("--cpu-sample-mb", type=float, default=12.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    from llm_map_reduce_summarizer_b200 import build, engine as E, _native as N
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: the path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    build.build()
+    eng = E.Engine(local)
+    b, mt, desc = workload(args, rank)
+    dev = torch.device("cuda", local)
+    st = torch.cuda.current_stream()
+    sp = st.cuda_stream
+
+    def dev_t(a):
+        return torch.from_numpy(a).to(dev)
+
+    dt = {k: dev_t(getattr(b, k)) for k in ("text", "seg_off", "start", "end", "speaker", "doc_off", "spk_bytes", "spk_off")}
+    ptrs = {k: v.data_ptr() for k, v in dt.items()}
+
+    def step_resident():
+        eng.preprocess(b, want_merged_text=False, stream=sp, device_ptrs=ptrs)
+        eng.chunk(mt, stream=sp)
+
+    # pinned host staging for the e2e path
+    pin_in = {k: torch.from_numpy(getattr(b, k)).pin_memory() for k in ("text", "seg_off", "start", "end", "speaker", "doc_off")}
+    hb = E.PackedBatch(pin_in["text"].numpy(), pin_in["seg_off"].numpy(), pin_in["start"].numpy(), pin_in["end"].numpy(),
+                       pin_in["speaker"].numpy(), pin_in["doc_off"].numpy(), b.speakers, None)
+    pin_out = {}
+
+    def step_e2e():
+        eng.preprocess(hb, want_merged_text=False, stream=sp)
+        eng.chunk(mt, stream=sp)
+        total = 0
+        for name, _ in OUT_ARRAYS:
+            nb = eng.array_into(name, None, 0)
+            if name not in pin_out or pin_out[name].numel() < nb:
+                pin_out[name] = torch.empty(max(nb, 1) + max(nb, 1) // 8, dtype=torch.uint8).pin_memory()
+            if nb:
+                eng.array_into(name, pin_out[name].data_ptr(), pin_out[name].numel(), N.TRC_MEM_HOST, sp)
+            total += nb
+        return total
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record(st)
+        for _ in range(steps):
+            fn()
+        e1.record(st)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    for _ in range(args.warmup):
+        step_resident()
+    counts = eng.counts()
+    clocks = ClockSampler(local)
+    l0 = eng.launches()
+    ms = timed(step_resident, args.steps)
+    launches = eng.launches() - l0
+    clk = clocks.stop()
+    tokens_local = counts["tokens"]
+    if world > 1:
+        t = torch.tensor([tokens_local], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        tokens_all = float(t.item())
+    else:
+        tokens_all = float(tokens_local)
+    value = tokens_all * args.steps / (ms / 1e3)
+
+    # per-kernel device times (events around each launch) -> roofline of the dominant kernel
+    eng.set_profiling(True)
+    for _ in range(args.steps):
+        step_resident()
+    prof = eng.profile()
+    eng.set_profiling(False)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    tot_ms = sum(v[0] for v in prof.values()) or 1.0
+    top = max(prof.items(), key=lambda kv: kv[1][0])
+    tname, (tms, tn) = top
+    kb = KERNEL_BYTES.get(tname, lambda c: 0)(counts)
+    per_launch_ms = tms / max(tn, 1)
+    ach = kb / (per_launch_ms / 1e3) / 1e9 if per_launch_ms > 0 else 0.0
+    A = algorithmic_bytes(counts)
+    pipe_gbs = A * args.steps / (ms / 1e3) / 1e9 if world == 1 else None
+    roofline = {"bound": "hbm", "kernel": tname, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": kb,
+                "kernel_ms_per_launch": per_launch_ms, "kernel_share_of_step": tms / tot_ms,
+                "pipeline": {"algorithmic_bytes_per_step": A, "achieved_gbs": pipe_gbs,
+                             "frac": (pipe_gbs / peak) if pipe_gbs else None},
+                "kernels_ms_per_step": {k: v[0] / args.steps for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0])}}
+
+    # end to end through the C ABI with host buffers
+    for _ in range(2):
+        d2h = step_e2e()
+    ms_e2e = timed(step_e2e, args.steps)
+    h2d = int(sum(getattr(b, k).nbytes for k in ("text", "seg_off", "start", "end", "speaker", "doc_off", "spk_bytes", "spk_off")))
+    e2e = {"value": tokens_all * args.steps / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+           "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps,
+           "api": "trc_preprocess + trc_chunk + trc_get_array (C ABI, pinned host buffers)"}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        docs, mts, nbytes = cpu_sample(b, mt, 100000, args.cpu_sample_mb * 1e6)
+        t0 = time.perf_counter()
+        tok = oracle_docs((docs, mts))
+        dtc = time.perf_counter() - t0
+        cpu = {"value": tok / dtc, "unit": UNIT, "cores": 1, "kind": "port",
+               "sample": "first %d documents (%.1f MB raw text) of the workload, %.1f s, oracle port (Python + tiktoken CoreBPE)"
+                         % (len(docs), nbytes / 1e6, dtc)}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "u8", "data": "synthetic",
+                "config": {"workload": "config %d: %s" % (args.config, desc), "scale": args.scale,
+                           "docs_per_gpu": b.n_doc, "segments_per_gpu": b.n_seg, "raw_text_bytes_per_gpu": int(counts["b_raw"]),
+                           "tokens_per_gpu_per_step": int(tokens_local), "chunks_per_gpu": counts["n_chunks"],
+                           "rank_table": eng.vocab_name, "l2": "inputs larger than L2 (text + segment arrays > 126 MB)"
+                           if h2d > 126e6 else "inputs smaller than L2: numbers are L2-warm",
+                           "parallelism": "documents sharded by rank, no collective"},
+                "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline}
+        if cpu:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,159 @@
+/* trchunk - C ABI of the B200 (sm_100a) preprocess+chunk library  (libtrchunk.so)
+ *
+ * The reference (consilience-dev/llm-map-reduce-summarizer) is pure Python and has no FFI; its boundary
+ * for this path is the Python import surface used at /root/reference/main.py:27-28,139-149.  The entry
+ * points below are what a ctypes binding of that surface needs: packed transcripts in, packed
+ * processed-segments / chunks out.  The drop-in modules that wrap them with the reference's exact
+ * Python signatures live in llm_map_reduce_summarizer_b200/{preprocessor,big_chunkeroosky}.py and the
+ * binding a maintainer would add to the reference is shown in INTEGRATION.md.
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 or a negative TRC_E* code and
+ * leaves a message for trc_last_error(); a context is bound to one CUDA device and must not be used
+ * from two threads at once; `stream` is a cudaStream_t passed as void* (NULL = the context's own).
+ * Input pointers are HOST pointers when `memory == TRC_MEM_HOST` (the library copies them to the
+ * device inside the call) or DEVICE pointers when `memory == TRC_MEM_DEVICE` (used in place).
+ */
+#ifndef TRCHUNK_H
+#define TRCHUNK_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TRC_OK 0
+#define TRC_ECUDA (-1)      /* CUDA runtime error, no device, or wrong architecture            */
+#define TRC_EINVAL (-2)     /* bad argument / call order                                        */
+#define TRC_ENOVOCAB (-3)   /* tables or vocabulary not loaded                                   */
+#define TRC_EUNSUPPORTED (-4) /* input outside the supported domain (reported, never approximated) */
+
+#define TRC_MEM_HOST 0
+#define TRC_MEM_DEVICE 1
+
+typedef struct trc_ctx trc_ctx;
+
+/* Life cycle.  trc_create fails (TRC_ECUDA) when no sm_100 device is present: there is no CPU path. */
+int trc_create(int device, trc_ctx** out);
+void trc_destroy(trc_ctx* ctx);
+const char* trc_last_error(trc_ctx* ctx);
+
+/* Unicode property table, one byte per code point (0x110000 entries, layout in
+ * tools/gen_unicode_tables.py).  Replaces the tables CPython's str.split()/re and the Rust regex crate
+ * carry internally (preprocessor.py:38,80,84; tiktoken pattern classes). */
+int trc_load_tables(trc_ctx* ctx, const uint8_t* props);
+
+/* Rank table of the BPE vocabulary + special-token literals.  Replaces
+ * tiktoken.get_encoding(tokenizer_name) at big_chunkeroosky.py:43 (rank == token id). */
+int trc_load_vocab(trc_ctx* ctx, const uint8_t* token_bytes, const int64_t* token_off, const int32_t* ranks,
+                   int32_t n_tokens, const uint8_t* special_bytes, const int64_t* special_off, int32_t n_special);
+
+/* A batch of transcripts ("documents").  Segment i owns text[seg_off[i] .. seg_off[i+1]) (UTF-8);
+ * document x owns segments [doc_off[x], doc_off[x+1]).  speaker[i] indexes the speaker string table,
+ * whose ids MUST be assigned in code-point order of the strings and MUST contain "" as id 0
+ * (big_chunkeroosky.py:166 sorts speakers; :485 uses ""). */
+typedef struct {
+  const uint8_t* text;
+  const int64_t* seg_off;      /* n_seg + 1 */
+  const double* start;         /* n_seg     */
+  const double* end;           /* n_seg     */
+  const int32_t* speaker;      /* n_seg     */
+  int64_t n_seg;
+  const int64_t* doc_off;      /* n_doc + 1 */
+  int64_t n_doc;
+  const uint8_t* spk_bytes;
+  const int64_t* spk_off;      /* n_spk + 1 */
+  int32_t n_spk;
+  int32_t memory;              /* TRC_MEM_HOST / TRC_MEM_DEVICE */
+  int32_t merge_same_speaker;  /* preprocessor.py:17 */
+  int32_t has_max_duration;    /* 0 == max_segment_duration is None, preprocessor.py:19,141 */
+  double max_duration;
+  int32_t preserve_timestamps; /* preprocessor.py:20 */
+  int32_t want_merged_text;    /* 1: also materialise the merged text buffer (TRC_A_MERGED) */
+} trc_batch;
+
+/* Stage P: preprocessor.preprocess_transcript (preprocessor.py:15-67) for every document of the batch:
+ * blank filter, clean_text, timestamp formatting, same-speaker merge, token count of every cleaned
+ * segment.  Results stay on the device inside the context until the next trc_preprocess. */
+int trc_preprocess(trc_ctx* ctx, const trc_batch* batch, void* stream);
+
+/* Stage C: BigChunkeroosky.chunk_transcript + postprocess_chunks (big_chunkeroosky.py:46-145,544-567)
+ * on the result of the last trc_preprocess.  doc_max_tokens[x] is max_tokens_per_chunk of document x
+ * (host pointer, n_doc entries); context_tokens as in big_chunkeroosky.py:28,42. */
+int trc_chunk(trc_ctx* ctx, const int32_t* doc_max_tokens, int32_t context_tokens, int32_t add_context,
+              void* stream);
+
+/* Counters of the current batch. */
+enum {
+  TRC_N_SEG = 0, TRC_N_KEPT, TRC_N_GROUPS, TRC_N_ITEMS, TRC_N_SUBS, TRC_N_CHUNKS, TRC_B_RAW, TRC_B_CLEAN,
+  TRC_B_MERGED, TRC_B_TWC, TRC_TOKENS, TRC_N_DOC, TRC_N_LONG_SPANS, TRC_N_ERR_DOCS, TRC_N_SENT, TRC_N_COUNTERS = 24
+};
+int trc_get_counts(trc_ctx* ctx, int64_t* counts /* TRC_N_COUNTERS */);
+
+/* Result arrays (device resident).  trc_get_array copies array `which` to dst (host or device memory
+ * per `memory`); with dst == NULL it only reports the size in bytes. */
+enum {
+  TRC_A_K2R = 0,      /* int32 [n_kept]      raw index of every kept (non-blank) segment                  */
+  TRC_A_COFF,         /* int64 [n_kept+1]    offsets into TRC_A_CLEAN                                      */
+  TRC_A_CLEAN,        /* uint8 [B_clean]     cleaned segment text (preprocessor.py:69-89)                  */
+  TRC_A_CTOK,         /* uint32[n_kept]      tokens of " " + cleaned text                                  */
+  TRC_A_GSTART,       /* int32 [m+1]         first kept segment of every merged segment                    */
+  TRC_A_POFF,         /* int64 [n_kept+1]    piece offsets into TRC_A_MERGED                               */
+  TRC_A_MERGED,       /* uint8 [B_merged]    merged segment text, groups back to back                      */
+  TRC_A_GTS,          /* uint8 [m*48]        start_formatted / end_formatted, 24-byte slots [len][chars]   */
+  TRC_A_GTOK,         /* int64 [m]           tokens of "[ts] speaker: text" (big_chunkeroosky.py:83)        */
+  TRC_A_ITEM_GROUP,   /* int32 [n_items]                                                                  */
+  TRC_A_ITEM_SUB,     /* int32 [n_items]     index into TRC_A_SUBS or -1                                   */
+  TRC_A_ITEM_TOK,     /* int32 [n_items]                                                                  */
+  TRC_A_ITEM_LEN,     /* int64 [n_items]     bytes of the item text inside TRC_A_TWC                       */
+  TRC_A_ITEM_DST,     /* int64 [n_items]     offset of the item text inside TRC_A_TWC                      */
+  TRC_A_SUBS,         /* trc_sub [n_subs]                                                                 */
+  TRC_A_CHUNKS,       /* trc_chunk_rec [n_chunks]                                                         */
+  TRC_A_SPK_LIST,     /* int32 [n_items]     sorted speaker ids of chunk c at [item0, item0+n_speakers)    */
+  TRC_A_TWC,          /* uint8 [B_twc]       text_with_context of all chunks back to back                  */
+  TRC_A_DOC_ERR,      /* int32 [n_doc]       0 ok, 1+k: special token k in the text (tiktoken ValueError), */
+                      /*                     -1 unsupported input                                          */
+  TRC_A_GDOC_OFF,     /* int64 [n_doc+1]     merged-segment range of every document                        */
+  TRC_A_CDOC_OFF,     /* int64 [n_doc+1]     chunk range of every document                                 */
+  TRC_A_CCHARS,       /* int32 [n_seg]       code points of the cleaned text of every RAW segment          */
+  TRC_A_SENT,         /* trc_sent [n_sent]   sentence / clause records of the sentence path                */
+  TRC_A__COUNT
+};
+int trc_get_array(trc_ctx* ctx, int which, void* dst, int64_t dst_bytes, int32_t memory, int64_t* nbytes,
+                  void* stream);
+
+/* Record layouts of TRC_A_SUBS / TRC_A_CHUNKS / TRC_A_SENT (mirrored by ctypes.Structure in _native.py). */
+typedef struct {
+  int32_t group, kind, r0, r1, start_src, end_src, tok, pad;
+  double start, end;
+  int64_t text_len;
+} trc_sub;
+
+typedef struct {
+  int32_t item0, item1, doc, chunk_index;
+  int64_t token_count;
+  double start_time, end_time, position_percentage;
+  int32_t pct_is_int_zero, start_kind, start_ref, n_speakers, hdr_len, err;
+  int64_t text_len, twc_off;
+} trc_chunk_rec;
+
+/* Token counting service: counts[i] = len(encode([" "] + bytes[off[i] .. off[i+1]))) for n strings.
+ * Replaces len(self.tokenizer.encode(x)) (big_chunkeroosky.py:83,298,370,510).  special[i] (may be
+ * NULL) receives the index of a special-token literal found in string i, or -1. */
+int trc_count_tokens(trc_ctx* ctx, const uint8_t* bytes, const int64_t* off, int64_t n, int32_t leading_space,
+                     int32_t memory, uint32_t* counts, int32_t* special, void* stream);
+
+/* Wall-clock free timing helper: device time in ms of the last trc_preprocess / trc_chunk pair, measured
+ * with CUDA events on the stream they ran on (0 if events were not recorded). */
+int trc_last_stage_ms(trc_ctx* ctx, float* preprocess_ms, float* chunk_ms);
+int trc_kernel_launches(trc_ctx* ctx, int64_t* launches);
+
+/* Per-kernel device timing for bench.py's roofline line: with profiling on, every kernel launch is
+ * bracketed by CUDA events on its stream; trc_get_profile returns "name total_ms launches\n" lines
+ * accumulated since profiling was switched on.  (No reference counterpart: the reference only has
+ * time.time() around the whole run, main.py:110,239.) */
+int trc_set_profiling(trc_ctx* ctx, int32_t on);
+int trc_get_profile(trc_ctx* ctx, char* buf, int64_t buf_bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

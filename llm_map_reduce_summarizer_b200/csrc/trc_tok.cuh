@@ -1,0 +1,176 @@
+// K2: token counting = cl100k pre-tokenisation (hand matcher with the regex's leftmost-first
+// alternation semantics) + byte-pair merge by minimum rank, leftmost on ties.
+// Replaces `len(self.tokenizer.encode(x))` at /root/reference/big_chunkeroosky.py:83,298,370,510, i.e. the
+// Rust CoreBPE of tiktoken==0.5.1 (third party, not under /root/reference; algorithm restated from
+// tiktoken/_educational.py:83-116 and the 0.5.1 pattern string, see oracle/tokenizer.py).
+//
+// A "unit" is a UTF-8 byte range with an optional VIRTUAL leading U+0020: every string the reference
+// tokenises decomposes at guaranteed match boundaries into  "[ts]" + " speaker:" + " text"  (DESIGN.md
+// §3), so the kernels count  " " + text  without ever materialising the concatenation.
+#pragma once
+#include "trc_common.cuh"
+
+struct TrcStr {        // logical string = [' '] + p[0..n)
+  const uint8_t* p;
+  int64_t n;           // logical length (including the virtual space)
+  int vs;              // 1 if a virtual leading space is present
+  TRC_HD uint8_t at(int64_t i) const { return (vs && i == 0) ? (uint8_t)' ' : p[i - vs]; }
+};
+
+TRC_HD uint32_t trc_sdecode(const TrcStr& S, int64_t i, int* len) {
+  if (S.vs && i == 0) { *len = 1; return ' '; }
+  return trc_decode(S.p, i - S.vs, S.n - S.vs, len);
+}
+
+// End (exclusive, logical index) of the regex match that starts at logical index p.
+// Alternatives in pattern order:
+//  1 (?i:'s|'t|'re|'ve|'m|'ll|'d)   2 [^\r\n\p{L}\p{N}]?\p{L}+   3 \p{N}{1,3}
+//  4  ?[^\s\p{L}\p{N}]+[\r\n]*      5 \s*[\r\n]+   6 \s+(?!\S)   7 \s+
+TRC_HD int64_t trc_span_end(const TrcTables& T, const TrcStr& S, int64_t p) {
+  const int64_t N = S.n;
+  int l0, l1 = 0, l2 = 0;
+  uint32_t c0 = trc_sdecode(S, p, &l0);
+  uint32_t k0 = TRC_RS(trc_prop(T, c0));
+  bool has1 = p + l0 < N;
+  uint32_t c1 = 0, k1 = 9;
+  if (has1) { c1 = trc_sdecode(S, p + l0, &l1); k1 = TRC_RS(trc_prop(T, c1)); }
+  if (c0 == '\'' && has1) {
+    uint32_t a = c1;
+    if (a == 's' || a == 'S' || a == 't' || a == 'T' || a == 'm' || a == 'M' || a == 'd' || a == 'D' || a == 0x17F)
+      return p + l0 + l1;
+    if (p + l0 + l1 < N) {
+      uint32_t b = trc_sdecode(S, p + l0 + l1, &l2);
+      bool e = (b == 'e' || b == 'E');
+      if (((a == 'r' || a == 'R') && e) || ((a == 'v' || a == 'V') && e) ||
+          ((a == 'l' || a == 'L') && (b == 'l' || b == 'L')))
+        return p + l0 + l1 + l2;
+    }
+  }
+  {  // alt 2
+    int64_t q = p;
+    uint32_t kq = k0;
+    if (k0 != TRC_RS_L && k0 != TRC_RS_N && c0 != '\r' && c0 != '\n' && has1 && k1 == TRC_RS_L) { q = p + l0; kq = k1; }
+    if (kq == TRC_RS_L) {
+      while (q < N) {
+        int l; uint32_t c = trc_sdecode(S, q, &l);
+        if (TRC_RS(trc_prop(T, c)) != TRC_RS_L) break;
+        q += l;
+      }
+      return q;
+    }
+  }
+  if (k0 == TRC_RS_N) {  // alt 3
+    int64_t q = p + l0;
+    int cnt = 1;
+    while (q < N && cnt < 3) {
+      int l; uint32_t c = trc_sdecode(S, q, &l);
+      if (TRC_RS(trc_prop(T, c)) != TRC_RS_N) break;
+      q += l; ++cnt;
+    }
+    return q;
+  }
+  {  // alt 4
+    int64_t q = p;
+    uint32_t kq = k0;
+    if (c0 == ' ' && has1 && k1 == TRC_RS_O) { q = p + l0; kq = k1; }
+    if (kq == TRC_RS_O) {
+      while (q < N) {
+        int l; uint32_t c = trc_sdecode(S, q, &l);
+        if (TRC_RS(trc_prop(T, c)) != TRC_RS_O) break;
+        q += l;
+      }
+      while (q < N) { uint8_t b = S.at(q); if (b != '\r' && b != '\n') break; ++q; }
+      return q;
+    }
+  }
+  // whitespace run [p, r)
+  int64_t r = p, last_nl = -1, last_start = p;
+  while (r < N) {
+    int l; uint32_t c = trc_sdecode(S, r, &l);
+    if (TRC_RS(trc_prop(T, c)) != TRC_RS_S) break;
+    if (c == '\r' || c == '\n') last_nl = r;
+    last_start = r;
+    r += l;
+  }
+  if (last_nl >= 0) return last_nl + 1;      // alt 5: through the last newline of the run
+  if (r == N) return r;                      // alt 6 at end of string
+  if (last_start > p) return last_start;     // alt 6: leave the last whitespace char to the next match
+  return r;                                  // alt 7
+}
+
+// Is the byte string a vocabulary entry?  (tiktoken: `if piece in ranks` => one token)
+TRC_HD bool trc_is_token(const TrcTables& T, const TrcStr& S, int64_t a, int n) {
+  uint64_t h = trc_hash_bytes([&](int i) { return S.at(a + i); }, n);
+  uint32_t fp = (uint32_t)(h >> 32);
+  uint32_t slot = (uint32_t)h & T.tokhash_mask;
+  for (;;) {
+    uint64_t e = T.tokhash[slot];
+    if (e == ~0ULL) return false;
+    if ((uint32_t)(e >> 32) == fp) {
+      uint32_t id = (uint32_t)e;
+      uint32_t o = T.tok_off[id];
+      if ((int)(T.tok_off[id + 1] - o) == n) {
+        bool eq = true;
+        for (int i = 0; i < n; ++i) if (T.tok_bytes[o + i] != S.at(a + i)) { eq = false; break; }
+        if (eq) return true;
+      }
+    }
+    slot = (slot + 1) & T.tokhash_mask;
+  }
+}
+
+// Byte-pair merge of a short span held in thread-local arrays; returns the number of parts left.
+TRC_HD int trc_bpe_short(const TrcTables& T, const uint32_t* byte_id, const TrcStr& S, int64_t a, int n) {
+  uint32_t id[TRC_SHORT_SPAN];
+  uint32_t rk[TRC_SHORT_SPAN];
+  for (int i = 0; i < n; ++i) id[i] = byte_id[S.at(a + i)];
+  int m = n;
+  for (int i = 0; i + 1 < m; ++i) rk[i] = trc_pair_rank(T, id[i], id[i + 1]);
+  for (;;) {
+    uint32_t best = TRC_NO_RANK; int bi = -1;
+    for (int i = 0; i + 1 < m; ++i) if (rk[i] < best) { best = rk[i]; bi = i; }
+    if (bi < 0) break;
+    id[bi] = best;                       // rank of the merged bytes == its token id
+    for (int j = bi + 1; j + 1 < m; ++j) { id[j] = id[j + 1]; rk[j] = rk[j + 1]; }
+    --m;
+    if (bi + 1 < m) rk[bi] = trc_pair_rank(T, id[bi], id[bi + 1]); else rk[bi] = TRC_NO_RANK;
+    if (bi > 0) rk[bi - 1] = trc_pair_rank(T, id[bi - 1], id[bi]);
+  }
+  return m;
+}
+
+// Index of a special-token literal contained in the unit's real bytes, or -1.
+TRC_HD int trc_find_special(const TrcTables& T, const uint8_t* p, int64_t n) {
+  for (int64_t i = 0; i < n; ++i) {
+    uint8_t b = p[i];
+    for (uint32_t k = 0; k < T.n_sp; ++k) {
+      uint32_t o = T.sp_off[k], L = T.sp_off[k + 1] - o;
+      if (L == 0 || T.sp_bytes[o] != b || i + (int64_t)L > n) continue;
+      bool eq = true;
+      for (uint32_t j = 1; j < L; ++j) if (p[i + j] != T.sp_bytes[o + j]) { eq = false; break; }
+      if (eq) return (int)k;
+    }
+  }
+  return -1;
+}
+
+// Token count of one unit.  Spans longer than TRC_SHORT_SPAN that are not vocabulary entries are handed
+// to `long_span(logical_start, length)` which returns their count (device: deferred to the block-wide
+// long-span kernel and returns 0; hostsim: computed inline).
+template <class LongSpan>
+TRC_HD uint32_t trc_count_unit(const TrcTables& T, const uint32_t* byte_id, const uint8_t* p, int64_t nbytes, int vs,
+                               LongSpan&& long_span) {
+  TrcStr S; S.p = p; S.n = nbytes + vs; S.vs = vs;
+  uint32_t total = 0;
+  int64_t q = 0;
+  while (q < S.n) {
+    int64_t e = trc_span_end(T, S, q);
+    int64_t len = e - q;
+    if (len == 1) total += 1;
+    else if (len <= 0x7fffffff && trc_is_token(T, S, q, (int)len)) total += 1;
+    else if (len <= TRC_SHORT_SPAN) total += (uint32_t)trc_bpe_short(T, byte_id, S, q, (int)len);
+    else total += long_span(q, len);
+    q = e;
+  }
+  return total;
+}

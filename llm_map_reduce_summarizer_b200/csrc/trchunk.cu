@@ -1,0 +1,996 @@
+// libtrchunk.so - kernels + C ABI (include/trchunk.h).  Build: see llm_map_reduce_summarizer_b200/build.py
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo --fmad=false -shared -Xcompiler -fPIC
+// --fmad=false: the merge cap, sub-chunk times and the percentage are fp64 mul/add chains that CPython
+// evaluates without contraction (preprocessor.py:134-153, big_chunkeroosky.py:182-184,351-366,475-506).
+#ifdef TRC_HOSTSIM
+#include "trc_hostshim.h"
+#else
+#include <cuda_runtime.h>
+#endif
+#include <stdio.h>
+#include <string>
+#include <vector>
+#include "../../include/trchunk.h"
+#include "trc_common.cuh"
+#include "trc_format.cuh"
+#include "trc_clean.cuh"
+#include "trc_tok.cuh"
+#include "trc_stages.cuh"
+#include "trc_sent.cuh"
+#include "trc_vocab_host.h"
+
+static_assert(sizeof(TrcSub) == sizeof(trc_sub), "trc_sub layout");
+static_assert(sizeof(TrcChunk) == sizeof(trc_chunk_rec), "trc_chunk_rec layout");
+
+// =====================================================================================================
+// context
+// =====================================================================================================
+struct Arena {
+  struct Block { char* p; size_t cap; };
+  std::vector<Block> blocks;
+  size_t used = 0;       // in the last block
+  size_t total_req = 0;  // bytes requested since reset
+  cudaError_t err = cudaSuccess;
+  void* alloc(size_t bytes) {
+    bytes = (bytes + 255) & ~(size_t)255;
+    if (bytes == 0) bytes = 256;
+    total_req += bytes;
+    if (blocks.empty() || used + bytes > blocks.back().cap) {
+      size_t cap = bytes > (size_t)(64u << 20) ? bytes : (size_t)(64u << 20);
+      if (!blocks.empty() && cap < blocks.back().cap) cap = blocks.back().cap;
+      char* p = nullptr;
+      cudaError_t e = cudaMalloc(&p, cap);
+      if (e != cudaSuccess) { err = e; return nullptr; }
+      blocks.push_back({p, cap});
+      used = 0;
+    }
+    void* r = blocks.back().p + used;
+    used += bytes;
+    return r;
+  }
+  // Start a new batch.  If the previous one spilled into several blocks, fuse them so the steady state
+  // is a single block and no cudaMalloc happens inside a timed region.
+  void reset() {
+    if (blocks.size() > 1) {
+      size_t need = total_req + total_req / 4;
+      for (auto& b : blocks) cudaFree(b.p);
+      blocks.clear();
+      char* p = nullptr;
+      if (cudaMalloc(&p, need) == cudaSuccess) blocks.push_back({p, need});
+    }
+    used = 0; total_req = 0; err = cudaSuccess;
+  }
+  void release() { for (auto& b : blocks) cudaFree(b.p); blocks.clear(); used = 0; }
+};
+
+struct LongEntry { int64_t unit, lstart, len, scratch_off; };
+
+struct trc_ctx {
+  int device = 0;
+  cudaStream_t own_stream = nullptr;
+  std::string err;
+  bool have_tables = false, have_vocab = false;
+  TrcTables T{};
+  uint8_t* d_props = nullptr;
+  uint32_t* d_byte_id = nullptr;
+  std::vector<void*> vocab_allocs;
+  uint32_t n_special = 0;
+  Arena arena;
+  TrcDev D{};
+  bool have_pre = false, have_chunk = false;
+  int64_t counts[TRC_N_COUNTERS] = {0};
+  int64_t* h_pin = nullptr;        // pinned scratch for small D2H reads (64 int64)
+  int64_t launches = 0;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  bool ev_pre = false, ev_chunk = false;
+  // optional per-kernel timing (trc_set_profiling): events around every launch
+  bool prof = false;
+  struct ProfRec { const char* name; cudaEvent_t a, b; };
+  std::vector<ProfRec> prof_recs;
+  std::vector<cudaEvent_t> prof_pool;
+  struct ProfAcc { std::string name; double ms; int64_t launches; };
+  std::vector<ProfAcc> prof_acc;
+  // sentence path
+  TrcSentState SS{};
+  // result array table
+  struct Arr { const void* p; int64_t bytes; } arr[TRC_A__COUNT] = {};
+};
+
+#define CK(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) {                                                                       \
+      ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_);                               \
+      return TRC_ECUDA;                                                                            \
+    }                                                                                              \
+  } while (0)
+
+#define ALLOC(ptr, type, count)                                                                    \
+  do {                                                                                             \
+    ptr = (type*)ctx->arena.alloc(sizeof(type) * (size_t)((count) > 0 ? (count) : 1));             \
+    if (!ptr) { ctx->err = std::string("device allocation failed: ") + cudaGetErrorString(ctx->arena.err); return TRC_ECUDA; } \
+  } while (0)
+
+static inline int grid_for(int64_t n, int block) {
+  int64_t g = (n + block - 1) / block;
+  if (g < 1) g = 1;
+  const int64_t cap = 148LL * 64;   // grid-stride beyond 64 waves of 148 SMs
+  return (int)(g > cap ? cap : g);
+}
+#ifdef TRC_HOSTSIM
+#define GSTRIDE(i, n) for (int64_t i = 0; i < (n); ++i)
+#define WSTRIDE(w, n) for (int64_t w = 0; w < (n); ++w)
+#define TRC_LANE 0
+#define TRC_NL 1
+#else
+#define GSTRIDE(i, n) for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < (n); i += (int64_t)gridDim.x * blockDim.x)
+#define WSTRIDE(w, n) for (int64_t w = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5; w < (n); w += ((int64_t)gridDim.x * blockDim.x) >> 5)
+#define TRC_LANE (threadIdx.x & 31)
+#define TRC_NL 32
+#endif
+
+// =====================================================================================================
+// K3: single-pass exclusive prefix sum with decoupled look-back (hand written; no CUB).
+// Tiles take their index from an atomic counter, so a tile only ever waits on tiles that already run.
+// Descriptor word: status (2 bits: 0 empty, 1 aggregate, 2 inclusive prefix) | value (62 bits).
+// =====================================================================================================
+#ifndef TRC_HOSTSIM
+#define SCAN_T 256
+#define SCAN_I 8
+#define SCAN_TILE (SCAN_T * SCAN_I)
+
+__device__ __forceinline__ unsigned long long ld_relaxed(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+template <class TIn>
+__global__ void __launch_bounds__(SCAN_T) k_scan_lookback(const TIn* __restrict__ in, int64_t* __restrict__ out, int64_t n,
+                                                          int64_t addc, unsigned long long* desc /* [0]=tile counter, [1..]=tiles */) {
+  __shared__ unsigned int s_tile;
+  __shared__ long long s_wsum[SCAN_T / 32];
+  __shared__ long long s_prefix;
+  if (threadIdx.x == 0) s_tile = (unsigned int)atomicAdd(desc, 1ULL);
+  __syncthreads();
+  const unsigned tile = s_tile;
+  unsigned long long* d = desc + 1;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int64_t base = (int64_t)tile * SCAN_TILE + (int64_t)threadIdx.x * SCAN_I;
+  long long v[SCAN_I];
+  long long tsum = 0;
+#pragma unroll
+  for (int k = 0; k < SCAN_I; ++k) {
+    int64_t idx = base + k;
+    v[k] = idx < n ? (long long)in[idx] + addc : 0;
+    tsum += v[k];
+  }
+  long long x = tsum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { long long y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+  if (lane == 31) s_wsum[wid] = x;
+  __syncthreads();
+  if (wid == 0) {
+    long long w = lane < SCAN_T / 32 ? s_wsum[lane] : 0;
+#pragma unroll
+    for (int o = 1; o < SCAN_T / 32; o <<= 1) { long long y = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += y; }
+    if (lane < SCAN_T / 32) s_wsum[lane] = w;
+  }
+  __syncthreads();
+  const long long block_total = s_wsum[SCAN_T / 32 - 1];
+  const long long texcl = (wid ? s_wsum[wid - 1] : 0) + x - tsum;
+  if (wid == 0) {
+    long long excl = 0;
+    if (tile == 0) {
+      if (lane == 0) st_relaxed(&d[0], (2ULL << 62) | (unsigned long long)block_total);
+    } else {
+      if (lane == 0) st_relaxed(&d[tile], (1ULL << 62) | (unsigned long long)block_total);
+      long long idx = (long long)tile - 1;
+      for (;;) {
+        long long my = idx - lane;
+        unsigned long long dv = (2ULL << 62);
+        if (my >= 0) {
+          dv = ld_relaxed(&d[my]);
+          while ((dv >> 62) == 0) dv = ld_relaxed(&d[my]);
+        }
+        unsigned st = (unsigned)(dv >> 62);
+        long long val = (long long)(dv & ((1ULL << 62) - 1));
+        unsigned ball = __ballot_sync(0xffffffffu, st == 2);
+        int first = ball ? __ffs(ball) - 1 : 31;
+        long long c = lane <= first ? val : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+        excl += c;
+        if (ball) break;
+        idx -= 32;
+      }
+      if (lane == 0) st_relaxed(&d[tile], (2ULL << 62) | (unsigned long long)(excl + block_total));
+    }
+    if (lane == 0) s_prefix = excl;
+  }
+  __syncthreads();
+  long long p = s_prefix + texcl;
+#pragma unroll
+  for (int k = 0; k < SCAN_I; ++k) {
+    int64_t idx = base + k;
+    if (idx < n) { out[idx] = p; p += v[k]; if (idx == n - 1) out[n] = p; }
+  }
+}
+
+#endif
+struct ScanWs { unsigned long long* desc; size_t cap_tiles; };
+
+static void prof_begin(trc_ctx* ctx, cudaStream_t st, const char* name);
+static void prof_end(trc_ctx* ctx, cudaStream_t st);
+template <class TIn>
+static int scan_excl(trc_ctx* ctx, cudaStream_t st, const TIn* in, int64_t* out, int64_t n, int64_t addc = 0) {
+  if (n <= 0) { CK(cudaMemsetAsync(out, 0, sizeof(int64_t), st)); return TRC_OK; }
+#ifdef TRC_HOSTSIM
+  { int64_t acc = 0; for (int64_t i = 0; i < n; ++i) { out[i] = acc; acc += (int64_t)in[i] + addc; } out[n] = acc; (void)st; return TRC_OK; }
+#else
+  int64_t tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+  unsigned long long* desc;
+  ALLOC(desc, unsigned long long, tiles + 1);
+  CK(cudaMemsetAsync(desc, 0, sizeof(unsigned long long) * (size_t)(tiles + 1), st));
+  prof_begin(ctx, st, "k_scan_lookback");
+  k_scan_lookback<TIn><<<(unsigned)tiles, SCAN_T, 0, st>>>(in, out, n, addc, desc);
+  prof_end(ctx, st);
+  ctx->launches++;
+  CK(cudaGetLastError());
+  return TRC_OK;
+#endif
+}
+
+// =====================================================================================================
+// kernels (thin wrappers around the per-unit routines)
+// =====================================================================================================
+__global__ void k_clean_count(TrcDev D, TrcTables T, int32_t* keep) {
+  GSTRIDE(i, D.n) {
+    int64_t a = D.seg_off[i], b = D.seg_off[i + 1];
+    TrcCleanOut r = trc_clean_segment<false>(T, D.text + a, b - a, nullptr);
+    D.clen[i] = r.bytes; D.cchars[i] = (int32_t)r.chars; keep[i] = r.bytes > 0;
+  }
+}
+
+__global__ void k_compact(TrcDev D, const int32_t* keep) {
+  GSTRIDE(i, D.n) {
+    if (keep[i]) {
+      int64_t j = D.kscan[i];
+      D.k2r[j] = (int32_t)i; D.coff[j] = D.cscan[i];
+      int64_t lo = 0, hi = D.n_doc;            // document of segment i: last x with doc_off[x] <= i
+      while (hi - lo > 1) { int64_t mid = (lo + hi) >> 1; if (D.doc_off[mid] <= i) lo = mid; else hi = mid; }
+      D.sdoc[j] = (int32_t)lo;
+    }
+    if (i == D.n - 1) D.coff[D.kscan[D.n]] = D.cscan[D.n];
+  }
+}
+
+__global__ void k_map_off(const int64_t* __restrict__ src_off, const int64_t* __restrict__ scan, int64_t* __restrict__ dst, int64_t n1) {
+  GSTRIDE(x, n1) dst[x] = scan[src_off[x]];
+}
+
+__global__ void k_clean_write(TrcDev D, TrcTables T) {
+  GSTRIDE(j, D.n_kept) {
+    int32_t r = D.k2r[j];
+    int64_t a = D.seg_off[r], b = D.seg_off[r + 1];
+    trc_clean_segment<true>(T, D.text + a, b - a, D.C + D.coff[j]);
+  }
+}
+
+#ifdef TRC_HOSTSIM
+static uint32_t hostsim_bpe_long(const TrcTables& T, const uint32_t* byte_id, const TrcStr& S, int64_t a, int64_t len) {
+  std::vector<uint32_t> id((size_t)len);
+  for (int64_t i = 0; i < len; ++i) id[i] = byte_id[S.at(a + i)];
+  for (;;) {
+    uint32_t best = TRC_NO_RANK; int64_t bi = -1;
+    for (int64_t i = 0; i + 1 < (int64_t)id.size(); ++i) { uint32_t r = trc_pair_rank(T, id[i], id[i + 1]); if (r < best) { best = r; bi = i; } }
+    if (bi < 0) break;
+    id[bi] = best; id.erase(id.begin() + bi + 1);
+  }
+  return (uint32_t)id.size();
+}
+#endif
+__global__ void k_count_units(TrcTables T, const uint32_t* __restrict__ byte_id, const uint8_t* __restrict__ bytes,
+                              const int64_t* __restrict__ ustart, const int64_t* __restrict__ uend, int64_t n, int vs,
+                              uint32_t* __restrict__ counts, int32_t* __restrict__ special, LongEntry* wl,
+                              unsigned long long* wl_cnt, int64_t wl_cap) {
+  GSTRIDE(j, n) {
+    const uint8_t* p = bytes + ustart[j];
+    int64_t nb = uend[j] - ustart[j];
+    uint32_t c = trc_count_unit(T, byte_id, p, nb, vs, [&](int64_t ls, int64_t len) -> uint32_t {
+#ifdef TRC_HOSTSIM
+      TrcStr S; S.p = p; S.n = nb + vs; S.vs = vs;
+      atomicAdd(&wl_cnt[0], 1ULL);
+      if (true) return hostsim_bpe_long(T, byte_id, S, ls, len);
+#endif
+      unsigned long long slot = atomicAdd(&wl_cnt[0], 1ULL);
+      unsigned long long off = atomicAdd(&wl_cnt[1], (unsigned long long)len);
+      if ((int64_t)slot < wl_cap) { LongEntry e; e.unit = j; e.lstart = ls; e.len = len; e.scratch_off = (int64_t)off; wl[slot] = e; }
+      return 0u;
+    });
+    counts[j] = c;
+    if (special) special[j] = trc_find_special(T, p, nb);
+  }
+}
+
+#ifndef TRC_HOSTSIM
+// Byte-pair merge of one long span per block; the four work arrays live in global scratch.
+#define LONG_T 256
+__global__ void __launch_bounds__(LONG_T) k_bpe_long(TrcTables T, const uint32_t* __restrict__ byte_id, const uint8_t* __restrict__ bytes,
+                                                     const int64_t* __restrict__ ustart, const int64_t* __restrict__ uend, int vs,
+                                                     uint32_t* counts, const LongEntry* __restrict__ wl, int64_t n_entries,
+                                                     uint32_t* __restrict__ scratch /* 4 words per span byte */, int64_t scratch_total) {
+  __shared__ unsigned long long s_red[LONG_T / 32];
+  __shared__ unsigned long long s_best;
+  for (int64_t w = blockIdx.x; w < n_entries; w += gridDim.x) {
+    const LongEntry e = wl[w];
+    TrcStr S; S.p = bytes + ustart[e.unit]; S.vs = vs; S.n = uend[e.unit] - ustart[e.unit] + vs;
+    const int64_t len = e.len;
+    uint32_t* id = scratch + e.scratch_off;
+    uint32_t* rk = scratch + scratch_total + e.scratch_off;
+    int32_t* nx = (int32_t*)(scratch + 2 * scratch_total + e.scratch_off);
+    int32_t* pv = (int32_t*)(scratch + 3 * scratch_total + e.scratch_off);
+    for (int64_t i = threadIdx.x; i < len; i += LONG_T) { id[i] = byte_id[S.at(e.lstart + i)]; nx[i] = (int32_t)(i + 1); pv[i] = (int32_t)(i - 1); }
+    __syncthreads();
+    for (int64_t i = threadIdx.x; i < len; i += LONG_T) rk[i] = i + 1 < len ? trc_pair_rank(T, id[i], id[i + 1]) : TRC_NO_RANK;
+    __syncthreads();
+    int64_t m = len;
+    for (;;) {
+      unsigned long long best = ~0ULL;
+      for (int64_t i = threadIdx.x; i < len; i += LONG_T) {
+        unsigned long long k = ((unsigned long long)rk[i] << 32) | (unsigned long long)i;
+        best = k < best ? k : best;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) { unsigned long long y = __shfl_xor_sync(0xffffffffu, best, o); best = y < best ? y : best; }
+      if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = best;
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        unsigned long long b = s_red[0];
+        for (int k = 1; k < LONG_T / 32; ++k) b = s_red[k] < b ? s_red[k] : b;
+        s_best = b;
+        uint32_t r = (uint32_t)(b >> 32);
+        if (r != TRC_NO_RANK) {
+          int32_t i = (int32_t)(b & 0xffffffffu);
+          int32_t j = nx[i], nj = nx[j];
+          id[i] = r; nx[i] = nj; rk[j] = TRC_NO_RANK;
+          if (nj < len) { pv[nj] = i; rk[i] = trc_pair_rank(T, r, id[nj]); } else rk[i] = TRC_NO_RANK;
+          int32_t p = pv[i];
+          if (p >= 0) rk[p] = trc_pair_rank(T, id[p], r);
+        }
+      }
+      __syncthreads();
+      if ((uint32_t)(s_best >> 32) == TRC_NO_RANK) break;
+      --m;
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) atomicAdd(&counts[e.unit], (uint32_t)m);
+    __syncthreads();
+  }
+}
+
+#endif
+__global__ void k_special_docs(TrcDev D, const int32_t* __restrict__ seg_special, const int32_t* __restrict__ spk_special) {
+  GSTRIDE(j, D.n_kept) {
+    if (seg_special[j] >= 0 || spk_special[D.spk[D.k2r[j]]] >= 0)
+      atomicMin((unsigned long long*)&D.doc_err_seg[D.sdoc[j]], (unsigned long long)j);
+  }
+}
+__global__ void k_doc_err(TrcDev D, const int32_t* __restrict__ seg_special, const int32_t* __restrict__ spk_special) {
+  GSTRIDE(x, D.n_doc) {
+    int64_t j = D.doc_err_seg[x];
+    if (j != INT64_MAX) {
+      int32_t s = spk_special[D.spk[D.k2r[j]]];
+      D.doc_err[x] = 1 + (s >= 0 ? s : seg_special[j]);
+    }
+  }
+}
+
+__global__ void k_build_spk_units(const uint8_t* __restrict__ spk_bytes, const int64_t* __restrict__ spk_off, int32_t n_spk,
+                                  uint8_t* __restrict__ ubytes, int64_t* __restrict__ uoff) {
+  GSTRIDE(s, n_spk) {
+    int64_t a = spk_off[s], b = spk_off[s + 1], o = a + s;
+    for (int64_t k = a; k < b; ++k) ubytes[o + (k - a)] = spk_bytes[k];
+    ubytes[o + (b - a)] = ':';
+    uoff[s] = o;
+    if (s == n_spk - 1) uoff[n_spk] = b + n_spk;
+  }
+}
+
+__global__ void k_fill_i64(int64_t* p, int64_t n, int64_t v) { GSTRIDE(i, n) p[i] = v; }
+__global__ void k_merge_next(TrcDev D) { GSTRIDE(j, D.n_kept) trc_merge_next(D, j); }
+__global__ void k_orbit(const int64_t* __restrict__ range_off, const int32_t* __restrict__ nxt, int32_t* flag, int64_t n_doc) {
+  GSTRIDE(x, n_doc) trc_orbit_walk(range_off, nxt, flag, x);
+}
+__global__ void k_scatter_starts(const int32_t* __restrict__ flag, const int64_t* __restrict__ scan, int32_t* starts, int64_t n) {
+  GSTRIDE(j, n) {
+    if (flag[j]) starts[scan[j]] = (int32_t)j;
+    if (j == n - 1) starts[scan[n]] = (int32_t)n;
+  }
+}
+__global__ void k_piece_len(TrcDev D, int32_t* plen_sub) {
+  GSTRIDE(j, D.n_kept) {
+    trc_piece_len(D, j);
+    if (plen_sub) {   // layout WITH timestamps, used for sub-chunk text when preserve_timestamps is off
+      int64_t g = D.gscan[j + 1] - 1;
+      int32_t a = D.gstart[g], b = D.gstart[g + 1];
+      int64_t len = D.coff[j + 1] - D.coff[j];
+      if (b - a > 1) { len += 3 + trc_ts_len(D.start[D.k2r[j]]); if (j + 1 < b) len += 1; }
+      plen_sub[j] = (int32_t)len;
+    }
+  }
+}
+__global__ void k_emit_merged(TrcDev D) { WSTRIDE(j, D.n_kept) trc_emit_merged(D, j, TRC_LANE, TRC_NL); }
+__global__ void k_group_stats(TrcDev D, TrcTables T) { GSTRIDE(g, D.m) trc_group_stats(D, T, g); }
+
+// ---- chunk stage
+__global__ void k_large_count(TrcDev D, TrcTables T, int32_t* nsub_g, int32_t* n_raw_large) {
+  GSTRIDE(g, D.m) {
+    int32_t a = D.gstart[g];
+    bool large = D.gtok[g] > (int64_t)D.doc_E[D.sdoc[a]];
+    int32_t ns = 0;
+    if (large) {
+      if (D.gstart[g + 1] - a > 1) ns = trc_split_combined<false>(D, T, g, nullptr);
+      else { ns = -1; atomicAdd(n_raw_large, 1); }   // sentence path: counted by the sentence stage
+    }
+    nsub_g[g] = ns;
+  }
+}
+__global__ void k_nitems(TrcDev D, const int32_t* __restrict__ nsub_g) {
+  GSTRIDE(g, D.m) {
+    int32_t a = D.gstart[g];
+    bool large = D.gtok[g] > (int64_t)D.doc_E[D.sdoc[a]];
+    D.nitems_g[g] = large ? nsub_g[g] : 1;
+  }
+}
+__global__ void k_large_write(TrcDev D, TrcTables T, const int32_t* __restrict__ nsub_g) {
+  GSTRIDE(g, D.m) {
+    int32_t a = D.gstart[g];
+    if (nsub_g[g] > 0 && D.gstart[g + 1] - a > 1) trc_split_combined<true>(D, T, g, D.subs + D.sub_off[g]);
+  }
+}
+__global__ void k_build_items(TrcDev D) {
+  GSTRIDE(g, D.m) {
+    trc_build_items(D, g);
+    int64_t t0 = D.item_off[g];
+    int32_t a = D.gstart[g], b = D.gstart[g + 1];
+    if (D.it_sub[t0] < 0) { for (int32_t j = a; j < b; ++j) D.pc_item[j] = (int32_t)t0; }
+    else {
+      int32_t cnt = D.nitems_g[g];
+      for (int32_t j = a; j < b; ++j) D.pc_item[j] = -1;
+      for (int32_t k = 0; k < cnt; ++k) {
+        const TrcSub& s = D.subs[D.it_sub[t0 + k]];
+        if (s.kind == 0) for (int32_t j = s.r0; j <= s.r1; ++j) D.pc_item[j] = (int32_t)(t0 + k);
+      }
+    }
+  }
+}
+__global__ void k_forced_list(TrcDev D, const int32_t* __restrict__ large_flag, const int64_t* __restrict__ large_scan, int64_t* forced_pos) {
+  GSTRIDE(g, D.m) if (large_flag[g]) forced_pos[large_scan[g]] = D.item_off[g];
+}
+__global__ void k_large_flag(TrcDev D, int32_t* large_flag) {
+  GSTRIDE(g, D.m) large_flag[g] = D.gtok[g] > (int64_t)D.doc_E[D.sdoc[D.gstart[g]]];
+}
+__global__ void k_pack_next(TrcDev D, const int64_t* __restrict__ forced_pos, int64_t n_forced) {
+  GSTRIDE(a, D.n_items) trc_pack_next(D, forced_pos, n_forced, a);
+}
+__global__ void k_chunk_record(TrcDev D) { GSTRIDE(c, D.n_chunks) trc_chunk_record(D, c); }
+__global__ void k_chunk_header(TrcDev D) { GSTRIDE(c, D.n_chunks) trc_chunk_header_write(D, c); }
+__global__ void k_emit_chunk_pieces(TrcDev D) { WSTRIDE(j, D.n_kept) trc_emit_chunk_piece(D, j, TRC_LANE, TRC_NL); }
+
+#include "trc_sent_kernels.cuh"
+
+// =====================================================================================================
+// host helpers
+// =====================================================================================================
+static cudaEvent_t prof_event(trc_ctx* ctx) {
+  cudaEvent_t e = nullptr;
+  if (!ctx->prof_pool.empty()) { e = ctx->prof_pool.back(); ctx->prof_pool.pop_back(); }
+  else cudaEventCreate(&e);
+  return e;
+}
+static void prof_begin(trc_ctx* ctx, cudaStream_t st, const char* name) {
+  if (!ctx->prof) return;
+  trc_ctx::ProfRec r; r.name = name; r.a = prof_event(ctx); r.b = prof_event(ctx);
+  cudaEventRecord(r.a, st);
+  ctx->prof_recs.push_back(r);
+}
+static void prof_end(trc_ctx* ctx, cudaStream_t st) {
+  if (!ctx->prof) return;
+  cudaEventRecord(ctx->prof_recs.back().b, st);
+}
+static void prof_collect(trc_ctx* ctx) {
+  for (auto& r : ctx->prof_recs) {
+    float ms = 0;
+    cudaEventSynchronize(r.b);
+    cudaEventElapsedTime(&ms, r.a, r.b);
+    bool found = false;
+    for (auto& a : ctx->prof_acc) if (a.name == r.name) { a.ms += ms; a.launches++; found = true; break; }
+    if (!found) ctx->prof_acc.push_back({r.name, (double)ms, 1});
+    ctx->prof_pool.push_back(r.a); ctx->prof_pool.push_back(r.b);
+  }
+  ctx->prof_recs.clear();
+}
+#ifdef TRC_HOSTSIM
+#define LAUNCH(kern, n, block, ...) do { if ((n) > 0) { kern(__VA_ARGS__); ctx->launches++; } } while (0)
+#else
+#define LAUNCH(kern, n, block, ...)                                                  \
+  do {                                                                               \
+    if ((n) > 0) {                                                                   \
+      prof_begin(ctx, st, #kern);                                                    \
+      kern<<<grid_for((n), (block)), (block), 0, st>>>(__VA_ARGS__);                 \
+      prof_end(ctx, st);                                                             \
+      ctx->launches++;                                                               \
+      CK(cudaGetLastError());                                                        \
+    }                                                                                \
+  } while (0)
+#endif
+#define LAUNCH_W(kern, nwarps, ...) LAUNCH(kern, (nwarps) * 32, 256, __VA_ARGS__)
+
+static int read_back(trc_ctx* ctx, cudaStream_t st, const void* dsrc, size_t bytes, void* hdst) {
+  // small counter reads: via pinned scratch, then one stream synchronise
+  if (bytes > 64 * sizeof(int64_t)) { ctx->err = "read_back too large"; return TRC_EINVAL; }
+  CK(cudaMemcpyAsync(ctx->h_pin, dsrc, bytes, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  memcpy(hdst, ctx->h_pin, bytes);
+  return TRC_OK;
+}
+
+template <class Tp>
+static int to_device(trc_ctx* ctx, cudaStream_t st, const Tp* src, int64_t count, int memory, const Tp** out) {
+  if (memory == TRC_MEM_DEVICE) { *out = src; return TRC_OK; }
+  Tp* d;
+  ALLOC(d, Tp, count);
+  if (count > 0) CK(cudaMemcpyAsync(d, src, sizeof(Tp) * (size_t)count, cudaMemcpyHostToDevice, st));
+  *out = d;
+  return TRC_OK;
+}
+
+// Token counts of n units (device pointers).  Long spans are finished by k_bpe_long after one sync.
+static int count_units(trc_ctx* ctx, cudaStream_t st, const uint8_t* bytes, const int64_t* ustart, const int64_t* uend,
+                       int64_t n, int64_t total_bytes, int vs, uint32_t* counts, int32_t* special, bool allow_sync_free) {
+  if (n <= 0) return TRC_OK;
+  int64_t cap = total_bytes / (TRC_SHORT_SPAN + 1) + 1;
+  LongEntry* wl; unsigned long long* wl_cnt;
+  ALLOC(wl, LongEntry, cap);
+  ALLOC(wl_cnt, unsigned long long, 2);
+  CK(cudaMemsetAsync(wl_cnt, 0, 16, st));
+  LAUNCH(k_count_units, n, 128, ctx->T, ctx->d_byte_id, bytes, ustart, uend, n, vs, counts, special, wl, wl_cnt, cap);
+  unsigned long long h[2];
+  int rc = read_back(ctx, st, wl_cnt, 16, h);
+  if (rc) return rc;
+  (void)allow_sync_free;
+#ifdef TRC_HOSTSIM
+  ctx->counts[TRC_N_LONG_SPANS] += (int64_t)h[0];
+  h[0] = 0;
+#endif
+  if (h[0] > 0) {
+#ifndef TRC_HOSTSIM
+    uint32_t* scratch;
+    ALLOC(scratch, uint32_t, 4 * (int64_t)h[1]);
+    int blocks = (int)(h[0] < 148 * 8 ? h[0] : 148 * 8);
+    prof_begin(ctx, st, "k_bpe_long");
+    k_bpe_long<<<blocks, LONG_T, 0, st>>>(ctx->T, ctx->d_byte_id, bytes, ustart, uend, vs, counts, wl, (int64_t)h[0], scratch, (int64_t)h[1]);
+    prof_end(ctx, st);
+    ctx->launches++;
+    CK(cudaGetLastError());
+    ctx->counts[TRC_N_LONG_SPANS] += (int64_t)h[0];
+#endif
+  }
+  return TRC_OK;
+}
+
+// =====================================================================================================
+// C ABI
+// =====================================================================================================
+extern "C" int trc_create(int device, trc_ctx** out) {
+  if (!out) return TRC_EINVAL;
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || device < 0 || device >= ndev) return TRC_ECUDA;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return TRC_ECUDA;
+  if (prop.major != 10) return TRC_ECUDA;   // built for sm_100a only
+  if (cudaSetDevice(device) != cudaSuccess) return TRC_ECUDA;
+  trc_ctx* ctx = new trc_ctx();
+  ctx->device = device;
+  if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaMallocHost(&ctx->h_pin, 64 * sizeof(int64_t)) != cudaSuccess) { delete ctx; return TRC_ECUDA; }
+  for (int k = 0; k < 4; ++k) cudaEventCreate(&ctx->ev[k]);
+  *out = ctx;
+  return TRC_OK;
+}
+
+extern "C" void trc_destroy(trc_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();
+  ctx->arena.release();
+  for (void* p : ctx->vocab_allocs) cudaFree(p);
+  if (ctx->d_props) cudaFree(ctx->d_props);
+  if (ctx->h_pin) cudaFreeHost(ctx->h_pin);
+  for (int k = 0; k < 4; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
+  if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+  delete ctx;
+}
+
+extern "C" const char* trc_last_error(trc_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+extern "C" int trc_load_tables(trc_ctx* ctx, const uint8_t* props) {
+  if (!ctx || !props) return TRC_EINVAL;
+  CK(cudaSetDevice(ctx->device));
+  if (!ctx->d_props) CK(cudaMalloc(&ctx->d_props, 0x110000));
+  CK(cudaMemcpy(ctx->d_props, props, 0x110000, cudaMemcpyHostToDevice));
+  ctx->T.props = ctx->d_props;
+  ctx->have_tables = true;
+  return TRC_OK;
+}
+
+template <class Tp>
+static int upload_vec(trc_ctx* ctx, const std::vector<Tp>& v, const Tp** out) {
+  void* d = nullptr;
+  CK(cudaMalloc(&d, sizeof(Tp) * (v.size() ? v.size() : 1)));
+  ctx->vocab_allocs.push_back(d);
+  if (!v.empty()) CK(cudaMemcpy(d, v.data(), sizeof(Tp) * v.size(), cudaMemcpyHostToDevice));
+  *out = (const Tp*)d;
+  return TRC_OK;
+}
+
+extern "C" int trc_load_vocab(trc_ctx* ctx, const uint8_t* token_bytes, const int64_t* token_off, const int32_t* ranks,
+                              int32_t n_tokens, const uint8_t* special_bytes, const int64_t* special_off, int32_t n_special) {
+  if (!ctx || !token_bytes || !token_off || !ranks) return TRC_EINVAL;
+  if (!ctx->have_tables) { ctx->err = "trc_load_tables must be called first"; return TRC_ENOVOCAB; }
+  CK(cudaSetDevice(ctx->device));
+  for (void* p : ctx->vocab_allocs) cudaFree(p);
+  ctx->vocab_allocs.clear();
+  ctx->have_vocab = false;
+  TrcHostVocab V;
+  std::string e = trc_build_host_vocab(token_bytes, token_off, ranks, n_tokens, special_bytes, special_off, n_special, V);
+  if (!e.empty()) { ctx->err = e; return TRC_EINVAL; }
+  int rc;
+  const uint32_t* byte_id;
+  if ((rc = upload_vec(ctx, V.tok_bytes, &ctx->T.tok_bytes))) return rc;
+  if ((rc = upload_vec(ctx, V.tok_off, &ctx->T.tok_off))) return rc;
+  if ((rc = upload_vec(ctx, V.tokhash, &ctx->T.tokhash))) return rc;
+  if ((rc = upload_vec(ctx, V.pairhash, &ctx->T.pairhash))) return rc;
+  if ((rc = upload_vec(ctx, V.byte_id, &byte_id))) return rc;
+  if ((rc = upload_vec(ctx, V.sp_bytes, &ctx->T.sp_bytes))) return rc;
+  if ((rc = upload_vec(ctx, V.sp_off, &ctx->T.sp_off))) return rc;
+  ctx->d_byte_id = (uint32_t*)byte_id;
+  ctx->T.n_tok = V.n_tok; ctx->T.n_sp = V.n_sp;
+  ctx->T.tokhash_mask = (uint32_t)V.tokhash.size() - 1;
+  ctx->T.pairhash_mask = (uint32_t)V.pairhash.size() - 1;
+  ctx->n_special = V.n_sp;
+  // token counts of the 1110 digit groups and of " [" with the kernels themselves
+  std::vector<uint8_t> pb; std::vector<int64_t> po;
+  trc_digit_probe_strings(pb, po);
+  int64_t np = (int64_t)po.size() - 1;
+  std::vector<uint8_t> zero(1111, 0);
+  const uint8_t* d_dc;
+  if ((rc = upload_vec(ctx, zero, &d_dc))) return rc;
+  ctx->T.dcount = d_dc; ctx->T.cnt_space_lbracket = 0;
+  ctx->have_vocab = true;
+  std::vector<uint32_t> cnt((size_t)np);
+  rc = trc_count_tokens(ctx, pb.data(), po.data(), np, 0, TRC_MEM_HOST, cnt.data(), nullptr, nullptr);
+  if (rc) { ctx->have_vocab = false; return rc; }
+  std::vector<uint8_t> dc(1111);
+  for (int64_t k = 0; k < 1110; ++k) dc[k] = (uint8_t)cnt[k];
+  CK(cudaMemcpy((void*)d_dc, dc.data(), 1110, cudaMemcpyHostToDevice));
+  ctx->T.cnt_space_lbracket = cnt[1110];
+  return TRC_OK;
+}
+
+extern "C" int trc_count_tokens(trc_ctx* ctx, const uint8_t* bytes, const int64_t* off, int64_t n, int32_t leading_space,
+                                int32_t memory, uint32_t* counts, int32_t* special, void* stream) {
+  if (!ctx || !off || !counts || n < 0) return TRC_EINVAL;
+  if (!ctx->have_vocab) { ctx->err = "vocabulary not loaded"; return TRC_ENOVOCAB; }
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : ctx->own_stream;
+  if (n == 0) return TRC_OK;
+  // this service uses its own short-lived allocations so that it never disturbs a resident batch
+  Arena saved = ctx->arena;
+  ctx->arena = Arena();
+  int rc = TRC_OK;
+  do {
+    int64_t total = 0;
+    const int64_t* d_off = nullptr; const uint8_t* d_bytes = nullptr;
+    if (memory == TRC_MEM_HOST) total = off[n];
+    else { int64_t tmp[1]; if ((rc = read_back(ctx, st, off + n, 8, tmp))) break; total = tmp[0]; }
+    if ((rc = to_device(ctx, st, off, n + 1, memory, &d_off))) break;
+    if ((rc = to_device(ctx, st, bytes, total, memory, &d_bytes))) break;
+    uint32_t* d_cnt; int32_t* d_sp = nullptr;
+    d_cnt = (uint32_t*)ctx->arena.alloc(sizeof(uint32_t) * (size_t)n);
+    if (special) d_sp = (int32_t*)ctx->arena.alloc(sizeof(int32_t) * (size_t)n);
+    if (!d_cnt || (special && !d_sp)) { ctx->err = "device allocation failed"; rc = TRC_ECUDA; break; }
+    if ((rc = count_units(ctx, st, d_bytes, d_off, d_off + 1, n, total, leading_space ? 1 : 0, d_cnt, d_sp, false))) break;
+    cudaMemcpyKind kind = memory == TRC_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
+    if (cudaMemcpyAsync(counts, d_cnt, sizeof(uint32_t) * (size_t)n, kind, st) != cudaSuccess ||
+        (special && cudaMemcpyAsync(special, d_sp, sizeof(int32_t) * (size_t)n, kind, st) != cudaSuccess) ||
+        cudaStreamSynchronize(st) != cudaSuccess) { ctx->err = "copy of token counts failed"; rc = TRC_ECUDA; break; }
+  } while (0);
+  ctx->arena.release();
+  ctx->arena = saved;
+  return rc;
+}
+
+static void set_arr(trc_ctx* ctx, int which, const void* p, int64_t bytes) { ctx->arr[which].p = p; ctx->arr[which].bytes = bytes; }
+
+extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
+  if (!ctx || !B) return TRC_EINVAL;
+  if (!ctx->have_vocab) { ctx->err = "vocabulary not loaded"; return TRC_ENOVOCAB; }
+  if (B->n_seg < 0 || B->n_doc < 0 || B->n_spk < 1 || B->n_seg >= (1LL << 31)) { ctx->err = "bad batch sizes"; return TRC_EINVAL; }
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : ctx->own_stream;
+  ctx->arena.reset();
+  ctx->have_pre = ctx->have_chunk = false;
+  for (auto& a : ctx->arr) a = {nullptr, 0};
+  for (auto& c : ctx->counts) c = 0;
+  TrcDev& D = ctx->D;
+  D = TrcDev{};
+  int rc;
+  CK(cudaEventRecord(ctx->ev[0], st));
+  const int64_t n = B->n_seg, nd = B->n_doc;
+  int64_t braw = 0, bspk = 0;
+  if (B->memory == TRC_MEM_HOST) { braw = n ? B->seg_off[n] : 0; bspk = B->spk_off[B->n_spk]; }
+  else {
+    int64_t t[1];
+    if (n) { if ((rc = read_back(ctx, st, B->seg_off + n, 8, t))) return rc; braw = t[0]; }
+    if ((rc = read_back(ctx, st, B->spk_off + B->n_spk, 8, t))) return rc; bspk = t[0];
+  }
+  if ((rc = to_device(ctx, st, B->text, braw, B->memory, &D.text))) return rc;
+  if ((rc = to_device(ctx, st, B->seg_off, n + 1, B->memory, &D.seg_off))) return rc;
+  if ((rc = to_device(ctx, st, B->start, n, B->memory, &D.start))) return rc;
+  if ((rc = to_device(ctx, st, B->end, n, B->memory, &D.end))) return rc;
+  if ((rc = to_device(ctx, st, B->speaker, n, B->memory, &D.spk))) return rc;
+  if ((rc = to_device(ctx, st, B->doc_off, nd + 1, B->memory, &D.doc_off))) return rc;
+  if ((rc = to_device(ctx, st, B->spk_bytes, bspk, B->memory, &D.spk_bytes))) return rc;
+  if ((rc = to_device(ctx, st, B->spk_off, (int64_t)B->n_spk + 1, B->memory, &D.spk_off))) return rc;
+  D.n = n; D.n_doc = nd; D.n_spk = B->n_spk;
+  D.merge = B->merge_same_speaker; D.has_cap = B->has_max_duration; D.cap = B->max_duration; D.preserve = B->preserve_timestamps;
+  ctx->counts[TRC_N_SEG] = n; ctx->counts[TRC_N_DOC] = nd; ctx->counts[TRC_B_RAW] = braw;
+
+  // speaker units: count(" " + speaker + ":") and special-token check of the speaker strings
+  uint8_t* spk_ub; int64_t* spk_uo; uint32_t* spk_tok; int32_t* spk_special;
+  ALLOC(spk_ub, uint8_t, bspk + B->n_spk); ALLOC(spk_uo, int64_t, B->n_spk + 1);
+  ALLOC(spk_tok, uint32_t, B->n_spk); ALLOC(spk_special, int32_t, B->n_spk);
+  LAUNCH(k_build_spk_units, (int64_t)B->n_spk, 128, D.spk_bytes, D.spk_off, B->n_spk, spk_ub, spk_uo);
+  if ((rc = count_units(ctx, st, spk_ub, spk_uo, spk_uo + 1, B->n_spk, bspk + B->n_spk, 1, spk_tok, spk_special, false))) return rc;
+  D.spk_tok = spk_tok;
+
+  // P1: clean (count -> scan -> write)
+  int32_t* keep;
+  ALLOC(D.clen, int64_t, n); ALLOC(D.cchars, int32_t, n); ALLOC(keep, int32_t, n);
+  ALLOC(D.kscan, int64_t, n + 1); ALLOC(D.cscan, int64_t, n + 1);
+  LAUNCH(k_clean_count, n, 128, D, ctx->T, keep);
+  if ((rc = scan_excl(ctx, st, keep, D.kscan, n))) return rc;
+  if ((rc = scan_excl(ctx, st, D.clen, D.cscan, n))) return rc;
+  int64_t h2[2] = {0, 0};
+  if (n) {
+    if ((rc = read_back(ctx, st, D.kscan + n, 8, &h2[0]))) return rc;
+    if ((rc = read_back(ctx, st, D.cscan + n, 8, &h2[1]))) return rc;
+  }
+  const int64_t nk = h2[0], bclean = h2[1];
+  D.n_kept = nk;
+  ctx->counts[TRC_N_KEPT] = nk; ctx->counts[TRC_B_CLEAN] = bclean;
+  ALLOC(D.k2r, int32_t, nk); ALLOC(D.coff, int64_t, nk + 1); ALLOC(D.C, uint8_t, bclean); ALLOC(D.sdoc, int32_t, nk);
+  ALLOC(D.kdoc_off, int64_t, nd + 1);
+  if (n == 0) CK(cudaMemsetAsync(D.coff, 0, 8, st));
+  LAUNCH(k_compact, n, 256, D, keep);
+  if (n) LAUNCH(k_map_off, nd + 1, 256, D.doc_off, D.kscan, D.kdoc_off, nd + 1);
+  else CK(cudaMemsetAsync(D.kdoc_off, 0, 8 * (size_t)(nd + 1), st));
+  LAUNCH(k_clean_write, nk, 128, D, ctx->T);
+
+  // P2: tokens of " " + cleaned text, special-token scan
+  int32_t* seg_special;
+  ALLOC(D.ctok, uint32_t, nk); ALLOC(seg_special, int32_t, nk);
+  ALLOC(D.doc_err, int32_t, nd); ALLOC(D.doc_err_seg, int64_t, nd);
+  CK(cudaMemsetAsync(D.doc_err, 0, 4 * (size_t)(nd > 0 ? nd : 1), st));
+  LAUNCH(k_fill_i64, nd, 256, D.doc_err_seg, nd, (int64_t)INT64_MAX);
+  if ((rc = count_units(ctx, st, D.C, D.coff, D.coff + 1, nk, bclean, 1, D.ctok, seg_special, true))) return rc;
+  LAUNCH(k_special_docs, nk, 256, D, seg_special, spk_special);
+  LAUNCH(k_doc_err, nd, 128, D, seg_special, spk_special);
+
+  // P3: merge
+  ALLOC(D.mnxt, int32_t, nk); ALLOC(D.gflag, int32_t, nk); ALLOC(D.gscan, int64_t, nk + 1);
+  LAUNCH(k_merge_next, nk, 256, D);
+  CK(cudaMemsetAsync(D.gflag, 0, 4 * (size_t)(nk > 0 ? nk : 1), st));
+  LAUNCH(k_orbit, nd, 64, D.kdoc_off, D.mnxt, D.gflag, nd);
+  if ((rc = scan_excl(ctx, st, D.gflag, D.gscan, nk))) return rc;
+  int64_t m = 0;
+  if (nk) { if ((rc = read_back(ctx, st, D.gscan + nk, 8, &m))) return rc; }
+  D.m = m; ctx->counts[TRC_N_GROUPS] = m;
+  ALLOC(D.gstart, int32_t, m + 1); ALLOC(D.gdoc_off, int64_t, nd + 1);
+  if (nk == 0) { CK(cudaMemsetAsync(D.gstart, 0, 4, st)); CK(cudaMemsetAsync(D.gdoc_off, 0, 8 * (size_t)(nd + 1), st)); }
+  LAUNCH(k_scatter_starts, nk, 256, D.gflag, D.gscan, D.gstart, nk);
+  if (nk) LAUNCH(k_map_off, nd + 1, 256, D.kdoc_off, D.gscan, D.gdoc_off, nd + 1);
+
+  // P4: piece layout of the merged text
+  int32_t* plen_sub = nullptr;
+  ALLOC(D.plen, int32_t, nk); ALLOC(D.poff, int64_t, nk + 1);
+  if (!D.preserve) { ALLOC(plen_sub, int32_t, nk); ALLOC(D.poffs, int64_t, nk + 1); } else D.poffs = D.poff;
+  LAUNCH(k_piece_len, nk, 256, D, plen_sub);
+  if ((rc = scan_excl(ctx, st, D.plen, D.poff, nk))) return rc;
+  if (!D.preserve) { if ((rc = scan_excl(ctx, st, plen_sub, D.poffs, nk))) return rc; }
+  int64_t bm = 0;
+  if (nk) { if ((rc = read_back(ctx, st, D.poff + nk, 8, &bm))) return rc; }
+  ctx->counts[TRC_B_MERGED] = bm;
+  if (B->want_merged_text) {
+    ALLOC(D.M, uint8_t, bm);
+    LAUNCH_W(k_emit_merged, nk, D);
+    set_arr(ctx, TRC_A_MERGED, D.M, bm);
+  }
+  // P5: group token totals, formatted lengths, formatted timestamps
+  ALLOC(D.gts, uint8_t, m * 48); ALLOC(D.gtok, int64_t, m); ALLOC(D.glen, int64_t, m);
+  LAUNCH(k_group_stats, m, 128, D, ctx->T);
+  CK(cudaEventRecord(ctx->ev[1], st));
+  ctx->ev_pre = true; ctx->ev_chunk = false;
+
+  set_arr(ctx, TRC_A_K2R, D.k2r, 4 * nk); set_arr(ctx, TRC_A_COFF, D.coff, 8 * (nk + 1)); set_arr(ctx, TRC_A_CLEAN, D.C, bclean);
+  set_arr(ctx, TRC_A_CTOK, D.ctok, 4 * nk); set_arr(ctx, TRC_A_GSTART, D.gstart, 4 * (m + 1));
+  set_arr(ctx, TRC_A_POFF, D.poff, 8 * (nk + 1)); set_arr(ctx, TRC_A_GTS, D.gts, 48 * m); set_arr(ctx, TRC_A_GTOK, D.gtok, 8 * m);
+  set_arr(ctx, TRC_A_DOC_ERR, D.doc_err, 4 * nd); set_arr(ctx, TRC_A_GDOC_OFF, D.gdoc_off, 8 * (nd + 1));
+  set_arr(ctx, TRC_A_CCHARS, D.cchars, 4 * n);
+  ctx->have_pre = true;
+  return TRC_OK;
+}
+
+extern "C" int trc_chunk(trc_ctx* ctx, const int32_t* doc_max_tokens, int32_t context_tokens, int32_t add_context, void* stream) {
+  if (!ctx || !doc_max_tokens) return TRC_EINVAL;
+  if (!ctx->have_pre) { ctx->err = "trc_chunk needs a preceding trc_preprocess"; return TRC_EINVAL; }
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : ctx->own_stream;
+  TrcDev& D = ctx->D;
+  int rc;
+  CK(cudaEventRecord(ctx->ev[2], st));
+  const int64_t nd = D.n_doc, nk = D.n_kept, m = D.m;
+  D.add_context = add_context ? 1 : 0;
+  {
+    std::vector<int32_t> E((size_t)(nd > 0 ? nd : 1));
+    for (int64_t x = 0; x < nd; ++x) E[x] = doc_max_tokens[x] - context_tokens;   // big_chunkeroosky.py:42
+    int32_t* dE;
+    ALLOC(dE, int32_t, nd);
+    CK(cudaMemcpyAsync(dE, E.data(), 4 * (size_t)(nd > 0 ? nd : 1), cudaMemcpyHostToDevice, st));
+    CK(cudaStreamSynchronize(st));
+    D.doc_E = dE;
+  }
+  // C1: over-budget segments -> sub-chunks
+  int32_t* nsub_g; int32_t* d_nraw;
+  ALLOC(nsub_g, int32_t, m); ALLOC(d_nraw, int32_t, 1); ALLOC(D.sub_off, int64_t, m + 1);
+  ALLOC(D.nitems_g, int32_t, m); ALLOC(D.item_off, int64_t, m + 1);
+  CK(cudaMemsetAsync(d_nraw, 0, 4, st));
+  LAUNCH(k_large_count, m, 128, D, ctx->T, nsub_g, d_nraw);
+  int32_t nraw = 0;
+  if (m) { if ((rc = read_back(ctx, st, d_nraw, 4, &nraw))) return rc; }
+  ctx->SS = TrcSentState{};
+  if (nraw > 0) { if ((rc = sentence_stage_count(ctx, st, nsub_g, nraw))) return rc; }
+  if ((rc = scan_excl(ctx, st, nsub_g, D.sub_off, m))) return rc;
+  LAUNCH(k_nitems, m, 256, D, nsub_g);
+  if ((rc = scan_excl(ctx, st, D.nitems_g, D.item_off, m))) return rc;
+  int64_t h2[2] = {0, 0};
+  if (m) {
+    if ((rc = read_back(ctx, st, D.sub_off + m, 8, &h2[0]))) return rc;
+    if ((rc = read_back(ctx, st, D.item_off + m, 8, &h2[1]))) return rc;
+  }
+  const int64_t nsub = h2[0], ni = h2[1];
+  D.n_subs = nsub; D.n_items = ni;
+  ctx->counts[TRC_N_SUBS] = nsub; ctx->counts[TRC_N_ITEMS] = ni;
+  ALLOC(D.subs, TrcSub, nsub);
+  LAUNCH(k_large_write, m, 128, D, ctx->T, nsub_g);
+  if (nraw > 0) { if ((rc = sentence_stage_write(ctx, st, nsub_g))) return rc; }
+  // C2: items
+  ALLOC(D.it_group, int32_t, ni); ALLOC(D.it_sub, int32_t, ni); ALLOC(D.it_tok, int32_t, ni); ALLOC(D.it_len, int64_t, ni);
+  ALLOC(D.it_forced, uint8_t, ni); ALLOC(D.pc_item, int32_t, nk);
+  ALLOC(D.W, int64_t, ni + 1); ALLOC(D.L, int64_t, ni + 1); ALLOC(D.idoc_off, int64_t, nd + 1);
+  LAUNCH(k_build_items, m, 128, D);
+  if ((rc = scan_excl(ctx, st, D.it_tok, D.W, ni))) return rc;
+  if ((rc = scan_excl(ctx, st, D.it_len, D.L, ni, 2))) return rc;
+  if (m) LAUNCH(k_map_off, nd + 1, 256, D.gdoc_off, D.item_off, D.idoc_off, nd + 1);
+  else CK(cudaMemsetAsync(D.idoc_off, 0, 8 * (size_t)(nd + 1), st));
+  // forced breaks = first item of every over-budget segment
+  int32_t* large_flag; int64_t* large_scan; int64_t* forced_pos;
+  ALLOC(large_flag, int32_t, m); ALLOC(large_scan, int64_t, m + 1);
+  LAUNCH(k_large_flag, m, 256, D, large_flag);
+  if ((rc = scan_excl(ctx, st, large_flag, large_scan, m))) return rc;
+  int64_t nforced = 0;
+  if (m) { if ((rc = read_back(ctx, st, large_scan + m, 8, &nforced))) return rc; }
+  ALLOC(forced_pos, int64_t, nforced);
+  LAUNCH(k_forced_list, m, 256, D, large_flag, large_scan, forced_pos);
+  // C3: greedy packing as orbit of pnxt
+  ALLOC(D.pnxt, int32_t, ni); ALLOC(D.cflag, int32_t, ni); ALLOC(D.cscanf, int64_t, ni + 1);
+  LAUNCH(k_pack_next, ni, 256, D, forced_pos, nforced);
+  CK(cudaMemsetAsync(D.cflag, 0, 4 * (size_t)(ni > 0 ? ni : 1), st));
+  LAUNCH(k_orbit, nd, 64, D.idoc_off, D.pnxt, D.cflag, nd);
+  if ((rc = scan_excl(ctx, st, D.cflag, D.cscanf, ni))) return rc;
+  int64_t nc = 0;
+  if (ni) { if ((rc = read_back(ctx, st, D.cscanf + ni, 8, &nc))) return rc; }
+  D.n_chunks = nc; ctx->counts[TRC_N_CHUNKS] = nc;
+  ALLOC(D.cstart, int32_t, nc + 1); ALLOC(D.cdoc_off, int64_t, nd + 1);
+  if (ni == 0) { CK(cudaMemsetAsync(D.cstart, 0, 4, st)); CK(cudaMemsetAsync(D.cdoc_off, 0, 8 * (size_t)(nd + 1), st)); }
+  LAUNCH(k_scatter_starts, ni, 256, D.cflag, D.cscanf, D.cstart, ni);
+  if (ni) LAUNCH(k_map_off, nd + 1, 256, D.idoc_off, D.cscanf, D.cdoc_off, nd + 1);
+  // C4: chunk records, headers
+  ALLOC(D.chunks, TrcChunk, nc); ALLOC(D.spk_list, int32_t, ni); ALLOC(D.twc_len, int64_t, nc); ALLOC(D.twc_scan, int64_t, nc + 1);
+  ALLOC(D.it_dst, int64_t, ni);
+  LAUNCH(k_chunk_record, nc, 64, D);
+  if ((rc = scan_excl(ctx, st, D.twc_len, D.twc_scan, nc))) return rc;
+  int64_t h3[2] = {0, 0};
+  if (nc) { if ((rc = read_back(ctx, st, D.twc_scan + nc, 8, &h3[0]))) return rc; }
+  if (ni) { if ((rc = read_back(ctx, st, D.W + ni, 8, &h3[1]))) return rc; }
+  const int64_t btwc = h3[0];
+  ctx->counts[TRC_B_TWC] = btwc; ctx->counts[TRC_TOKENS] = h3[1];
+  ALLOC(D.twc, uint8_t, btwc);
+  LAUNCH(k_chunk_header, nc, 64, D);
+  // C5: item text
+  LAUNCH_W(k_emit_chunk_pieces, nk, D);
+  if (nraw > 0) { if ((rc = sentence_stage_emit(ctx, st))) return rc; }
+  CK(cudaEventRecord(ctx->ev[3], st));
+  ctx->ev_chunk = true;
+  // error documents
+  set_arr(ctx, TRC_A_ITEM_GROUP, D.it_group, 4 * ni); set_arr(ctx, TRC_A_ITEM_SUB, D.it_sub, 4 * ni);
+  set_arr(ctx, TRC_A_ITEM_TOK, D.it_tok, 4 * ni); set_arr(ctx, TRC_A_ITEM_LEN, D.it_len, 8 * ni);
+  set_arr(ctx, TRC_A_ITEM_DST, D.it_dst, 8 * ni); set_arr(ctx, TRC_A_SUBS, D.subs, (int64_t)sizeof(TrcSub) * nsub);
+  set_arr(ctx, TRC_A_CHUNKS, D.chunks, (int64_t)sizeof(TrcChunk) * nc); set_arr(ctx, TRC_A_SPK_LIST, D.spk_list, 4 * ni);
+  set_arr(ctx, TRC_A_TWC, D.twc, btwc); set_arr(ctx, TRC_A_CDOC_OFF, D.cdoc_off, 8 * (nd + 1));
+  set_arr(ctx, TRC_A_SENT, ctx->SS.recs, (int64_t)sizeof(TrcSent) * ctx->SS.n_recs);
+  ctx->counts[TRC_N_SENT] = ctx->SS.n_recs;
+  ctx->have_chunk = true;
+  return TRC_OK;
+}
+
+extern "C" int trc_get_counts(trc_ctx* ctx, int64_t* counts) {
+  if (!ctx || !counts) return TRC_EINVAL;
+  for (int k = 0; k < TRC_N_COUNTERS; ++k) counts[k] = ctx->counts[k];
+  return TRC_OK;
+}
+
+extern "C" int trc_get_array(trc_ctx* ctx, int which, void* dst, int64_t dst_bytes, int32_t memory, int64_t* nbytes, void* stream) {
+  if (!ctx || which < 0 || which >= TRC_A__COUNT) return TRC_EINVAL;
+  if (!ctx->have_pre) { ctx->err = "no batch resident"; return TRC_EINVAL; }
+  const trc_ctx::Arr& a = ctx->arr[which];
+  if (nbytes) *nbytes = a.bytes;
+  if (!dst) return TRC_OK;
+  if (!a.p && a.bytes > 0) { ctx->err = "array not produced by the stages run so far"; return TRC_EINVAL; }
+  if (dst_bytes < a.bytes) { ctx->err = "destination too small"; return TRC_EINVAL; }
+  if (a.bytes == 0) return TRC_OK;
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : ctx->own_stream;
+  CK(cudaMemcpyAsync(dst, a.p, (size_t)a.bytes, memory == TRC_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, st));
+  if (memory == TRC_MEM_HOST) CK(cudaStreamSynchronize(st));
+  return TRC_OK;
+}
+
+extern "C" int trc_last_stage_ms(trc_ctx* ctx, float* pre, float* chk) {
+  if (!ctx) return TRC_EINVAL;
+  CK(cudaSetDevice(ctx->device));
+  if (pre) { *pre = 0; if (ctx->ev_pre) { CK(cudaEventSynchronize(ctx->ev[1])); CK(cudaEventElapsedTime(pre, ctx->ev[0], ctx->ev[1])); } }
+  if (chk) { *chk = 0; if (ctx->ev_chunk) { CK(cudaEventSynchronize(ctx->ev[3])); CK(cudaEventElapsedTime(chk, ctx->ev[2], ctx->ev[3])); } }
+  return TRC_OK;
+}
+
+extern "C" int trc_set_profiling(trc_ctx* ctx, int32_t on) {
+  if (!ctx) return TRC_EINVAL;
+  prof_collect(ctx);
+  ctx->prof = on != 0;
+  ctx->prof_acc.clear();
+  return TRC_OK;
+}
+
+extern "C" int trc_get_profile(trc_ctx* ctx, char* buf, int64_t buf_bytes) {
+  if (!ctx || !buf || buf_bytes < 1) return TRC_EINVAL;
+  CK(cudaSetDevice(ctx->device));
+  prof_collect(ctx);
+  std::string s;
+  for (auto& a : ctx->prof_acc) { char line[256]; snprintf(line, sizeof line, "%s %.6f %lld\n", a.name.c_str(), a.ms, (long long)a.launches); s += line; }
+  if ((int64_t)s.size() + 1 > buf_bytes) { ctx->err = "profile buffer too small"; return TRC_EINVAL; }
+  memcpy(buf, s.c_str(), s.size() + 1);
+  return TRC_OK;
+}
+
+extern "C" int trc_kernel_launches(trc_ctx* ctx, int64_t* launches) {
+  if (!ctx || !launches) return TRC_EINVAL;
+  *launches = ctx->launches;
+  return TRC_OK;
+}

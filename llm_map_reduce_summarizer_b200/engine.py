@@ -1,0 +1,347 @@
+"""Host side of the path: packing (flat UTF-8 buffer + CSR offsets), the ctypes calls, and dict
+materialisation in the reference's output format.  No compute happens here.
+"""
+import ctypes as C
+import math
+import os
+
+import numpy as np
+
+from . import _native as N
+from . import vocab as _vocab
+
+
+class TrcError(RuntimeError):
+    pass
+
+
+class PackedBatch:
+    """A batch of transcripts in the C ABI's layout (include/trchunk.h: trc_batch)."""
+
+    def __init__(self, text, seg_off, start, end, speaker, doc_off, speakers, originals=None):
+        self.text = np.ascontiguousarray(text, dtype=np.uint8)
+        self.seg_off = np.ascontiguousarray(seg_off, dtype=np.int64)
+        self.start = np.ascontiguousarray(start, dtype=np.float64)
+        self.end = np.ascontiguousarray(end, dtype=np.float64)
+        self.speaker = np.ascontiguousarray(speaker, dtype=np.int32)
+        self.doc_off = np.ascontiguousarray(doc_off, dtype=np.int64)
+        self.speakers = list(speakers)               # id -> str, sorted, speakers[0] == ""
+        self.spk_bytes, self.spk_off = _vocab.pack_strings([s.encode("utf-8") for s in self.speakers])
+        self.originals = originals                   # (start objects, end objects) per raw segment, or None
+
+    @property
+    def n_seg(self):
+        return len(self.start)
+
+    @property
+    def n_doc(self):
+        return len(self.doc_off) - 1
+
+
+def pack_documents(docs):
+    """list of transcripts (each a list of {start,end,text,speaker} dicts) -> PackedBatch.
+    Mirrors the defaults of preprocessor.py:46-50 (`segment.get(key, default)`)."""
+    texts, starts, ends, spk_names, doc_off = [], [], [], [], [0]
+    for segs in docs:
+        for seg in segs:
+            t = seg.get("text", "")
+            t.strip                                    # same AttributeError as the reference for non-str text
+            texts.append(t.encode("utf-8"))           # lone surrogates raise UnicodeEncodeError (unsupported)
+            starts.append(seg.get("start", 0))
+            ends.append(seg.get("end", 0))
+            s = seg.get("speaker", "")
+            if not isinstance(s, str):
+                raise TypeError("speaker must be a str (the reference's header join fails otherwise)")
+            spk_names.append(s)
+        doc_off.append(len(texts))
+    names = sorted(set(spk_names) | {""})
+    ids = {s: i for i, s in enumerate(names)}
+    buf, off = _vocab.pack_strings(texts)
+    st = np.array([float(x) for x in starts], dtype=np.float64)
+    en = np.array([float(x) for x in ends], dtype=np.float64)
+    for arr in (st, en):
+        if arr.size and not np.isfinite(arr).all():
+            if np.isnan(arr).any():
+                raise ValueError("cannot convert float NaN to integer")
+            raise OverflowError("cannot convert float infinity to integer")
+    spk = np.array([ids[s] for s in spk_names], dtype=np.int32)
+    return PackedBatch(buf, off, st, en, spk, np.array(doc_off, dtype=np.int64), names, (starts, ends))
+
+
+class Engine:
+    """One context on one GPU.  Not thread-safe (one engine per thread / per rank)."""
+
+    def __init__(self, device=0, lib_path=None, tokenizer_name="cl100k_base"):
+        self.lib = N.load_library(lib_path)
+        h = C.c_void_p()
+        rc = self.lib.trc_create(int(device), C.byref(h))
+        if rc != 0:
+            raise TrcError(
+                f"trc_create(device={device}) failed ({N.ERRORS.get(rc, rc)}): a CUDA device of compute capability "
+                "10.x (B200, sm_100a) is required; this library has no CPU path")
+        self.h = h
+        self.device = device
+        props = _vocab.load_props()
+        self._check(self.lib.trc_load_tables(self.h, props.ctypes.data))
+        self.vocab_name, toks, ranks = _vocab.load_rank_table(tokenizer_name)
+        tb, to = _vocab.pack_strings(toks)
+        rk = np.array(ranks, dtype=np.int32)
+        self.specials = list(_vocab.SPECIALS)
+        sb, so = _vocab.pack_strings([s.encode() for s in self.specials])
+        self._check(self.lib.trc_load_vocab(self.h, tb.ctypes.data, to.ctypes.data, rk.ctypes.data, len(ranks),
+                                            sb.ctypes.data, so.ctypes.data, len(self.specials)))
+        self.batch = None
+        self.batch_serial = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.trc_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            msg = self.lib.trc_last_error(self.h).decode("utf-8", "replace")
+            if rc == -4:
+                raise NotImplementedError(msg)
+            raise TrcError(f"{N.ERRORS.get(rc, rc)}: {msg}")
+
+    # ---- stages ---------------------------------------------------------------------------------------
+    def preprocess(self, batch, merge_same_speaker=True, max_segment_duration=120, preserve_timestamps=True,
+                   want_merged_text=True, stream=None, device_ptrs=None):
+        """Stage P on a PackedBatch (host arrays), or on device pointers when `device_ptrs` is given
+        (dict with the trc_batch pointer fields as ints)."""
+        b = N.Batch()
+        if device_ptrs is None:
+            b.text, b.seg_off = batch.text.ctypes.data, batch.seg_off.ctypes.data
+            b.start, b.end, b.speaker = batch.start.ctypes.data, batch.end.ctypes.data, batch.speaker.ctypes.data
+            b.doc_off = batch.doc_off.ctypes.data
+            b.spk_bytes, b.spk_off = batch.spk_bytes.ctypes.data, batch.spk_off.ctypes.data
+            b.memory = N.TRC_MEM_HOST
+        else:
+            for k in ("text", "seg_off", "start", "end", "speaker", "doc_off", "spk_bytes", "spk_off"):
+                setattr(b, k, device_ptrs[k])
+            b.memory = N.TRC_MEM_DEVICE
+        b.n_seg, b.n_doc, b.n_spk = batch.n_seg, batch.n_doc, len(batch.speakers)
+        b.merge_same_speaker = 1 if merge_same_speaker else 0
+        b.has_max_duration = 0 if max_segment_duration is None else 1
+        b.max_duration = float(max_segment_duration) if max_segment_duration is not None else 0.0
+        b.preserve_timestamps = 1 if preserve_timestamps else 0
+        b.want_merged_text = 1 if want_merged_text else 0
+        self._keep = (batch, b)
+        self._check(self.lib.trc_preprocess(self.h, C.byref(b), stream))
+        self.batch = batch
+        self.batch_serial += 1
+        return self.batch_serial
+
+    def chunk(self, doc_max_tokens, context_tokens=150, add_context=True, stream=None):
+        mt = np.ascontiguousarray(doc_max_tokens, dtype=np.int32)
+        if mt.shape != (self.batch.n_doc,):
+            raise ValueError("doc_max_tokens must have one entry per document")
+        self._check(self.lib.trc_chunk(self.h, mt.ctypes.data, int(context_tokens), 1 if add_context else 0, stream))
+
+    def counts(self):
+        c = np.zeros(N.N_COUNTERS, dtype=np.int64)
+        self._check(self.lib.trc_get_counts(self.h, c.ctypes.data))
+        return {k: int(c[i]) for i, k in enumerate(N.COUNTERS)}
+
+    def array(self, name, dtype, stream=None):
+        nb = C.c_int64()
+        self._check(self.lib.trc_get_array(self.h, N.A[name], None, 0, N.TRC_MEM_HOST, C.byref(nb), stream))
+        dt = np.dtype(dtype)
+        out = np.empty(nb.value // dt.itemsize, dtype=dt)
+        if nb.value:
+            self._check(self.lib.trc_get_array(self.h, N.A[name], out.ctypes.data, nb.value, N.TRC_MEM_HOST,
+                                               C.byref(nb), stream))
+        return out
+
+    def array_into(self, name, dst_ptr, dst_bytes, memory=N.TRC_MEM_HOST, stream=None):
+        nb = C.c_int64()
+        self._check(self.lib.trc_get_array(self.h, N.A[name], dst_ptr, dst_bytes, memory, C.byref(nb), stream))
+        return nb.value
+
+    def stage_ms(self):
+        a, b = C.c_float(), C.c_float()
+        self._check(self.lib.trc_last_stage_ms(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def launches(self):
+        n = C.c_int64()
+        self._check(self.lib.trc_kernel_launches(self.h, C.byref(n)))
+        return n.value
+
+    def set_profiling(self, on):
+        self._check(self.lib.trc_set_profiling(self.h, 1 if on else 0))
+
+    def profile(self):
+        """{kernel name: (total ms, launches)} since profiling was switched on."""
+        buf = C.create_string_buffer(1 << 16)
+        self._check(self.lib.trc_get_profile(self.h, buf, len(buf)))
+        out = {}
+        for line in buf.value.decode().splitlines():
+            name, ms, n = line.split()
+            out[name] = (float(ms), int(n))
+        return out
+
+    def count_tokens(self, strings, leading_space=False):
+        """len(encode(s)) for each str (big_chunkeroosky.py:83) - returns (counts, special_index)."""
+        buf, off = _vocab.pack_strings([s.encode("utf-8") for s in strings])
+        cnt = np.zeros(len(strings), dtype=np.uint32)
+        sp = np.zeros(len(strings), dtype=np.int32)
+        self._check(self.lib.trc_count_tokens(self.h, buf.ctypes.data, off.ctypes.data, len(strings),
+                                              1 if leading_space else 0, N.TRC_MEM_HOST, cnt.ctypes.data,
+                                              sp.ctypes.data, None))
+        return cnt, sp
+
+    # ---- materialisation ------------------------------------------------------------------------------
+    def fetch_processed(self):
+        """Arrays of stage P for the resident batch."""
+        r = {"k2r": self.array("K2R", "<i4"), "coff": self.array("COFF", "<i8"), "clean": self.array("CLEAN", "u1"),
+             "gstart": self.array("GSTART", "<i4"), "poff": self.array("POFF", "<i8"),
+             "merged": self.array("MERGED", "u1"), "gts": self.array("GTS", "u1"), "gtok": self.array("GTOK", "<i8"),
+             "gdoc_off": self.array("GDOC_OFF", "<i8"), "ctok": self.array("CTOK", "<u4")}
+        return r
+
+    def fetch_chunks(self):
+        return {"item_group": self.array("ITEM_GROUP", "<i4"), "item_sub": self.array("ITEM_SUB", "<i4"),
+                "item_tok": self.array("ITEM_TOK", "<i4"), "item_len": self.array("ITEM_LEN", "<i8"),
+                "item_dst": self.array("ITEM_DST", "<i8"), "subs": self.array("SUBS", N.SUB_DTYPE),
+                "chunks": self.array("CHUNKS", N.CHUNK_DTYPE), "spk_list": self.array("SPK_LIST", "<i4"),
+                "twc": self.array("TWC", "u1"), "doc_err": self.array("DOC_ERR", "<i4"),
+                "cdoc_off": self.array("CDOC_OFF", "<i8"), "sent": self.array("SENT", N.SENT_DTYPE)}
+
+
+class _Text:
+    """Slices of a UTF-8 byte buffer as str; ASCII buffers are decoded once."""
+
+    def __init__(self, arr):
+        self.b = arr.tobytes()
+        self.s = self.b.decode("ascii") if self.b.isascii() else None
+
+    def get(self, a, b):
+        return self.s[a:b] if self.s is not None else self.b[a:b].decode("utf-8")
+
+
+def build_processed(batch, P, doc=0):
+    """Processed-segment dicts of document `doc` in the reference's format (preprocessor.py:45-52,203-213)."""
+    starts, ends = batch.originals if batch.originals is not None else (batch.start.tolist(), batch.end.tolist())
+    k2r, coff, gstart, poff, gts = P["k2r"], P["coff"], P["gstart"], P["poff"], P["gts"]
+    clean, merged = _Text(P["clean"]), _Text(P["merged"])
+    gts_b = gts.tobytes()
+    out = []
+    g0, g1 = int(P["gdoc_off"][doc]), int(P["gdoc_off"][doc + 1])
+    names = batch.speakers
+    spk = batch.speaker
+    for g in range(g0, g1):
+        a, b = int(gstart[g]), int(gstart[g + 1])
+        ra, rb = int(k2r[a]), int(k2r[b - 1])
+        o = g * 48
+        sf = gts_b[o + 1:o + 1 + gts_b[o]].decode("ascii")
+        ef = gts_b[o + 25:o + 25 + gts_b[o + 24]].decode("ascii")
+        d = {"start": starts[ra], "end": ends[rb], "start_formatted": sf, "end_formatted": ef,
+             "speaker": names[spk[ra]], "text": merged.get(int(poff[a]), int(poff[b]))}
+        if b - a > 1:
+            d["is_combined"] = True
+            d["original_segments"] = b - a
+            d["segment_timestamps"] = [{"start": starts[int(k2r[j])], "end": ends[int(k2r[j])],
+                                        "text": clean.get(int(coff[j]), int(coff[j + 1]))} for j in range(a, b)]
+        out.append(d)
+    return out
+
+
+def special_token_error(engine, k):
+    tok = engine.specials[k]
+    return ValueError(
+        f"Encountered text corresponding to disallowed special token {tok!r}.\n"
+        "If you want this text to be encoded as a special token, "
+        f"pass it to `allowed_special`, e.g. `allowed_special={{{tok!r}, ...}}`.\n"
+        f"If you want this text to be encoded as normal text, disable the check for this token "
+        f"by passing `disallowed_special=(enc.special_tokens_set - {{{tok!r}}})`.\n"
+        "To disable this check for all special tokens, pass `disallowed_special=()`.\n")
+
+
+def build_chunks(engine, batch, P, R, processed, doc=0):
+    """Chunk dicts of document `doc` (big_chunkeroosky.py:147-195, key order SURVEY.md A.10).
+    `processed` is the list returned by build_processed for the same document (objects are aliased)."""
+    err = int(R["doc_err"][doc])
+    if err > 0:
+        raise special_token_error(engine, err - 1)
+    if err < 0:
+        raise NotImplementedError("document uses a construct outside the supported domain")
+    starts, ends = batch.originals if batch.originals is not None else (batch.start.tolist(), batch.end.tolist())
+    k2r, gstart = P["k2r"], P["gstart"]
+    g0 = int(P["gdoc_off"][doc])
+    twc = _Text(R["twc"])
+    ch = R["chunks"]
+    subs = R["subs"]
+    names = batch.speakers
+    c0, c1 = int(R["cdoc_off"][doc]), int(R["cdoc_off"][doc + 1])
+    item_group, item_sub, item_dst, item_len = R["item_group"], R["item_sub"], R["item_dst"], R["item_len"]
+    sub_cache = {}
+
+    def sub_dict(si, t):
+        if si in sub_cache:
+            return sub_cache[si]
+        s = subs[si]
+        g = int(s["group"])
+        parent = processed[g - g0]
+        text = twc.get(int(item_dst[t]), int(item_dst[t] + item_len[t]))
+        st = starts[int(k2r[s["start_src"]])] if s["start_src"] >= 0 else float(s["start"])
+        en = ends[int(k2r[s["end_src"]])] if s["end_src"] >= 0 else float(s["end"])
+        if s["kind"] == 2:
+            d = {"start": st, "end": en, "speaker": "", "text": text, "is_sub_chunk": True, "is_clause": True}
+        else:
+            d = {"start": st, "end": en, "speaker": parent["speaker"], "text": text, "is_sub_chunk": True,
+                 "parent_segment_start": parent["start"], "parent_segment_end": parent["end"]}
+        sub_cache[si] = d
+        return d
+
+    out = []
+    total = c1 - c0
+    for c in range(c0, c1):
+        r = ch[c]
+        if r["err"]:
+            raise NotImplementedError("position_percentage outside the exactly formatted range (|x| >= 2**59)")
+        segs = []
+        for t in range(int(r["item0"]), int(r["item1"])):
+            si = int(item_sub[t])
+            segs.append(processed[int(item_group[t]) - g0] if si < 0 else sub_dict(si, t))
+        o = int(r["twc_off"])
+        hdr = int(r["hdr_len"])
+        body0 = o + (hdr + 2 if hdr > 0 else 0)          # the header is never empty when add_context is on
+        body1 = body0 + int(r["text_len"])
+        text = twc.get(body0, body1)
+        tw = twc.get(o, body1) if hdr > 0 else text
+        start_time = processed[int(r["start_ref"]) - g0]["start"] if r["start_kind"] == 0 else segs[0]["start"]
+        end_time = segs[-1]["end"]
+        d = {"segments": segs, "text": text, "token_count": int(r["token_count"]), "start_time": start_time,
+             "end_time": end_time,
+             "speakers": [names[int(i)] for i in R["spk_list"][int(r["item0"]):int(r["item0"]) + int(r["n_speakers"])]],
+             "chunk_index": int(r["chunk_index"]), "total_chunks": total,
+             "position_percentage": 0 if r["pct_is_int_zero"] else float(r["position_percentage"]),
+             "text_with_context": tw}
+        out.append(d)
+    return out
+
+
+_ENGINES = {}
+
+
+def default_engine(tokenizer_name="cl100k_base"):
+    """Process-wide engine used by the drop-in modules (device from $TRCHUNK_DEVICE, default 0)."""
+    dev = int(os.environ.get("TRCHUNK_DEVICE", "0"))
+    key = (dev, tokenizer_name)
+    if key not in _ENGINES:
+        _ENGINES[key] = Engine(dev, None, tokenizer_name)
+    return _ENGINES[key]
+
+
+def set_default_engine(engine, tokenizer_name="cl100k_base"):
+    """Install an already constructed engine as the drop-in modules' engine."""
+    dev = int(os.environ.get("TRCHUNK_DEVICE", "0"))
+    _ENGINES[(dev, tokenizer_name)] = engine

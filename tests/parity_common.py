@@ -1,0 +1,56 @@
+"""Shared comparison helpers: run an Engine (CUDA or hostsim) through the drop-in modules and compare
+with golden vectors / the oracle."""
+import json
+
+from conftest import quiet
+from llm_map_reduce_summarizer_b200 import engine as E, preprocessor as PP, big_chunkeroosky as BC
+
+
+def run_dropin(eng, segments, max_tokens=4000, merge=True, max_dur=120, preserve=True, add_context=True):
+    E.set_default_engine(eng)
+    with quiet():
+        proc = PP.preprocess_transcript(segments, merge, None, max_dur, preserve)
+        c = BC.BigChunkeroosky(max_tokens_per_chunk=max_tokens)
+        chunks = c.postprocess_chunks(c.chunk_transcript(proc, add_context))
+    return proc, chunks
+
+
+def same(a, b):
+    return json.dumps(a) == json.dumps(b)
+
+
+def first_diff(a, b):
+    if a is None or b is None or len(a) != len(b):
+        return "len %s vs %s" % (None if a is None else len(a), None if b is None else len(b))
+    for i, (x, y) in enumerate(zip(a, b)):
+        if json.dumps(x) != json.dumps(y):
+            for k in x:
+                if json.dumps(x[k]) != json.dumps(y.get(k)):
+                    return "item %d key %s: %r != %r" % (i, k, repr(x[k])[:200], repr(y.get(k))[:200])
+            return "item %d differs" % i
+    return ""
+
+
+def check_fuzz_cases(eng, cases, require_all=True):
+    n_ok = 0
+    for i, cs in enumerate(cases):
+        kw = cs["kw"]
+        E.set_default_engine(eng)
+        with quiet():
+            proc = PP.preprocess_transcript(cs["segments"], kw["merge"], None, kw["max_dur"], kw["preserve"])
+        assert same(list(proc), cs["proc"]), "case %d preprocess: %s" % (i, first_diff(list(proc), cs["proc"]))
+        err, chunks = None, None
+        try:
+            with quiet():
+                c = BC.BigChunkeroosky(max_tokens_per_chunk=kw["max_tokens"])
+                chunks = c.postprocess_chunks(c.chunk_transcript(proc, kw["add_context"]))
+        except ValueError:
+            err = "ValueError"
+        except NotImplementedError:
+            if require_all:
+                raise
+            continue
+        assert err == cs["error"], "case %d error %r != %r" % (i, err, cs["error"])
+        assert same(chunks, cs["chunks"]), "case %d chunks: %s" % (i, first_diff(chunks, cs["chunks"]))
+        n_ok += 1
+    return n_ok

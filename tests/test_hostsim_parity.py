@@ -1,0 +1,75 @@
+"""Stage logic + host orchestration (product sources compiled for the host, tests/hostsim) against the
+golden vectors and the oracle.  CPU only; the GPU parity tests proper are tests/test_gpu_parity.py."""
+import json
+
+import numpy as np
+
+import parity_common as pc
+from conftest import load_golden
+from llm_map_reduce_summarizer_b200 import engine as E, preprocessor as PP, synth
+from oracle import chunker as OC, preprocess as OP, tokenizer as TK
+from test_oracle_golden import sha
+
+
+def test_example_all_configs(hostsim_engine):
+    segs = load_golden("example_segments.json.gz")
+    for name, e in load_golden("example_expected.json").items():
+        kw = e["kw"]
+        proc, chunks = pc.run_dropin(hostsim_engine, segs, kw["max_tokens"], kw.get("merge", True), kw.get("max_dur", 120),
+                                     kw.get("preserve", True), kw.get("add_context", True))
+        assert sha(list(proc)) == e["proc_sha256"], name
+        assert sha(chunks) == e["chunks_sha256"], name
+
+
+def test_kats(hostsim_engine):
+    E.set_default_engine(hostsim_engine)
+    kat = load_golden("kat.json")
+    for s, want in kat["clean_text"]:
+        assert PP.clean_text(s) == want, repr(s)
+    for x, want in kat["format_timestamp"]:
+        assert PP.format_timestamp(x) == want, x
+    for m in kat["merge"]:
+        proc, _ = pc.run_dropin(hostsim_engine, m["segments"], 100000, True, m["cap"])
+        assert sha(list(proc)) == m["sha256"], m["name"]
+
+
+def test_fuzz_cases(hostsim_engine):
+    n = pc.check_fuzz_cases(hostsim_engine, load_golden("fuzz_cases.json.gz"), require_all=True)
+    assert n == 160
+
+
+def test_token_counts_vs_corebpe(hostsim_engine):
+    import random
+    enc = TK.encoding()
+    rng = random.Random(11)
+    alpha = ["a", "b", "Z", "é", "1", "2", "٣", " ", "  ", "\n", "\r", "\t", " ", "'", "'s", "'LL", "'ſ", ".", ",",
+             "!", "?", "-", "(", "你", "_", "x0", " ", "​", "[00:05]", " don't", "hello", " world", "ing", "tion"]
+    strs = ["".join(rng.choice(alpha) for _ in range(rng.randint(0, 40))) for _ in range(4000)]
+    strs += ["a" * 200, "ab" * 300, "!" * 100, " " * 70, "x" * 49, "y" * 48, "0123456789" * 9, "né" * 60]
+    for lead in (False, True):
+        cnt, _ = hostsim_engine.count_tokens(strs, leading_space=lead)
+        for s, c in zip(strs, cnt):
+            assert c == len(enc.encode_ordinary((" " if lead else "") + s)), repr(s)
+
+
+def test_synthetic_docs_vs_oracle(hostsim_engine):
+    e = hostsim_engine
+    for num, scale in ((3, 0.004), (5, 0.004), (2, 0.05)):
+        b, mt, _ = synth.config(num, scale)
+        e.preprocess(b)
+        e.chunk(mt)
+        P, R = e.fetch_processed(), e.fetch_chunks()
+        for x in range(b.n_doc):
+            segs = synth.doc_to_segments(b, x)
+            op = OP.preprocess(segs)
+            oc = OC.ChunkerOracle(int(mt[x])).chunk(op)
+            pp = E.build_processed(b, P, x)
+            assert json.dumps(pp) == json.dumps(op), (num, x)
+            assert json.dumps(E.build_chunks(e, b, P, R, pp, x)) == json.dumps(oc), (num, x)
+
+
+def test_empty_inputs(hostsim_engine):
+    proc, chunks = pc.run_dropin(hostsim_engine, [])
+    assert list(proc) == [] and chunks == []
+    proc, chunks = pc.run_dropin(hostsim_engine, [{"start": 0, "end": 1, "text": "  \t", "speaker": "A"}])
+    assert list(proc) == [] and chunks == []
