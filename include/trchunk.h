@@ -135,6 +135,17 @@ typedef struct {
   int64_t text_len, twc_off;
 } trc_chunk_rec;
 
+typedef struct {            /* sentence (kind 1) / clause (kind 2) of an over-budget un-merged segment */
+  int32_t group, kind;
+  int64_t off, len;         /* byte range in TRC_A_CLEAN */
+  int32_t chars, tok;
+  double start, end;
+  int32_t sub, last_in_sub;
+  int64_t off_in_sub;
+  int32_t parent, ncl;
+  int64_t cl0;
+} trc_sent;
+
 /* Token counting service: counts[i] = len(encode([" "] + bytes[off[i] .. off[i+1]))) for n strings.
  * Replaces len(self.tokenizer.encode(x)) (big_chunkeroosky.py:83,298,370,510).  special[i] (may be
  * NULL) receives the index of a special-token literal found in string i, or -1. */

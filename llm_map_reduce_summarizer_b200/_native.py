@@ -30,7 +30,8 @@ CHUNK_DTYPE = [("item0", "<i4"), ("item1", "<i4"), ("doc", "<i4"), ("chunk_index
                ("start_kind", "<i4"), ("start_ref", "<i4"), ("n_speakers", "<i4"), ("hdr_len", "<i4"), ("err", "<i4"),
                ("text_len", "<i8"), ("twc_off", "<i8")]
 SENT_DTYPE = [("group", "<i4"), ("kind", "<i4"), ("off", "<i8"), ("len", "<i8"), ("chars", "<i4"), ("tok", "<i4"),
-              ("start", "<f8"), ("end", "<f8")]
+              ("start", "<f8"), ("end", "<f8"), ("sub", "<i4"), ("last_in_sub", "<i4"), ("off_in_sub", "<i8"),
+              ("parent", "<i4"), ("ncl", "<i4"), ("cl0", "<i8")]
 
 EXPORTS = ["trc_create", "trc_destroy", "trc_last_error", "trc_load_tables", "trc_load_vocab", "trc_preprocess",
            "trc_chunk", "trc_get_counts", "trc_get_array", "trc_count_tokens", "trc_last_stage_ms", "trc_kernel_launches", "trc_set_profiling",

@@ -1,7 +1,297 @@
-// Sentence path kernels + host staging (placeholder until the Punkt classifier lands).
-static int sentence_stage_count(trc_ctx* ctx, cudaStream_t, int32_t*, int32_t nraw) {
-  ctx->err = "over-budget un-merged segment: sentence path not built yet (" + std::to_string(nraw) + " segments)";
-  return TRC_EUNSUPPORTED;
+// Sentence path: kernels + host staging (included by trchunk.cu after the context definition).
+// big_chunkeroosky.py:331-433 (sentence greedy), :437-542 (clause greedy).
+
+// ---- records ---------------------------------------------------------------------------------------
+__global__ void k_rl_list(TrcDev D, const int32_t* __restrict__ nsub_g, const int64_t* __restrict__ rl_scan, int32_t* rl_groups,
+                          int64_t* rl_len) {
+  GSTRIDE(g, D.m) if (nsub_g[g] < 0) {
+    int64_t q = rl_scan[g];
+    rl_groups[q] = (int32_t)g;
+    int32_t j = D.gstart[g];
+    rl_len[q] = D.coff[j + 1] - D.coff[j];
+  }
 }
-static int sentence_stage_write(trc_ctx*, cudaStream_t, const int32_t*) { return TRC_OK; }
-static int sentence_stage_emit(trc_ctx*, cudaStream_t) { return TRC_OK; }
+__global__ void k_rl_flag(TrcDev D, const int32_t* __restrict__ nsub_g, int32_t* flag) { GSTRIDE(g, D.m) flag[g] = nsub_g[g] < 0; }
+
+TRC_HD int64_t rl_find(const int64_t* boff, int64_t n, int64_t pos) {   // last q with boff[q] <= pos
+  int64_t lo = 0, hi = n;
+  while (hi - lo > 1) { int64_t mid = (lo + hi) >> 1; if (boff[mid] <= pos) lo = mid; else hi = mid; }
+  return lo;
+}
+
+// one thread per text byte of the over-budget raw segments: Punkt break decision
+__global__ void k_punkt_breaks(TrcDev D, TrcTables T, TrcSentState S, int64_t total, int32_t* brk) {
+  GSTRIDE(p, total) {
+    int64_t q = rl_find(S.rl_boff, S.n_rl, p);
+    int32_t j = D.gstart[S.rl_groups[q]];
+    const uint8_t* s = D.C + D.coff[j];
+    int64_t n = D.coff[j + 1] - D.coff[j];
+    int64_t i = p - S.rl_boff[q];
+    brk[p] = pk_sentend(s[i]) && pk_is_break(T, s, n, i);
+  }
+}
+__global__ void k_brk_pos(const int32_t* __restrict__ brk, const int64_t* __restrict__ bscan, int64_t total, int64_t* pos) {
+  GSTRIDE(p, total) if (brk[p]) pos[bscan[p]] = p;
+}
+__global__ void k_sent_counts(TrcSentState S, const int64_t* __restrict__ bscan, int32_t* ns) {
+  GSTRIDE(q, S.n_rl) ns[q] = (int32_t)(bscan[S.rl_boff[q + 1]] - bscan[S.rl_boff[q]]) + 1;
+}
+
+// one thread per sentence slice: slice bounds, realignment with its neighbours, strip, code points
+__global__ void k_sent_build(TrcDev D, TrcSentState S, const int64_t* __restrict__ bscan, const int64_t* __restrict__ brk_pos,
+                             int64_t* chars64) {
+  GSTRIDE(r, S.n_sent) {
+    int64_t q = rl_find(S.sent_off, S.n_rl, r);
+    int32_t g = S.rl_groups[q];
+    int32_t j = D.gstart[g];
+    const uint8_t* s = D.C + D.coff[j];
+    int64_t n = D.coff[j + 1] - D.coff[j];
+    int64_t i = r - S.sent_off[q];
+    int64_t nb = S.sent_off[q + 1] - S.sent_off[q] - 1;     // breaks of this segment
+    int64_t b0 = bscan[S.rl_boff[q]];
+    auto slice = [&](int64_t k, int64_t* a, int64_t* b) {   // _slices_from_text
+      if (k == 0) *a = 0;
+      else { int64_t c = brk_pos[b0 + k - 1] - S.rl_boff[q]; *a = pk_nonword(s[c + 1]) ? c + 1 : c + 2; }
+      *b = k < nb ? (brk_pos[b0 + k] - S.rl_boff[q]) + 1 : n;
+    };
+    int64_t a, b, k0 = 0, e0 = 0, k1 = 0, e1 = 0;
+    slice(i, &a, &b);
+    if (i > 0) pk_realign(s, a, b, &k0, &e0);               // _realign_boundaries
+    int64_t sa = a + e0, sb = b;
+    if (i < nb) { int64_t a2, b2; slice(i + 1, &a2, &b2); pk_realign(s, a2, b2, &k1, &e1); if (k1) sb = a2 + k1; }
+    while (sa < sb && s[sa] == ' ') ++sa;                   // sentence.strip()  (:357)
+    while (sb > sa && s[sb - 1] == ' ') --sb;
+    if (sb < sa) sb = sa;
+    TrcSent& R = S.recs[r];
+    R.group = g; R.kind = 1; R.off = D.coff[j] + sa; R.len = sb - sa; R.chars = pk_count_chars(s, sa, sb);
+    R.tok = 0; R.sub = -1; R.last_in_sub = 0; R.off_in_sub = 0; R.parent = -1; R.ncl = 0; R.cl0 = 0; R.start = 0; R.end = 0;
+    chars64[r] = R.chars;
+  }
+}
+
+// sentence times (:351-366) and the unit range for token counting
+__global__ void k_sent_times(TrcDev D, TrcSentState S, const int64_t* __restrict__ cscan, int64_t* ustart, int64_t* uend) {
+  GSTRIDE(r, S.n_sent) {
+    TrcSent& R = S.recs[r];
+    int64_t q = rl_find(S.sent_off, S.n_rl, r);
+    int32_t j = D.gstart[R.group];
+    int32_t raw = D.k2r[j];
+    double st = D.start[raw], en = D.end[raw];
+    double span = en - st;
+    int32_t chars = D.cchars[raw];
+    double tpc = chars > 0 ? span / (double)chars : 0.0;
+    int64_t done = cscan[r] - cscan[S.sent_off[q]];
+    double m1 = tpc * (double)done;
+    R.start = st + m1;
+    double m2 = tpc * (double)R.chars;
+    R.end = R.start + m2;
+    ustart[r] = R.off; uend[r] = R.off + R.len;
+  }
+}
+
+__global__ void k_sent_tok(TrcDev D, TrcTables T, TrcSentState S, const uint32_t* __restrict__ cnt, int32_t* ncl) {
+  GSTRIDE(r, S.n_sent) {
+    TrcSent& R = S.recs[r];
+    int32_t n = 0;
+    if (R.len > 0) {
+      R.tok = 2 + trc_ts_tokens(T, R.start) + (int32_t)cnt[r];
+      int64_t E = D.doc_E[D.sdoc[D.gstart[R.group]]];
+      if (R.tok > E) n = pk_clauses(D.C, R.off, R.off + R.len, [](int32_t, int64_t, int64_t) {});
+    }
+    R.ncl = n; ncl[r] = n;
+  }
+}
+
+// one thread per over-budget sentence: clause records with times (:474-506)
+__global__ void k_clause_build(TrcDev D, TrcSentState S, const int64_t* __restrict__ clscan, int64_t* ustart, int64_t* uend) {
+  GSTRIDE(r, S.n_sent) {
+    TrcSent& P = S.recs[r];
+    if (P.ncl == 0) continue;
+    P.cl0 = S.n_sent + clscan[r];
+    double span = P.end - P.start;
+    double tpc = P.chars > 0 ? span / (double)P.chars : 0.0;
+    int64_t done = 0;
+    const uint8_t* s = D.C;
+    pk_clauses(s, P.off, P.off + P.len, [&](int32_t k, int64_t ca, int64_t cb) {
+      while (ca < cb && s[ca] == ' ') ++ca;
+      while (cb > ca && s[cb - 1] == ' ') --cb;
+      TrcSent& R = S.recs[P.cl0 + k];
+      R.group = P.group; R.kind = 2; R.off = ca; R.len = cb - ca; R.chars = pk_count_chars(s, ca, cb);
+      R.tok = 0; R.sub = -1; R.last_in_sub = 0; R.off_in_sub = 0; R.parent = (int32_t)r; R.ncl = 0; R.cl0 = 0;
+      double m1 = tpc * (double)done;
+      R.start = P.start + m1;
+      double m2 = tpc * (double)R.chars;
+      R.end = R.start + m2;
+      done += R.chars;
+      int64_t u = clscan[r] + k;
+      ustart[u] = ca; uend[u] = cb;
+    });
+  }
+}
+__global__ void k_clause_tok(TrcTables T, TrcSentState S, const uint32_t* __restrict__ cnt, int64_t n_cl) {
+  GSTRIDE(u, n_cl) { TrcSent& R = S.recs[S.n_sent + u]; R.tok = R.len > 0 ? 2 + trc_ts_tokens(T, R.start) + (int32_t)cnt[u] : 0; }
+}
+
+// ---- nested greedy, one thread per over-budget raw segment -----------------------------------------------
+struct SubAcc {
+  int64_t tok, text_len; int32_t r0, r1, n; double start, end; int32_t start_src;
+};
+
+template <bool WRITE>
+TRC_HD void sg_flush(const TrcDev& D, TrcSentState& S, TrcSub* out, int32_t& ns, int64_t sub_base, int32_t g, int32_t kind, SubAcc& a) {
+  if (WRITE) {
+    TrcSub& s = out[ns];
+    s.group = g; s.kind = kind; s.r0 = a.r0; s.r1 = a.r1; s.start_src = a.start_src; s.end_src = -1; s.tok = (int32_t)a.tok; s.pad = 0;
+    s.start = a.start; s.end = a.end; s.text_len = a.text_len;
+    for (int32_t r = a.r0; r <= a.r1; ++r) if (S.recs[r].sub == -2) S.recs[r].sub = (int32_t)(sub_base + ns);
+    for (int32_t r = a.r1; r >= a.r0; --r) if (S.recs[r].sub == (int32_t)(sub_base + ns)) { S.recs[r].last_in_sub = 1; break; }
+  }
+  ++ns;
+}
+template <bool WRITE>
+TRC_HD void sg_append(TrcSentState& S, SubAcc& a, int32_t r, const TrcSent& R) {
+  int64_t piece = 1 + trc_ts_len(R.start) + 2 + R.len;
+  if (a.n == 0) { a.r0 = r; a.text_len = 0; }
+  if (WRITE) { S.recs[r].sub = -2; S.recs[r].off_in_sub = a.n ? a.text_len + 1 : 0; }
+  a.text_len += piece + (a.n ? 1 : 0);
+  a.tok += R.tok; a.r1 = r; a.n += 1; a.end = R.end;
+}
+
+template <bool WRITE>
+TRC_HD int32_t trc_split_sentences(const TrcDev& D, TrcSentState S, int64_t q, TrcSub* out, int64_t sub_base) {
+  int32_t g = S.rl_groups[q];
+  int32_t j = D.gstart[g];
+  int64_t E = D.doc_E[D.sdoc[j]];
+  int32_t ns = 0;
+  SubAcc cur; cur.tok = 0; cur.text_len = 0; cur.n = 0; cur.r0 = cur.r1 = -1; cur.start = D.start[D.k2r[j]]; cur.end = 0; cur.start_src = j;
+  for (int64_t r = S.sent_off[q]; r < S.sent_off[q + 1]; ++r) {
+    const TrcSent R = S.recs[r];
+    if (R.len == 0) continue;
+    if (R.tok > E) {
+      // clause sub-chunks of this sentence (:437-542)
+      SubAcc cl; cl.tok = 0; cl.text_len = 0; cl.n = 0; cl.r0 = cl.r1 = -1; cl.start = R.start; cl.end = 0; cl.start_src = -1;
+      // an existing sub-chunk is closed first (:378-381), but it is appended BEFORE the clause chunks
+      if (cur.tok > 0) { cur.end = R.start; sg_flush<WRITE>(D, S, out, ns, sub_base, g, 1, cur); }
+      for (int64_t c = R.cl0; c < R.cl0 + R.ncl; ++c) {
+        const TrcSent C = S.recs[c];
+        if (C.len == 0) continue;
+        if (cl.tok + C.tok > E && cl.tok > 0) {
+          sg_flush<WRITE>(D, S, out, ns, sub_base, g, 2, cl);
+          cl.tok = 0; cl.text_len = 0; cl.n = 0; cl.start = C.start; cl.start_src = -1;
+        }
+        sg_append<WRITE>(S, cl, (int32_t)c, C);
+      }
+      if (cl.tok > 0) sg_flush<WRITE>(D, S, out, ns, sub_base, g, 2, cl);
+      cur.tok = 0; cur.text_len = 0; cur.n = 0; cur.start = R.end; cur.start_src = -1;     // :387-399
+    } else if (cur.tok + R.tok > E && cur.tok > 0) {
+      cur.end = R.start;                                                                   // :404
+      sg_flush<WRITE>(D, S, out, ns, sub_base, g, 1, cur);
+      cur.tok = 0; cur.text_len = 0; cur.n = 0; cur.start = R.start; cur.start_src = -1;   // :409-421
+      sg_append<WRITE>(S, cur, (int32_t)r, R);
+    } else {
+      sg_append<WRITE>(S, cur, (int32_t)r, R);                                             // :423-429
+    }
+  }
+  if (cur.tok > 0) sg_flush<WRITE>(D, S, out, ns, sub_base, g, 1, cur);
+  return ns;
+}
+
+__global__ void k_sent_greedy_count(TrcDev D, TrcSentState S, int32_t* nsub_g) {
+  GSTRIDE(q, S.n_rl) nsub_g[S.rl_groups[q]] = trc_split_sentences<false>(D, S, q, nullptr, 0);
+}
+__global__ void k_sent_greedy_write(TrcDev D, TrcSentState S) {
+  GSTRIDE(q, S.n_rl) { int64_t base = D.sub_off[S.rl_groups[q]]; trc_split_sentences<true>(D, S, q, D.subs + base, base); }
+}
+
+// K6 for sentence/clause records: "[ts] text" (+ joining space) into the item text; warp per record
+__global__ void k_emit_sent_recs(TrcDev D, TrcSentState S) {
+  WSTRIDE(r, S.n_recs) {
+    const TrcSent R = S.recs[r];
+    if (R.sub < 0) continue;
+    const TrcSub& sb = D.subs[R.sub];
+    int64_t t = D.item_off[sb.group] + (R.sub - D.sub_off[sb.group]);
+    uint8_t* base = D.twc + D.it_dst[t];
+    int lane = TRC_LANE, nl = TRC_NL;
+    if (R.off_in_sub == 0 && lane == 0 && t > D.chunks[D.cscanf[t + 1] - 1].item0) { base[-2] = '\n'; base[-1] = '\n'; }
+    uint8_t* dst = base + R.off_in_sub;
+    uint8_t buf[TRC_TS_MAX + 4];
+    int tl = trc_fmt_ts(R.start, buf + 1);
+    buf[0] = '['; buf[tl + 1] = ']'; buf[tl + 2] = ' ';
+    for (int k = lane; k < tl + 3; k += nl) dst[k] = buf[k];
+    const uint8_t* src = D.C + R.off;
+    for (int64_t k = lane; k < R.len; k += nl) dst[tl + 3 + k] = src[k];
+    if (!R.last_in_sub && lane == 0) dst[tl + 3 + R.len] = ' ';
+  }
+}
+
+// ---- host staging -----------------------------------------------------------------------------------------
+static int count_units(trc_ctx* ctx, cudaStream_t st, const uint8_t* bytes, const int64_t* ustart, const int64_t* uend,
+                       int64_t n, int64_t total_bytes, int vs, uint32_t* counts, int32_t* special, bool allow_sync_free);
+
+static int sentence_stage_count(trc_ctx* ctx, cudaStream_t st, int32_t* nsub_g, int32_t nraw) {
+  TrcDev& D = ctx->D;
+  TrcSentState& S = ctx->SS;
+  int rc;
+  const int64_t m = D.m;
+  // list of over-budget raw segments and their byte prefix
+  int32_t* flag; int64_t* rl_scan; int32_t* rl_groups; int64_t* rl_len; int64_t* rl_boff;
+  ALLOC(flag, int32_t, m); ALLOC(rl_scan, int64_t, m + 1); ALLOC(rl_groups, int32_t, nraw); ALLOC(rl_len, int64_t, nraw);
+  ALLOC(rl_boff, int64_t, nraw + 1);
+  LAUNCH(k_rl_flag, m, 256, D, nsub_g, flag);
+  if ((rc = scan_excl(ctx, st, flag, rl_scan, m))) return rc;
+  LAUNCH(k_rl_list, m, 256, D, nsub_g, rl_scan, rl_groups, rl_len);
+  if ((rc = scan_excl(ctx, st, rl_len, rl_boff, (int64_t)nraw))) return rc;
+  int64_t total = 0;
+  if ((rc = read_back(ctx, st, rl_boff + nraw, 8, &total))) return rc;
+  S.rl_groups = rl_groups; S.n_rl = nraw; S.rl_boff = rl_boff;
+  // Punkt breaks
+  int32_t* brk; int64_t* bscan;
+  ALLOC(brk, int32_t, total); ALLOC(bscan, int64_t, total + 1);
+  LAUNCH(k_punkt_breaks, total, 128, D, ctx->T, S, total, brk);
+  if ((rc = scan_excl(ctx, st, brk, bscan, total))) return rc;
+  int64_t nbrk = 0;
+  if ((rc = read_back(ctx, st, bscan + total, 8, &nbrk))) return rc;
+  int64_t* brk_pos; int32_t* ns; int64_t* sent_off;
+  ALLOC(brk_pos, int64_t, nbrk); ALLOC(ns, int32_t, nraw); ALLOC(sent_off, int64_t, nraw + 1);
+  LAUNCH(k_brk_pos, total, 256, brk, bscan, total, brk_pos);
+  LAUNCH(k_sent_counts, (int64_t)nraw, 128, S, bscan, ns);
+  if ((rc = scan_excl(ctx, st, ns, sent_off, (int64_t)nraw))) return rc;
+  S.sent_off = sent_off;
+  S.n_sent = nbrk + nraw;
+  // sentence records (the clause records are appended once their number is known)
+  TrcSent* recs0; int64_t* chars64; int64_t* cscan; int64_t* ustart; int64_t* uend; uint32_t* cnt; int32_t* ncl; int64_t* clscan;
+  ALLOC(recs0, TrcSent, S.n_sent); ALLOC(chars64, int64_t, S.n_sent); ALLOC(cscan, int64_t, S.n_sent + 1);
+  ALLOC(ustart, int64_t, S.n_sent); ALLOC(uend, int64_t, S.n_sent); ALLOC(cnt, uint32_t, S.n_sent); ALLOC(ncl, int32_t, S.n_sent);
+  ALLOC(clscan, int64_t, S.n_sent + 1);
+  S.recs = recs0; S.n_recs = S.n_sent;
+  LAUNCH(k_sent_build, S.n_sent, 128, D, S, bscan, brk_pos, chars64);
+  if ((rc = scan_excl(ctx, st, chars64, cscan, S.n_sent))) return rc;
+  LAUNCH(k_sent_times, S.n_sent, 128, D, S, cscan, ustart, uend);
+  if ((rc = count_units(ctx, st, D.C, ustart, uend, S.n_sent, total, 1, cnt, nullptr, false))) return rc;
+  LAUNCH(k_sent_tok, S.n_sent, 128, D, ctx->T, S, cnt, ncl);
+  if ((rc = scan_excl(ctx, st, ncl, clscan, S.n_sent))) return rc;
+  int64_t ncls = 0;
+  if ((rc = read_back(ctx, st, clscan + S.n_sent, 8, &ncls))) return rc;
+  if (ncls > 0) {
+    TrcSent* recs;
+    ALLOC(recs, TrcSent, S.n_sent + ncls);
+    CK(cudaMemcpyAsync(recs, recs0, sizeof(TrcSent) * (size_t)S.n_sent, cudaMemcpyDeviceToDevice, st));
+    S.recs = recs; S.n_recs = S.n_sent + ncls;
+    int64_t* cus; int64_t* cue; uint32_t* ccnt;
+    ALLOC(cus, int64_t, ncls); ALLOC(cue, int64_t, ncls); ALLOC(ccnt, uint32_t, ncls);
+    LAUNCH(k_clause_build, S.n_sent, 64, D, S, clscan, cus, cue);
+    if ((rc = count_units(ctx, st, D.C, cus, cue, ncls, total, 1, ccnt, nullptr, false))) return rc;
+    LAUNCH(k_clause_tok, ncls, 128, ctx->T, S, ccnt, ncls);
+  }
+  LAUNCH(k_sent_greedy_count, (int64_t)nraw, 64, D, S, nsub_g);
+  return TRC_OK;
+}
+
+static int sentence_stage_write(trc_ctx* ctx, cudaStream_t st, const int32_t*) {
+  LAUNCH(k_sent_greedy_write, ctx->SS.n_rl, 64, ctx->D, ctx->SS);
+  return TRC_OK;
+}
+static int sentence_stage_emit(trc_ctx* ctx, cudaStream_t st) {
+  LAUNCH_W(k_emit_sent_recs, ctx->SS.n_recs, ctx->D, ctx->SS);
+  return TRC_OK;
+}

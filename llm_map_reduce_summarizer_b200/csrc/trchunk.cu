@@ -21,6 +21,7 @@
 
 static_assert(sizeof(TrcSub) == sizeof(trc_sub), "trc_sub layout");
 static_assert(sizeof(TrcChunk) == sizeof(trc_chunk_rec), "trc_chunk_rec layout");
+static_assert(sizeof(TrcSent) == sizeof(trc_sent), "trc_sent layout");
 
 // =====================================================================================================
 // context
@@ -481,8 +482,6 @@ __global__ void k_chunk_record(TrcDev D) { GSTRIDE(c, D.n_chunks) trc_chunk_reco
 __global__ void k_chunk_header(TrcDev D) { GSTRIDE(c, D.n_chunks) trc_chunk_header_write(D, c); }
 __global__ void k_emit_chunk_pieces(TrcDev D) { WSTRIDE(j, D.n_kept) trc_emit_chunk_piece(D, j, TRC_LANE, TRC_NL); }
 
-#include "trc_sent_kernels.cuh"
-
 // =====================================================================================================
 // host helpers
 // =====================================================================================================
@@ -582,6 +581,8 @@ static int count_units(trc_ctx* ctx, cudaStream_t st, const uint8_t* bytes, cons
   }
   return TRC_OK;
 }
+
+#include "trc_sent_kernels.cuh"
 
 // =====================================================================================================
 // C ABI

@@ -54,3 +54,37 @@ def check_fuzz_cases(eng, cases, require_all=True):
         assert same(chunks, cs["chunks"]), "case %d chunks: %s" % (i, first_diff(chunks, cs["chunks"]))
         n_ok += 1
     return n_ok
+
+
+def sentence_fuzz(eng, n_cases, seed):
+    """Over-budget un-merged segments: Punkt sentences, clause splits, 20-word splits, nested greedy."""
+    import random
+    import fuzzgen
+    from oracle import chunker as OC, preprocess as OP
+    rng = random.Random(seed)
+    extra = ["!!!", "?!", ".)", '."', ".'", "..", "...", "--", "Mr.", "a.", "b.c.", "3.", "-3.5.", "1,2.", "x.y", "(z)", "\"q\"",
+             "end.", "End.", "É.", "é", "no;", "yes:", "so,", "A", "the", "of", "and"]
+    bad = 0
+    for it in range(n_cases):
+        nseg = rng.randint(1, 4)
+        segs = []
+        t = 0.0
+        for k in range(nseg):
+            words = [rng.choice(fuzzgen.WORDS + extra) for _ in range(rng.randint(30, 260))]
+            if rng.random() < 0.15:
+                words = [w.strip(",.;:?!") or "w" for w in words]          # forces the 20-word path
+            elif rng.random() < 0.2:
+                words = [w.replace(".", "").replace("?", "").replace("!", "") or "w" for w in words]   # clause path
+            d = rng.choice([10.0, 61, 333.33, 0.5])
+            segs.append({"start": t if rng.random() < 0.5 else int(t), "end": t + d, "text": " ".join(words),
+                         "speaker": rng.choice(["A", "B", ""])})
+            t += d
+        mt = rng.choice([158, 165, 180, 220, 300])
+        op = OP.preprocess(segs, rng.random() < 0.5)
+        merge = "is_combined" in json.dumps(op)
+        proc, chunks = run_dropin(eng, segs, mt, merge=merge)
+        op = OP.preprocess(segs, merge)
+        oc = OC.ChunkerOracle(mt).chunk(op)
+        assert same(list(proc), op), "case %d preprocess" % it
+        assert same(chunks, oc), "case %d: %s" % (it, first_diff(chunks, oc))
+    return n_cases

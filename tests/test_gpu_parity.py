@@ -132,3 +132,7 @@ def test_idempotent_rerun(gpu_engine):
     a = e.array("TWC", "u1").tobytes()
     e.preprocess(b); e.chunk(mt)
     assert a == e.array("TWC", "u1").tobytes()
+
+
+def test_sentence_path_fuzz(gpu_engine):
+    pc.sentence_fuzz(gpu_engine, 300, 1234)

@@ -73,3 +73,7 @@ def test_empty_inputs(hostsim_engine):
     assert list(proc) == [] and chunks == []
     proc, chunks = pc.run_dropin(hostsim_engine, [{"start": 0, "end": 1, "text": "  \t", "speaker": "A"}])
     assert list(proc) == [] and chunks == []
+
+
+def test_sentence_path_fuzz(hostsim_engine):
+    pc.sentence_fuzz(hostsim_engine, 300, 99)
