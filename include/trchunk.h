@@ -164,6 +164,22 @@ int trc_kernel_launches(trc_ctx* ctx, int64_t* launches);
 int trc_set_profiling(trc_ctx* ctx, int32_t on);
 int trc_get_profile(trc_ctx* ctx, char* buf, int64_t buf_bytes);
 
+/* Token count of ONE pre-tokenised span without allocating anything.  (No counterpart in the
+ * reference: tiktoken allocates freely on the host.)  For embedders that must not allocate device
+ * memory while running - a server whose own pool already owns all of HBM, a plugin host that bans
+ * driver allocations after start-up, a loop that cannot take the device-wide stall of cudaMalloc/
+ * cudaFree - this does what the long-span path of trc_count_tokens does (vocabulary hit => 1, else
+ * byte-pair merge by minimum rank, leftmost first) with its work arrays in a fixed 1 MiB array inside
+ * the library image, present on every GPU that loads the library until the process exits.
+ *   d_span  : DEVICE pointer, n_bytes bytes forming one span (the caller has already split the text);
+ *   d_count : DEVICE pointer to one uint32 that receives the count; the call is asynchronous on `stream`.
+ * Limit: 1 <= n_bytes <= 65536, larger spans are rejected with TRC_EINVAL and a message.
+ * The first call on a device looks up the array's device address once; make that call before starting
+ * any stream capture.  All calls on a device share the array and it is not cleared between calls (the
+ * kernel initialises what it reads), so calls that overlap on the GPU race: issue them on one stream
+ * or order them yourself. */
+int trc_bpe_span_count_static(trc_ctx* ctx, const uint8_t* d_span, int64_t n_bytes, uint32_t* d_count, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -35,7 +35,7 @@ SENT_DTYPE = [("group", "<i4"), ("kind", "<i4"), ("off", "<i8"), ("len", "<i8"),
 
 EXPORTS = ["trc_create", "trc_destroy", "trc_last_error", "trc_load_tables", "trc_load_vocab", "trc_preprocess",
            "trc_chunk", "trc_get_counts", "trc_get_array", "trc_count_tokens", "trc_last_stage_ms", "trc_kernel_launches", "trc_set_profiling",
-           "trc_get_profile"]
+           "trc_get_profile", "trc_bpe_span_count_static"]
 
 
 def load_library(path=None):
@@ -62,4 +62,6 @@ def load_library(path=None):
     lib.trc_kernel_launches.argtypes = [vp, C.POINTER(i64)]
     lib.trc_set_profiling.argtypes = [vp, i32]
     lib.trc_get_profile.argtypes = [vp, C.c_char_p, i64]
+    if hasattr(lib, "trc_bpe_span_count_static"):
+        lib.trc_bpe_span_count_static.argtypes = [vp, vp, i64, vp, vp]
     return lib

@@ -995,3 +995,108 @@ extern "C" int trc_kernel_launches(trc_ctx* ctx, int64_t* launches) {
   *launches = ctx->launches;
   return TRC_OK;
 }
+
+
+#ifndef TRC_HOSTSIM
+// =====================================================================================================
+// Allocation-free span counter.
+//
+// Some embedders of this library are not allowed to allocate device memory once they are running: a
+// serving process that has handed all of HBM to its own pool at start-up, a plugin host that forbids
+// driver allocations after initialisation, or a latency-critical loop that cannot afford the implicit
+// device-wide synchronisation a cudaMalloc/cudaFree brings.  The normal long-span merge (k_bpe_long)
+// takes its four work arrays from the context arena, which may grow.  This variant does the same merge
+// for ONE span with its work arrays in a fixed array that lives in the library image, so the call
+// itself allocates nothing; the caller supplies the input bytes and the output word.
+//
+// The array is shared by every call on the device and keeps whatever the previous call left in it.
+// The kernel writes each of the entries it will read before reading them, so no clearing pass is needed,
+// but two calls that overlap on the GPU (different streams) would corrupt each other: serialise them.
+// =====================================================================================================
+#include <mutex>
+#define TRC_STATIC_SPAN_MAX 65536                     /* bytes per span; 4 x 4 B per byte = 1 MiB per GPU */
+static __device__ __align__(256) uint32_t g_span_scratch[4 * TRC_STATIC_SPAN_MAX];
+static std::mutex g_span_mu;
+static uint32_t* g_span_scratch_addr[64] = {nullptr};  // device address of the array, per device ordinal
+
+__global__ void __launch_bounds__(LONG_T) k_bpe_span_static(TrcTables T, const uint32_t* __restrict__ byte_id,
+                                                            const uint8_t* __restrict__ span, int64_t len,
+                                                            uint32_t* __restrict__ out_count, uint32_t* scratch) {
+  __shared__ unsigned long long s_red[LONG_T / 32];
+  __shared__ unsigned long long s_best;
+  __shared__ int s_whole;
+  TrcStr S; S.p = span; S.vs = 0; S.n = len;
+  if (threadIdx.x == 0) s_whole = (len == 1 || trc_is_token(T, S, 0, (int)len)) ? 1 : 0;
+  __syncthreads();
+  if (s_whole) { if (threadIdx.x == 0) *out_count = 1u; return; }
+  uint32_t* id = scratch;
+  uint32_t* rk = scratch + TRC_STATIC_SPAN_MAX;
+  int32_t* nx = (int32_t*)(scratch + 2 * TRC_STATIC_SPAN_MAX);
+  int32_t* pv = (int32_t*)(scratch + 3 * TRC_STATIC_SPAN_MAX);
+  for (int64_t i = threadIdx.x; i < len; i += LONG_T) { id[i] = byte_id[span[i]]; nx[i] = (int32_t)(i + 1); pv[i] = (int32_t)(i - 1); }
+  __syncthreads();
+  for (int64_t i = threadIdx.x; i < len; i += LONG_T) rk[i] = i + 1 < len ? trc_pair_rank(T, id[i], id[i + 1]) : TRC_NO_RANK;
+  __syncthreads();
+  int64_t m = len;
+  for (;;) {
+    unsigned long long best = ~0ULL;
+    for (int64_t i = threadIdx.x; i < len; i += LONG_T) {
+      unsigned long long k = ((unsigned long long)rk[i] << 32) | (unsigned long long)i;
+      best = k < best ? k : best;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { unsigned long long y = __shfl_xor_sync(0xffffffffu, best, o); best = y < best ? y : best; }
+    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = best;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      unsigned long long b = s_red[0];
+      for (int k = 1; k < LONG_T / 32; ++k) b = s_red[k] < b ? s_red[k] : b;
+      s_best = b;
+      uint32_t r = (uint32_t)(b >> 32);
+      if (r != TRC_NO_RANK) {
+        int32_t i = (int32_t)(b & 0xffffffffu);
+        int32_t j = nx[i], nj = nx[j];
+        id[i] = r; nx[i] = nj; rk[j] = TRC_NO_RANK;
+        if (nj < len) { pv[nj] = i; rk[i] = trc_pair_rank(T, r, id[nj]); } else rk[i] = TRC_NO_RANK;
+        int32_t p = pv[i];
+        if (p >= 0) rk[p] = trc_pair_rank(T, id[p], r);
+      }
+    }
+    __syncthreads();
+    if ((uint32_t)(s_best >> 32) == TRC_NO_RANK) break;
+    --m;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *out_count = (uint32_t)m;
+}
+
+extern "C" int trc_bpe_span_count_static(trc_ctx* ctx, const uint8_t* d_span, int64_t n_bytes, uint32_t* d_count, void* stream) {
+  if (!ctx || !d_span || !d_count) return TRC_EINVAL;
+  if (!ctx->have_vocab) { ctx->err = "vocabulary not loaded"; return TRC_ENOVOCAB; }
+  if (n_bytes < 1) { ctx->err = "trc_bpe_span_count_static: the span must have at least one byte"; return TRC_EINVAL; }
+  if (n_bytes > TRC_STATIC_SPAN_MAX) {
+    ctx->err = "trc_bpe_span_count_static: span of " + std::to_string(n_bytes) + " bytes exceeds the built-in work area (limit " +
+               std::to_string(TRC_STATIC_SPAN_MAX) + " bytes); use trc_count_tokens for longer spans";
+    return TRC_EINVAL;
+  }
+  if (ctx->device < 0 || ctx->device >= 64) { ctx->err = "device ordinal out of range"; return TRC_EINVAL; }
+  CK(cudaSetDevice(ctx->device));
+  uint32_t* scratch;
+  {
+    // first call on this device: resolve the device address of the array (the host-side symbol is only
+    // a handle).  This is a one-off; make that first call outside any stream capture.
+    std::lock_guard<std::mutex> lk(g_span_mu);
+    if (!g_span_scratch_addr[ctx->device]) {
+      void* p = nullptr;
+      CK(cudaGetSymbolAddress(&p, g_span_scratch));
+      g_span_scratch_addr[ctx->device] = (uint32_t*)p;
+    }
+    scratch = g_span_scratch_addr[ctx->device];
+  }
+  cudaStream_t st = stream ? (cudaStream_t)stream : ctx->own_stream;
+  k_bpe_span_static<<<1, LONG_T, 0, st>>>(ctx->T, ctx->d_byte_id, d_span, n_bytes, d_count, scratch);
+  ctx->launches++;
+  CK(cudaGetLastError());
+  return TRC_OK;
+}
+#endif
