@@ -12,11 +12,13 @@
 struct TrcCleanOut {
   int64_t bytes;   // cleaned length in UTF-8 bytes (0 => segment is blank and is dropped)
   int64_t chars;   // cleaned length in code points (len(text) of the processed segment)
+  int32_t spaces;  // U+0020 characters emitted (every one of them starts a pre-tokeniser match)
 };
 
 template <bool WRITE>
 TRC_HD TrcCleanOut trc_clean_segment(const TrcTables& T, const uint8_t* in, int64_t n, uint8_t* out) {
   int64_t o = 0, nch = 0;
+  int32_t nsp = 0;
   bool seen = false, pending = false, in_word = false, cand = false, w_pending = false;
   bool have_prev = false, gap0 = false;
   int64_t w_start = 0, w_chars = 0, p_start = 0, p_len = 0;
@@ -31,11 +33,11 @@ TRC_HD TrcCleanOut trc_clean_segment(const TrcTables& T, const uint8_t* in, int6
         if (in[w_start + k] != in[p_start + k]) { dup = false; break; }
     }
     if (!dup) {
-      if (w_pending) { if (WRITE) out[o] = ' '; ++o; ++nch; lastb = ' '; }
+      if (w_pending) { if (WRITE) out[o] = ' '; ++o; ++nch; ++nsp; lastb = ' '; }
       uint8_t f = in[w_start];
       if ((lastb == '.' || lastb == '!' || lastb == '?') && ((f >= 'A' && f <= 'Z') || (f >= 'a' && f <= 'z'))) {
         if (WRITE) out[o] = ' ';
-        ++o; ++nch;
+        ++o; ++nch; ++nsp;
       }
       if (WRITE) for (int64_t k = 0; k < len; ++k) out[o + k] = in[w_start + k];
       o += len; nch += w_chars;
@@ -64,7 +66,7 @@ TRC_HD TrcCleanOut trc_clean_segment(const TrcTables& T, const uint8_t* in, int6
       seen = true;
     } else {
       if (in_word) end_word(i);
-      if (pending) { if (WRITE) out[o] = ' '; ++o; ++nch; pending = false; }
+      if (pending) { if (WRITE) out[o] = ' '; ++o; ++nch; ++nsp; pending = false; }
       if (WRITE) for (int k = 0; k < len; ++k) out[o + k] = in[i + k];
       o += len; ++nch;
       lastb = in[i + len - 1];
@@ -74,6 +76,6 @@ TRC_HD TrcCleanOut trc_clean_segment(const TrcTables& T, const uint8_t* in, int6
     i += len;
   }
   if (in_word) end_word(n);
-  TrcCleanOut r; r.bytes = o; r.chars = nch;
+  TrcCleanOut r; r.bytes = o; r.chars = nch; r.spaces = nsp;
   return r;
 }

@@ -48,7 +48,26 @@ struct TrcTables {
   // token counts of digit groups: index = value + (len==1 ? 0 : len==2 ? 10 : 110)
   const uint8_t* dcount;   // 1110 entries
   uint32_t cnt_space_lbracket;  // count(" [")
+  // fast paths (exact): Rust class of the 128 ASCII bytes; sets of ALL vocabulary entries of <= 8 and
+  // 9..16 bytes that contain no 0x00 byte, keyed by their zero-padded little-endian bytes
+  const uint8_t* acls;          // 128 entries
+  const uint64_t* tok8;  uint32_t tok8_mask;    // empty slot = 0 (no key is 0: keys have no NUL bytes, len >= 1)
+  const uint64_t* tok16; uint32_t tok16_mask;   // pairs (lo, hi); empty = (0,0)
+  const uint64_t* hot8_src; uint32_t hot8_size; // direct-mapped image of the lowest-rank <=8-byte tokens (kernels copy it to smem)
+  uint64_t sp_first[4];         // bitmap of first bytes of the special-token literals
 };
+
+TRC_HD uint64_t trc_mix64(uint64_t x);
+
+// Per-kernel view of the small tables a kernel may have staged in shared memory.
+struct TrcFast {
+  const uint8_t* acls;     // ASCII class table (global or shared)
+  const uint64_t* hot8;    // direct-mapped hot set in shared memory, or nullptr
+  uint32_t hot8_mask;
+};
+TRC_HD TrcFast trc_fast_default(const TrcTables& T) { TrcFast F; F.acls = T.acls; F.hot8 = nullptr; F.hot8_mask = 0; return F; }
+TRC_HD uint32_t trc_cls(const TrcTables& T, const TrcFast& F, uint32_t cp) { return cp < 128u ? (uint32_t)F.acls[cp] : TRC_RS(T.props[cp]); }
+TRC_HD uint32_t trc_key8_slot(uint64_t key, uint32_t mask) { return (uint32_t)(trc_mix64(key) >> 20) & mask; }
 
 // ---- UTF-8 (input is produced by Python's str.encode('utf-8'): always well formed) -----------------
 TRC_HD int trc_u8len(uint8_t b) { return b < 0x80 ? 1 : (b < 0xE0 ? 2 : (b < 0xF0 ? 3 : 4)); }

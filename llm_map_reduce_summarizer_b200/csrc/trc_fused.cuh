@@ -1,0 +1,326 @@
+// K1a + K2 fused: one pass over the raw text.  Persistent CTAs take tiles of FUSE_SEGS raw segments from
+// an atomic counter.  A tile is staged in shared memory with 16-byte loads and cleaned there with the
+// byte-parallel local rules of trc_clean_par.cuh (preprocessor.py:69-89): all lanes of a warp work on 32
+// consecutive bytes, output positions come from warp ballots + a scan of per-strip totals.  The cleaned
+// tile is tokenised in shared memory word by word (big_chunkeroosky.py:83 via the decomposition of
+// thread per whitespace-delimited word, uniform work per thread) and written out once, at
+// the offset obtained by a decoupled look-back over the tiles' (cleaned bytes, kept segments) aggregates.
+// Replaces the count -> scan -> compact -> write -> tokenise sequence of the v1 kernels.
+// Tiles that do not fit the staging buffers take the slow lane (sequential per-segment routines on global
+// memory) inside the same kernel.  CUDA only; the per-unit routines it calls are host-testable.
+#pragma once
+
+#define FUSE_T 512
+#define FUSE_NW (FUSE_T / 32)
+#define FUSE_SEGS 256
+#define FUSE_IN_CAP 20480
+#define FUSE_OUT_CAP 30720
+#define FUSE_WORD_CAP 5120
+#define FUSE_HOT 2048
+#define FUSE_STRIPS (FUSE_IN_CAP / 32)
+
+struct FuseSmem {
+  uint8_t in[FUSE_IN_CAP + 32];
+  union { uint8_t cls[FUSE_IN_CAP]; uint8_t out[FUSE_OUT_CAP]; } x;
+  union { uint8_t code[FUSE_IN_CAP]; struct { uint16_t wstart[FUSE_WORD_CAP]; uint16_t wseg[FUSE_WORD_CAP]; } w; } z;
+  uint64_t hot8[FUSE_HOT];
+  int32_t strip_base[FUSE_STRIPS + 1];
+  uint16_t strip_seg[FUSE_STRIPS];
+  int32_t rel[FUSE_SEGS + 1];
+  int32_t loff[FUSE_SEGS + 1];
+  int32_t len[FUSE_SEGS], nw[FUSE_SEGS], woff[FUSE_SEGS], koff[FUSE_SEGS], tok[FUSE_SEGS], chars[FUSE_SEGS];
+  int32_t wsum[3][FUSE_NW];
+  int32_t tot[3];
+  unsigned int tile;
+  long long gbase, kbase;
+};
+
+struct FuseArgs {
+  unsigned long long* tile_counter;
+  unsigned long long* desc_bytes;   // look-back descriptors, one per tile
+  unsigned long long* desc_kept;
+  int64_t* totals;                  // [0] kept segments, [1] cleaned bytes
+  int64_t text_bytes;
+  int32_t* seg_special;
+  LongEntry* wl; unsigned long long* wl_cnt; int64_t wl_cap;
+};
+
+__device__ __forceinline__ long long fuse_lookback(unsigned long long* d, unsigned tile, long long aggregate, int lane) {
+  long long excl = 0;
+  if (tile == 0) { if (lane == 0) st_relaxed(&d[0], (2ULL << 62) | (unsigned long long)aggregate); return 0; }
+  if (lane == 0) st_relaxed(&d[tile], (1ULL << 62) | (unsigned long long)aggregate);
+  long long idx = (long long)tile - 1;
+  for (;;) {
+    long long my = idx - lane;
+    unsigned long long dv = (2ULL << 62);
+    if (my >= 0) { dv = ld_relaxed(&d[my]); while ((dv >> 62) == 0) dv = ld_relaxed(&d[my]); }
+    unsigned st = (unsigned)(dv >> 62);
+    long long val = (long long)(dv & ((1ULL << 62) - 1));
+    unsigned ball = __ballot_sync(0xffffffffu, st == 2);
+    int first = ball ? __ffs(ball) - 1 : 31;
+    long long c = lane <= first ? val : 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    excl += c;
+    if (ball) break;
+    idx -= 32;
+  }
+  if (lane == 0) st_relaxed(&d[tile], (2ULL << 62) | (unsigned long long)(excl + aggregate));
+  return excl;
+}
+
+// exclusive block scan of three int32 values; totals land in S.tot[]
+__device__ __forceinline__ void fuse_scan3(FuseSmem& S, int lane, int wid, int32_t v0, int32_t v1, int32_t v2, int32_t* e0, int32_t* e1,
+                                           int32_t* e2) {
+  int32_t x0 = v0, x1 = v1, x2 = v2;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int32_t y0 = __shfl_up_sync(0xffffffffu, x0, o), y1 = __shfl_up_sync(0xffffffffu, x1, o), y2 = __shfl_up_sync(0xffffffffu, x2, o);
+    if (lane >= o) { x0 += y0; x1 += y1; x2 += y2; }
+  }
+  __syncthreads();                      // protects wsum/tot of a previous use
+  if (lane == 31) { S.wsum[0][wid] = x0; S.wsum[1][wid] = x1; S.wsum[2][wid] = x2; }
+  __syncthreads();
+  if (wid == 0) {
+    int32_t w0 = lane < FUSE_NW ? S.wsum[0][lane] : 0, w1 = lane < FUSE_NW ? S.wsum[1][lane] : 0, w2 = lane < FUSE_NW ? S.wsum[2][lane] : 0;
+#pragma unroll
+    for (int o = 1; o < FUSE_NW; o <<= 1) {
+      int32_t y0 = __shfl_up_sync(0xffffffffu, w0, o), y1 = __shfl_up_sync(0xffffffffu, w1, o), y2 = __shfl_up_sync(0xffffffffu, w2, o);
+      if (lane >= o) { w0 += y0; w1 += y1; w2 += y2; }
+    }
+    if (lane < FUSE_NW) { S.wsum[0][lane] = w0; S.wsum[1][lane] = w1; S.wsum[2][lane] = w2; }
+    if (lane == FUSE_NW - 1) { S.tot[0] = w0; S.tot[1] = w1; S.tot[2] = w2; }
+  }
+  __syncthreads();
+  *e0 = (wid ? S.wsum[0][wid - 1] : 0) + x0 - v0;
+  *e1 = (wid ? S.wsum[1][wid - 1] : 0) + x1 - v1;
+  *e2 = (wid ? S.wsum[2][wid - 1] : 0) + x2 - v2;
+}
+
+__global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTables T, const uint32_t* __restrict__ byte_id, FuseArgs A,
+                                                               int64_t ntiles) {
+  extern __shared__ __align__(16) unsigned char fuse_raw[];
+  FuseSmem& S = *reinterpret_cast<FuseSmem*>(fuse_raw);
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const unsigned lt = (1u << lane) - 1u;
+  for (int k = tid; k < FUSE_HOT; k += FUSE_T) S.hot8[k] = T.hot8_src[k];
+  TrcFast F; F.acls = T.acls; F.hot8 = S.hot8; F.hot8_mask = FUSE_HOT - 1;
+  __syncthreads();
+  for (;;) {
+    if (tid == 0) S.tile = (unsigned int)atomicAdd(A.tile_counter, 1ULL);
+    __syncthreads();
+    const unsigned tile = S.tile;
+    if ((int64_t)tile >= ntiles) break;
+    const int64_t s0 = (int64_t)tile * FUSE_SEGS;
+    const int ns = (int)((D.n - s0) < FUSE_SEGS ? (D.n - s0) : FUSE_SEGS);
+    const int64_t raw0 = D.seg_off[s0], raw1 = D.seg_off[s0 + ns];
+    const int al = (int)(raw0 & 15);
+    const int64_t base = raw0 - al;
+    const int32_t span = (int32_t)((raw1 - base) < (1 << 30) ? (raw1 - base) : (1 << 30));
+    const bool fast_in = (raw1 - base) <= FUSE_IN_CAP;
+    for (int k = tid; k <= ns; k += FUSE_T) S.rel[k] = (int32_t)(D.seg_off[s0 + k] - base);
+    int32_t mylen = 0, mynw = 0, mykeep = 0, mychars = 0, loff = 0, woff = 0, koff = 0;
+    int32_t tot_out = 0, tot_words = 0, tot_kept = 0;
+    long long gbase = 0, kbase = 0;
+    bool fast_out = false;
+    if (fast_in) {
+      // ================= fast lane: byte-parallel clean in shared memory =================
+      for (int32_t k = tid * 16; k < span; k += FUSE_T * 16) {
+        if (base + k + 16 <= A.text_bytes) *reinterpret_cast<int4*>(&S.in[k]) = *reinterpret_cast<const int4*>(D.text + base + k);
+        else for (int q = 0; q < 16 && base + k + q < A.text_bytes; ++q) S.in[k + q] = D.text[base + k + q];
+      }
+      const int nstrips = (span + 31) >> 5;
+      __syncthreads();
+      // segment of the first byte of every strip
+      if (tid < ns) {
+        int32_t a = S.rel[tid], b = S.rel[tid + 1];
+        if (b > a) for (int32_t s = (a + 31) >> 5; (s << 5) < b; ++s) S.strip_seg[s] = (uint16_t)tid;
+      }
+      if (tid == 0) S.strip_seg[0] = 0;
+      __syncthreads();
+      // P1 classify
+      for (int s = wid; s < nstrips; s += FUSE_NW) {
+        int32_t k = (s << 5) + lane;
+        if (k < al) { S.x.cls[k] = 0; S.z.code[k] = 0; }      // bytes of the previous tile in the aligned prefix
+        else if (k < span) {
+          int i = S.strip_seg[s];
+          while (i + 1 < ns && S.rel[i + 1] <= k) ++i;
+          cp_classify(T, S.in, S.x.cls, S.z.code, k, S.rel[i + 1]);
+        }
+      }
+      __syncthreads();
+      // P2 duplicate-word marks
+      for (int s = wid; s < nstrips; s += FUSE_NW) {
+        int32_t k = (s << 5) + lane;
+        if (k >= al && k < span) {
+          int i = S.strip_seg[s];
+          while (i + 1 < ns && S.rel[i + 1] <= k) ++i;
+          cp_mark_dup(S.in, S.x.cls, S.z.code, k, S.rel[i], S.rel[i + 1]);
+        }
+      }
+      __syncthreads();
+      // P3 output codes + per-strip output sizes
+      for (int s = wid; s < nstrips; s += FUSE_NW) {
+        int32_t k = (s << 5) + lane;
+        uint32_t r = 0;
+        if (k >= al && k < span) {
+          int i = S.strip_seg[s];
+          while (i + 1 < ns && S.rel[i + 1] <= k) ++i;
+          r = cp_code(S.in, S.x.cls, S.z.code, k, S.rel[i], S.rel[i + 1]);
+        }
+        unsigned m1 = __ballot_sync(0xffffffffu, r != 0), m2 = __ballot_sync(0xffffffffu, r == 3);
+        if (lane == 0) S.strip_base[s] = __popc(m1) + __popc(m2);
+      }
+      __syncthreads();
+      if (wid == 0) {                       // exclusive scan of the strip totals
+        int32_t carry = 0;
+        for (int b0 = 0; b0 < nstrips; b0 += 32) {
+          int32_t v = b0 + lane < nstrips ? S.strip_base[b0 + lane] : 0, x = v;
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) { int32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+          if (b0 + lane < nstrips) S.strip_base[b0 + lane] = carry + x - v;
+          carry += __shfl_sync(0xffffffffu, x, 31);
+        }
+        if (lane == 0) S.strip_base[nstrips] = carry;
+      }
+      __syncthreads();
+      tot_out = S.strip_base[nstrips];
+      // output offset of every segment start
+      for (int i = tid; i <= ns; i += FUSE_T) {
+        int32_t k = S.rel[i], pos;
+        if (k >= span) pos = tot_out;
+        else { pos = S.strip_base[k >> 5]; for (int32_t j = k & ~31; j < k; ++j) pos += cp_outlen(S.z.code[j]); }
+        S.loff[i] = pos;
+      }
+      __syncthreads();
+      if (tid < ns) { loff = S.loff[tid]; mylen = S.loff[tid + 1] - loff; mykeep = mylen > 0; }
+      int32_t d0, d1;
+      fuse_scan3(S, lane, wid, mykeep, 0, 0, &koff, &d0, &d1);
+      tot_kept = S.tot[0];
+      if (wid == 0) {
+        long long gb = fuse_lookback(A.desc_bytes, tile, tot_out, lane);
+        long long kb = fuse_lookback(A.desc_kept, tile, tot_kept, lane);
+        if (lane == 0) { S.gbase = gb; S.kbase = kb; }
+      }
+      __syncthreads();
+      gbase = S.gbase; kbase = S.kbase;
+      fast_out = tot_out <= FUSE_OUT_CAP;
+      // scatter (cls is dead: out may overwrite it)
+      {
+        uint8_t* dst = fast_out ? S.x.out : D.C + gbase;
+        for (int s = wid; s < nstrips; s += FUSE_NW) {
+          int32_t k = (s << 5) + lane;
+          uint32_t r = (k >= al && k < span) ? S.z.code[k] : 0u;
+          unsigned m1 = __ballot_sync(0xffffffffu, r != 0), m2 = __ballot_sync(0xffffffffu, r == 3);
+          int32_t pos = S.strip_base[s] + __popc(m1 & lt) + __popc(m2 & lt);
+          if (r == 1) dst[pos] = S.in[k];
+          else if (r == 2) dst[pos] = ' ';
+          else if (r == 3) { dst[pos] = ' '; dst[pos + 1] = S.in[k]; }
+        }
+      }
+      __syncthreads();
+      if (fast_out) {                        // the cleaned tile leaves shared memory once, coalesced
+        uint8_t* dstg = D.C + gbase;
+        for (int32_t k = tid; k < tot_out; k += FUSE_T) dstg[k] = S.x.out[k];
+      }
+      // words and code points per segment
+      if (tid < ns && mylen > 0) {
+        const uint8_t* p = fast_out ? S.x.out + loff : D.C + gbase + loff;
+        int32_t sp = 0, cc = 0;
+        for (int32_t k = 0; k < mylen; ++k) { uint8_t c = p[k]; sp += c == ' '; cc += (c & 0xC0) != 0x80; }
+        mynw = sp + 1; mychars = cc;
+      }
+      fuse_scan3(S, lane, wid, mynw, 0, 0, &woff, &d0, &d1);
+      tot_words = S.tot[0];
+      fast_out = fast_out && tot_words <= FUSE_WORD_CAP;
+    } else {
+      // ================= slow lane: sequential per-segment routines on global memory =================
+      const uint8_t* src = D.text + base;
+      int32_t a = 0, b = 0;
+      if (tid < ns) {
+        a = S.rel[tid]; b = S.rel[tid + 1];
+        TrcCleanOut r = trc_clean_segment<false>(T, src + a, b - a, nullptr);
+        mylen = (int32_t)r.bytes; mychars = (int32_t)r.chars; mykeep = r.bytes > 0;
+      }
+      int32_t d1;
+      fuse_scan3(S, lane, wid, mylen, mykeep, 0, &loff, &koff, &d1);
+      tot_out = S.tot[0]; tot_kept = S.tot[1];
+      if (wid == 0) {
+        long long gb = fuse_lookback(A.desc_bytes, tile, tot_out, lane);
+        long long kb = fuse_lookback(A.desc_kept, tile, tot_kept, lane);
+        if (lane == 0) { S.gbase = gb; S.kbase = kb; }
+      }
+      __syncthreads();
+      gbase = S.gbase; kbase = S.kbase;
+      if (tid < ns && mylen > 0) trc_clean_segment<true>(T, src + a, b - a, D.C + gbase + loff);
+    }
+    if (tid < FUSE_SEGS) S.tok[tid] = 0;
+    __syncthreads();
+    // ---- tokens of " " + cleaned text, special-token scan
+    int32_t mysp = -1;
+    if (fast_out) {
+      if (tid < ns && mylen > 0) {
+        int32_t w = woff;
+        S.z.w.wstart[w] = (uint16_t)loff; S.z.w.wseg[w] = (uint16_t)tid; ++w;
+        for (int32_t k = 0; k < mylen; ++k)
+          if (S.x.out[loff + k] == ' ') { S.z.w.wstart[w] = (uint16_t)(loff + k); S.z.w.wseg[w] = (uint16_t)tid; ++w; }
+        mysp = trc_find_special(T, S.x.out + loff, mylen);
+      }
+      if (tid < ns) { S.len[tid] = mylen; S.koff[tid] = koff; }
+      __syncthreads();
+      for (int32_t w = tid; w < tot_words; w += FUSE_T) {
+        const int seg = S.z.w.wseg[w];
+        const int32_t st = S.z.w.wstart[w];
+        const int32_t sl = S.loff[seg];
+        const int32_t en = (w + 1 < tot_words && S.z.w.wseg[w + 1] == seg) ? (int32_t)S.z.w.wstart[w + 1] : sl + S.len[seg];
+        const int vs = st == sl ? 1 : 0;
+        const int64_t j = kbase + S.koff[seg];
+        uint32_t c = trc_count_unit(T, F, byte_id, S.x.out + st, en - st, vs, [&](int64_t ls, int64_t len) -> uint32_t {
+          unsigned long long slot = atomicAdd(&A.wl_cnt[0], 1ULL);
+          unsigned long long off = atomicAdd(&A.wl_cnt[1], (unsigned long long)len);
+          if ((int64_t)slot < A.wl_cap) { LongEntry e; e.unit = j; e.lstart = ls + (vs ? 0 : (st - sl + 1)); e.len = len; e.scratch_off = (int64_t)off; A.wl[slot] = e; }
+          return 0u;
+        });
+        atomicAdd(&S.tok[seg], (int32_t)c);
+      }
+    } else if (tid < ns && mylen > 0) {
+      const int64_t j = kbase + koff;
+      const uint8_t* p = D.C + gbase + loff;
+      uint32_t c = trc_count_unit(T, F, byte_id, p, mylen, 1, [&](int64_t ls, int64_t len) -> uint32_t {
+        unsigned long long slot = atomicAdd(&A.wl_cnt[0], 1ULL);
+        unsigned long long off = atomicAdd(&A.wl_cnt[1], (unsigned long long)len);
+        if ((int64_t)slot < A.wl_cap) { LongEntry e; e.unit = j; e.lstart = ls; e.len = len; e.scratch_off = (int64_t)off; A.wl[slot] = e; }
+        return 0u;
+      });
+      S.tok[tid] = (int32_t)c;
+      mysp = trc_find_special(T, p, mylen);
+    }
+    __syncthreads();
+    // ---- outputs
+    if (tid < ns) {
+      D.cchars[s0 + tid] = mychars;
+      if (mykeep) {
+        const int64_t j = kbase + koff;
+        const int64_t i = s0 + tid;
+        D.k2r[j] = (int32_t)i; D.coff[j] = gbase + loff; D.ctok[j] = (uint32_t)S.tok[tid]; A.seg_special[j] = mysp;
+        int64_t lo = 0, hi = D.n_doc;
+        while (hi - lo > 1) { int64_t mid = (lo + hi) >> 1; if (D.doc_off[mid] <= i) lo = mid; else hi = mid; }
+        D.sdoc[j] = (int32_t)lo;
+      }
+    }
+    if (tid == 0 && s0 + ns == D.n) {
+      D.coff[kbase + tot_kept] = gbase + tot_out;
+      A.totals[0] = kbase + tot_kept; A.totals[1] = gbase + tot_out;
+    }
+    __syncthreads();
+  }
+}
+
+// kdoc_off[x] = first kept segment whose document is >= x   (sdoc is non-decreasing)
+__global__ void k_doc_ranges(const int32_t* __restrict__ sdoc, int64_t n_kept, int64_t* kdoc_off, int64_t n_doc) {
+  GSTRIDE(x, n_doc + 1) {
+    int64_t lo = 0, hi = n_kept;
+    while (lo < hi) { int64_t mid = (lo + hi) >> 1; if (sdoc[mid] < x) lo = mid + 1; else hi = mid; }
+    kdoc_off[x] = lo;
+  }
+}

@@ -26,14 +26,14 @@ TRC_HD uint32_t trc_sdecode(const TrcStr& S, int64_t i, int* len) {
 // Alternatives in pattern order:
 //  1 (?i:'s|'t|'re|'ve|'m|'ll|'d)   2 [^\r\n\p{L}\p{N}]?\p{L}+   3 \p{N}{1,3}
 //  4  ?[^\s\p{L}\p{N}]+[\r\n]*      5 \s*[\r\n]+   6 \s+(?!\S)   7 \s+
-TRC_HD int64_t trc_span_end(const TrcTables& T, const TrcStr& S, int64_t p) {
+TRC_HD int64_t trc_span_end(const TrcTables& T, const TrcFast& F, const TrcStr& S, int64_t p) {
   const int64_t N = S.n;
   int l0, l1 = 0, l2 = 0;
   uint32_t c0 = trc_sdecode(S, p, &l0);
-  uint32_t k0 = TRC_RS(trc_prop(T, c0));
+  uint32_t k0 = trc_cls(T, F, c0);
   bool has1 = p + l0 < N;
   uint32_t c1 = 0, k1 = 9;
-  if (has1) { c1 = trc_sdecode(S, p + l0, &l1); k1 = TRC_RS(trc_prop(T, c1)); }
+  if (has1) { c1 = trc_sdecode(S, p + l0, &l1); k1 = trc_cls(T, F, c1); }
   if (c0 == '\'' && has1) {
     uint32_t a = c1;
     if (a == 's' || a == 'S' || a == 't' || a == 'T' || a == 'm' || a == 'M' || a == 'd' || a == 'D' || a == 0x17F)
@@ -53,7 +53,7 @@ TRC_HD int64_t trc_span_end(const TrcTables& T, const TrcStr& S, int64_t p) {
     if (kq == TRC_RS_L) {
       while (q < N) {
         int l; uint32_t c = trc_sdecode(S, q, &l);
-        if (TRC_RS(trc_prop(T, c)) != TRC_RS_L) break;
+        if (trc_cls(T, F, c) != TRC_RS_L) break;
         q += l;
       }
       return q;
@@ -64,7 +64,7 @@ TRC_HD int64_t trc_span_end(const TrcTables& T, const TrcStr& S, int64_t p) {
     int cnt = 1;
     while (q < N && cnt < 3) {
       int l; uint32_t c = trc_sdecode(S, q, &l);
-      if (TRC_RS(trc_prop(T, c)) != TRC_RS_N) break;
+      if (trc_cls(T, F, c) != TRC_RS_N) break;
       q += l; ++cnt;
     }
     return q;
@@ -76,7 +76,7 @@ TRC_HD int64_t trc_span_end(const TrcTables& T, const TrcStr& S, int64_t p) {
     if (kq == TRC_RS_O) {
       while (q < N) {
         int l; uint32_t c = trc_sdecode(S, q, &l);
-        if (TRC_RS(trc_prop(T, c)) != TRC_RS_O) break;
+        if (trc_cls(T, F, c) != TRC_RS_O) break;
         q += l;
       }
       while (q < N) { uint8_t b = S.at(q); if (b != '\r' && b != '\n') break; ++q; }
@@ -87,7 +87,7 @@ TRC_HD int64_t trc_span_end(const TrcTables& T, const TrcStr& S, int64_t p) {
   int64_t r = p, last_nl = -1, last_start = p;
   while (r < N) {
     int l; uint32_t c = trc_sdecode(S, r, &l);
-    if (TRC_RS(trc_prop(T, c)) != TRC_RS_S) break;
+    if (trc_cls(T, F, c) != TRC_RS_S) break;
     if (c == '\r' || c == '\n') last_nl = r;
     last_start = r;
     r += l;
@@ -99,7 +99,43 @@ TRC_HD int64_t trc_span_end(const TrcTables& T, const TrcStr& S, int64_t p) {
 }
 
 // Is the byte string a vocabulary entry?  (tiktoken: `if piece in ranks` => one token)
-TRC_HD bool trc_is_token(const TrcTables& T, const TrcStr& S, int64_t a, int n) {
+TRC_HD bool trc_is_token_generic(const TrcTables& T, const TrcStr& S, int64_t a, int n);
+
+// Exact membership test with the <=16-byte key sets; longer spans (and spans holding a NUL byte) use the
+// hashed byte-string table.
+TRC_HD bool trc_is_token(const TrcTables& T, const TrcFast& F, const TrcStr& S, int64_t a, int n) {
+  if (n <= 16) {
+    uint64_t lo = 0, hi = 0;
+    bool nul = false;
+    for (int i = 0; i < n; ++i) {
+      uint64_t b = S.at(a + i);
+      nul |= (b == 0);
+      if (i < 8) lo |= b << (8 * i); else hi |= b << (8 * (i - 8));
+    }
+    if (!nul) {
+      if (n <= 8) {
+        if (F.hot8 && F.hot8[trc_key8_slot(lo, F.hot8_mask)] == lo) return true;
+        uint32_t slot = trc_key8_slot(lo, T.tok8_mask);
+        for (;;) {
+          uint64_t e = T.tok8[slot];
+          if (e == lo) return true;
+          if (e == 0) return false;
+          slot = (slot + 1) & T.tok8_mask;
+        }
+      }
+      uint32_t slot = trc_key8_slot(lo ^ (hi * 0x9E3779B97F4A7C15ULL), T.tok16_mask);
+      for (;;) {
+        uint64_t e0 = T.tok16[2 * (size_t)slot], e1 = T.tok16[2 * (size_t)slot + 1];
+        if (e0 == lo && e1 == hi) return true;
+        if (e0 == 0 && e1 == 0) return false;
+        slot = (slot + 1) & T.tok16_mask;
+      }
+    }
+  }
+  return trc_is_token_generic(T, S, a, n);
+}
+
+TRC_HD bool trc_is_token_generic(const TrcTables& T, const TrcStr& S, int64_t a, int n) {
   uint64_t h = trc_hash_bytes([&](int i) { return S.at(a + i); }, n);
   uint32_t fp = (uint32_t)(h >> 32);
   uint32_t slot = (uint32_t)h & T.tokhash_mask;
@@ -143,6 +179,7 @@ TRC_HD int trc_bpe_short(const TrcTables& T, const uint32_t* byte_id, const TrcS
 TRC_HD int trc_find_special(const TrcTables& T, const uint8_t* p, int64_t n) {
   for (int64_t i = 0; i < n; ++i) {
     uint8_t b = p[i];
+    if (!((T.sp_first[b >> 6] >> (b & 63)) & 1ULL)) continue;
     for (uint32_t k = 0; k < T.n_sp; ++k) {
       uint32_t o = T.sp_off[k], L = T.sp_off[k + 1] - o;
       if (L == 0 || T.sp_bytes[o] != b || i + (int64_t)L > n) continue;
@@ -158,16 +195,16 @@ TRC_HD int trc_find_special(const TrcTables& T, const uint8_t* p, int64_t n) {
 // to `long_span(logical_start, length)` which returns their count (device: deferred to the block-wide
 // long-span kernel and returns 0; hostsim: computed inline).
 template <class LongSpan>
-TRC_HD uint32_t trc_count_unit(const TrcTables& T, const uint32_t* byte_id, const uint8_t* p, int64_t nbytes, int vs,
-                               LongSpan&& long_span) {
+TRC_HD uint32_t trc_count_unit(const TrcTables& T, const TrcFast& F, const uint32_t* byte_id, const uint8_t* p, int64_t nbytes,
+                               int vs, LongSpan&& long_span) {
   TrcStr S; S.p = p; S.n = nbytes + vs; S.vs = vs;
   uint32_t total = 0;
   int64_t q = 0;
   while (q < S.n) {
-    int64_t e = trc_span_end(T, S, q);
+    int64_t e = trc_span_end(T, F, S, q);
     int64_t len = e - q;
     if (len == 1) total += 1;
-    else if (len <= 0x7fffffff && trc_is_token(T, S, q, (int)len)) total += 1;
+    else if (len <= 0x7fffffff && trc_is_token(T, F, S, q, (int)len)) total += 1;
     else if (len <= TRC_SHORT_SPAN) total += (uint32_t)trc_bpe_short(T, byte_id, S, q, (int)len);
     else total += long_span(q, len);
     q = e;

@@ -16,6 +16,8 @@ struct TrcHostVocab {
   std::vector<uint32_t> byte_id;   // 256
   std::vector<uint8_t> sp_bytes;
   std::vector<uint32_t> sp_off;
+  std::vector<uint64_t> tok8, tok16, hot8;
+  uint64_t sp_first[4] = {0, 0, 0, 0};
   uint32_t n_tok = 0, n_sp = 0;
   uint64_t n_pairs = 0;
 };
@@ -96,12 +98,45 @@ static inline std::string trc_build_host_vocab(const uint8_t* token_bytes, const
     while (V.pairhash[slot] != ~0ULL) slot = (slot + 1) & (psz - 1);
     V.pairhash[slot] = e;
   }
+  // exact-key sets for tokens of <= 8 and 9..16 bytes without NUL bytes; hot8 = direct-mapped image of the
+  // lowest-rank short tokens (rank order ~ merge frequency), kept by whoever claims a slot first
+  {
+    std::vector<uint64_t> k8; std::vector<std::pair<uint64_t, uint64_t>> k16;
+    for (uint32_t r = 0; r < ntok; ++r) {
+      if (src[r] < 0) continue;
+      const uint8_t* p = &V.tok_bytes[V.tok_off[r]];
+      uint32_t len = V.tok_off[r + 1] - V.tok_off[r];
+      if (len > 16) continue;
+      uint64_t lo = 0, hi = 0; bool nul = false;
+      for (uint32_t i = 0; i < len; ++i) { uint64_t b = p[i]; nul |= b == 0; if (i < 8) lo |= b << (8 * i); else hi |= b << (8 * (i - 8)); }
+      if (nul) continue;
+      if (len <= 8) k8.push_back(lo); else k16.push_back({lo, hi});
+    }
+    uint32_t s8 = trc_pow2_at_least(k8.size() * 2), s16 = trc_pow2_at_least(k16.size() * 2);
+    V.tok8.assign(s8, 0); V.tok16.assign(2 * (size_t)s16, 0);
+    const uint32_t HOT = 4096;
+    V.hot8.assign(HOT, 0);
+    for (uint64_t k : k8) {          // k8 is in rank order
+      uint32_t slot = trc_key8_slot(k, s8 - 1);
+      while (V.tok8[slot] != 0) slot = (slot + 1) & (s8 - 1);
+      V.tok8[slot] = k;
+      uint32_t hs = trc_key8_slot(k, HOT - 1);
+      if (V.hot8[hs] == 0) V.hot8[hs] = k;
+    }
+    for (auto& k : k16) {
+      uint32_t slot = trc_key8_slot(k.first ^ (k.second * 0x9E3779B97F4A7C15ULL), s16 - 1);
+      while (V.tok16[2 * (size_t)slot] != 0 || V.tok16[2 * (size_t)slot + 1] != 0) slot = (slot + 1) & (s16 - 1);
+      V.tok16[2 * (size_t)slot] = k.first; V.tok16[2 * (size_t)slot + 1] = k.second;
+    }
+  }
   if (n_special > TRC_MAX_SPECIALS) return "too many special tokens";
   V.n_sp = (uint32_t)n_special;
   V.sp_off.assign(n_special + 1, 0);
   for (int32_t k = 0; k < n_special; ++k) V.sp_off[k + 1] = V.sp_off[k] + (uint32_t)(special_off[k + 1] - special_off[k]);
   V.sp_bytes.assign(V.sp_off[n_special] + 1, 0);
   if (n_special) memcpy(V.sp_bytes.data(), special_bytes + special_off[0], V.sp_off[n_special]);
+  for (int32_t k = 0; k < n_special; ++k)
+    if (V.sp_off[k + 1] > V.sp_off[k]) { uint8_t b = V.sp_bytes[V.sp_off[k]]; V.sp_first[b >> 6] |= 1ULL << (b & 63); }
   return "";
 }
 

@@ -14,6 +14,7 @@
 #include "trc_common.cuh"
 #include "trc_format.cuh"
 #include "trc_clean.cuh"
+#include "trc_clean_par.cuh"
 #include "trc_tok.cuh"
 #include "trc_stages.cuh"
 #include "trc_sent.cuh"
@@ -73,12 +74,14 @@ struct trc_ctx {
   bool have_tables = false, have_vocab = false;
   TrcTables T{};
   uint8_t* d_props = nullptr;
+  uint8_t* d_acls = nullptr;
   uint32_t* d_byte_id = nullptr;
   std::vector<void*> vocab_allocs;
   uint32_t n_special = 0;
   Arena arena;
   TrcDev D{};
   bool have_pre = false, have_chunk = false;
+  bool use_fused = true;          // single-pass clean+tokenise kernel (TRCHUNK_NO_FUSED=1 selects the v1 kernels)
   int64_t counts[TRC_N_COUNTERS] = {0};
   int64_t* h_pin = nullptr;        // pinned scratch for small D2H reads (64 int64)
   int64_t launches = 0;
@@ -256,6 +259,40 @@ __global__ void k_clean_count(TrcDev D, TrcTables T, int32_t* keep) {
   }
 }
 
+#ifdef TRC_HOSTSIM
+// Host test build only: the byte-parallel formulation of clean_text (trc_clean_par.cuh), one segment at a
+// time, so the CPU suite checks the rules the fused CUDA kernel applies per tile.
+static void hostsim_clean_par_count(TrcDev D, TrcTables T, int32_t* keep, uint8_t* cls, uint8_t* code) {
+  for (int64_t i = 0; i < D.n; ++i) {
+    int64_t a = D.seg_off[i];
+    int32_t n = (int32_t)(D.seg_off[i + 1] - a);
+    const uint8_t* in = D.text + a;
+    for (int32_t k = 0; k < n; ++k) cp_classify(T, in, cls + a, code + a, k, n);
+    for (int32_t k = 0; k < n; ++k) cp_mark_dup(in, cls + a, code + a, k, 0, n);
+    int64_t len = 0; int32_t chars = 0;
+    for (int32_t k = 0; k < n; ++k) {
+      uint32_t r = cp_code(in, cls + a, code + a, k, 0, n);
+      len += cp_outlen(r);
+      chars += (r == 3) ? 2 : ((r == 2 || (r == 1 && !(cls[a + k] & CP_CONT))) ? 1 : 0);
+    }
+    D.clen[i] = len; D.cchars[i] = chars; keep[i] = len > 0;
+  }
+}
+static void hostsim_clean_par_write(TrcDev D, const uint8_t* code) {
+  for (int64_t j = 0; j < D.n_kept; ++j) {
+    int32_t r = D.k2r[j];
+    int64_t a = D.seg_off[r], b = D.seg_off[r + 1];
+    uint8_t* o = D.C + D.coff[j];
+    for (int64_t k = a; k < b; ++k) {
+      uint8_t c = code[k];
+      if (c == 1) *o++ = D.text[k];
+      else if (c == 2) *o++ = ' ';
+      else if (c == 3) { *o++ = ' '; *o++ = D.text[k]; }
+    }
+  }
+}
+#endif
+
 __global__ void k_compact(TrcDev D, const int32_t* keep) {
   GSTRIDE(i, D.n) {
     if (keep[i]) {
@@ -301,7 +338,7 @@ __global__ void k_count_units(TrcTables T, const uint32_t* __restrict__ byte_id,
   GSTRIDE(j, n) {
     const uint8_t* p = bytes + ustart[j];
     int64_t nb = uend[j] - ustart[j];
-    uint32_t c = trc_count_unit(T, byte_id, p, nb, vs, [&](int64_t ls, int64_t len) -> uint32_t {
+    uint32_t c = trc_count_unit(T, trc_fast_default(T), byte_id, p, nb, vs, [&](int64_t ls, int64_t len) -> uint32_t {
 #ifdef TRC_HOSTSIM
       TrcStr S; S.p = p; S.n = nb + vs; S.vs = vs;
       atomicAdd(&wl_cnt[0], 1ULL);
@@ -374,6 +411,10 @@ __global__ void __launch_bounds__(LONG_T) k_bpe_long(TrcTables T, const uint32_t
 }
 
 #endif
+#ifndef TRC_HOSTSIM
+#include "trc_fused.cuh"
+#endif
+
 __global__ void k_special_docs(TrcDev D, const int32_t* __restrict__ seg_special, const int32_t* __restrict__ spk_special) {
   GSTRIDE(j, D.n_kept) {
     if (seg_special[j] >= 0 || spk_special[D.spk[D.k2r[j]]] >= 0)
@@ -601,6 +642,7 @@ extern "C" int trc_create(int device, trc_ctx** out) {
   if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaMallocHost(&ctx->h_pin, 64 * sizeof(int64_t)) != cudaSuccess) { delete ctx; return TRC_ECUDA; }
   for (int k = 0; k < 4; ++k) cudaEventCreate(&ctx->ev[k]);
+  { const char* e = getenv("TRCHUNK_NO_FUSED"); ctx->use_fused = !(e && e[0] == '1'); }
   *out = ctx;
   return TRC_OK;
 }
@@ -612,6 +654,7 @@ extern "C" void trc_destroy(trc_ctx* ctx) {
   ctx->arena.release();
   for (void* p : ctx->vocab_allocs) cudaFree(p);
   if (ctx->d_props) cudaFree(ctx->d_props);
+  if (ctx->d_acls) cudaFree(ctx->d_acls);
   if (ctx->h_pin) cudaFreeHost(ctx->h_pin);
   for (int k = 0; k < 4; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
@@ -626,6 +669,13 @@ extern "C" int trc_load_tables(trc_ctx* ctx, const uint8_t* props) {
   if (!ctx->d_props) CK(cudaMalloc(&ctx->d_props, 0x110000));
   CK(cudaMemcpy(ctx->d_props, props, 0x110000, cudaMemcpyHostToDevice));
   ctx->T.props = ctx->d_props;
+  {
+    uint8_t acls[128];
+    for (int c = 0; c < 128; ++c) acls[c] = (uint8_t)TRC_RS(props[c]);
+    if (!ctx->d_acls) CK(cudaMalloc(&ctx->d_acls, 128));
+    CK(cudaMemcpy(ctx->d_acls, acls, 128, cudaMemcpyHostToDevice));
+    ctx->T.acls = ctx->d_acls;
+  }
   ctx->have_tables = true;
   return TRC_OK;
 }
@@ -660,6 +710,12 @@ extern "C" int trc_load_vocab(trc_ctx* ctx, const uint8_t* token_bytes, const in
   if ((rc = upload_vec(ctx, V.byte_id, &byte_id))) return rc;
   if ((rc = upload_vec(ctx, V.sp_bytes, &ctx->T.sp_bytes))) return rc;
   if ((rc = upload_vec(ctx, V.sp_off, &ctx->T.sp_off))) return rc;
+  if ((rc = upload_vec(ctx, V.tok8, &ctx->T.tok8))) return rc;
+  if ((rc = upload_vec(ctx, V.tok16, &ctx->T.tok16))) return rc;
+  if ((rc = upload_vec(ctx, V.hot8, &ctx->T.hot8_src))) return rc;
+  ctx->T.tok8_mask = (uint32_t)V.tok8.size() - 1; ctx->T.tok16_mask = (uint32_t)(V.tok16.size() / 2) - 1;
+  ctx->T.hot8_size = (uint32_t)V.hot8.size();
+  for (int k = 0; k < 4; ++k) ctx->T.sp_first[k] = V.sp_first[k];
   ctx->d_byte_id = (uint32_t*)byte_id;
   ctx->T.n_tok = V.n_tok; ctx->T.n_sp = V.n_sp;
   ctx->T.tokhash_mask = (uint32_t)V.tokhash.size() - 1;
@@ -761,10 +817,74 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   if ((rc = count_units(ctx, st, spk_ub, spk_uo, spk_uo + 1, B->n_spk, bspk + B->n_spk, 1, spk_tok, spk_special, false))) return rc;
   D.spk_tok = spk_tok;
 
+  int64_t nk = 0, bclean = 0;
+  int32_t* seg_special = nullptr;
+  ALLOC(D.doc_err, int32_t, nd); ALLOC(D.doc_err_seg, int64_t, nd);
+  CK(cudaMemsetAsync(D.doc_err, 0, 4 * (size_t)(nd > 0 ? nd : 1), st));
+  LAUNCH(k_fill_i64, nd, 256, D.doc_err_seg, nd, (int64_t)INT64_MAX);
+#ifndef TRC_HOSTSIM
+  if (ctx->use_fused) {
+    // P1+P2 fused: single pass, outputs sized by upper bounds (cleaned text <= 1.5 x raw, kept <= n)
+    ALLOC(D.cchars, int32_t, n); ALLOC(D.k2r, int32_t, n); ALLOC(D.coff, int64_t, n + 1); ALLOC(D.sdoc, int32_t, n);
+    ALLOC(D.ctok, uint32_t, n); ALLOC(seg_special, int32_t, n); ALLOC(D.kdoc_off, int64_t, nd + 1);
+    const int64_t ccap = braw + braw / 2 + 64;
+    ALLOC(D.C, uint8_t, ccap);
+    if (n == 0) { CK(cudaMemsetAsync(D.coff, 0, 8, st)); CK(cudaMemsetAsync(D.kdoc_off, 0, 8 * (size_t)(nd + 1), st)); }
+    else {
+      const int64_t ntiles = (n + FUSE_SEGS - 1) / FUSE_SEGS;
+      FuseArgs A;
+      unsigned long long* fz;
+      ALLOC(fz, unsigned long long, 2 * ntiles + 8);
+      CK(cudaMemsetAsync(fz, 0, 8 * (size_t)(2 * ntiles + 8), st));
+      A.tile_counter = fz; A.wl_cnt = fz + 2; A.totals = (int64_t*)(fz + 4); A.desc_bytes = fz + 8; A.desc_kept = fz + 8 + ntiles;
+      A.text_bytes = braw; A.seg_special = seg_special;
+      A.wl_cap = ccap / (TRC_SHORT_SPAN + 1) + 1;
+      ALLOC(A.wl, LongEntry, A.wl_cap);
+      static bool attr_done[64] = {false};
+      if (!attr_done[ctx->device & 63]) {
+        CK(cudaFuncSetAttribute(k_clean_tok_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FuseSmem)));
+        attr_done[ctx->device & 63] = true;
+      }
+      int blocks = (int)(ntiles < 148 * 2 ? ntiles : 148 * 2);
+      prof_begin(ctx, st, "k_clean_tok_fused");
+      k_clean_tok_fused<<<blocks, FUSE_T, sizeof(FuseSmem), st>>>(D, ctx->T, ctx->d_byte_id, A, ntiles);
+      prof_end(ctx, st);
+      ctx->launches++;
+      CK(cudaGetLastError());
+      unsigned long long h[6];
+      if ((rc = read_back(ctx, st, fz + 2, 32, h))) return rc;      // wl count, wl scratch, n_kept, bclean
+      nk = (int64_t)h[2]; bclean = (int64_t)h[3];
+      D.n_kept = nk;
+      if (h[0] > 0) {
+        uint32_t* scratch;
+        ALLOC(scratch, uint32_t, 4 * (int64_t)h[1]);
+        int lblocks = (int)(h[0] < 148 * 8 ? h[0] : 148 * 8);
+        prof_begin(ctx, st, "k_bpe_long");
+        k_bpe_long<<<lblocks, LONG_T, 0, st>>>(ctx->T, ctx->d_byte_id, D.C, D.coff, D.coff + 1, 1, D.ctok, A.wl, (int64_t)h[0], scratch, (int64_t)h[1]);
+        prof_end(ctx, st);
+        ctx->launches++;
+        CK(cudaGetLastError());
+        ctx->counts[TRC_N_LONG_SPANS] += (int64_t)h[0];
+      }
+      LAUNCH(k_doc_ranges, nd + 1, 128, D.sdoc, nk, D.kdoc_off, nd);
+    }
+    ctx->counts[TRC_N_KEPT] = nk; ctx->counts[TRC_B_CLEAN] = bclean;
+  } else
+#endif
+  {
   // P1: clean (count -> scan -> write)
   int32_t* keep;
   ALLOC(D.clen, int64_t, n); ALLOC(D.cchars, int32_t, n); ALLOC(keep, int32_t, n);
   ALLOC(D.kscan, int64_t, n + 1); ALLOC(D.cscan, int64_t, n + 1);
+#ifdef TRC_HOSTSIM
+  uint8_t* hs_cls = nullptr; uint8_t* hs_code = nullptr;
+  const char* hs_seq = getenv("TRCHUNK_HOSTSIM_SEQ");
+  const bool hs_par = !(hs_seq && hs_seq[0] == '1');
+  if (hs_par) {
+    ALLOC(hs_cls, uint8_t, braw); ALLOC(hs_code, uint8_t, braw);
+    hostsim_clean_par_count(D, ctx->T, keep, hs_cls, hs_code);
+  } else
+#endif
   LAUNCH(k_clean_count, n, 128, D, ctx->T, keep);
   if ((rc = scan_excl(ctx, st, keep, D.kscan, n))) return rc;
   if ((rc = scan_excl(ctx, st, D.clen, D.cscan, n))) return rc;
@@ -773,7 +893,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
     if ((rc = read_back(ctx, st, D.kscan + n, 8, &h2[0]))) return rc;
     if ((rc = read_back(ctx, st, D.cscan + n, 8, &h2[1]))) return rc;
   }
-  const int64_t nk = h2[0], bclean = h2[1];
+  nk = h2[0]; bclean = h2[1];
   D.n_kept = nk;
   ctx->counts[TRC_N_KEPT] = nk; ctx->counts[TRC_B_CLEAN] = bclean;
   ALLOC(D.k2r, int32_t, nk); ALLOC(D.coff, int64_t, nk + 1); ALLOC(D.C, uint8_t, bclean); ALLOC(D.sdoc, int32_t, nk);
@@ -782,15 +902,15 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   LAUNCH(k_compact, n, 256, D, keep);
   if (n) LAUNCH(k_map_off, nd + 1, 256, D.doc_off, D.kscan, D.kdoc_off, nd + 1);
   else CK(cudaMemsetAsync(D.kdoc_off, 0, 8 * (size_t)(nd + 1), st));
+#ifdef TRC_HOSTSIM
+  if (hs_par) hostsim_clean_par_write(D, hs_code); else
+#endif
   LAUNCH(k_clean_write, nk, 128, D, ctx->T);
 
   // P2: tokens of " " + cleaned text, special-token scan
-  int32_t* seg_special;
   ALLOC(D.ctok, uint32_t, nk); ALLOC(seg_special, int32_t, nk);
-  ALLOC(D.doc_err, int32_t, nd); ALLOC(D.doc_err_seg, int64_t, nd);
-  CK(cudaMemsetAsync(D.doc_err, 0, 4 * (size_t)(nd > 0 ? nd : 1), st));
-  LAUNCH(k_fill_i64, nd, 256, D.doc_err_seg, nd, (int64_t)INT64_MAX);
   if ((rc = count_units(ctx, st, D.C, D.coff, D.coff + 1, nk, bclean, 1, D.ctok, seg_special, true))) return rc;
+  }
   LAUNCH(k_special_docs, nk, 256, D, seg_special, spk_special);
   LAUNCH(k_doc_err, nd, 128, D, seg_special, spk_special);
 
@@ -1026,7 +1146,7 @@ __global__ void __launch_bounds__(LONG_T) k_bpe_span_static(TrcTables T, const u
   __shared__ unsigned long long s_best;
   __shared__ int s_whole;
   TrcStr S; S.p = span; S.vs = 0; S.n = len;
-  if (threadIdx.x == 0) s_whole = (len == 1 || trc_is_token(T, S, 0, (int)len)) ? 1 : 0;
+  if (threadIdx.x == 0) s_whole = (len == 1 || trc_is_token(T, trc_fast_default(T), S, 0, (int)len)) ? 1 : 0;
   __syncthreads();
   if (s_whole) { if (threadIdx.x == 0) *out_count = 1u; return; }
   uint32_t* id = scratch;
