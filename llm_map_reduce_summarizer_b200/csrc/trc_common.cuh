@@ -48,6 +48,7 @@ struct TrcTables {
   // token counts of digit groups: index = value + (len==1 ? 0 : len==2 ? 10 : 110)
   const uint8_t* dcount;   // 1110 entries
   uint32_t cnt_space_lbracket;  // count(" [")
+  uint32_t dcount_ready;        // 0 while the digit-group table itself is being computed
   // fast paths (exact): Rust class of the 128 ASCII bytes; sets of ALL vocabulary entries of <= 8 and
   // 9..16 bytes that contain no 0x00 byte, keyed by their zero-padded little-endian bytes
   const uint8_t* acls;          // 128 entries
@@ -67,7 +68,11 @@ struct TrcFast {
 };
 TRC_HD TrcFast trc_fast_default(const TrcTables& T) { TrcFast F; F.acls = T.acls; F.hot8 = nullptr; F.hot8_mask = 0; return F; }
 TRC_HD uint32_t trc_cls(const TrcTables& T, const TrcFast& F, uint32_t cp) { return cp < 128u ? (uint32_t)F.acls[cp] : TRC_RS(T.props[cp]); }
-TRC_HD uint32_t trc_key8_slot(uint64_t key, uint32_t mask) { return (uint32_t)(trc_mix64(key) >> 20) & mask; }
+TRC_HD uint32_t trc_key8_slot(uint64_t key, uint32_t mask) {   // cheap 32-bit mix: keys are short byte strings
+  uint32_t x = (uint32_t)key ^ ((uint32_t)(key >> 32) * 0x9E3779B1u);
+  x *= 0x85EBCA6Bu; x ^= x >> 15; x *= 0xC2B2AE35u; x ^= x >> 13;
+  return x & mask;
+}
 
 // ---- UTF-8 (input is produced by Python's str.encode('utf-8'): always well formed) -----------------
 TRC_HD int trc_u8len(uint8_t b) { return b < 0x80 ? 1 : (b < 0xE0 ? 2 : (b < 0xF0 ? 3 : 4)); }

@@ -66,6 +66,7 @@ struct TrcDev {
   int64_t* idoc_off; int32_t* pnxt; int32_t* cflag; int64_t* cscanf; int64_t n_chunks; int32_t* cstart;
   int64_t* cdoc_off; TrcChunk* chunks; int32_t* spk_list; int64_t* twc_len; int64_t* twc_scan; uint8_t* twc; int64_t* it_dst;
   TrcSub* subs; int64_t n_subs; int64_t* sub_off; int32_t* pc_item;
+  int64_t* pdst; uint8_t* pflag;           // per piece: destination of its text in TWC (-1: none), bit0 "[ts] " prefix, bit1 joining space
   int32_t* doc_err;                        // per document: 0 ok, 1+k special token k found, -1 unsupported
   int64_t* doc_err_seg;
 };
@@ -392,4 +393,63 @@ TRC_HD void trc_emit_chunk_piece(const TrcDev& D, int64_t j, int lane, int nl) {
   if (j == p0 && lane == 0 && t > D.chunks[D.cscanf[t + 1] - 1].item0) { base[-2] = '\n'; base[-1] = '\n'; }
   const int64_t* po = s >= 0 ? D.poffs : D.poff;
   trc_emit_piece(D, j, base + pre + (po[j] - po[p0]), comb && (D.preserve || s >= 0), comb && j < p1, lane, nl);
+}
+
+
+// ---- C5 (v2): item layout once per item, then a flat copy per piece ---------------------------------------
+// One call per item t: writes the "\n\n" that precedes the item and, for whole segments, the
+// "[ts] speaker: " prefix; records for every piece of the item where its text goes.
+TRC_HD void trc_item_layout(const TrcDev& D, int64_t t) {
+  int32_t g = D.it_group[t];
+  int32_t s = D.it_sub[t];
+  if (s >= 0 && D.subs[s].kind != 0) return;           // sentence / clause items are laid out by k_emit_sent_recs
+  int32_t ga = D.gstart[g], gb = D.gstart[g + 1];
+  int32_t p0 = s >= 0 ? D.subs[s].r0 : ga;
+  int32_t p1 = s >= 0 ? D.subs[s].r1 : gb - 1;
+  bool comb = gb - ga > 1;
+  uint8_t* base = D.twc + D.it_dst[t];
+  int64_t pre = 0;
+  if (s < 0) {
+    int32_t r = D.k2r[ga];
+    int32_t sp = D.spk[r];
+    int64_t sl = D.spk_off[sp + 1] - D.spk_off[sp];
+    uint8_t buf[TRC_TS_MAX + 4];
+    int tl = trc_fmt_ts(D.start[r], buf + 1);
+    buf[0] = '['; buf[tl + 1] = ']'; buf[tl + 2] = ' ';
+    for (int k = 0; k < tl + 3; ++k) base[k] = buf[k];
+    for (int64_t k = 0; k < sl; ++k) base[tl + 3 + k] = D.spk_bytes[D.spk_off[sp] + k];
+    base[tl + 3 + sl] = ':'; base[tl + 4 + sl] = ' ';
+    pre = tl + 5 + sl;
+  }
+  if (t > D.chunks[D.cscanf[t + 1] - 1].item0) { base[-2] = '\n'; base[-1] = '\n'; }
+  const int64_t* po = s >= 0 ? D.poffs : D.poff;
+  bool with_ts = comb && (D.preserve || s >= 0);
+  for (int32_t j = p0; j <= p1; ++j) {
+    D.pdst[j] = D.it_dst[t] + pre + (po[j] - po[p0]);
+    D.pflag[j] = (uint8_t)((with_ts ? 1 : 0) | ((comb && j < p1) ? 2 : 0));
+  }
+}
+
+// One call per (piece, lane of an 8-lane group): "[ts] " (lane 0) + the cleaned text + the joining space.
+TRC_HD void trc_emit_piece_flat(const TrcDev& D, int64_t j, int lane, int nl) {
+  int64_t d = D.pdst[j];
+  if (d < 0) return;
+  uint8_t f = D.pflag[j];
+  uint8_t* dst = D.twc + d;
+  int64_t o = 0;
+  if (f & 1) {
+    double st = D.start[D.k2r[j]];
+    o = trc_ts_len(st) + 3;
+    if (lane == 0) {
+      uint8_t buf[TRC_TS_MAX + 4];
+      int tl = trc_fmt_ts(st, buf + 1);
+      buf[0] = '['; buf[tl + 1] = ']'; buf[tl + 2] = ' ';
+      for (int k = 0; k < tl + 3; ++k) dst[k] = buf[k];
+    }
+  }
+  int64_t c0 = D.coff[j];
+  int64_t len = D.coff[j + 1] - c0;
+  const uint8_t* src = D.C + c0;
+  for (int64_t k = lane; k < len; k += nl) dst[o + k] = src[k];
+  if ((f & 2) && lane == nl - 1) dst[o + len] = ' ';
 }

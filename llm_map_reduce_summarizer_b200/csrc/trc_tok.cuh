@@ -201,6 +201,51 @@ TRC_HD uint32_t trc_count_unit(const TrcTables& T, const TrcFast& F, const uint3
   uint32_t total = 0;
   int64_t q = 0;
   while (q < S.n) {
+    // ---- fast paths for the three span shapes that make up ordinary text (all ASCII, exact) --------------
+    {
+      const uint8_t c0 = S.at(q);
+      const uint32_t k0 = c0 < 0x80 ? (uint32_t)F.acls[c0] : 9u;
+      if (c0 == ' ' || k0 == TRC_RS_L) {
+        // alt 2: optional ' ' then ASCII letters, at most 8 bytes, ended by an ASCII non-letter or the end
+        uint64_t key = c0; int k = 1; uint8_t b = 0; bool more = false;
+        while ((more = (q + k < S.n)) && k < 9) {
+          b = S.at(q + k);
+          if (b >= 0x80 || F.acls[b] != TRC_RS_L) break;
+          if (k < 8) key |= (uint64_t)b << (8 * k);
+          ++k;
+        }
+        const int nlet = k - (c0 == ' ' ? 1 : 0);
+        if (nlet >= 1 && k <= 8 && (!more || b < 0x80)) {
+          bool hit = k == 1;
+          if (!hit) {
+            if (F.hot8 && F.hot8[trc_key8_slot(key, F.hot8_mask)] == key) hit = true;
+            else {
+              uint32_t slot = trc_key8_slot(key, T.tok8_mask);
+              for (;;) { uint64_t e8 = T.tok8[slot]; if (e8 == key) { hit = true; break; } if (e8 == 0) break; slot = (slot + 1) & T.tok8_mask; }
+            }
+          }
+          total += hit ? 1u : (uint32_t)trc_bpe_short(T, byte_id, S, q, k);
+          q += k;
+          continue;
+        }
+      } else if (k0 == TRC_RS_O) {
+        // alt 4 of length 1: an ASCII punctuation byte not followed by a letter (alt 1/2), another
+        // punctuation byte, a newline or a non-ASCII character
+        bool single = q + 1 == S.n;
+        if (!single) { uint8_t b = S.at(q + 1); single = b < 0x80 && b != '\r' && b != '\n' && (F.acls[b] == TRC_RS_N || F.acls[b] == TRC_RS_S); }
+        if (single) { total += 1; q += 1; continue; }
+      } else if (k0 == TRC_RS_N) {
+        // alt 3: up to three ASCII digits; the count comes from the digit-group table
+        int k = 1, v = c0 - '0'; bool ok = true;
+        while (k < 3 && q + k < S.n) {
+          uint8_t b = S.at(q + k);
+          if (b >= 0x80) { ok = false; break; }
+          if (F.acls[b] != TRC_RS_N) break;
+          v = v * 10 + (b - '0'); ++k;
+        }
+        if (ok && T.dcount_ready) { total += T.dcount[v + (k == 1 ? 0 : (k == 2 ? 10 : 110))]; q += k; continue; }
+      }
+    }
     int64_t e = trc_span_end(T, F, S, q);
     int64_t len = e - q;
     if (len == 1) total += 1;

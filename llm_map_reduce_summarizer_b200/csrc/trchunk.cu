@@ -522,6 +522,15 @@ __global__ void k_pack_next(TrcDev D, const int64_t* __restrict__ forced_pos, in
 __global__ void k_chunk_record(TrcDev D) { GSTRIDE(c, D.n_chunks) trc_chunk_record(D, c); }
 __global__ void k_chunk_header(TrcDev D) { GSTRIDE(c, D.n_chunks) trc_chunk_header_write(D, c); }
 __global__ void k_emit_chunk_pieces(TrcDev D) { WSTRIDE(j, D.n_kept) trc_emit_chunk_piece(D, j, TRC_LANE, TRC_NL); }
+__global__ void k_item_layout(TrcDev D) { GSTRIDE(t, D.n_items) trc_item_layout(D, t); }
+#ifdef TRC_HOSTSIM
+__global__ void k_emit_pieces_flat(TrcDev D) { GSTRIDE(j, D.n_kept) trc_emit_piece_flat(D, j, 0, 1); }
+#else
+__global__ void k_emit_pieces_flat(TrcDev D) {   // 8 lanes per piece
+  for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; (q >> 3) < D.n_kept; q += (int64_t)gridDim.x * blockDim.x)
+    trc_emit_piece_flat(D, q >> 3, (int)(q & 7), 8);
+}
+#endif
 
 // =====================================================================================================
 // host helpers
@@ -728,7 +737,7 @@ extern "C" int trc_load_vocab(trc_ctx* ctx, const uint8_t* token_bytes, const in
   std::vector<uint8_t> zero(1111, 0);
   const uint8_t* d_dc;
   if ((rc = upload_vec(ctx, zero, &d_dc))) return rc;
-  ctx->T.dcount = d_dc; ctx->T.cnt_space_lbracket = 0;
+  ctx->T.dcount = d_dc; ctx->T.cnt_space_lbracket = 0; ctx->T.dcount_ready = 0;
   ctx->have_vocab = true;
   std::vector<uint32_t> cnt((size_t)np);
   rc = trc_count_tokens(ctx, pb.data(), po.data(), np, 0, TRC_MEM_HOST, cnt.data(), nullptr, nullptr);
@@ -737,6 +746,7 @@ extern "C" int trc_load_vocab(trc_ctx* ctx, const uint8_t* token_bytes, const in
   for (int64_t k = 0; k < 1110; ++k) dc[k] = (uint8_t)cnt[k];
   CK(cudaMemcpy((void*)d_dc, dc.data(), 1110, cudaMemcpyHostToDevice));
   ctx->T.cnt_space_lbracket = cnt[1110];
+  ctx->T.dcount_ready = 1;
   return TRC_OK;
 }
 
@@ -1044,8 +1054,11 @@ extern "C" int trc_chunk(trc_ctx* ctx, const int32_t* doc_max_tokens, int32_t co
   ctx->counts[TRC_B_TWC] = btwc; ctx->counts[TRC_TOKENS] = h3[1];
   ALLOC(D.twc, uint8_t, btwc);
   LAUNCH(k_chunk_header, nc, 64, D);
-  // C5: item text
-  LAUNCH_W(k_emit_chunk_pieces, nk, D);
+  // C5: item text (layout per item, then a flat copy per piece)
+  ALLOC(D.pdst, int64_t, nk); ALLOC(D.pflag, uint8_t, nk);
+  CK(cudaMemsetAsync(D.pdst, 0xff, 8 * (size_t)(nk > 0 ? nk : 1), st));
+  LAUNCH(k_item_layout, ni, 128, D);
+  LAUNCH(k_emit_pieces_flat, nk * 8, 256, D);
   if (nraw > 0) { if ((rc = sentence_stage_emit(ctx, st))) return rc; }
   CK(cudaEventRecord(ctx->ev[3], st));
   ctx->ev_chunk = true;
