@@ -50,8 +50,21 @@ TRC_HD void cp_mark_dup(const uint8_t* in, const uint8_t* cls, uint8_t* code, in
   code[q] = CP_DROPSPACE;
 }
 
-// P3.  Returns the output code of byte k (and stores it).
-TRC_HD uint32_t cp_code(const uint8_t* in, const uint8_t* cls, uint8_t* code, int32_t k, int32_t a, int32_t b) {
+// Cheap filter in front of cp_mark_dup: first byte of a \w-run that directly follows whitespace.
+TRC_HD bool cp_dup_candidate(const uint8_t* cls, int32_t k, int32_t a) {
+  uint8_t c = cls[k];
+  return (c & CP_WORD) && !(c & CP_CONT) && k > a && (cls[k - 1] & CP_SPACE);
+}
+
+// First non-whitespace byte of segment [a,b) (== b for a blank segment): whitespace before it is leading.
+TRC_HD int32_t cp_first_nonspace(const uint8_t* cls, int32_t a, int32_t b) {
+  int32_t p = a;
+  while (p < b && (cls[p] & CP_SPACE)) ++p;
+  return p;
+}
+
+// P3.  Returns the output code of byte k (and stores it).  fns = cp_first_nonspace of the segment.
+TRC_HD uint32_t cp_code(const uint8_t* in, const uint8_t* cls, uint8_t* code, int32_t k, int32_t a, int32_t b, int32_t fns) {
   uint8_t c = cls[k], d = code[k];
   uint32_t r;
   if (d == CP_DROP) r = 0;
@@ -59,11 +72,7 @@ TRC_HD uint32_t cp_code(const uint8_t* in, const uint8_t* cls, uint8_t* code, in
     r = 0;
     if (!(c & CP_CONT) && d != CP_DROPSPACE) {
       int32_t kn = k + trc_u8len(in[k]);
-      if (kn < b && !(cls[kn] & CP_SPACE)) {
-        int32_t p = k;
-        while (p > a && (cls[p - 1] & CP_SPACE)) --p;
-        if (p > a) r = 2;
-      }
+      if (kn < b && !(cls[kn] & CP_SPACE) && k > fns) r = 2;
     }
   } else {
     uint8_t ch = in[k];

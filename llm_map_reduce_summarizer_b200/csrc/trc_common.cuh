@@ -29,7 +29,8 @@
 #define TRC_RS_S 3u
 
 #define TRC_MAX_SPECIALS 8
-#define TRC_SHORT_SPAN 48  // spans up to this many bytes are merged in thread-local memory
+#define TRC_SHORT_SPAN 48
+#define TRC_HOT8 2048     // slots of the direct-mapped hot set of short tokens (host image == shared-memory copy)  // spans up to this many bytes are merged in thread-local memory
 
 struct TrcTables {
   const uint8_t* props;  // 0x110000 entries

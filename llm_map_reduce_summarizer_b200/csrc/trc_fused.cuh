@@ -13,10 +13,11 @@
 #define FUSE_T 512
 #define FUSE_NW (FUSE_T / 32)
 #define FUSE_SEGS 256
-#define FUSE_IN_CAP 20480
-#define FUSE_OUT_CAP 30720
-#define FUSE_WORD_CAP 5120
-#define FUSE_HOT 2048
+#define FUSE_IN_CAP 18432
+#define FUSE_OUT_CAP 26624
+#define FUSE_WORD_CAP 4608
+#define FUSE_CAND_CAP 3072
+#define FUSE_HOT TRC_HOT8
 #define FUSE_STRIPS (FUSE_IN_CAP / 32)
 
 struct FuseSmem {
@@ -24,6 +25,9 @@ struct FuseSmem {
   union { uint8_t cls[FUSE_IN_CAP]; uint8_t out[FUSE_OUT_CAP]; } x;
   union { uint8_t code[FUSE_IN_CAP]; struct { uint16_t wstart[FUSE_WORD_CAP]; uint16_t wseg[FUSE_WORD_CAP]; } w; } z;
   uint64_t hot8[FUSE_HOT];
+  uint32_t cand[FUSE_CAND_CAP];     // duplicate-word candidates: byte index | segment << 16
+  int32_t fns[FUSE_SEGS];
+  int32_t ncand;
   int32_t strip_base[FUSE_STRIPS + 1];
   uint16_t strip_seg[FUSE_STRIPS];
   int32_t rel[FUSE_SEGS + 1];
@@ -32,6 +36,7 @@ struct FuseSmem {
   int32_t wsum[3][FUSE_NW];
   int32_t tot[3];
   unsigned int tile;
+  int32_t nslow;
   long long gbase, kbase;
 };
 
@@ -43,7 +48,9 @@ struct FuseArgs {
   int64_t text_bytes;
   int32_t* seg_special;
   LongEntry* wl; unsigned long long* wl_cnt; int64_t wl_cap;
+  unsigned long long* phase;        // optional: cycles per phase summed over CTAs (diagnostics, TRCHUNK_PHASES=1)
 };
+#define FUSE_PH(i) do { if (A.phase && tid == 0) { long long now_ = clock64(); atomicAdd(&A.phase[i], (unsigned long long)(now_ - ph_t)); ph_t = now_; } } while (0)
 
 __device__ __forceinline__ long long fuse_lookback(unsigned long long* d, unsigned tile, long long aggregate, int lane) {
   long long excl = 0;
@@ -106,6 +113,7 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
   for (int k = tid; k < FUSE_HOT; k += FUSE_T) S.hot8[k] = T.hot8_src[k];
   TrcFast F; F.acls = T.acls; F.hot8 = S.hot8; F.hot8_mask = FUSE_HOT - 1;
   __syncthreads();
+  long long ph_t = clock64();
   for (;;) {
     if (tid == 0) S.tile = (unsigned int)atomicAdd(A.tile_counter, 1ULL);
     __syncthreads();
@@ -131,6 +139,7 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
       }
       const int nstrips = (span + 31) >> 5;
       __syncthreads();
+      FUSE_PH(0);
       // segment of the first byte of every strip
       if (tid < ns) {
         int32_t a = S.rel[tid], b = S.rel[tid + 1];
@@ -149,16 +158,50 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
         }
       }
       __syncthreads();
-      // P2 duplicate-word marks
+      FUSE_PH(1);
+      // P2 duplicate-word marks: cheap per-byte filter, candidates compacted, then handled densely
+      if (tid == 0) S.ncand = 0;
+      if (tid < ns) S.fns[tid] = cp_first_nonspace(S.x.cls, S.rel[tid], S.rel[tid + 1]);
+      __syncthreads();
       for (int s = wid; s < nstrips; s += FUSE_NW) {
         int32_t k = (s << 5) + lane;
+        bool cnd = false; int i = 0;
         if (k >= al && k < span) {
-          int i = S.strip_seg[s];
+          i = S.strip_seg[s];
           while (i + 1 < ns && S.rel[i + 1] <= k) ++i;
-          cp_mark_dup(S.in, S.x.cls, S.z.code, k, S.rel[i], S.rel[i + 1]);
+          cnd = cp_dup_candidate(S.x.cls, k, S.rel[i]);
+        }
+        unsigned m = __ballot_sync(0xffffffffu, cnd);
+        if (m) {
+          int32_t b0 = 0;
+          if (lane == 0) b0 = atomicAdd(&S.ncand, __popc(m));
+          b0 = __shfl_sync(0xffffffffu, b0, 0);
+          int32_t slot = b0 + __popc(m & lt);
+          if (cnd && slot < FUSE_CAND_CAP) S.cand[slot] = (uint32_t)k | ((uint32_t)i << 16);
         }
       }
       __syncthreads();
+      {
+        const int32_t nc = S.ncand;
+        if (nc <= FUSE_CAND_CAP) {
+          for (int32_t c = tid; c < nc; c += FUSE_T) {
+            uint32_t e = S.cand[c];
+            int i = (int)(e >> 16);
+            cp_mark_dup(S.in, S.x.cls, S.z.code, (int32_t)(e & 0xffffu), S.rel[i], S.rel[i + 1]);
+          }
+        } else {                                 // list overflow: undecimated pass (same marks)
+          for (int s = wid; s < nstrips; s += FUSE_NW) {
+            int32_t k = (s << 5) + lane;
+            if (k >= al && k < span) {
+              int i = S.strip_seg[s];
+              while (i + 1 < ns && S.rel[i + 1] <= k) ++i;
+              cp_mark_dup(S.in, S.x.cls, S.z.code, k, S.rel[i], S.rel[i + 1]);
+            }
+          }
+        }
+      }
+      __syncthreads();
+      FUSE_PH(2);
       // P3 output codes + per-strip output sizes
       for (int s = wid; s < nstrips; s += FUSE_NW) {
         int32_t k = (s << 5) + lane;
@@ -166,7 +209,7 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
         if (k >= al && k < span) {
           int i = S.strip_seg[s];
           while (i + 1 < ns && S.rel[i + 1] <= k) ++i;
-          r = cp_code(S.in, S.x.cls, S.z.code, k, S.rel[i], S.rel[i + 1]);
+          r = cp_code(S.in, S.x.cls, S.z.code, k, S.rel[i], S.rel[i + 1], S.fns[i]);
         }
         unsigned m1 = __ballot_sync(0xffffffffu, r != 0), m2 = __ballot_sync(0xffffffffu, r == 3);
         if (lane == 0) S.strip_base[s] = __popc(m1) + __popc(m2);
@@ -193,6 +236,7 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
         S.loff[i] = pos;
       }
       __syncthreads();
+      FUSE_PH(3);
       if (tid < ns) { loff = S.loff[tid]; mylen = S.loff[tid + 1] - loff; mykeep = mylen > 0; }
       int32_t d0, d1;
       fuse_scan3(S, lane, wid, mykeep, 0, 0, &koff, &d0, &d1);
@@ -204,6 +248,7 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
       }
       __syncthreads();
       gbase = S.gbase; kbase = S.kbase;
+      FUSE_PH(4);
       fast_out = tot_out <= FUSE_OUT_CAP;
       // scatter (cls is dead: out may overwrite it)
       {
@@ -223,6 +268,7 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
         uint8_t* dstg = D.C + gbase;
         for (int32_t k = tid; k < tot_out; k += FUSE_T) dstg[k] = S.x.out[k];
       }
+      FUSE_PH(5);
       // words and code points per segment
       if (tid < ns && mylen > 0) {
         const uint8_t* p = fast_out ? S.x.out + loff : D.C + gbase + loff;
@@ -268,7 +314,24 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
       }
       if (tid < ns) { S.len[tid] = mylen; S.koff[tid] = koff; }
       __syncthreads();
+      FUSE_PH(6);
+      // fast pass: words made only of the common ASCII span shapes; the rest is queued and handled densely
+      if (tid == 0) S.nslow = 0;
+      __syncthreads();
+      uint16_t* slow = reinterpret_cast<uint16_t*>(S.in);
       for (int32_t w = tid; w < tot_words; w += FUSE_T) {
+        const int seg = S.z.w.wseg[w];
+        const int32_t st = S.z.w.wstart[w];
+        const int32_t sl = S.loff[seg];
+        const int32_t en = (w + 1 < tot_words && S.z.w.wseg[w + 1] == seg) ? (int32_t)S.z.w.wstart[w + 1] : sl + S.len[seg];
+        uint32_t c = 0;
+        if (trc_count_word_fast(T, F, S.x.out + st, en - st, st == sl ? 1 : 0, &c)) atomicAdd(&S.tok[seg], (int32_t)c);
+        else slow[atomicAdd(&S.nslow, 1)] = (uint16_t)w;
+      }
+      __syncthreads();
+      const int32_t nslow = S.nslow;
+      for (int32_t q = tid; q < nslow; q += FUSE_T) {
+        const int32_t w = slow[q];
         const int seg = S.z.w.wseg[w];
         const int32_t st = S.z.w.wstart[w];
         const int32_t sl = S.loff[seg];
@@ -296,6 +359,7 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
       mysp = trc_find_special(T, p, mylen);
     }
     __syncthreads();
+    FUSE_PH(7);
     // ---- outputs
     if (tid < ns) {
       D.cchars[s0 + tid] = mychars;
@@ -313,6 +377,7 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
       A.totals[0] = kbase + tot_kept; A.totals[1] = gbase + tot_out;
     }
     __syncthreads();
+    FUSE_PH(8);
   }
 }
 

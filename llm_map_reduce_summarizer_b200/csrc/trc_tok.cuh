@@ -191,6 +191,70 @@ TRC_HD int trc_find_special(const TrcTables& T, const uint8_t* p, int64_t n) {
   return -1;
 }
 
+// Fast paths for the three span shapes that make up ordinary text (all ASCII, exact).  Returns the end
+// of the span that starts at q and adds its token count to *total, or -1 when the generic matcher must
+// decide.  With MERGE=false a short letter span that is not a vocabulary entry also returns -1 (the
+// caller queues the word for the generic path instead of merging inline).
+template <bool MERGE>
+TRC_HD int64_t trc_fast_span(const TrcTables& T, const TrcFast& F, const uint32_t* byte_id, const TrcStr& S, int64_t q, uint32_t* total) {
+  const uint8_t c0 = S.at(q);
+  const uint32_t k0 = c0 < 0x80 ? (uint32_t)F.acls[c0] : 9u;
+  if (c0 == ' ' || k0 == TRC_RS_L) {
+    // alt 2: optional ' ' then ASCII letters, at most 8 bytes, ended by an ASCII non-letter or the end
+    uint64_t key = c0; int k = 1; uint8_t b = 0; bool more = false;
+    while ((more = (q + k < S.n)) && k < 9) {
+      b = S.at(q + k);
+      if (b >= 0x80 || F.acls[b] != TRC_RS_L) break;
+      if (k < 8) key |= (uint64_t)b << (8 * k);
+      ++k;
+    }
+    const int nlet = k - (c0 == ' ' ? 1 : 0);
+    if (nlet >= 1 && k <= 8 && (!more || b < 0x80)) {
+      bool hit = k == 1;
+      if (!hit) {
+        if (F.hot8 && F.hot8[trc_key8_slot(key, F.hot8_mask)] == key) hit = true;
+        else {
+          uint32_t slot = trc_key8_slot(key, T.tok8_mask);
+          for (;;) { uint64_t e8 = T.tok8[slot]; if (e8 == key) { hit = true; break; } if (e8 == 0) break; slot = (slot + 1) & T.tok8_mask; }
+        }
+      }
+      if (hit) *total += 1u;
+      else if (MERGE) *total += (uint32_t)trc_bpe_short(T, byte_id, S, q, k);
+      else return -1;
+      return q + k;
+    }
+  } else if (k0 == TRC_RS_O) {
+    // alt 4 of length 1: an ASCII punctuation byte followed by a digit, whitespace (not a newline) or the end
+    bool single = q + 1 == S.n;
+    if (!single) { uint8_t b = S.at(q + 1); single = b < 0x80 && b != '\r' && b != '\n' && (F.acls[b] == TRC_RS_N || F.acls[b] == TRC_RS_S); }
+    if (single) { *total += 1; return q + 1; }
+  } else if (k0 == TRC_RS_N) {
+    // alt 3: up to three ASCII digits; the count comes from the digit-group table
+    int k = 1, v = c0 - '0'; bool ok = true;
+    while (k < 3 && q + k < S.n) {
+      uint8_t b = S.at(q + k);
+      if (b >= 0x80) { ok = false; break; }
+      if (F.acls[b] != TRC_RS_N) break;
+      v = v * 10 + (b - '0'); ++k;
+    }
+    if (ok && T.dcount_ready) { *total += T.dcount[v + (k == 1 ? 0 : (k == 2 ? 10 : 110))]; return q + k; }
+  }
+  return -1;
+}
+
+// A whole word through the fast paths only: false when any of its spans needs the generic matcher.
+TRC_HD bool trc_count_word_fast(const TrcTables& T, const TrcFast& F, const uint8_t* p, int64_t nbytes, int vs, uint32_t* count) {
+  TrcStr S; S.p = p; S.n = nbytes + vs; S.vs = vs;
+  uint32_t total = 0;
+  int64_t q = 0;
+  while (q < S.n) {
+    q = trc_fast_span<false>(T, F, nullptr, S, q, &total);
+    if (q < 0) return false;
+  }
+  *count = total;
+  return true;
+}
+
 // Token count of one unit.  Spans longer than TRC_SHORT_SPAN that are not vocabulary entries are handed
 // to `long_span(logical_start, length)` which returns their count (device: deferred to the block-wide
 // long-span kernel and returns 0; hostsim: computed inline).
@@ -201,50 +265,9 @@ TRC_HD uint32_t trc_count_unit(const TrcTables& T, const TrcFast& F, const uint3
   uint32_t total = 0;
   int64_t q = 0;
   while (q < S.n) {
-    // ---- fast paths for the three span shapes that make up ordinary text (all ASCII, exact) --------------
     {
-      const uint8_t c0 = S.at(q);
-      const uint32_t k0 = c0 < 0x80 ? (uint32_t)F.acls[c0] : 9u;
-      if (c0 == ' ' || k0 == TRC_RS_L) {
-        // alt 2: optional ' ' then ASCII letters, at most 8 bytes, ended by an ASCII non-letter or the end
-        uint64_t key = c0; int k = 1; uint8_t b = 0; bool more = false;
-        while ((more = (q + k < S.n)) && k < 9) {
-          b = S.at(q + k);
-          if (b >= 0x80 || F.acls[b] != TRC_RS_L) break;
-          if (k < 8) key |= (uint64_t)b << (8 * k);
-          ++k;
-        }
-        const int nlet = k - (c0 == ' ' ? 1 : 0);
-        if (nlet >= 1 && k <= 8 && (!more || b < 0x80)) {
-          bool hit = k == 1;
-          if (!hit) {
-            if (F.hot8 && F.hot8[trc_key8_slot(key, F.hot8_mask)] == key) hit = true;
-            else {
-              uint32_t slot = trc_key8_slot(key, T.tok8_mask);
-              for (;;) { uint64_t e8 = T.tok8[slot]; if (e8 == key) { hit = true; break; } if (e8 == 0) break; slot = (slot + 1) & T.tok8_mask; }
-            }
-          }
-          total += hit ? 1u : (uint32_t)trc_bpe_short(T, byte_id, S, q, k);
-          q += k;
-          continue;
-        }
-      } else if (k0 == TRC_RS_O) {
-        // alt 4 of length 1: an ASCII punctuation byte not followed by a letter (alt 1/2), another
-        // punctuation byte, a newline or a non-ASCII character
-        bool single = q + 1 == S.n;
-        if (!single) { uint8_t b = S.at(q + 1); single = b < 0x80 && b != '\r' && b != '\n' && (F.acls[b] == TRC_RS_N || F.acls[b] == TRC_RS_S); }
-        if (single) { total += 1; q += 1; continue; }
-      } else if (k0 == TRC_RS_N) {
-        // alt 3: up to three ASCII digits; the count comes from the digit-group table
-        int k = 1, v = c0 - '0'; bool ok = true;
-        while (k < 3 && q + k < S.n) {
-          uint8_t b = S.at(q + k);
-          if (b >= 0x80) { ok = false; break; }
-          if (F.acls[b] != TRC_RS_N) break;
-          v = v * 10 + (b - '0'); ++k;
-        }
-        if (ok && T.dcount_ready) { total += T.dcount[v + (k == 1 ? 0 : (k == 2 ? 10 : 110))]; q += k; continue; }
-      }
+      int64_t nq = trc_fast_span<true>(T, F, byte_id, S, q, &total);
+      if (nq >= 0) { q = nq; continue; }
     }
     int64_t e = trc_span_end(T, F, S, q);
     int64_t len = e - q;

@@ -114,7 +114,7 @@ static inline std::string trc_build_host_vocab(const uint8_t* token_bytes, const
     }
     uint32_t s8 = trc_pow2_at_least(k8.size() * 2), s16 = trc_pow2_at_least(k16.size() * 2);
     V.tok8.assign(s8, 0); V.tok16.assign(2 * (size_t)s16, 0);
-    const uint32_t HOT = 4096;
+    const uint32_t HOT = TRC_HOT8;
     V.hot8.assign(HOT, 0);
     for (uint64_t k : k8) {          // k8 is in rank order
       uint32_t slot = trc_key8_slot(k, s8 - 1);

@@ -268,10 +268,11 @@ static void hostsim_clean_par_count(TrcDev D, TrcTables T, int32_t* keep, uint8_
     int32_t n = (int32_t)(D.seg_off[i + 1] - a);
     const uint8_t* in = D.text + a;
     for (int32_t k = 0; k < n; ++k) cp_classify(T, in, cls + a, code + a, k, n);
-    for (int32_t k = 0; k < n; ++k) cp_mark_dup(in, cls + a, code + a, k, 0, n);
+    for (int32_t k = 0; k < n; ++k) if (cp_dup_candidate(cls + a, k, 0)) cp_mark_dup(in, cls + a, code + a, k, 0, n);
     int64_t len = 0; int32_t chars = 0;
+    const int32_t fns = cp_first_nonspace(cls + a, 0, n);
     for (int32_t k = 0; k < n; ++k) {
-      uint32_t r = cp_code(in, cls + a, code + a, k, 0, n);
+      uint32_t r = cp_code(in, cls + a, code + a, k, 0, n, fns);
       len += cp_outlen(r);
       chars += (r == 3) ? 2 : ((r == 2 || (r == 1 && !(cls[a + k] & CP_CONT))) ? 1 : 0);
     }
@@ -844,9 +845,11 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       const int64_t ntiles = (n + FUSE_SEGS - 1) / FUSE_SEGS;
       FuseArgs A;
       unsigned long long* fz;
-      ALLOC(fz, unsigned long long, 2 * ntiles + 8);
-      CK(cudaMemsetAsync(fz, 0, 8 * (size_t)(2 * ntiles + 8), st));
-      A.tile_counter = fz; A.wl_cnt = fz + 2; A.totals = (int64_t*)(fz + 4); A.desc_bytes = fz + 8; A.desc_kept = fz + 8 + ntiles;
+      ALLOC(fz, unsigned long long, 2 * ntiles + 24);
+      CK(cudaMemsetAsync(fz, 0, 8 * (size_t)(2 * ntiles + 24), st));
+      A.tile_counter = fz; A.wl_cnt = fz + 2; A.totals = (int64_t*)(fz + 4); A.desc_bytes = fz + 24; A.desc_kept = fz + 24 + ntiles;
+      static const bool want_phases = getenv("TRCHUNK_PHASES") != nullptr;
+      A.phase = want_phases ? fz + 8 : nullptr;
       A.text_bytes = braw; A.seg_special = seg_special;
       A.wl_cap = ccap / (TRC_SHORT_SPAN + 1) + 1;
       ALLOC(A.wl, LongEntry, A.wl_cap);
@@ -865,6 +868,14 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       if ((rc = read_back(ctx, st, fz + 2, 32, h))) return rc;      // wl count, wl scratch, n_kept, bclean
       nk = (int64_t)h[2]; bclean = (int64_t)h[3];
       D.n_kept = nk;
+      if (want_phases) {
+        unsigned long long ph[16];
+        if ((rc = read_back(ctx, st, fz + 8, 9 * 8, ph))) return rc;
+        unsigned long long tot = 0; for (int k = 0; k < 9; ++k) tot += ph[k];
+        fprintf(stderr, "[trchunk phases %%] load %.1f  P1 %.1f  P2 %.1f  P3+scan %.1f  lookback %.1f  scatter+copy %.1f  words %.1f  tokenize %.1f  outputs %.1f\n",
+                100.0 * ph[0] / tot, 100.0 * ph[1] / tot, 100.0 * ph[2] / tot, 100.0 * ph[3] / tot, 100.0 * ph[4] / tot, 100.0 * ph[5] / tot,
+                100.0 * ph[6] / tot, 100.0 * ph[7] / tot, 100.0 * ph[8] / tot);
+      }
       if (h[0] > 0) {
         uint32_t* scratch;
         ALLOC(scratch, uint32_t, 4 * (int64_t)h[1]);
