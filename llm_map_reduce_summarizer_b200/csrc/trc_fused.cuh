@@ -21,24 +21,28 @@
 #define FUSE_STRIPS (FUSE_IN_CAP / 32)
 
 struct FuseSmem {
-  uint8_t in[FUSE_IN_CAP + 32];
-  union { uint8_t cls[FUSE_IN_CAP]; uint8_t out[FUSE_OUT_CAP]; } x;
-  union { uint8_t code[FUSE_IN_CAP]; struct { uint16_t wstart[FUSE_WORD_CAP]; uint16_t wseg[FUSE_WORD_CAP]; } w; } z;
+  union {                                     // raw tile; after the scatter: sorted word list
+    uint8_t in[FUSE_IN_CAP + 32];
+    struct { uint16_t wstart[FUSE_WORD_CAP]; uint16_t wseg[FUSE_WORD_CAP]; } w;
+  } y;
+  union { uint8_t cls[FUSE_IN_CAP]; uint8_t out[FUSE_OUT_CAP]; } x;   // classes (+segment delta); later the cleaned tile
+  union { uint8_t code[FUSE_IN_CAP]; uint16_t slow[FUSE_WORD_CAP]; } z; // output codes (+segment delta); later the slow-word list
   uint64_t hot8[FUSE_HOT];
-  uint32_t cand[FUSE_CAND_CAP];     // duplicate-word candidates: byte index | segment << 16
-  int32_t fns[FUSE_SEGS];
-  int32_t ncand;
-  int32_t strip_base[FUSE_STRIPS + 1];
+  uint32_t cand[FUSE_CAND_CAP];               // duplicate-word candidates: byte index | segment << 16
+  uint16_t st_out[FUSE_STRIPS + 1], st_sp[FUSE_STRIPS + 1], st_ct[FUSE_STRIPS + 1];   // per strip: bytes, spaces, continuation bytes
   uint16_t strip_seg[FUSE_STRIPS];
+  uint8_t pre_out[FUSE_SEGS + 1], pre_sp[FUSE_SEGS + 1], pre_ct[FUSE_SEGS + 1];       // strip-relative prefixes at segment starts
+  uint16_t spb[FUSE_SEGS + 1], ctb[FUSE_SEGS + 1];
   int32_t rel[FUSE_SEGS + 1];
   int32_t loff[FUSE_SEGS + 1];
-  int32_t len[FUSE_SEGS], nw[FUSE_SEGS], woff[FUSE_SEGS], koff[FUSE_SEGS], tok[FUSE_SEGS], chars[FUSE_SEGS];
+  int32_t fns[FUSE_SEGS], len[FUSE_SEGS], koff[FUSE_SEGS], tok[FUSE_SEGS], spmin[FUSE_SEGS];
   int32_t wsum[3][FUSE_NW];
   int32_t tot[3];
+  int32_t ncand, nslow;
   unsigned int tile;
-  int32_t nslow;
   long long gbase, kbase;
 };
+static_assert(sizeof(FuseSmem) <= 115200, "two CTAs per SM");
 
 struct FuseArgs {
   unsigned long long* tile_counter;
@@ -134,8 +138,8 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
     if (fast_in) {
       // ================= fast lane: byte-parallel clean in shared memory =================
       for (int32_t k = tid * 16; k < span; k += FUSE_T * 16) {
-        if (base + k + 16 <= A.text_bytes) *reinterpret_cast<int4*>(&S.in[k]) = *reinterpret_cast<const int4*>(D.text + base + k);
-        else for (int q = 0; q < 16 && base + k + q < A.text_bytes; ++q) S.in[k + q] = D.text[base + k + q];
+        if (base + k + 16 <= A.text_bytes) *reinterpret_cast<int4*>(&S.y.in[k]) = *reinterpret_cast<const int4*>(D.text + base + k);
+        else for (int q = 0; q < 16 && base + k + q < A.text_bytes; ++q) S.y.in[k + q] = D.text[base + k + q];
       }
       const int nstrips = (span + 31) >> 5;
       __syncthreads();
@@ -147,14 +151,24 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
       }
       if (tid == 0) S.strip_seg[0] = 0;
       __syncthreads();
-      // P1 classify
+      // P1 classify; bits 3..7 of cls keep the byte's segment relative to its strip's first segment
       for (int s = wid; s < nstrips; s += FUSE_NW) {
         int32_t k = (s << 5) + lane;
         if (k < al) { S.x.cls[k] = 0; S.z.code[k] = 0; }      // bytes of the previous tile in the aligned prefix
         else if (k < span) {
-          int i = S.strip_seg[s];
+          const int i0 = S.strip_seg[s];
+          int i = i0;
           while (i + 1 < ns && S.rel[i + 1] <= k) ++i;
-          cp_classify(T, S.in, S.x.cls, S.z.code, k, S.rel[i + 1]);
+          cp_classify(T, S.y.in, S.x.cls, S.z.code, k, S.rel[i + 1]);
+          const uint8_t c = S.y.in[k];
+          if (c < 0x80 || c >= 0xC0) {
+            int d = i - i0; if (d > 31) d = 31;
+            S.x.cls[k] |= (uint8_t)(d << 3);
+            if (c >= 0xC0) {
+              const int len = trc_u8len(c);
+              for (int q = 1; q < len && k + q < span; ++q) { int dd = i - (int)S.strip_seg[(k + q) >> 5]; if (dd > 31) dd = 31; S.x.cls[k + q] |= (uint8_t)(dd << 3); }
+            }
+          }
         }
       }
       __syncthreads();
@@ -167,8 +181,9 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
         int32_t k = (s << 5) + lane;
         bool cnd = false; int i = 0;
         if (k >= al && k < span) {
-          i = S.strip_seg[s];
-          while (i + 1 < ns && S.rel[i + 1] <= k) ++i;
+          const int d = S.x.cls[k] >> 3;
+          i = S.strip_seg[s] + d;
+          if (d == 31) while (i + 1 < ns && S.rel[i + 1] <= k) ++i;
           cnd = cp_dup_candidate(S.x.cls, k, S.rel[i]);
         }
         unsigned m = __ballot_sync(0xffffffffu, cnd);
@@ -187,7 +202,7 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
           for (int32_t c = tid; c < nc; c += FUSE_T) {
             uint32_t e = S.cand[c];
             int i = (int)(e >> 16);
-            cp_mark_dup(S.in, S.x.cls, S.z.code, (int32_t)(e & 0xffffu), S.rel[i], S.rel[i + 1]);
+            cp_mark_dup(S.y.in, S.x.cls, S.z.code, (int32_t)(e & 0xffffu), S.rel[i], S.rel[i + 1]);
           }
         } else {                                 // list overflow: undecimated pass (same marks)
           for (int s = wid; s < nstrips; s += FUSE_NW) {
@@ -195,52 +210,74 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
             if (k >= al && k < span) {
               int i = S.strip_seg[s];
               while (i + 1 < ns && S.rel[i + 1] <= k) ++i;
-              cp_mark_dup(S.in, S.x.cls, S.z.code, k, S.rel[i], S.rel[i + 1]);
+              cp_mark_dup(S.y.in, S.x.cls, S.z.code, k, S.rel[i], S.rel[i + 1]);
             }
           }
         }
       }
       __syncthreads();
       FUSE_PH(2);
-      // P3 output codes + per-strip output sizes
+      // P3 output codes; per strip: output bytes, emitted spaces, emitted continuation bytes; the lane that
+      // owns a segment's first byte records the strip-relative prefixes for that segment
       for (int s = wid; s < nstrips; s += FUSE_NW) {
         int32_t k = (s << 5) + lane;
-        uint32_t r = 0;
-        if (k >= al && k < span) {
-          int i = S.strip_seg[s];
-          while (i + 1 < ns && S.rel[i + 1] <= k) ++i;
-          r = cp_code(S.in, S.x.cls, S.z.code, k, S.rel[i], S.rel[i + 1], S.fns[i]);
+        uint32_t r = 0; bool cont = false; int i = 0;
+        const bool live = k >= al && k < span;
+        if (live) {
+          const uint8_t cl = S.x.cls[k];
+          const int d = cl >> 3;
+          i = S.strip_seg[s] + d;
+          if (d == 31) while (i + 1 < ns && S.rel[i + 1] <= k) ++i;
+          r = cp_code(S.y.in, S.x.cls, S.z.code, k, S.rel[i], S.rel[i + 1], S.fns[i]);
+          cont = r == 1 && (cl & CP_CONT);
+          S.z.code[k] = (uint8_t)(r | (d << 2));
         }
-        unsigned m1 = __ballot_sync(0xffffffffu, r != 0), m2 = __ballot_sync(0xffffffffu, r == 3);
-        if (lane == 0) S.strip_base[s] = __popc(m1) + __popc(m2);
+        const unsigned m1 = __ballot_sync(0xffffffffu, r != 0), m2 = __ballot_sync(0xffffffffu, r == 3);
+        const unsigned ms = __ballot_sync(0xffffffffu, r >= 2), mc = __ballot_sync(0xffffffffu, cont);
+        if (lane == 0) { S.st_out[s] = (uint16_t)(__popc(m1) + __popc(m2)); S.st_sp[s] = (uint16_t)__popc(ms); S.st_ct[s] = (uint16_t)__popc(mc); }
+        if (live && S.rel[i] == k) {
+          const uint8_t po = (uint8_t)(__popc(m1 & lt) + __popc(m2 & lt)), ps = (uint8_t)__popc(ms & lt), pc = (uint8_t)__popc(mc & lt);
+          for (int ii = i; ii >= 0 && S.rel[ii] == k; --ii) { S.pre_out[ii] = po; S.pre_sp[ii] = ps; S.pre_ct[ii] = pc; }
+        }
       }
       __syncthreads();
-      if (wid == 0) {                       // exclusive scan of the strip totals
-        int32_t carry = 0;
+      if (wid == 0) {                       // exclusive scans of the three strip totals
+        int32_t c0 = 0, c1 = 0, c2 = 0;
         for (int b0 = 0; b0 < nstrips; b0 += 32) {
-          int32_t v = b0 + lane < nstrips ? S.strip_base[b0 + lane] : 0, x = v;
+          const bool in_r = b0 + lane < nstrips;
+          int32_t v0 = in_r ? S.st_out[b0 + lane] : 0, v1 = in_r ? S.st_sp[b0 + lane] : 0, v2 = in_r ? S.st_ct[b0 + lane] : 0;
+          int32_t x0 = v0, x1 = v1, x2 = v2;
 #pragma unroll
-          for (int o = 1; o < 32; o <<= 1) { int32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
-          if (b0 + lane < nstrips) S.strip_base[b0 + lane] = carry + x - v;
-          carry += __shfl_sync(0xffffffffu, x, 31);
+          for (int o = 1; o < 32; o <<= 1) {
+            int32_t y0 = __shfl_up_sync(0xffffffffu, x0, o), y1 = __shfl_up_sync(0xffffffffu, x1, o), y2 = __shfl_up_sync(0xffffffffu, x2, o);
+            if (lane >= o) { x0 += y0; x1 += y1; x2 += y2; }
+          }
+          if (in_r) { S.st_out[b0 + lane] = (uint16_t)(c0 + x0 - v0); S.st_sp[b0 + lane] = (uint16_t)(c1 + x1 - v1); S.st_ct[b0 + lane] = (uint16_t)(c2 + x2 - v2); }
+          c0 += __shfl_sync(0xffffffffu, x0, 31); c1 += __shfl_sync(0xffffffffu, x1, 31); c2 += __shfl_sync(0xffffffffu, x2, 31);
         }
-        if (lane == 0) S.strip_base[nstrips] = carry;
+        if (lane == 0) { S.st_out[nstrips] = (uint16_t)c0; S.st_sp[nstrips] = (uint16_t)c1; S.st_ct[nstrips] = (uint16_t)c2; }
       }
       __syncthreads();
-      tot_out = S.strip_base[nstrips];
-      // output offset of every segment start
-      for (int i = tid; i <= ns; i += FUSE_T) {
-        int32_t k = S.rel[i], pos;
-        if (k >= span) pos = tot_out;
-        else { pos = S.strip_base[k >> 5]; for (int32_t j = k & ~31; j < k; ++j) pos += cp_outlen(S.z.code[j]); }
-        S.loff[i] = pos;
+      tot_out = S.st_out[nstrips];
+      const int32_t tot_sp = S.st_sp[nstrips], tot_ct = S.st_ct[nstrips];
+      for (int i = tid; i <= ns; i += FUSE_T) {           // prefixes at every segment start
+        const int32_t k = S.rel[i];
+        if (k >= span) { S.loff[i] = tot_out; S.spb[i] = (uint16_t)tot_sp; S.ctb[i] = (uint16_t)tot_ct; }
+        else { const int s = k >> 5; S.loff[i] = S.st_out[s] + S.pre_out[i]; S.spb[i] = (uint16_t)(S.st_sp[s] + S.pre_sp[i]); S.ctb[i] = (uint16_t)(S.st_ct[s] + S.pre_ct[i]); }
       }
       __syncthreads();
       FUSE_PH(3);
-      if (tid < ns) { loff = S.loff[tid]; mylen = S.loff[tid + 1] - loff; mykeep = mylen > 0; }
-      int32_t d0, d1;
-      fuse_scan3(S, lane, wid, mykeep, 0, 0, &koff, &d0, &d1);
-      tot_kept = S.tot[0];
+      int32_t myspb = 0;
+      if (tid < ns) {
+        loff = S.loff[tid]; mylen = S.loff[tid + 1] - loff; mykeep = mylen > 0;
+        myspb = S.spb[tid];
+        mynw = mykeep ? (int32_t)S.spb[tid + 1] - myspb + 1 : 0;
+        mychars = mylen - ((int32_t)S.ctb[tid + 1] - (int32_t)S.ctb[tid]);
+      }
+      int32_t d1;
+      fuse_scan3(S, lane, wid, mykeep, mynw, 0, &koff, &woff, &d1);
+      tot_kept = S.tot[0]; tot_words = S.tot[1];
+      if (tid < ns) { S.len[tid] = mylen; S.koff[tid] = koff; S.spmin[tid] = 0x7fffffff; }
       if (wid == 0) {
         long long gb = fuse_lookback(A.desc_bytes, tile, tot_out, lane);
         long long kb = fuse_lookback(A.desc_kept, tile, tot_kept, lane);
@@ -255,12 +292,12 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
         uint8_t* dst = fast_out ? S.x.out : D.C + gbase;
         for (int s = wid; s < nstrips; s += FUSE_NW) {
           int32_t k = (s << 5) + lane;
-          uint32_t r = (k >= al && k < span) ? S.z.code[k] : 0u;
+          uint32_t r = (k >= al && k < span) ? (S.z.code[k] & 3u) : 0u;
           unsigned m1 = __ballot_sync(0xffffffffu, r != 0), m2 = __ballot_sync(0xffffffffu, r == 3);
-          int32_t pos = S.strip_base[s] + __popc(m1 & lt) + __popc(m2 & lt);
-          if (r == 1) dst[pos] = S.in[k];
+          int32_t pos = S.st_out[s] + __popc(m1 & lt) + __popc(m2 & lt);
+          if (r == 1) dst[pos] = S.y.in[k];
           else if (r == 2) dst[pos] = ' ';
-          else if (r == 3) { dst[pos] = ' '; dst[pos + 1] = S.in[k]; }
+          else if (r == 3) { dst[pos] = ' '; dst[pos + 1] = S.y.in[k]; }
         }
       }
       __syncthreads();
@@ -269,16 +306,41 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
         for (int32_t k = tid; k < tot_out; k += FUSE_T) dstg[k] = S.x.out[k];
       }
       FUSE_PH(5);
-      // words and code points per segment
-      if (tid < ns && mylen > 0) {
-        const uint8_t* p = fast_out ? S.x.out + loff : D.C + gbase + loff;
-        int32_t sp = 0, cc = 0;
-        for (int32_t k = 0; k < mylen; ++k) { uint8_t c = p[k]; sp += c == ' '; cc += (c & 0xC0) != 0x80; }
-        mynw = sp + 1; mychars = cc;
-      }
-      fuse_scan3(S, lane, wid, mynw, 0, 0, &woff, &d0, &d1);
-      tot_words = S.tot[0];
       fast_out = fast_out && tot_words <= FUSE_WORD_CAP;
+      if (fast_out) {
+        // sorted word list (the raw tile is dead): a word starts at every emitted space and at every segment start
+        for (int s = wid; s < nstrips; s += FUSE_NW) {
+          int32_t k = (s << 5) + lane;
+          uint32_t cd = (k >= al && k < span) ? S.z.code[k] : 0u;
+          const uint32_t r = cd & 3u;
+          unsigned m1 = __ballot_sync(0xffffffffu, r != 0), m2 = __ballot_sync(0xffffffffu, r == 3), ms = __ballot_sync(0xffffffffu, r >= 2);
+          if (r >= 2) {
+            const int d = (int)(cd >> 2);
+            int i = S.strip_seg[s] + d;
+            if (d == 31) while (i + 1 < ns && S.rel[i + 1] <= k) ++i;
+            const int32_t pos = S.st_out[s] + __popc(m1 & lt) + __popc(m2 & lt);
+            const int32_t w = S.st_sp[s] + __popc(ms & lt) + S.koff[i] + 1;
+            S.y.w.wstart[w] = (uint16_t)pos; S.y.w.wseg[w] = (uint16_t)i;
+          }
+        }
+        if (tid < ns && mylen > 0) { const int32_t w = myspb + koff; S.y.w.wstart[w] = (uint16_t)loff; S.y.w.wseg[w] = (uint16_t)tid; }
+        // special-token literals in the cleaned tile
+        for (int32_t x = tid; x < tot_out; x += FUSE_T) {
+          const uint8_t b = S.x.out[x];
+          if ((T.sp_first[b >> 6] >> (b & 63)) & 1ULL) {
+            int lo = 0, hi = ns;                   // segment of output byte x: last i with loff[i] <= x
+            while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (S.loff[mid] <= x) lo = mid; else hi = mid; }
+            const int32_t end = S.loff[lo] + S.len[lo];
+            for (uint32_t q = 0; q < T.n_sp; ++q) {
+              const uint32_t o = T.sp_off[q], L = T.sp_off[q + 1] - o;
+              if (L == 0 || T.sp_bytes[o] != b || x + (int32_t)L > end) continue;
+              bool eq = true;
+              for (uint32_t j = 1; j < L; ++j) if (S.x.out[x + j] != T.sp_bytes[o + j]) { eq = false; break; }
+              if (eq) { atomicMin(&S.spmin[lo], (x << 4) | (int32_t)q); break; }
+            }
+          }
+        }
+      }
     } else {
       // ================= slow lane: sequential per-segment routines on global memory =================
       const uint8_t* src = D.text + base;
@@ -305,25 +367,16 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
     // ---- tokens of " " + cleaned text, special-token scan
     int32_t mysp = -1;
     if (fast_out) {
-      if (tid < ns && mylen > 0) {
-        int32_t w = woff;
-        S.z.w.wstart[w] = (uint16_t)loff; S.z.w.wseg[w] = (uint16_t)tid; ++w;
-        for (int32_t k = 0; k < mylen; ++k)
-          if (S.x.out[loff + k] == ' ') { S.z.w.wstart[w] = (uint16_t)(loff + k); S.z.w.wseg[w] = (uint16_t)tid; ++w; }
-        mysp = trc_find_special(T, S.x.out + loff, mylen);
-      }
-      if (tid < ns) { S.len[tid] = mylen; S.koff[tid] = koff; }
-      __syncthreads();
       FUSE_PH(6);
       // fast pass: words made only of the common ASCII span shapes; the rest is queued and handled densely
       if (tid == 0) S.nslow = 0;
       __syncthreads();
-      uint16_t* slow = reinterpret_cast<uint16_t*>(S.in);
+      uint16_t* slow = S.z.slow;
       for (int32_t w = tid; w < tot_words; w += FUSE_T) {
-        const int seg = S.z.w.wseg[w];
-        const int32_t st = S.z.w.wstart[w];
+        const int seg = S.y.w.wseg[w];
+        const int32_t st = S.y.w.wstart[w];
         const int32_t sl = S.loff[seg];
-        const int32_t en = (w + 1 < tot_words && S.z.w.wseg[w + 1] == seg) ? (int32_t)S.z.w.wstart[w + 1] : sl + S.len[seg];
+        const int32_t en = (w + 1 < tot_words && S.y.w.wseg[w + 1] == seg) ? (int32_t)S.y.w.wstart[w + 1] : sl + S.len[seg];
         uint32_t c = 0;
         if (trc_count_word_fast(T, F, S.x.out + st, en - st, st == sl ? 1 : 0, &c)) atomicAdd(&S.tok[seg], (int32_t)c);
         else slow[atomicAdd(&S.nslow, 1)] = (uint16_t)w;
@@ -332,10 +385,10 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
       const int32_t nslow = S.nslow;
       for (int32_t q = tid; q < nslow; q += FUSE_T) {
         const int32_t w = slow[q];
-        const int seg = S.z.w.wseg[w];
-        const int32_t st = S.z.w.wstart[w];
+        const int seg = S.y.w.wseg[w];
+        const int32_t st = S.y.w.wstart[w];
         const int32_t sl = S.loff[seg];
-        const int32_t en = (w + 1 < tot_words && S.z.w.wseg[w + 1] == seg) ? (int32_t)S.z.w.wstart[w + 1] : sl + S.len[seg];
+        const int32_t en = (w + 1 < tot_words && S.y.w.wseg[w + 1] == seg) ? (int32_t)S.y.w.wstart[w + 1] : sl + S.len[seg];
         const int vs = st == sl ? 1 : 0;
         const int64_t j = kbase + S.koff[seg];
         uint32_t c = trc_count_unit(T, F, byte_id, S.x.out + st, en - st, vs, [&](int64_t ls, int64_t len) -> uint32_t {
@@ -359,6 +412,7 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
       mysp = trc_find_special(T, p, mylen);
     }
     __syncthreads();
+    if (fast_out && tid < ns) { const int32_t v = S.spmin[tid]; mysp = v == 0x7fffffff ? -1 : (v & 15); }
     FUSE_PH(7);
     // ---- outputs
     if (tid < ns) {
