@@ -131,6 +131,7 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
     const int32_t span = (int32_t)((raw1 - base) < (1 << 30) ? (raw1 - base) : (1 << 30));
     const bool fast_in = (raw1 - base) <= FUSE_IN_CAP;
     for (int k = tid; k <= ns; k += FUSE_T) S.rel[k] = (int32_t)(D.seg_off[s0 + k] - base);
+    __syncthreads();                          // rel[] is read across threads by both lanes
     int32_t mylen = 0, mynw = 0, mykeep = 0, mychars = 0, loff = 0, woff = 0, koff = 0;
     int32_t tot_out = 0, tot_words = 0, tot_kept = 0;
     long long gbase = 0, kbase = 0;

@@ -136,3 +136,12 @@ def test_idempotent_rerun(gpu_engine):
 
 def test_sentence_path_fuzz(gpu_engine):
     pc.sentence_fuzz(gpu_engine, 300, 1234)
+
+
+def test_config4_monologues(gpu_engine):
+    """One long transcript: huge same-speaker groups (combined-piece path) + 20-80 KB monologues
+    (sentence, clause and 20-word paths); the slow lane of the fused kernel handles the giant segments."""
+    b, mt, _ = synth.config(4, 0.03)
+    _check_docs(gpu_engine, b, mt, [0])
+    c = gpu_engine.counts()
+    assert c["n_sent"] > 1000 and c["n_subs"] > 100
