@@ -68,6 +68,20 @@ typedef struct {
   double max_duration;
   int32_t preserve_timestamps; /* preprocessor.py:20 */
   int32_t want_merged_text;    /* 1: also materialise the merged text buffer (TRC_A_MERGED) */
+  /* --- already processed input: chunk_transcript called on a list that did not come from this library
+   * (big_chunkeroosky.py:46 accepts any list of processed-segment dicts).  With already_processed = 1 the
+   * "segments" above are the PIECES of the processed segments (segment_timestamps entries of a combined
+   * segment, else the segment itself), their text is used verbatim (no clean_text) and the grouping is
+   * given instead of computed.  The segments' own start/end/text are verified on the device against what
+   * the pieces imply (preprocessor.py:186-213); a mismatch marks the document unsupported (-1). */
+  int32_t already_processed;
+  int32_t reserved_;
+  const int64_t* group_off;    /* n_groups + 1 piece ranges */
+  int64_t n_groups;
+  const double* group_start;   /* n_groups */
+  const double* group_end;     /* n_groups */
+  const uint8_t* full_text;    /* the segments' own text, back to back */
+  const int64_t* full_off;     /* n_groups + 1 */
 } trc_batch;
 
 /* Stage P: preprocessor.preprocess_transcript (preprocessor.py:15-67) for every document of the batch:

@@ -20,7 +20,10 @@ class Batch(C.Structure):
                 ("speaker", C.c_void_p), ("n_seg", C.c_int64), ("doc_off", C.c_void_p), ("n_doc", C.c_int64),
                 ("spk_bytes", C.c_void_p), ("spk_off", C.c_void_p), ("n_spk", C.c_int32), ("memory", C.c_int32),
                 ("merge_same_speaker", C.c_int32), ("has_max_duration", C.c_int32), ("max_duration", C.c_double),
-                ("preserve_timestamps", C.c_int32), ("want_merged_text", C.c_int32)]
+                ("preserve_timestamps", C.c_int32), ("want_merged_text", C.c_int32),
+                ("already_processed", C.c_int32), ("reserved_", C.c_int32), ("group_off", C.c_void_p),
+                ("n_groups", C.c_int64), ("group_start", C.c_void_p), ("group_end", C.c_void_p),
+                ("full_text", C.c_void_p), ("full_off", C.c_void_p)]
 
 
 SUB_DTYPE = [("group", "<i4"), ("kind", "<i4"), ("r0", "<i4"), ("r1", "<i4"), ("start_src", "<i4"), ("end_src", "<i4"),

@@ -29,10 +29,7 @@ class BigChunkeroosky:
         ok = (h is not None and len(processed_segments) == len(h["ids"])
               and all(id(d) == i for d, i in zip(processed_segments, h["ids"])))
         if not ok:
-            raise NotImplementedError(
-                "chunk_transcript accepts the list returned by this package's preprocess_transcript "
-                "(the reference's only call pattern, main.py:139-149); arbitrary hand-built segment lists "
-                "are not packed for the device yet")
+            return self._chunk_foreign(processed_segments, add_context)
         eng = h["engine"]
         if eng.batch_serial != h["serial"]:              # another batch replaced it: run stage P again
             h["serial"] = eng.preprocess(h["batch"], want_merged_text=True, **h["params"])
@@ -43,6 +40,32 @@ class BigChunkeroosky:
             c["total_chunks"] = None                    # filled by postprocess_chunks, as in the reference (:170)
         print(f"Chunkeroosky: Created {len(chunks)} chunks from {len(processed_segments)} segments")  # :143
         return chunks
+
+    def _chunk_foreign(self, processed_segments, add_context):
+        """A list that did not come from this package's preprocess_transcript (hand-built, reloaded from
+        JSON, edited ...): the dicts are packed as they are (texts verbatim, pieces from
+        'segment_timestamps') and chunked on the device.  The device verifies that every combined
+        segment's own start/end/text is what its pieces imply (preprocessor.py:186-213); anything else is
+        outside the supported domain and raises instead of being approximated."""
+        eng = self._engine
+        batch = _eng.pack_processed(processed_segments)
+        last = None
+        for preserve in (True, False):           # combined text with "[ts] " markers, or plain joins (:190-200)
+            eng.preprocess(batch, merge_same_speaker=True, max_segment_duration=None, preserve_timestamps=preserve,
+                           want_merged_text=True)
+            eng.chunk([self.max_tokens_per_chunk], self.context_tokens, add_context)
+            R = eng.fetch_chunks()
+            if int(R["doc_err"][0]) != -1:
+                P = eng.fetch_processed()
+                chunks = _eng.build_chunks(eng, batch, P, R, processed_segments, 0)
+                for c in chunks:
+                    c["total_chunks"] = None
+                print(f"Chunkeroosky: Created {len(chunks)} chunks from {len(processed_segments)} segments")  # :143
+                return chunks
+            last = R
+        raise NotImplementedError(
+            "processed segments whose own start/end/text differ from what their segment_timestamps imply, "
+            "or an over-budget segment whose text is not whitespace-normalised, are outside the device path")
 
     def postprocess_chunks(self, chunks: List[Dict[Any, Any]]) -> List[Dict[Any, Any]]:
         """big_chunkeroosky.py:544-567 (the clause speaker fix-up never fires: clause segments carry no

@@ -28,6 +28,14 @@ __global__ void k_punkt_breaks(TrcDev D, TrcTables T, TrcSentState S, int64_t to
     int64_t n = D.coff[j + 1] - D.coff[j];
     int64_t i = p - S.rl_boff[q];
     brk[p] = pk_sentend(s[i]) && pk_is_break(T, s, n, i);
+    // domain check (only ever fails for text that did not come through clean_text): the sentence path
+    // assumes single U+0020 between words and no leading/trailing whitespace
+    uint8_t c = s[i];
+    bool bad = false;
+    if (c == ' ') bad = (i == 0 || i + 1 == n || s[i + 1] == ' ');
+    else if (c < 0x80) bad = (T.props[c] & TRC_P_SPACE) != 0;
+    else if (c >= 0xC0) { int l; uint32_t cp = trc_decode(s, i, n, &l); bad = (T.props[cp] & TRC_P_SPACE) != 0; }
+    if (bad) D.doc_err[D.sdoc[j]] = -1;
   }
 }
 __global__ void k_brk_pos(const int32_t* __restrict__ brk, const int64_t* __restrict__ bscan, int64_t total, int64_t* pos) {

@@ -444,6 +444,33 @@ __global__ void k_build_spk_units(const uint8_t* __restrict__ spk_bytes, const i
 }
 
 __global__ void k_fill_i64(int64_t* p, int64_t n, int64_t v) { GSTRIDE(i, n) p[i] = v; }
+// ---- already-processed input (include/trchunk.h: trc_batch.already_processed)
+__global__ void k_identity_pieces(TrcDev D) {
+  GSTRIDE(j, D.n_kept) {
+    D.k2r[j] = (int32_t)j;
+    int64_t lo = 0, hi = D.n_doc;
+    while (hi - lo > 1) { int64_t mid = (lo + hi) >> 1; if (D.doc_off[mid] <= j) lo = mid; else hi = mid; }
+    D.sdoc[j] = (int32_t)lo;
+    int32_t c = 0;
+    for (int64_t k = D.coff[j]; k < D.coff[j + 1]; ++k) c += (D.C[k] & 0xC0) != 0x80;
+    D.cchars[j] = c;
+  }
+}
+__global__ void k_flag_groups(const int64_t* __restrict__ group_off, int64_t m, int32_t* gflag) { GSTRIDE(g, m) gflag[group_off[g]] = 1; }
+__global__ void k_verify_groups(TrcDev D, TrcTables T, const double* __restrict__ gs, const double* __restrict__ ge,
+                                const uint8_t* __restrict__ full, const int64_t* __restrict__ full_off, const uint32_t* __restrict__ ftok) {
+  GSTRIDE(g, D.m) {
+    int32_t a = D.gstart[g], b = D.gstart[g + 1];
+    bool ok = D.start[D.k2r[a]] == gs[g] && D.end[D.k2r[b - 1]] == ge[g];
+    int64_t len = D.poff[b] - D.poff[a];
+    ok = ok && len == full_off[g + 1] - full_off[g];
+    if (ok) { const uint8_t* x = D.M + D.poff[a]; const uint8_t* y = full + full_off[g]; for (int64_t k = 0; k < len; ++k) if (x[k] != y[k]) { ok = false; break; } }
+    if (!ok) D.doc_err[D.sdoc[a]] = -1;
+    // tokens of the segment as the reference counts them: on its OWN text (big_chunkeroosky.py:82-83)
+    D.gtok[g] = 2 + trc_ts_tokens(T, D.start[D.k2r[a]]) + D.spk_tok[D.spk[D.k2r[a]]] + ftok[g];
+  }
+}
+
 __global__ void k_merge_next(TrcDev D) { GSTRIDE(j, D.n_kept) trc_merge_next(D, j); }
 __global__ void k_orbit(const int64_t* __restrict__ range_off, const int32_t* __restrict__ nxt, int32_t* flag, int64_t n_doc) {
   GSTRIDE(x, n_doc) trc_orbit_walk(range_off, nxt, flag, x);
@@ -833,6 +860,18 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   ALLOC(D.doc_err, int32_t, nd); ALLOC(D.doc_err_seg, int64_t, nd);
   CK(cudaMemsetAsync(D.doc_err, 0, 4 * (size_t)(nd > 0 ? nd : 1), st));
   LAUNCH(k_fill_i64, nd, 256, D.doc_err_seg, nd, (int64_t)INT64_MAX);
+  const bool modeB = B->already_processed != 0;
+  if (modeB) {
+    if (!B->group_off || !B->group_start || !B->group_end || !B->full_text || !B->full_off || B->n_groups < 0) {
+      ctx->err = "already_processed needs group_off, group_start, group_end, full_text and full_off"; return TRC_EINVAL;
+    }
+    nk = n; bclean = braw; D.n_kept = n;
+    D.C = const_cast<uint8_t*>(D.text); D.coff = const_cast<int64_t*>(D.seg_off); D.kdoc_off = const_cast<int64_t*>(D.doc_off);
+    ALLOC(D.cchars, int32_t, n); ALLOC(D.k2r, int32_t, n); ALLOC(D.sdoc, int32_t, n); ALLOC(D.ctok, uint32_t, n); ALLOC(seg_special, int32_t, n);
+    LAUNCH(k_identity_pieces, n, 128, D);
+    if ((rc = count_units(ctx, st, D.C, D.coff, D.coff + 1, n, braw, 1, D.ctok, seg_special, false))) return rc;
+    ctx->counts[TRC_N_KEPT] = nk; ctx->counts[TRC_B_CLEAN] = bclean;
+  } else
 #ifndef TRC_HOSTSIM
   if (ctx->use_fused) {
     // P1+P2 fused: single pass, outputs sized by upper bounds (cleaned text <= 1.5 x raw, kept <= n)
@@ -937,9 +976,15 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
 
   // P3: merge
   ALLOC(D.mnxt, int32_t, nk); ALLOC(D.gflag, int32_t, nk); ALLOC(D.gscan, int64_t, nk + 1);
-  LAUNCH(k_merge_next, nk, 256, D);
   CK(cudaMemsetAsync(D.gflag, 0, 4 * (size_t)(nk > 0 ? nk : 1), st));
-  LAUNCH(k_orbit, nd, 64, D.kdoc_off, D.mnxt, D.gflag, nd);
+  const int64_t* d_group_off = nullptr;
+  if (modeB) {
+    if ((rc = to_device(ctx, st, B->group_off, B->n_groups + 1, B->memory, &d_group_off))) return rc;
+    LAUNCH(k_flag_groups, B->n_groups, 256, d_group_off, B->n_groups, D.gflag);
+  } else {
+    LAUNCH(k_merge_next, nk, 256, D);
+    LAUNCH(k_orbit, nd, 64, D.kdoc_off, D.mnxt, D.gflag, nd);
+  }
   if ((rc = scan_excl(ctx, st, D.gflag, D.gscan, nk))) return rc;
   int64_t m = 0;
   if (nk) { if ((rc = read_back(ctx, st, D.gscan + nk, 8, &m))) return rc; }
@@ -959,7 +1004,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   int64_t bm = 0;
   if (nk) { if ((rc = read_back(ctx, st, D.poff + nk, 8, &bm))) return rc; }
   ctx->counts[TRC_B_MERGED] = bm;
-  if (B->want_merged_text) {
+  if (B->want_merged_text || modeB) {
     ALLOC(D.M, uint8_t, bm);
     LAUNCH_W(k_emit_merged, nk, D);
     set_arr(ctx, TRC_A_MERGED, D.M, bm);
@@ -967,6 +1012,21 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   // P5: group token totals, formatted lengths, formatted timestamps
   ALLOC(D.gts, uint8_t, m * 48); ALLOC(D.gtok, int64_t, m); ALLOC(D.glen, int64_t, m);
   LAUNCH(k_group_stats, m, 128, D, ctx->T);
+  if (modeB) {
+    if (m != B->n_groups) { ctx->err = "group_off does not describe the pieces"; return TRC_EINVAL; }
+    const double* d_gs; const double* d_ge; const uint8_t* d_full; const int64_t* d_foff;
+    int64_t bfull = 0;
+    if (B->memory == TRC_MEM_HOST) bfull = B->full_off[m];
+    else { int64_t t1[1]; if ((rc = read_back(ctx, st, B->full_off + m, 8, t1))) return rc; bfull = t1[0]; }
+    if ((rc = to_device(ctx, st, B->group_start, m, B->memory, &d_gs))) return rc;
+    if ((rc = to_device(ctx, st, B->group_end, m, B->memory, &d_ge))) return rc;
+    if ((rc = to_device(ctx, st, B->full_text, bfull, B->memory, &d_full))) return rc;
+    if ((rc = to_device(ctx, st, B->full_off, m + 1, B->memory, &d_foff))) return rc;
+    uint32_t* ftok; int32_t* fsp;
+    ALLOC(ftok, uint32_t, m); ALLOC(fsp, int32_t, m);
+    if ((rc = count_units(ctx, st, d_full, d_foff, d_foff + 1, m, bfull, 1, ftok, fsp, false))) return rc;
+    LAUNCH(k_verify_groups, m, 128, D, ctx->T, d_gs, d_ge, d_full, d_foff, ftok);
+  }
   CK(cudaEventRecord(ctx->ev[1], st));
   ctx->ev_pre = true; ctx->ev_chunk = false;
 

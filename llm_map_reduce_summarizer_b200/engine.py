@@ -68,6 +68,53 @@ def pack_documents(docs):
     return PackedBatch(buf, off, st, en, spk, np.array(doc_off, dtype=np.int64), names, (starts, ends))
 
 
+class ProcessedBatch(PackedBatch):
+    """Already processed segments (big_chunkeroosky.py:46 accepts any such list): the PIECES are the packed
+    segments; `groups` holds the C ABI's extra arrays (include/trchunk.h: trc_batch.already_processed)."""
+    groups = None
+
+
+def pack_processed(segments):
+    """One transcript given as processed-segment dicts (the output format of preprocess_transcript,
+    preprocessor.py:45-52,203-213) -> ProcessedBatch."""
+    texts, starts, ends, spk_names, group_off, gs, ge, full = [], [], [], [], [0], [], [], []
+    for seg in segments:
+        sp = seg["speaker"]
+        if not isinstance(sp, str):
+            raise TypeError("speaker must be a str (the reference's header join fails otherwise)")
+        if "segment_timestamps" in seg and seg.get("is_combined", False):
+            pieces = seg["segment_timestamps"]
+            if len(pieces) < 2:
+                raise NotImplementedError("combined segment with fewer than two segment_timestamps entries")
+        else:
+            pieces = [seg]
+        for p in pieces:
+            texts.append(p["text"].encode("utf-8"))
+            starts.append(p["start"])
+            ends.append(p["end"])
+            spk_names.append(sp)
+        group_off.append(len(texts))
+        gs.append(float(seg["start"]))
+        ge.append(float(seg["end"]))
+        full.append(seg["text"].encode("utf-8"))
+    names = sorted(set(spk_names) | {""})
+    ids = {s: i for i, s in enumerate(names)}
+    buf, off = _vocab.pack_strings(texts)
+    st = np.array([float(x) for x in starts], dtype=np.float64)
+    en = np.array([float(x) for x in ends], dtype=np.float64)
+    for arr in (st, en):
+        if arr.size and not np.isfinite(arr).all():
+            if np.isnan(arr).any():
+                raise ValueError("cannot convert float NaN to integer")
+            raise OverflowError("cannot convert float infinity to integer")
+    b = ProcessedBatch(buf, off, st, en, np.array([ids[s] for s in spk_names], dtype=np.int32),
+                       np.array([0, len(texts)], dtype=np.int64), names, (starts, ends))
+    fb, fo = _vocab.pack_strings(full)
+    b.groups = {"group_off": np.array(group_off, dtype=np.int64), "group_start": np.array(gs, dtype=np.float64),
+                "group_end": np.array(ge, dtype=np.float64), "full_text": fb, "full_off": fo}
+    return b
+
+
 class Engine:
     """One context on one GPU.  Not thread-safe (one engine per thread / per rank)."""
 
@@ -133,6 +180,14 @@ class Engine:
         b.max_duration = float(max_segment_duration) if max_segment_duration is not None else 0.0
         b.preserve_timestamps = 1 if preserve_timestamps else 0
         b.want_merged_text = 1 if want_merged_text else 0
+        g = getattr(batch, "groups", None)
+        if g is not None:
+            if device_ptrs is not None:
+                raise ValueError("already-processed batches are passed from host memory")
+            b.already_processed = 1
+            b.group_off, b.n_groups = g["group_off"].ctypes.data, len(g["group_start"])
+            b.group_start, b.group_end = g["group_start"].ctypes.data, g["group_end"].ctypes.data
+            b.full_text, b.full_off = g["full_text"].ctypes.data, g["full_off"].ctypes.data
         self._keep = (batch, b)
         self._check(self.lib.trc_preprocess(self.h, C.byref(b), stream))
         self.batch = batch

@@ -31,14 +31,20 @@ def first_diff(a, b):
     return ""
 
 
-def check_fuzz_cases(eng, cases, require_all=True):
+def check_fuzz_cases(eng, cases, require_all=True, foreign=False):
+    """foreign=True: chunk_transcript gets a plain deep copy of the REFERENCE's processed list (a list
+    this package did not produce), exercising the already-processed entry of the C ABI."""
+    import copy
     n_ok = 0
     for i, cs in enumerate(cases):
         kw = cs["kw"]
         E.set_default_engine(eng)
-        with quiet():
-            proc = PP.preprocess_transcript(cs["segments"], kw["merge"], None, kw["max_dur"], kw["preserve"])
-        assert same(list(proc), cs["proc"]), "case %d preprocess: %s" % (i, first_diff(list(proc), cs["proc"]))
+        if foreign:
+            proc = copy.deepcopy(cs["proc"])
+        else:
+            with quiet():
+                proc = PP.preprocess_transcript(cs["segments"], kw["merge"], None, kw["max_dur"], kw["preserve"])
+            assert same(list(proc), cs["proc"]), "case %d preprocess: %s" % (i, first_diff(list(proc), cs["proc"]))
         err, chunks = None, None
         try:
             with quiet():

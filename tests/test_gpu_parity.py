@@ -145,3 +145,27 @@ def test_config4_monologues(gpu_engine):
     _check_docs(gpu_engine, b, mt, [0])
     c = gpu_engine.counts()
     assert c["n_sent"] > 1000 and c["n_subs"] > 100
+
+
+def test_foreign_processed_lists(gpu_engine):
+    """chunk_transcript on lists this package did not produce (here: the reference's own processed lists)."""
+    n = pc.check_fuzz_cases(gpu_engine, load_golden("fuzz_cases.json.gz"), require_all=True, foreign=True)
+    assert n == 160
+    segs = load_golden("example_segments.json.gz")
+    from oracle import preprocess as OP2, chunker as OC2
+    proc = OP2.preprocess(segs)
+    want = OC2.ChunkerOracle(2000).chunk(proc)
+    E.set_default_engine(gpu_engine)
+    from conftest import quiet
+    from llm_map_reduce_summarizer_b200 import big_chunkeroosky as BC2
+    with quiet():
+        c = BC2.BigChunkeroosky(max_tokens_per_chunk=2000)
+        got = c.postprocess_chunks(c.chunk_transcript(proc))
+    assert pc.same(got, want)
+    assert all(a is b for ch in got for a, b in zip(ch["segments"], ch["segments"])) and got[0]["segments"][0] is proc[0]
+    # an inconsistent combined segment is refused, not approximated
+    import copy, pytest
+    bad = copy.deepcopy(proc)
+    bad[0]["text"] = bad[0]["text"] + " edited"
+    with quiet(), pytest.raises(NotImplementedError):
+        c.chunk_transcript(bad)

@@ -77,3 +77,27 @@ def test_empty_inputs(hostsim_engine):
 
 def test_sentence_path_fuzz(hostsim_engine):
     pc.sentence_fuzz(hostsim_engine, 300, 99)
+
+
+def test_foreign_processed_lists(hostsim_engine):
+    """chunk_transcript on lists this package did not produce (here: the reference's own processed lists)."""
+    n = pc.check_fuzz_cases(hostsim_engine, load_golden("fuzz_cases.json.gz"), require_all=True, foreign=True)
+    assert n == 160
+    segs = load_golden("example_segments.json.gz")
+    from oracle import preprocess as OP2, chunker as OC2
+    proc = OP2.preprocess(segs)
+    want = OC2.ChunkerOracle(2000).chunk(proc)
+    E.set_default_engine(hostsim_engine)
+    from conftest import quiet
+    from llm_map_reduce_summarizer_b200 import big_chunkeroosky as BC2
+    with quiet():
+        c = BC2.BigChunkeroosky(max_tokens_per_chunk=2000)
+        got = c.postprocess_chunks(c.chunk_transcript(proc))
+    assert pc.same(got, want)
+    assert all(a is b for ch in got for a, b in zip(ch["segments"], ch["segments"])) and got[0]["segments"][0] is proc[0]
+    # an inconsistent combined segment is refused, not approximated
+    import copy, pytest
+    bad = copy.deepcopy(proc)
+    bad[0]["text"] = bad[0]["text"] + " edited"
+    with quiet(), pytest.raises(NotImplementedError):
+        c.chunk_transcript(bad)
