@@ -73,7 +73,9 @@ typedef struct {
    * "segments" above are the PIECES of the processed segments (segment_timestamps entries of a combined
    * segment, else the segment itself), their text is used verbatim (no clean_text) and the grouping is
    * given instead of computed.  The segments' own start/end/text are verified on the device against what
-   * the pieces imply (preprocessor.py:186-213); a mismatch marks the document unsupported (-1). */
+   * the pieces imply (preprocessor.py:186-213); a mismatch marks the document unsupported (-1).
+   * With group_off == NULL the pieces are merged as usual (combine_same_speaker_segments,
+   * preprocessor.py:109-165, on already cleaned segments) and nothing is verified. */
   int32_t already_processed;
   int32_t reserved_;
   const int64_t* group_off;    /* n_groups + 1 piece ranges */

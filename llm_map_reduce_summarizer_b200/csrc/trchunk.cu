@@ -862,8 +862,8 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   LAUNCH(k_fill_i64, nd, 256, D.doc_err_seg, nd, (int64_t)INT64_MAX);
   const bool modeB = B->already_processed != 0;
   if (modeB) {
-    if (!B->group_off || !B->group_start || !B->group_end || !B->full_text || !B->full_off || B->n_groups < 0) {
-      ctx->err = "already_processed needs group_off, group_start, group_end, full_text and full_off"; return TRC_EINVAL;
+    if (B->group_off && (!B->group_start || !B->group_end || !B->full_text || !B->full_off || B->n_groups < 0)) {
+      ctx->err = "already_processed with group_off needs group_start, group_end, full_text and full_off"; return TRC_EINVAL;
     }
     nk = n; bclean = braw; D.n_kept = n;
     D.C = const_cast<uint8_t*>(D.text); D.coff = const_cast<int64_t*>(D.seg_off); D.kdoc_off = const_cast<int64_t*>(D.doc_off);
@@ -978,7 +978,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   ALLOC(D.mnxt, int32_t, nk); ALLOC(D.gflag, int32_t, nk); ALLOC(D.gscan, int64_t, nk + 1);
   CK(cudaMemsetAsync(D.gflag, 0, 4 * (size_t)(nk > 0 ? nk : 1), st));
   const int64_t* d_group_off = nullptr;
-  if (modeB) {
+  if (modeB && B->group_off) {
     if ((rc = to_device(ctx, st, B->group_off, B->n_groups + 1, B->memory, &d_group_off))) return rc;
     LAUNCH(k_flag_groups, B->n_groups, 256, d_group_off, B->n_groups, D.gflag);
   } else {
@@ -1012,7 +1012,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   // P5: group token totals, formatted lengths, formatted timestamps
   ALLOC(D.gts, uint8_t, m * 48); ALLOC(D.gtok, int64_t, m); ALLOC(D.glen, int64_t, m);
   LAUNCH(k_group_stats, m, 128, D, ctx->T);
-  if (modeB) {
+  if (modeB && B->group_off) {
     if (m != B->n_groups) { ctx->err = "group_off does not describe the pieces"; return TRC_EINVAL; }
     const double* d_gs; const double* d_ge; const uint8_t* d_full; const int64_t* d_foff;
     int64_t bfull = 0;

@@ -185,9 +185,10 @@ class Engine:
             if device_ptrs is not None:
                 raise ValueError("already-processed batches are passed from host memory")
             b.already_processed = 1
-            b.group_off, b.n_groups = g["group_off"].ctypes.data, len(g["group_start"])
-            b.group_start, b.group_end = g["group_start"].ctypes.data, g["group_end"].ctypes.data
-            b.full_text, b.full_off = g["full_text"].ctypes.data, g["full_off"].ctypes.data
+            if g:
+                b.group_off, b.n_groups = g["group_off"].ctypes.data, len(g["group_start"])
+                b.group_start, b.group_end = g["group_start"].ctypes.data, g["group_end"].ctypes.data
+                b.full_text, b.full_off = g["full_text"].ctypes.data, g["full_off"].ctypes.data
         self._keep = (batch, b)
         self._check(self.lib.trc_preprocess(self.h, C.byref(b), stream))
         self.batch = batch
@@ -282,8 +283,10 @@ class _Text:
         return self.s[a:b] if self.s is not None else self.b[a:b].decode("utf-8")
 
 
-def build_processed(batch, P, doc=0):
-    """Processed-segment dicts of document `doc` in the reference's format (preprocessor.py:45-52,203-213)."""
+def build_processed(batch, P, doc=0, piece_dicts=None):
+    """Processed-segment dicts of document `doc` in the reference's format (preprocessor.py:45-52,203-213).
+    piece_dicts: the caller's own processed dicts when the pieces came in already processed; a group of
+    one is then returned as that very object (preprocessor.py:181-183)."""
     starts, ends = batch.originals if batch.originals is not None else (batch.start.tolist(), batch.end.tolist())
     k2r, coff, gstart, poff, gts = P["k2r"], P["coff"], P["gstart"], P["poff"], P["gts"]
     clean, merged = _Text(P["clean"]), _Text(P["merged"])
@@ -295,6 +298,9 @@ def build_processed(batch, P, doc=0):
     for g in range(g0, g1):
         a, b = int(gstart[g]), int(gstart[g + 1])
         ra, rb = int(k2r[a]), int(k2r[b - 1])
+        if piece_dicts is not None and b - a == 1:
+            out.append(piece_dicts[ra])
+            continue
         o = g * 48
         sf = gts_b[o + 1:o + 1 + gts_b[o]].decode("ascii")
         ef = gts_b[o + 25:o + 25 + gts_b[o + 24]].decode("ascii")

@@ -63,21 +63,37 @@ def format_timestamp(seconds: float) -> str:
 
 def combine_same_speaker_segments(segments: List[Dict[Any, Any]], max_duration: Optional[int] = 120,
                                   preserve_timestamps: bool = True) -> List[Dict[Any, Any]]:
-    """preprocessor.py:109-165.  Input: already processed (cleaned) segment dicts."""
+    """preprocessor.py:109-165.  Input: already processed (cleaned) segment dicts; only the merge runs."""
     if not segments:
         return []
-    raise NotImplementedError(
-        "combine_same_speaker_segments on pre-cleaned dicts is not a separate device entry point; "
-        "call preprocess_transcript (the only caller on the reference's path, main.py:139-143)")
+    eng = _eng.default_engine()
+    pieces = [{"start": s["start"], "end": s["end"], "text": s["text"], "speaker": s["speaker"]} for s in segments]
+    batch = _eng.pack_documents([pieces])
+    batch.groups = {}                       # already processed: texts verbatim, grouping computed by the merge kernels
+    eng.preprocess(batch, merge_same_speaker=True, max_segment_duration=max_duration,
+                   preserve_timestamps=bool(preserve_timestamps), want_merged_text=True)
+    P = eng.fetch_processed()
+    out = _eng.build_processed(batch, P, 0, piece_dicts=segments)
+    print(f"Preprocessing: Found {len({s['speaker'] for s in segments})} unique speakers in transcript")   # :130
+    print(f"Preprocessing: Combined {len(segments)} segments into {len(out)} segments")                     # :161
+    print(f"Preprocessing: Compression ratio: {len(out) / len(segments):.2f}")                              # :163
+    return out
 
 
 def create_combined_segment(segments: List[Dict[Any, Any]], preserve_timestamps: bool = True) -> Dict[Any, Any]:
-    """preprocessor.py:167-215."""
+    """preprocessor.py:167-215: the given segments as ONE combined segment."""
     if not segments:
         return {}
     if len(segments) == 1:
         return segments[0]
-    raise NotImplementedError("see combine_same_speaker_segments")
+    eng = _eng.default_engine()
+    sp = segments[0]["speaker"]
+    pieces = [{"start": s["start"], "end": s["end"], "text": s["text"], "speaker": sp} for s in segments]
+    batch = _eng.pack_documents([pieces])
+    batch.groups = {}
+    eng.preprocess(batch, merge_same_speaker=True, max_segment_duration=None,
+                   preserve_timestamps=bool(preserve_timestamps), want_merged_text=True)
+    return _eng.build_processed(batch, eng.fetch_processed(), 0, piece_dicts=segments)[0]
 
 
 def aggregate_by_time_interval(segments: List[Dict[Any, Any]], interval_seconds: int) -> List[Dict[Any, Any]]:

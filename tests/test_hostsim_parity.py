@@ -101,3 +101,28 @@ def test_foreign_processed_lists(hostsim_engine):
     bad[0]["text"] = bad[0]["text"] + " edited"
     with quiet(), pytest.raises(NotImplementedError):
         c.chunk_transcript(bad)
+
+
+def test_combine_helpers(hostsim_engine):
+    """combine_same_speaker_segments / create_combined_segment on already cleaned dicts
+    (preprocessor.py:109-215): clean-then-combine must equal preprocess_transcript."""
+    import random
+    import fuzzgen
+    from conftest import quiet
+    E.set_default_engine(hostsim_engine)
+    rng = random.Random(77)
+    for _ in range(40):
+        segs = fuzzgen.rand_transcript(rng)
+        cap = rng.choice([1, 30, 120, None])
+        pres = rng.random() < 0.8
+        want = OP.preprocess(segs, True, None, cap, pres)
+        unmerged = OP.preprocess(segs, False)
+        with quiet():
+            got = PP.combine_same_speaker_segments(unmerged, cap, pres)
+        assert json.dumps(got) == json.dumps(want)
+        assert all(g is u for g in got if "is_combined" not in g for u in unmerged if u is g) 
+        if len(unmerged) >= 2:
+            with quiet():
+                one = PP.create_combined_segment(unmerged[:4], pres)
+            assert one["original_segments"] == min(4, len(unmerged)) and one["is_combined"] is True
+            assert one["text"].count(unmerged[0]["text"]) >= 1
