@@ -1,0 +1,434 @@
+// K1a + K2 fused, third generation: every lane owns an 8-byte CELL of the tile (one 64-bit load), the clean
+// rules (preprocessor.py:38,69-89) are evaluated on bit masks (trc_swar.cuh) and only the rare cases
+// (multi-byte characters, whitespace runs across a cell edge, duplicate-word candidates) take scalar side
+// paths.  A warp covers 256 bytes per step.  Tile scheduling, look-back compaction, word-parallel token
+// counting (big_chunkeroosky.py:83 via DESIGN.md §3) and the slow lane are those of trc_fused.cuh.
+#pragma once
+
+#define F3_T 512
+#define F3_NW (F3_T / 32)
+#define F3_SEGS 256
+#define F3_IN_CAP 18432
+#define F3_OUT_CAP 26624
+#define F3_WORD_CAP 4608
+#define F3_CAND_CAP 2560
+#define F3_NCELL (F3_IN_CAP / 8)
+#define F3_NSTEP (F3_IN_CAP / 256)
+#define F3_MASKS 9
+#define F3_MSTRIDE (F3_NCELL + 8)
+
+struct F3Smem {
+  union alignas(16) {                         // raw tile; after the scatter: sorted word list
+    unsigned long long in64[F3_IN_CAP / 8 + 4];
+    uint8_t in[F3_IN_CAP + 32];
+    struct { uint16_t wstart[F3_WORD_CAP]; uint16_t wseg[F3_WORD_CAP]; } w;
+  } y;
+  union alignas(16) {                         // bit masks (sp w ct lt ep bd drop ds lead); after the word list: slow words
+    uint8_t m[F3_MASKS][F3_MSTRIDE];
+    uint16_t slow[F3_WORD_CAP];
+  } z;
+  uint8_t out[F3_OUT_CAP];
+  uint64_t hot8[TRC_HOT8];
+  uint16_t cand[F3_CAND_CAP];
+  uint16_t pre_o[F3_NCELL + 32], pre_s[F3_NCELL + 32];   // per cell: output bytes / spaces before it, inside its step
+  uint16_t st_o[F3_NSTEP + 1], st_s[F3_NSTEP + 1], st_t[F3_NSTEP + 1];
+  uint16_t step_seg[F3_NSTEP];
+  uint16_t sg_o[F3_SEGS + 1], sg_s[F3_SEGS + 1], sg_t[F3_SEGS + 1];   // step-relative prefixes at segment starts
+  uint16_t spb[F3_SEGS + 1], ctb[F3_SEGS + 1];
+  int32_t rel[F3_SEGS + 1];
+  int32_t loff[F3_SEGS + 1];
+  int32_t len[F3_SEGS], koff[F3_SEGS], tok[F3_SEGS], spmin[F3_SEGS];
+  int32_t wsum[3][F3_NW];
+  int32_t tot[3];
+  int32_t ncand, nslow;
+  unsigned int tile;
+  long long gbase, kbase;
+};
+static_assert(sizeof(F3Smem) <= 115200, "two CTAs per SM");
+
+__device__ __forceinline__ void f3_scan3(F3Smem& S, int lane, int wid, int32_t v0, int32_t v1, int32_t v2, int32_t* e0, int32_t* e1, int32_t* e2) {
+  int32_t x0 = v0, x1 = v1, x2 = v2;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int32_t y0 = __shfl_up_sync(0xffffffffu, x0, o), y1 = __shfl_up_sync(0xffffffffu, x1, o), y2 = __shfl_up_sync(0xffffffffu, x2, o);
+    if (lane >= o) { x0 += y0; x1 += y1; x2 += y2; }
+  }
+  __syncthreads();
+  if (lane == 31) { S.wsum[0][wid] = x0; S.wsum[1][wid] = x1; S.wsum[2][wid] = x2; }
+  __syncthreads();
+  if (wid == 0) {
+    int32_t w0 = lane < F3_NW ? S.wsum[0][lane] : 0, w1 = lane < F3_NW ? S.wsum[1][lane] : 0, w2 = lane < F3_NW ? S.wsum[2][lane] : 0;
+#pragma unroll
+    for (int o = 1; o < F3_NW; o <<= 1) {
+      int32_t y0 = __shfl_up_sync(0xffffffffu, w0, o), y1 = __shfl_up_sync(0xffffffffu, w1, o), y2 = __shfl_up_sync(0xffffffffu, w2, o);
+      if (lane >= o) { w0 += y0; w1 += y1; w2 += y2; }
+    }
+    if (lane < F3_NW) { S.wsum[0][lane] = w0; S.wsum[1][lane] = w1; S.wsum[2][lane] = w2; }
+    if (lane == F3_NW - 1) { S.tot[0] = w0; S.tot[1] = w1; S.tot[2] = w2; }
+  }
+  __syncthreads();
+  *e0 = (wid ? S.wsum[0][wid - 1] : 0) + x0 - v0;
+  *e1 = (wid ? S.wsum[1][wid - 1] : 0) + x1 - v1;
+  *e2 = (wid ? S.wsum[2][wid - 1] : 0) + x2 - v2;
+}
+
+// segment of tile byte k, starting the search at the first segment of k's step
+__device__ __forceinline__ int f3_seg_of(const F3Smem& S, int ns, int32_t k) {
+  int i = S.step_seg[k >> 8];
+  while (i + 1 < ns && S.rel[i + 1] <= k) ++i;
+  return i;
+}
+
+__global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTables T, const uint32_t* __restrict__ byte_id, FuseArgs A,
+                                                              int64_t ntiles) {
+  extern __shared__ __align__(16) unsigned char fuse_raw[];
+  F3Smem& S = *reinterpret_cast<F3Smem*>(fuse_raw);
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  for (int k = tid; k < TRC_HOT8; k += F3_T) S.hot8[k] = T.hot8_src[k];
+  TrcFast F; F.acls = T.acls; F.hot8 = S.hot8; F.hot8_mask = TRC_HOT8 - 1;
+  SwMasks M;
+  M.sp = S.z.m[0]; M.w = S.z.m[1]; M.ct = S.z.m[2]; M.lt = S.z.m[3]; M.ep = S.z.m[4]; M.bd = S.z.m[5]; M.drop = S.z.m[6]; M.ds = S.z.m[7];
+  uint8_t* const mlead = S.z.m[8];
+  uint8_t* const c_cp = M.drop; uint8_t* const c_se = M.ds; uint8_t* const c_in = M.lt;    // codes overwrite own-cell-only masks
+  __syncthreads();
+  long long ph_t = clock64();
+  for (;;) {
+    if (tid == 0) S.tile = (unsigned int)atomicAdd(A.tile_counter, 1ULL);
+    __syncthreads();
+    const unsigned tile = S.tile;
+    if ((int64_t)tile >= ntiles) break;
+    const int64_t s0 = (int64_t)tile * F3_SEGS;
+    const int ns = (int)((D.n - s0) < F3_SEGS ? (D.n - s0) : F3_SEGS);
+    const int64_t raw0 = D.seg_off[s0], raw1 = D.seg_off[s0 + ns];
+    const int al = (int)(raw0 & 15);
+    const int64_t base = raw0 - al;
+    const int32_t span = (int32_t)((raw1 - base) < (1 << 30) ? (raw1 - base) : (1 << 30));
+    const bool fast_in = (raw1 - base) <= F3_IN_CAP;
+    for (int k = tid; k <= ns; k += F3_T) S.rel[k] = (int32_t)(D.seg_off[s0 + k] - base);
+    __syncthreads();
+    int32_t mylen = 0, mynw = 0, mykeep = 0, mychars = 0, loff = 0, woff = 0, koff = 0;
+    int32_t tot_out = 0, tot_words = 0, tot_kept = 0;
+    long long gbase = 0, kbase = 0;
+    bool fast_out = false;
+    if (fast_in) {
+      const int ncell = (span + 7) >> 3, nstep = (span + 255) >> 8;
+      M.ncell = ncell;
+      // ---- load the tile (16-byte loads), clear the masks that are built with atomics
+      for (int32_t k = tid * 16; k < nstep * 256 + 16; k += F3_T * 16) {
+        int4 v = make_int4(0, 0, 0, 0);
+        if (k < span) {
+          if (base + k + 16 <= A.text_bytes) v = *reinterpret_cast<const int4*>(D.text + base + k);
+          else { __align__(16) uint8_t tmp[16]; for (int q = 0; q < 16; ++q) tmp[q] = base + k + q < A.text_bytes ? D.text[base + k + q] : 0; v = *reinterpret_cast<int4*>(tmp); }
+        }
+        *reinterpret_cast<int4*>(&S.y.in[k]) = v;
+      }
+      for (int k = tid; k < (F3_MSTRIDE * 3) / 4; k += F3_T) reinterpret_cast<uint32_t*>(S.z.m[5])[k] = 0u;   // bd, drop, ds
+      if (tid == 0) S.ncand = 0;
+      __syncthreads();
+      FUSE_PH(0);
+      if (tid < ns) {
+        const int32_t a = S.rel[tid], b = S.rel[tid + 1];
+        if (b > a) {
+          sw_or_bit(M.bd, a);
+          for (int32_t s = (a + 255) >> 8; (s << 8) < b; ++s) S.step_seg[s] = (uint16_t)tid;
+        }
+      }
+      if (tid == 0) S.step_seg[0] = 0;
+      // ---- A: ASCII classes of every cell
+      for (int st = wid; st < nstep; st += F3_NW) {
+        const int c = (st << 5) + lane;
+        const SwCell cl = sw_classify(S.y.in64[c]);
+        M.sp[c] = (uint8_t)cl.sp; M.w[c] = (uint8_t)cl.w; M.ct[c] = (uint8_t)cl.ct; M.lt[c] = (uint8_t)cl.lt; M.ep[c] = (uint8_t)cl.ep;
+        mlead[c] = (uint8_t)cl.lead;
+      }
+      __syncthreads();
+      // ---- A2: multi-byte characters (code point lookup by the owner of the lead byte)
+      for (int st = wid; st < nstep; st += F3_NW) {
+        const int c = (st << 5) + lane;
+        const uint32_t ld = mlead[c];
+        if (ld) sw_fix_multibyte(T, S.y.in, M, c, ld, span);
+      }
+      __syncthreads();
+      FUSE_PH(1);
+      // ---- B: duplicate-word candidates, compacted, then decided densely
+      for (int st = wid; st < nstep; st += F3_NW) {
+        const int c = (st << 5) + lane;
+        const int32_t k0 = c << 3;
+        uint32_t valid = 0xffu;
+        if (k0 < al) valid &= (al - k0 >= 8) ? 0u : (0xffu << (al - k0));
+        if (k0 + 8 > span) valid &= (span <= k0) ? 0u : (0xffu >> (k0 + 8 - span));
+        uint32_t cand = (c < ncell) ? sw_dup_candidates(M, c, valid & 0xffu) : 0u;
+        const int cnt = __popc(cand);
+        int x = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+        int b0 = 0;
+        if (lane == 31 && x) b0 = atomicAdd(&S.ncand, x);
+        b0 = __shfl_sync(0xffffffffu, b0, 31);
+        int slot = b0 + x - cnt;
+        while (cand) {
+          const int bit = __ffs(cand) - 1;
+          cand &= cand - 1;
+          if (slot < F3_CAND_CAP) S.cand[slot] = (uint16_t)(k0 + bit);
+          ++slot;
+        }
+      }
+      __syncthreads();
+      {
+        const int32_t nc = S.ncand;
+        if (nc <= F3_CAND_CAP) {
+          for (int32_t q = tid; q < nc; q += F3_T) {
+            const int32_t k = S.cand[q];
+            const int i = f3_seg_of(S, ns, k);
+            sw_mark_dup(S.y.in, M, k, S.rel[i], S.rel[i + 1]);
+          }
+        } else {                                 // list overflow: every cell walks its own candidates
+          for (int st = wid; st < nstep; st += F3_NW) {
+            const int c = (st << 5) + lane;
+            const int32_t k0 = c << 3;
+            uint32_t valid = 0xffu;
+            if (k0 < al) valid &= (al - k0 >= 8) ? 0u : (0xffu << (al - k0));
+            if (k0 + 8 > span) valid &= (span <= k0) ? 0u : (0xffu >> (k0 + 8 - span));
+            uint32_t cand = (c < ncell) ? sw_dup_candidates(M, c, valid & 0xffu) : 0u;
+            while (cand) {
+              const int bit = __ffs(cand) - 1;
+              cand &= cand - 1;
+              const int i = f3_seg_of(S, ns, k0 + bit);
+              sw_mark_dup(S.y.in, M, k0 + bit, S.rel[i], S.rel[i + 1]);
+            }
+          }
+        }
+      }
+      __syncthreads();
+      FUSE_PH(2);
+      // ---- C: output codes, per-cell prefixes inside the step, step totals, prefixes at segment starts
+      for (int st = wid; st < nstep; st += F3_NW) {
+        const int c = (st << 5) + lane;
+        SwCodes r; r.copy = r.space = r.ins = 0;
+        uint32_t ctm = 0, bd = 0;
+        if (c < ncell) { r = sw_cell_codes(S.y.in, M, c, al, span); ctm = M.ct[c]; bd = M.bd[c]; }
+        const uint32_t o = __popc(r.copy) + __popc(r.space) + __popc(r.ins), s = __popc(r.space) + __popc(r.ins), t = __popc(r.copy & ctm);
+        uint32_t v = o | (s << 11) | (t << 21), x = v;
+#pragma unroll
+        for (int q = 1; q < 32; q <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, q); if (lane >= q) x += y; }
+        const uint32_t ex = x - v;
+        if (c < ncell) { c_cp[c] = (uint8_t)r.copy; c_se[c] = (uint8_t)r.space; c_in[c] = (uint8_t)r.ins; }
+        S.pre_o[c] = (uint16_t)(ex & 0x7ffu); S.pre_s[c] = (uint16_t)((ex >> 11) & 0x3ffu);
+        if (lane == 31) { S.st_o[st] = (uint16_t)(x & 0x7ffu); S.st_s[st] = (uint16_t)((x >> 11) & 0x3ffu); S.st_t[st] = (uint16_t)(x >> 21); }
+        const int32_t k0 = c << 3;
+        if (k0 + 8 <= al) bd = 0; else if (k0 < al) bd &= 0xffu << (al - k0);
+        while (bd) {                              // segments that start in this cell
+          const int bit = __ffs(bd) - 1;
+          bd &= bd - 1;
+          const int32_t k = k0 + bit;
+          if (k >= span) break;
+          const uint32_t below = (1u << bit) - 1u;
+          const uint16_t po = (uint16_t)((ex & 0x7ffu) + __popc((r.copy | r.space) & below) + __popc(r.ins & below));
+          const uint16_t ps = (uint16_t)(((ex >> 11) & 0x3ffu) + __popc((r.space | r.ins) & below));
+          const uint16_t pt = (uint16_t)((ex >> 21) + __popc(r.copy & ctm & below));
+          const int i = f3_seg_of(S, ns, k);
+          for (int ii = i; ii >= 0 && S.rel[ii] == k; --ii) { S.sg_o[ii] = po; S.sg_s[ii] = ps; S.sg_t[ii] = pt; }
+        }
+      }
+      __syncthreads();
+      if (wid == 0) {                       // exclusive scans of the step totals (at most 72 steps)
+        int32_t c0 = 0, c1 = 0, c2 = 0;
+        for (int b0 = 0; b0 < nstep; b0 += 32) {
+          const bool in_r = b0 + lane < nstep;
+          int32_t v0 = in_r ? S.st_o[b0 + lane] : 0, v1 = in_r ? S.st_s[b0 + lane] : 0, v2 = in_r ? S.st_t[b0 + lane] : 0;
+          int32_t x0 = v0, x1 = v1, x2 = v2;
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            int32_t y0 = __shfl_up_sync(0xffffffffu, x0, o), y1 = __shfl_up_sync(0xffffffffu, x1, o), y2 = __shfl_up_sync(0xffffffffu, x2, o);
+            if (lane >= o) { x0 += y0; x1 += y1; x2 += y2; }
+          }
+          if (in_r) { S.st_o[b0 + lane] = (uint16_t)(c0 + x0 - v0); S.st_s[b0 + lane] = (uint16_t)(c1 + x1 - v1); S.st_t[b0 + lane] = (uint16_t)(c2 + x2 - v2); }
+          c0 += __shfl_sync(0xffffffffu, x0, 31); c1 += __shfl_sync(0xffffffffu, x1, 31); c2 += __shfl_sync(0xffffffffu, x2, 31);
+        }
+        if (lane == 0) { S.st_o[nstep] = (uint16_t)c0; S.st_s[nstep] = (uint16_t)c1; S.st_t[nstep] = (uint16_t)c2; }
+      }
+      __syncthreads();
+      tot_out = S.st_o[nstep];
+      const int32_t tot_sp = S.st_s[nstep], tot_ct = S.st_t[nstep];
+      for (int i = tid; i <= ns; i += F3_T) {
+        const int32_t k = S.rel[i];
+        if (k >= span) { S.loff[i] = tot_out; S.spb[i] = (uint16_t)tot_sp; S.ctb[i] = (uint16_t)tot_ct; }
+        else { const int s = k >> 8; S.loff[i] = S.st_o[s] + S.sg_o[i]; S.spb[i] = (uint16_t)(S.st_s[s] + S.sg_s[i]); S.ctb[i] = (uint16_t)(S.st_t[s] + S.sg_t[i]); }
+      }
+      __syncthreads();
+      FUSE_PH(3);
+      int32_t myspb = 0;
+      if (tid < ns) {
+        loff = S.loff[tid]; mylen = S.loff[tid + 1] - loff; mykeep = mylen > 0;
+        myspb = S.spb[tid];
+        mynw = mykeep ? (int32_t)S.spb[tid + 1] - myspb + 1 : 0;
+        mychars = mylen - ((int32_t)S.ctb[tid + 1] - (int32_t)S.ctb[tid]);
+      }
+      int32_t d1;
+      f3_scan3(S, lane, wid, mykeep, mynw, 0, &koff, &woff, &d1);
+      tot_kept = S.tot[0]; tot_words = S.tot[1];
+      if (tid < ns) { S.len[tid] = mylen; S.koff[tid] = koff; S.spmin[tid] = 0x7fffffff; }
+      if (wid == 0) {
+        long long gb = fuse_lookback(A.desc_bytes, tile, tot_out, lane);
+        long long kb = fuse_lookback(A.desc_kept, tile, tot_kept, lane);
+        if (lane == 0) { S.gbase = gb; S.kbase = kb; }
+      }
+      __syncthreads();
+      gbase = S.gbase; kbase = S.kbase;
+      FUSE_PH(4);
+      fast_out = tot_out <= F3_OUT_CAP;
+      // ---- D: scatter
+      {
+        uint8_t* dst = fast_out ? S.out : D.C + gbase;
+        for (int st = wid; st < nstep; st += F3_NW) {
+          const int c = (st << 5) + lane;
+          if (c >= ncell) continue;
+          uint32_t cp = c_cp[c], se = c_se[c], in = c_in[c];
+          if (!(cp | se)) continue;
+          int32_t pos = S.st_o[st] + S.pre_o[c];
+          const unsigned long long x = S.y.in64[c];
+#pragma unroll
+          for (int bit = 0; bit < 8; ++bit) {
+            if ((in >> bit) & 1u) dst[pos++] = ' ';
+            if ((cp >> bit) & 1u) dst[pos++] = (uint8_t)(x >> (8 * bit));
+            else if ((se >> bit) & 1u) dst[pos++] = ' ';
+          }
+        }
+      }
+      __syncthreads();
+      if (fast_out) {                        // the cleaned tile leaves shared memory once, coalesced
+        uint8_t* dstg = D.C + gbase;
+        for (int32_t k = tid; k < tot_out; k += F3_T) dstg[k] = S.out[k];
+      }
+      FUSE_PH(5);
+      fast_out = fast_out && tot_words <= F3_WORD_CAP;
+      if (fast_out) {
+        // sorted word list (the raw tile is dead): a word starts at every emitted space and at every segment start
+        for (int st = wid; st < nstep; st += F3_NW) {
+          const int c = (st << 5) + lane;
+          if (c >= ncell) continue;
+          const uint32_t cp = c_cp[c], se = c_se[c], in = c_in[c];
+          uint32_t sm = se | in;
+          if (!sm) continue;
+          const int32_t pbase = S.st_o[st] + S.pre_o[c], sbase = S.st_s[st] + S.pre_s[c];
+          const int32_t k0 = c << 3;
+          while (sm) {
+            const int bit = __ffs(sm) - 1;
+            const uint32_t below = (1u << bit) - 1u;
+            const int i = f3_seg_of(S, ns, k0 + bit);
+            const int32_t pos = pbase + __popc((cp | se) & below) + __popc(in & below);
+            const int32_t w = sbase + __popc((se | in) & below) + S.koff[i] + 1;
+            S.y.w.wstart[w] = (uint16_t)pos; S.y.w.wseg[w] = (uint16_t)i;
+            sm &= sm - 1;
+          }
+        }
+        if (tid < ns && mylen > 0) { const int32_t w = myspb + koff; S.y.w.wstart[w] = (uint16_t)loff; S.y.w.wseg[w] = (uint16_t)tid; }
+        // special-token literals in the cleaned tile
+        for (int32_t x = tid; x < tot_out; x += F3_T) {
+          const uint8_t b = S.out[x];
+          if ((T.sp_first[b >> 6] >> (b & 63)) & 1ULL) {
+            int lo = 0, hi = ns;
+            while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (S.loff[mid] <= x) lo = mid; else hi = mid; }
+            const int32_t end = S.loff[lo] + S.len[lo];
+            for (uint32_t q = 0; q < T.n_sp; ++q) {
+              const uint32_t o = T.sp_off[q], L = T.sp_off[q + 1] - o;
+              if (L == 0 || T.sp_bytes[o] != b || x + (int32_t)L > end) continue;
+              bool eq = true;
+              for (uint32_t j = 1; j < L; ++j) if (S.out[x + j] != T.sp_bytes[o + j]) { eq = false; break; }
+              if (eq) { atomicMin(&S.spmin[lo], (x << 4) | (int32_t)q); break; }
+            }
+          }
+        }
+      }
+    } else {
+      // ================= slow lane: sequential per-segment routines on global memory =================
+      const uint8_t* src = D.text + base;
+      int32_t a = 0, b = 0;
+      if (tid < ns) {
+        a = S.rel[tid]; b = S.rel[tid + 1];
+        TrcCleanOut r = trc_clean_segment<false>(T, src + a, b - a, nullptr);
+        mylen = (int32_t)r.bytes; mychars = (int32_t)r.chars; mykeep = r.bytes > 0;
+      }
+      int32_t d1;
+      f3_scan3(S, lane, wid, mylen, mykeep, 0, &loff, &koff, &d1);
+      tot_out = S.tot[0]; tot_kept = S.tot[1];
+      if (wid == 0) {
+        long long gb = fuse_lookback(A.desc_bytes, tile, tot_out, lane);
+        long long kb = fuse_lookback(A.desc_kept, tile, tot_kept, lane);
+        if (lane == 0) { S.gbase = gb; S.kbase = kb; }
+      }
+      __syncthreads();
+      gbase = S.gbase; kbase = S.kbase;
+      if (tid < ns && mylen > 0) trc_clean_segment<true>(T, src + a, b - a, D.C + gbase + loff);
+    }
+    if (tid < F3_SEGS) S.tok[tid] = 0;
+    __syncthreads();
+    // ---- tokens of " " + cleaned text
+    int32_t mysp = -1;
+    if (fast_out) {
+      FUSE_PH(6);
+      if (tid == 0) S.nslow = 0;
+      __syncthreads();
+      uint16_t* slow = S.z.slow;                 // the masks are dead
+      for (int32_t w = tid; w < tot_words; w += F3_T) {
+        const int seg = S.y.w.wseg[w];
+        const int32_t st = S.y.w.wstart[w];
+        const int32_t sl = S.loff[seg];
+        const int32_t en = (w + 1 < tot_words && S.y.w.wseg[w + 1] == seg) ? (int32_t)S.y.w.wstart[w + 1] : sl + S.len[seg];
+        uint32_t c = 0;
+        if (trc_count_word_fast(T, F, S.out + st, en - st, st == sl ? 1 : 0, &c)) atomicAdd(&S.tok[seg], (int32_t)c);
+        else slow[atomicAdd(&S.nslow, 1)] = (uint16_t)w;
+      }
+      __syncthreads();
+      const int32_t nslow = S.nslow;
+      for (int32_t q = tid; q < nslow; q += F3_T) {
+        const int32_t w = slow[q];
+        const int seg = S.y.w.wseg[w];
+        const int32_t st = S.y.w.wstart[w];
+        const int32_t sl = S.loff[seg];
+        const int32_t en = (w + 1 < tot_words && S.y.w.wseg[w + 1] == seg) ? (int32_t)S.y.w.wstart[w + 1] : sl + S.len[seg];
+        const int vs = st == sl ? 1 : 0;
+        const int64_t j = kbase + S.koff[seg];
+        uint32_t c = trc_count_unit(T, F, byte_id, S.out + st, en - st, vs, [&](int64_t ls, int64_t len) -> uint32_t {
+          unsigned long long slot = atomicAdd(&A.wl_cnt[0], 1ULL);
+          unsigned long long off = atomicAdd(&A.wl_cnt[1], (unsigned long long)len);
+          if ((int64_t)slot < A.wl_cap) { LongEntry e; e.unit = j; e.lstart = ls + (vs ? 0 : (st - sl + 1)); e.len = len; e.scratch_off = (int64_t)off; A.wl[slot] = e; }
+          return 0u;
+        });
+        atomicAdd(&S.tok[seg], (int32_t)c);
+      }
+    } else if (tid < ns && mylen > 0) {
+      const int64_t j = kbase + koff;
+      const uint8_t* p = D.C + gbase + loff;
+      uint32_t c = trc_count_unit(T, F, byte_id, p, mylen, 1, [&](int64_t ls, int64_t len) -> uint32_t {
+        unsigned long long slot = atomicAdd(&A.wl_cnt[0], 1ULL);
+        unsigned long long off = atomicAdd(&A.wl_cnt[1], (unsigned long long)len);
+        if ((int64_t)slot < A.wl_cap) { LongEntry e; e.unit = j; e.lstart = ls; e.len = len; e.scratch_off = (int64_t)off; A.wl[slot] = e; }
+        return 0u;
+      });
+      S.tok[tid] = (int32_t)c;
+      mysp = trc_find_special(T, p, mylen);
+    }
+    __syncthreads();
+    if (fast_out && tid < ns) { const int32_t v = S.spmin[tid]; mysp = v == 0x7fffffff ? -1 : (v & 15); }
+    FUSE_PH(7);
+    // ---- outputs
+    if (tid < ns) {
+      D.cchars[s0 + tid] = mychars;
+      if (mykeep) {
+        const int64_t j = kbase + koff;
+        const int64_t i = s0 + tid;
+        D.k2r[j] = (int32_t)i; D.coff[j] = gbase + loff; D.ctok[j] = (uint32_t)S.tok[tid]; A.seg_special[j] = mysp;
+        int64_t lo = 0, hi = D.n_doc;
+        while (hi - lo > 1) { int64_t mid = (lo + hi) >> 1; if (D.doc_off[mid] <= i) lo = mid; else hi = mid; }
+        D.sdoc[j] = (int32_t)lo;
+      }
+    }
+    if (tid == 0 && s0 + ns == D.n) {
+      D.coff[kbase + tot_kept] = gbase + tot_out;
+      A.totals[0] = kbase + tot_kept; A.totals[1] = gbase + tot_out;
+    }
+    __syncthreads();
+    FUSE_PH(8);
+  }
+}

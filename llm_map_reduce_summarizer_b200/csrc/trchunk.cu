@@ -15,6 +15,7 @@
 #include "trc_format.cuh"
 #include "trc_clean.cuh"
 #include "trc_clean_par.cuh"
+#include "trc_swar.cuh"
 #include "trc_tok.cuh"
 #include "trc_stages.cuh"
 #include "trc_sent.cuh"
@@ -82,6 +83,7 @@ struct trc_ctx {
   TrcDev D{};
   bool have_pre = false, have_chunk = false;
   bool use_fused = true;          // single-pass clean+tokenise kernel (TRCHUNK_NO_FUSED=1 selects the v1 kernels)
+  int fused_gen = 3;              // TRCHUNK_FUSED=2 selects the byte-per-lane kernel, 3 the 8-byte-cell kernel
   int64_t counts[TRC_N_COUNTERS] = {0};
   int64_t* h_pin = nullptr;        // pinned scratch for small D2H reads (64 int64)
   int64_t launches = 0;
@@ -279,6 +281,53 @@ static void hostsim_clean_par_count(TrcDev D, TrcTables T, int32_t* keep, uint8_
     D.clen[i] = len; D.cchars[i] = chars; keep[i] = len > 0;
   }
 }
+// The 8-byte-cell (SWAR) formulation, whole batch as one tile: validates the bit logic of trc_swar.cuh.
+static void hostsim_clean_swar(TrcDev D, TrcTables T, int32_t* keep, uint8_t* code, int64_t braw) {
+  const int32_t nb = (int32_t)braw, ncell = (nb + 7) / 8 + 1;
+  std::vector<uint8_t> buf(8 * (size_t)ncell + 8, 0), arr(8 * (size_t)ncell + 64, 0), leadv(ncell, 0);
+  if (nb) memcpy(buf.data(), D.text, nb);
+  SwMasks M; M.ncell = ncell;
+  M.sp = arr.data(); M.w = M.sp + ncell + 4; M.ct = M.w + ncell + 4; M.lt = M.ct + ncell + 4; M.ep = M.lt + ncell + 4;
+  M.bd = M.ep + ncell + 4; M.drop = M.bd + ncell + 4; M.ds = M.drop + ncell + 4;
+  for (int64_t i = 0; i < D.n; ++i) if (D.seg_off[i + 1] > D.seg_off[i]) sw_or_bit(M.bd, (int32_t)D.seg_off[i]);
+  for (int32_t c = 0; c < ncell; ++c) {
+    uint64_t x; memcpy(&x, buf.data() + 8 * (size_t)c, 8);
+    SwCell cl = sw_classify(x);
+    M.sp[c] = (uint8_t)cl.sp; M.w[c] = (uint8_t)cl.w; M.ct[c] = (uint8_t)cl.ct; M.lt[c] = (uint8_t)cl.lt; M.ep[c] = (uint8_t)cl.ep;
+    leadv[c] = (uint8_t)cl.lead;
+  }
+  for (int32_t c = 0; c < ncell; ++c) if (leadv[c]) sw_fix_multibyte(T, buf.data(), M, c, leadv[c], nb);
+  int64_t seg = 0;
+  for (int32_t c = 0; c < ncell; ++c) {
+    uint32_t cand = sw_dup_candidates(M, c, 0xffu);
+    while (cand) {
+      int bit = 0; while (!((cand >> bit) & 1u)) ++bit;
+      cand &= cand - 1;
+      int32_t k = c * 8 + bit;
+      if (k >= nb) continue;
+      while (seg + 1 < D.n && D.seg_off[seg + 1] <= k) ++seg;
+      sw_mark_dup(buf.data(), M, k, (int32_t)D.seg_off[seg], (int32_t)D.seg_off[seg + 1]);
+    }
+  }
+  for (int32_t c = 0; c < ncell; ++c) {
+    SwCodes r = sw_cell_codes(buf.data(), M, c, 0, nb);
+    for (int bit = 0; bit < 8; ++bit) {
+      int32_t k = c * 8 + bit;
+      if (k >= nb) break;
+      code[k] = ((r.ins >> bit) & 1u) ? 3 : (((r.space >> bit) & 1u) ? 2 : (((r.copy >> bit) & 1u) ? 1 : 0));
+    }
+  }
+  for (int64_t i = 0; i < D.n; ++i) {
+    int64_t len = 0; int32_t chars = 0;
+    for (int64_t k = D.seg_off[i]; k < D.seg_off[i + 1]; ++k) {
+      uint8_t r = code[k];
+      len += cp_outlen(r);
+      chars += (r == 3) ? 2 : ((r == 2 || (r == 1 && (D.text[k] & 0xC0) != 0x80)) ? 1 : 0);
+    }
+    D.clen[i] = len; D.cchars[i] = chars; keep[i] = len > 0;
+  }
+}
+
 static void hostsim_clean_par_write(TrcDev D, const uint8_t* code) {
   for (int64_t j = 0; j < D.n_kept; ++j) {
     int32_t r = D.k2r[j];
@@ -414,6 +463,7 @@ __global__ void __launch_bounds__(LONG_T) k_bpe_long(TrcTables T, const uint32_t
 #endif
 #ifndef TRC_HOSTSIM
 #include "trc_fused.cuh"
+#include "trc_fused3.cuh"
 #endif
 
 __global__ void k_special_docs(TrcDev D, const int32_t* __restrict__ seg_special, const int32_t* __restrict__ spk_special) {
@@ -680,6 +730,7 @@ extern "C" int trc_create(int device, trc_ctx** out) {
       cudaMallocHost(&ctx->h_pin, 64 * sizeof(int64_t)) != cudaSuccess) { delete ctx; return TRC_ECUDA; }
   for (int k = 0; k < 4; ++k) cudaEventCreate(&ctx->ev[k]);
   { const char* e = getenv("TRCHUNK_NO_FUSED"); ctx->use_fused = !(e && e[0] == '1'); }
+  { const char* e = getenv("TRCHUNK_FUSED"); if (e && e[0] == '2') ctx->fused_gen = 2; }
   *out = ctx;
   return TRC_OK;
 }
@@ -895,11 +946,17 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       static bool attr_done[64] = {false};
       if (!attr_done[ctx->device & 63]) {
         CK(cudaFuncSetAttribute(k_clean_tok_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FuseSmem)));
+        CK(cudaFuncSetAttribute(k_clean_tok_fused3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(F3Smem)));
         attr_done[ctx->device & 63] = true;
       }
       int blocks = (int)(ntiles < 148 * 2 ? ntiles : 148 * 2);
-      prof_begin(ctx, st, "k_clean_tok_fused");
-      k_clean_tok_fused<<<blocks, FUSE_T, sizeof(FuseSmem), st>>>(D, ctx->T, ctx->d_byte_id, A, ntiles);
+      if (ctx->fused_gen >= 3) {
+        prof_begin(ctx, st, "k_clean_tok_fused3");
+        k_clean_tok_fused3<<<blocks, F3_T, sizeof(F3Smem), st>>>(D, ctx->T, ctx->d_byte_id, A, ntiles);
+      } else {
+        prof_begin(ctx, st, "k_clean_tok_fused");
+        k_clean_tok_fused<<<blocks, FUSE_T, sizeof(FuseSmem), st>>>(D, ctx->T, ctx->d_byte_id, A, ntiles);
+      }
       prof_end(ctx, st);
       ctx->launches++;
       CK(cudaGetLastError());
@@ -939,10 +996,12 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
 #ifdef TRC_HOSTSIM
   uint8_t* hs_cls = nullptr; uint8_t* hs_code = nullptr;
   const char* hs_seq = getenv("TRCHUNK_HOSTSIM_SEQ");
-  const bool hs_par = !(hs_seq && hs_seq[0] == '1');
+  const char* hs_mode = getenv("TRCHUNK_HOSTSIM_CLEAN");          // "swar" (default) | "par" | "seq"
+  const bool hs_par = !(hs_seq && hs_seq[0] == '1') && !(hs_mode && hs_mode[0] == 's' && hs_mode[1] == 'e');
   if (hs_par) {
     ALLOC(hs_cls, uint8_t, braw); ALLOC(hs_code, uint8_t, braw);
-    hostsim_clean_par_count(D, ctx->T, keep, hs_cls, hs_code);
+    if (hs_mode && hs_mode[0] == 'p') hostsim_clean_par_count(D, ctx->T, keep, hs_cls, hs_code);
+    else hostsim_clean_swar(D, ctx->T, keep, hs_code, braw);
   } else
 #endif
   LAUNCH(k_clean_count, n, 128, D, ctx->T, keep);
