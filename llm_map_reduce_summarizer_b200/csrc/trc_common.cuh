@@ -57,6 +57,7 @@ struct TrcTables {
   const uint64_t* tok16; uint32_t tok16_mask;   // pairs (lo, hi); empty = (0,0)
   const uint64_t* hot8_src; uint32_t hot8_size; // direct-mapped image of the lowest-rank <=8-byte tokens (kernels copy it to smem)
   uint64_t sp_first[4];         // bitmap of first bytes of the special-token literals
+  uint32_t sp_single;           // the one ASCII byte every special literal starts with, or 0x100
 };
 
 TRC_HD uint64_t trc_mix64(uint64_t x);
@@ -73,6 +74,18 @@ TRC_HD uint32_t trc_key8_slot(uint64_t key, uint32_t mask) {   // cheap 32-bit m
   uint32_t x = (uint32_t)key ^ ((uint32_t)(key >> 32) * 0x9E3779B1u);
   x *= 0x85EBCA6Bu; x ^= x >> 15; x *= 0xC2B2AE35u; x ^= x >> 13;
   return x & mask;
+}
+
+TRC_HD uint32_t trc_ctz32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+  return (uint32_t)(__ffs((int)x) - 1);
+#else
+  return (uint32_t)__builtin_ctz(x);
+#endif
+}
+// bit 7 of each byte of (a, b) -> 16-bit mask (a = bytes 0..7)
+TRC_HD uint32_t sw_pack16(uint64_t a, uint64_t b) {
+  return (uint32_t)(((a >> 7) * 0x0102040810204080ULL) >> 56) | ((uint32_t)(((b >> 7) * 0x0102040810204080ULL) >> 56) << 8);
 }
 
 // ---- UTF-8 (input is produced by Python's str.encode('utf-8'): always well formed) -----------------

@@ -44,6 +44,8 @@ struct FuseSmem {
 };
 static_assert(sizeof(FuseSmem) <= 115200, "two CTAs per SM");
 
+struct SlowWord { int64_t pos; int32_t len_vs; int32_t unit; };   // byte offset in the cleaned text, length | vs << 31, kept segment
+
 struct FuseArgs {
   unsigned long long* tile_counter;
   unsigned long long* desc_bytes;   // look-back descriptors, one per tile
@@ -53,6 +55,7 @@ struct FuseArgs {
   int32_t* seg_special;
   LongEntry* wl; unsigned long long* wl_cnt; int64_t wl_cap;
   unsigned long long* phase;        // optional: cycles per phase summed over CTAs (diagnostics, TRCHUNK_PHASES=1)
+  SlowWord* sl; unsigned long long* sl_cnt; int64_t sl_cap;   // words left to the generic matcher (k_count_slow_words)
 };
 #define FUSE_PH(i) do { if (A.phase && tid == 0) { long long now_ = clock64(); atomicAdd(&A.phase[i], (unsigned long long)(now_ - ph_t)); ph_t = now_; } } while (0)
 
@@ -60,6 +63,34 @@ __device__ __forceinline__ long long fuse_lookback(unsigned long long* d, unsign
   long long excl = 0;
   if (tile == 0) { if (lane == 0) st_relaxed(&d[0], (2ULL << 62) | (unsigned long long)aggregate); return 0; }
   if (lane == 0) st_relaxed(&d[tile], (1ULL << 62) | (unsigned long long)aggregate);
+  long long idx = (long long)tile - 1;
+  for (;;) {
+    long long my = idx - lane;
+    unsigned long long dv = (2ULL << 62);
+    if (my >= 0) { dv = ld_relaxed(&d[my]); while ((dv >> 62) == 0) dv = ld_relaxed(&d[my]); }
+    unsigned st = (unsigned)(dv >> 62);
+    long long val = (long long)(dv & ((1ULL << 62) - 1));
+    unsigned ball = __ballot_sync(0xffffffffu, st == 2);
+    int first = ball ? __ffs(ball) - 1 : 31;
+    long long c = lane <= first ? val : 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    excl += c;
+    if (ball) break;
+    idx -= 32;
+  }
+  if (lane == 0) st_relaxed(&d[tile], (2ULL << 62) | (unsigned long long)(excl + aggregate));
+  return excl;
+}
+
+// The same protocol in two halves: publish the aggregate as soon as it is known, resolve the exclusive
+// prefix only when it is needed (by then the predecessors have long published theirs).
+__device__ __forceinline__ void fuse_publish(unsigned long long* d, unsigned tile, long long aggregate) {
+  st_relaxed(&d[tile], ((tile == 0 ? 2ULL : 1ULL) << 62) | (unsigned long long)aggregate);
+}
+__device__ __forceinline__ long long fuse_resolve(unsigned long long* d, unsigned tile, long long aggregate, int lane) {
+  if (tile == 0) return 0;
+  long long excl = 0;
   long long idx = (long long)tile - 1;
   for (;;) {
     long long my = idx - lane;
@@ -442,5 +473,27 @@ __global__ void k_doc_ranges(const int32_t* __restrict__ sdoc, int64_t n_kept, i
     int64_t lo = 0, hi = n_kept;
     while (lo < hi) { int64_t mid = (lo + hi) >> 1; if (sdoc[mid] < x) lo = mid + 1; else hi = mid; }
     kdoc_off[x] = lo;
+  }
+}
+
+
+// Words the fused kernel could not decide with its fast paths (non-ASCII, spans that need byte-pair merging):
+// one thread per word with the generic matcher, at full occupancy instead of a few lanes of a busy CTA.
+__global__ void k_count_slow_words(TrcDev D, TrcTables T, const uint32_t* __restrict__ byte_id, const SlowWord* __restrict__ sl, int64_t n,
+                                   LongEntry* wl, unsigned long long* wl_cnt, int64_t wl_cap) {
+  const TrcFast F = trc_fast_default(T);
+  GSTRIDE(q, n) {
+    const SlowWord w = sl[q];
+    const int vs = (int)((uint32_t)w.len_vs >> 31);
+    const int64_t len = w.len_vs & 0x7fffffff;
+    const int64_t j = w.unit;
+    const int64_t rel = w.pos - D.coff[j];
+    uint32_t c = trc_count_unit(T, F, byte_id, D.C + w.pos, len, vs, [&](int64_t ls, int64_t slen) -> uint32_t {
+      unsigned long long slot = atomicAdd(&wl_cnt[0], 1ULL);
+      unsigned long long off = atomicAdd(&wl_cnt[1], (unsigned long long)slen);
+      if ((int64_t)slot < wl_cap) { LongEntry e; e.unit = j; e.lstart = ls + (vs ? 0 : rel + 1); e.len = slen; e.scratch_off = (int64_t)off; wl[slot] = e; }
+      return 0u;
+    });
+    atomicAdd(&D.ctok[j], c);
   }
 }

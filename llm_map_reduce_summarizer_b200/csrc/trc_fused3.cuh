@@ -27,7 +27,7 @@ struct F3Smem {
     uint8_t m[F3_MASKS][F3_MSTRIDE];
     uint16_t slow[F3_WORD_CAP];
   } z;
-  uint8_t out[F3_OUT_CAP];
+  alignas(16) uint8_t out[F3_OUT_CAP + 32];
   uint64_t hot8[TRC_HOT8];
   uint16_t cand[F3_CAND_CAP];
   uint16_t pre_o[F3_NCELL + 32], pre_s[F3_NCELL + 32];   // per cell: output bytes / spaces before it, inside its step
@@ -40,9 +40,9 @@ struct F3Smem {
   int32_t len[F3_SEGS], koff[F3_SEGS], tok[F3_SEGS], spmin[F3_SEGS];
   int32_t wsum[3][F3_NW];
   int32_t tot[3];
-  int32_t ncand, nslow;
+  int32_t ncand, nslow, has_sp;
   unsigned int tile;
-  long long gbase, kbase;
+  long long gbase, kbase, slbase;
 };
 static_assert(sizeof(F3Smem) <= 115200, "two CTAs per SM");
 
@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
         *reinterpret_cast<int4*>(&S.y.in[k]) = v;
       }
       for (int k = tid; k < (F3_MSTRIDE * 3) / 4; k += F3_T) reinterpret_cast<uint32_t*>(S.z.m[5])[k] = 0u;   // bd, drop, ds
-      if (tid == 0) S.ncand = 0;
+      if (tid == 0) { S.ncand = 0; S.has_sp = T.sp_single < 0x100u ? 0 : 1; }
       __syncthreads();
       FUSE_PH(0);
       if (tid < ns) {
@@ -137,7 +137,12 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
       // ---- A: ASCII classes of every cell
       for (int st = wid; st < nstep; st += F3_NW) {
         const int c = (st << 5) + lane;
-        const SwCell cl = sw_classify(S.y.in64[c]);
+        const unsigned long long xx = S.y.in64[c];
+        const SwCell cl = sw_classify(xx);
+        if (T.sp_single < 0x100u) {
+          const uint64_t tt = (xx & ~SW_H) | SW_H;
+          if (sw_ge(tt, T.sp_single) & ~sw_ge(tt, T.sp_single + 1) & ~(xx & SW_H)) S.has_sp = 1;
+        }
         M.sp[c] = (uint8_t)cl.sp; M.w[c] = (uint8_t)cl.w; M.ct[c] = (uint8_t)cl.ct; M.lt[c] = (uint8_t)cl.lt; M.ep[c] = (uint8_t)cl.ep;
         mlead[c] = (uint8_t)cl.lead;
       }
@@ -268,15 +273,19 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
       f3_scan3(S, lane, wid, mykeep, mynw, 0, &koff, &woff, &d1);
       tot_kept = S.tot[0]; tot_words = S.tot[1];
       if (tid < ns) { S.len[tid] = mylen; S.koff[tid] = koff; S.spmin[tid] = 0x7fffffff; }
-      if (wid == 0) {
-        long long gb = fuse_lookback(A.desc_bytes, tile, tot_out, lane);
-        long long kb = fuse_lookback(A.desc_kept, tile, tot_kept, lane);
-        if (lane == 0) { S.gbase = gb; S.kbase = kb; }
-      }
-      __syncthreads();
-      gbase = S.gbase; kbase = S.kbase;
-      FUSE_PH(4);
       fast_out = tot_out <= F3_OUT_CAP;
+      if (tid == 0) { fuse_publish(A.desc_bytes, tile, tot_out); fuse_publish(A.desc_kept, tile, tot_kept); }
+      if (!fast_out) {                        // scatter straight to global memory needs the offsets now
+        if (wid == 0) {
+          long long gb = fuse_resolve(A.desc_bytes, tile, tot_out, lane);
+          long long kb = fuse_resolve(A.desc_kept, tile, tot_kept, lane);
+          if (lane == 0) { S.gbase = gb; S.kbase = kb; }
+        }
+        __syncthreads();
+        gbase = S.gbase; kbase = S.kbase;
+      }
+      const bool resolved_early = !fast_out;
+      FUSE_PH(4);
       // ---- D: scatter
       {
         uint8_t* dst = fast_out ? S.out : D.C + gbase;
@@ -296,12 +305,21 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
         }
       }
       __syncthreads();
-      if (fast_out) {                        // the cleaned tile leaves shared memory once, coalesced
+      FUSE_PH(5);
+      const bool out_in_smem = fast_out;
+      fast_out = fast_out && tot_words <= F3_WORD_CAP;
+      if (out_in_smem && !fast_out) {         // too many words for the list: resolve now, write the tile out, count per segment
+        if (wid == 0) {
+          long long gb = fuse_resolve(A.desc_bytes, tile, tot_out, lane);
+          long long kb = fuse_resolve(A.desc_kept, tile, tot_kept, lane);
+          if (lane == 0) { S.gbase = gb; S.kbase = kb; }
+        }
+        __syncthreads();
+        gbase = S.gbase; kbase = S.kbase;
         uint8_t* dstg = D.C + gbase;
         for (int32_t k = tid; k < tot_out; k += F3_T) dstg[k] = S.out[k];
       }
-      FUSE_PH(5);
-      fast_out = fast_out && tot_words <= F3_WORD_CAP;
+      (void)resolved_early;
       if (fast_out) {
         // sorted word list (the raw tile is dead): a word starts at every emitted space and at every segment start
         for (int st = wid; st < nstep; st += F3_NW) {
@@ -323,8 +341,8 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
           }
         }
         if (tid < ns && mylen > 0) { const int32_t w = myspb + koff; S.y.w.wstart[w] = (uint16_t)loff; S.y.w.wseg[w] = (uint16_t)tid; }
-        // special-token literals in the cleaned tile
-        for (int32_t x = tid; x < tot_out; x += F3_T) {
+        // special-token literals in the cleaned tile (skipped when no byte can start one)
+        if (S.has_sp) for (int32_t x = tid; x < tot_out; x += F3_T) {
           const uint8_t b = S.out[x];
           if ((T.sp_first[b >> 6] >> (b & 63)) & 1ULL) {
             int lo = 0, hi = ns;
@@ -376,11 +394,45 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
         const int32_t sl = S.loff[seg];
         const int32_t en = (w + 1 < tot_words && S.y.w.wseg[w + 1] == seg) ? (int32_t)S.y.w.wstart[w + 1] : sl + S.len[seg];
         uint32_t c = 0;
-        if (trc_count_word_fast(T, F, S.out + st, en - st, st == sl ? 1 : 0, &c)) atomicAdd(&S.tok[seg], (int32_t)c);
+        const int vs = st == sl ? 1 : 0, n = en - st, Lw = n + vs;
+        bool done = false;
+        if (Lw <= 16) {
+          const uint32_t* p32 = reinterpret_cast<const uint32_t*>(S.out + (st & ~3));
+          const unsigned sh = (unsigned)(st & 3) * 8u;
+          const uint32_t w0 = p32[0], w1 = p32[1], w2 = p32[2], w3 = p32[3], w4 = p32[4];
+          uint64_t lo = (uint64_t)__funnelshift_r(w0, w1, sh) | ((uint64_t)__funnelshift_r(w1, w2, sh) << 32);
+          uint64_t hi = (uint64_t)__funnelshift_r(w2, w3, sh) | ((uint64_t)__funnelshift_r(w3, w4, sh) << 32);
+          if (vs) { hi = (hi << 8) | (lo >> 56); lo = (lo << 8) | (uint64_t)' '; }
+          if (Lw < 8) { lo &= (1ULL << (8 * Lw)) - 1; hi = 0; } else if (Lw == 8) hi = 0; else if (Lw < 16) hi &= (1ULL << (8 * (Lw - 8))) - 1;
+          done = trc_count_word16(T, F, lo, hi, Lw, &c);
+        }
+        if (!done) done = trc_count_word_fast(T, F, S.out + st, n, vs, &c);
+        if (done) atomicAdd(&S.tok[seg], (int32_t)c);
         else slow[atomicAdd(&S.nslow, 1)] = (uint16_t)w;
       }
       __syncthreads();
+      FUSE_PH(9);
+      // the global offsets are needed from here on (long-span work list, outputs): predecessors published long ago
+      if (wid == 0) {
+        long long gb = fuse_resolve(A.desc_bytes, tile, tot_out, lane);
+        long long kb = fuse_resolve(A.desc_kept, tile, tot_kept, lane);
+        if (lane == 0) { S.gbase = gb; S.kbase = kb; }
+      }
+      __syncthreads();
+      gbase = S.gbase; kbase = S.kbase;
+      {                                        // the cleaned tile leaves shared memory once, coalesced
+        uint8_t* dstg = D.C + gbase;
+        for (int32_t k = tid; k < tot_out; k += F3_T) dstg[k] = S.out[k];
+      }
+      FUSE_PH(10);
       const int32_t nslow = S.nslow;
+      // words for the generic matcher: handed to k_count_slow_words (full occupancy) unless its list is full
+      if (tid == 0) {
+        unsigned long long b0 = nslow ? atomicAdd(A.sl_cnt, (unsigned long long)nslow) : 0ULL;
+        S.slbase = ((int64_t)b0 + nslow <= A.sl_cap) ? (long long)b0 : -1LL;
+      }
+      __syncthreads();
+      const long long slbase = S.slbase;
       for (int32_t q = tid; q < nslow; q += F3_T) {
         const int32_t w = slow[q];
         const int seg = S.y.w.wseg[w];
@@ -389,6 +441,11 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
         const int32_t en = (w + 1 < tot_words && S.y.w.wseg[w + 1] == seg) ? (int32_t)S.y.w.wstart[w + 1] : sl + S.len[seg];
         const int vs = st == sl ? 1 : 0;
         const int64_t j = kbase + S.koff[seg];
+        if (slbase >= 0) {
+          SlowWord e; e.pos = gbase + st; e.len_vs = (en - st) | (vs << 31); e.unit = (int32_t)j;
+          A.sl[slbase + q] = e;
+          continue;
+        }
         uint32_t c = trc_count_unit(T, F, byte_id, S.out + st, en - st, vs, [&](int64_t ls, int64_t len) -> uint32_t {
           unsigned long long slot = atomicAdd(&A.wl_cnt[0], 1ULL);
           unsigned long long off = atomicAdd(&A.wl_cnt[1], (unsigned long long)len);

@@ -114,7 +114,7 @@ TRC_HD bool trc_is_token(const TrcTables& T, const TrcFast& F, const TrcStr& S, 
     }
     if (!nul) {
       if (n <= 8) {
-        if (F.hot8 && F.hot8[trc_key8_slot(lo, F.hot8_mask)] == lo) return true;
+        if (F.hot8) { const uint32_t hs = trc_key8_slot(lo, F.hot8_mask); if (F.hot8[hs] == lo || F.hot8[hs ^ 1] == lo) return true; }
         uint32_t slot = trc_key8_slot(lo, T.tok8_mask);
         for (;;) {
           uint64_t e = T.tok8[slot];
@@ -191,6 +191,100 @@ TRC_HD int trc_find_special(const TrcTables& T, const uint8_t* p, int64_t n) {
   return -1;
 }
 
+// ---- whole-word fast path on 16 packed bytes --------------------------------------------------------------
+// A "word" here is a space (real or virtual) followed by non-space bytes, at most 16 bytes in total, given
+// as two little-endian 64-bit words (zero padded).  Handles the shapes that make up ordinary cleaned text:
+//   ' ' letters                      -> one span (alt 2)
+//   ' ' letters + one ASCII "other"  -> alt 2 + alt 4 of length 1 (trailing , . ? ! ; : ' ...)
+//   ' ' letters + contraction        -> alt 2 + alt 1 ('s 't 'm 'd 'll 've 're, any case)
+// Letter spans must be vocabulary entries (exact-key sets); anything else returns false and the caller
+// uses the generic matcher.  Exact: every decision is the regex's decision for these shapes.
+TRC_HD uint64_t trc_swar_letters(uint64_t x) {          // bit 7 of every byte that is an ASCII letter
+  const uint64_t H = 0x8080808080808080ULL, L = 0x0101010101010101ULL;
+  const uint64_t t = ((x | 0x2020202020202020ULL) & ~H) | H;   // lower-cased, high bit forced
+  const uint64_t ge_a = (t - L * 0x61) & H, ge_z1 = (t - L * 0x7b) & H;
+  return ge_a & ~ge_z1 & ~(x & H);
+}
+
+TRC_HD bool trc_key_is_token(const TrcTables& T, const TrcFast& F, uint64_t lo, uint64_t hi, int n) {
+  if (n <= 8) {
+    if (F.hot8) { const uint32_t hs = trc_key8_slot(lo, F.hot8_mask); if (F.hot8[hs] == lo || F.hot8[hs ^ 1] == lo) return true; }
+    uint32_t slot = trc_key8_slot(lo, T.tok8_mask);
+    for (;;) { uint64_t e = T.tok8[slot]; if (e == lo) return true; if (e == 0) return false; slot = (slot + 1) & T.tok8_mask; }
+  }
+  uint32_t slot = trc_key8_slot(lo ^ (hi * 0x9E3779B97F4A7C15ULL), T.tok16_mask);
+  for (;;) {
+    uint64_t e0 = T.tok16[2 * (size_t)slot], e1 = T.tok16[2 * (size_t)slot + 1];
+    if (e0 == lo && e1 == hi) return true;
+    if (e0 == 0 && e1 == 0) return false;
+    slot = (slot + 1) & T.tok16_mask;
+  }
+}
+
+// byte i of the 16 packed bytes
+TRC_HD uint8_t trc_b16(uint64_t lo, uint64_t hi, int i) { return i < 8 ? (uint8_t)(lo >> (8 * i)) : (uint8_t)(hi >> (8 * (i - 8))); }
+// bytes [a, a+n) of the 16 packed bytes as a zero-padded key (n <= 16)
+TRC_HD void trc_sub16(uint64_t lo, uint64_t hi, int a, int n, uint64_t* klo, uint64_t* khi) {
+  uint64_t l = lo, h = hi;
+  if (a >= 8) { l = hi >> (8 * (a - 8)); h = 0; }
+  else if (a > 0) { l = (lo >> (8 * a)) | (hi << (8 * (8 - a))); h = hi >> (8 * a); }
+  if (n < 8) { l &= (1ULL << (8 * n)) - 1; h = 0; } else if (n == 8) h = 0; else if (n < 16) h &= (1ULL << (8 * (n - 8))) - 1;
+  *klo = l; *khi = h;
+}
+
+// Tokens of an all-ASCII word of at most 16 bytes whose first byte is the space that precedes it: the
+// regex alternatives 1-4 evaluated on class bit masks (letters / digits / other), one vocabulary probe
+// per span.  Returns false (caller falls back to the generic matcher) when a byte is not ASCII, a
+// whitespace or control-class byte appears inside the word, or a multi-byte span is not a vocabulary
+// entry (it then needs byte-pair merging).
+TRC_HD bool trc_count_word16(const TrcTables& T, const TrcFast& F, uint64_t lo, uint64_t hi, int n, uint32_t* count) {
+  if (n < 2 || n > 16 || (lo & 0xff) != ' ') return false;
+  const uint64_t H = 0x8080808080808080ULL, L = 0x0101010101010101ULL;
+  if ((lo | hi) & H) return false;                                         // non-ASCII byte
+  const uint32_t all = (n == 16) ? 0xffffu : ((1u << n) - 1u);
+  const uint32_t lm = sw_pack16(trc_swar_letters(lo), trc_swar_letters(hi)) & all;
+  const uint64_t tl = lo | H, th = hi | H;
+  const uint32_t dm = sw_pack16(((tl - L * 0x30) & H) & ~((tl - L * 0x3a) & H), ((th - L * 0x30) & H) & ~((th - L * 0x3a) & H)) & all;
+  const uint32_t ctl = sw_pack16(~((tl - L * 0x21) & H) & H, ~((th - L * 0x21) & H) & H) & all & ~1u;   // bytes < 0x21 after the space
+  if (ctl) return false;
+  if (sw_pack16(~((tl - L * 0x7f) & H) & H, ~((th - L * 0x7f) & H) & H) != 0xffffu) return false;         // DEL
+  uint32_t total = 0;
+  int p = 0;
+  while (p < n) {
+    const uint32_t rest_l = lm >> p, rest_d = dm >> p;
+    int len;
+    const uint8_t c0 = trc_b16(lo, hi, p);
+    if (rest_l & 1u) {                                                     // alt 2: letters
+      len = (int)trc_ctz32(~rest_l);
+    } else if (c0 == '\'' && p + 1 < n && (rest_l & 2u)) {                 // alt 1 before alt 2
+      const uint8_t a1 = trc_b16(lo, hi, p + 1) | 0x20, a2 = (p + 2 < n) ? (uint8_t)(trc_b16(lo, hi, p + 2) | 0x20) : 0;
+      if (a1 == 's' || a1 == 't' || a1 == 'm' || a1 == 'd') len = 2;
+      else if ((a1 == 'l' && a2 == 'l') || (a1 == 'v' && a2 == 'e') || (a1 == 'r' && a2 == 'e')) len = ((lm >> (p + 2)) & 1u) ? 3 : 0;
+      else len = 0;
+      if (len == 0) len = 1 + (int)trc_ctz32(~(rest_l >> 1));              // alt 2: "'" + letters
+    } else if (rest_d & 1u) {                                              // alt 3: up to three digits
+      len = (int)trc_ctz32(~rest_d); if (len > 3) len = 3;
+    } else if (rest_l & 2u) {                                              // alt 2: one other byte (or the space) + letters
+      len = 1 + (int)trc_ctz32(~(rest_l >> 1));
+    } else {                                                               // alt 4: [space] other+   /  alt 7: lone space
+      const uint32_t om = ~(lm | dm) & all;                                // other bytes (the space at 0 is handled by q)
+      int q = p;
+      if (p == 0) { if (n > 1 && ((om >> 1) & 1u)) q = 1; else { total += 1; p = 1; continue; } }   // ' ' + other, or ' ' alone (before a digit)
+      len = (q - p) + (int)trc_ctz32(~(om >> q));
+    }
+    if (len == 1) total += 1;
+    else {
+      uint64_t kl, kh;
+      trc_sub16(lo, hi, p, len, &kl, &kh);
+      if (!trc_key_is_token(T, F, kl, kh, len)) return false;
+      total += 1;
+    }
+    p += len;
+  }
+  *count = total;
+  return true;
+}
+
 // Fast paths for the three span shapes that make up ordinary text (all ASCII, exact).  Returns the end
 // of the span that starts at q and adds its token count to *total, or -1 when the generic matcher must
 // decide.  With MERGE=false a short letter span that is not a vocabulary entry also returns -1 (the
@@ -212,7 +306,8 @@ TRC_HD int64_t trc_fast_span(const TrcTables& T, const TrcFast& F, const uint32_
     if (nlet >= 1 && k <= 8 && (!more || b < 0x80)) {
       bool hit = k == 1;
       if (!hit) {
-        if (F.hot8 && F.hot8[trc_key8_slot(key, F.hot8_mask)] == key) hit = true;
+        uint32_t hs_ = F.hot8 ? trc_key8_slot(key, F.hot8_mask) : 0u;
+        if (F.hot8 && (F.hot8[hs_] == key || F.hot8[hs_ ^ 1] == key)) hit = true;
         else {
           uint32_t slot = trc_key8_slot(key, T.tok8_mask);
           for (;;) { uint64_t e8 = T.tok8[slot]; if (e8 == key) { hit = true; break; } if (e8 == 0) break; slot = (slot + 1) & T.tok8_mask; }
@@ -265,6 +360,18 @@ TRC_HD uint32_t trc_count_unit(const TrcTables& T, const TrcFast& F, const uint3
   uint32_t total = 0;
   int64_t q = 0;
   while (q < S.n) {
+    if (S.at(q) == ' ') {                                    // whole-word fast path (also the fused kernel's)
+      uint64_t lo = ' ', hi = 0; int k = 1; bool fits = true;
+      while (q + k < S.n) {
+        const uint8_t b = S.at(q + k);
+        if (b == ' ') break;
+        if (k >= 16) { fits = false; break; }
+        if (k < 8) lo |= (uint64_t)b << (8 * k); else hi |= (uint64_t)b << (8 * (k - 8));
+        ++k;
+      }
+      uint32_t c = 0;
+      if (fits && trc_count_word16(T, F, lo, hi, k, &c)) { total += c; q += k; continue; }
+    }
     {
       int64_t nq = trc_fast_span<true>(T, F, byte_id, S, q, &total);
       if (nq >= 0) { q = nq; continue; }

@@ -120,8 +120,12 @@ static inline std::string trc_build_host_vocab(const uint8_t* token_bytes, const
       uint32_t slot = trc_key8_slot(k, s8 - 1);
       while (V.tok8[slot] != 0) slot = (slot + 1) & (s8 - 1);
       V.tok8[slot] = k;
-      uint32_t hs = trc_key8_slot(k, HOT - 1);
-      if (V.hot8[hs] == 0) V.hot8[hs] = k;
+      // hot set: word-shaped keys only (space or letter first), lowest rank first, two candidate slots
+      const uint8_t f0 = (uint8_t)k;
+      if (f0 == ' ' || ((f0 | 0x20) >= 'a' && (f0 | 0x20) <= 'z')) {
+        uint32_t hs = trc_key8_slot(k, HOT - 1);
+        if (V.hot8[hs] == 0) V.hot8[hs] = k; else if (V.hot8[hs ^ 1] == 0) V.hot8[hs ^ 1] = k;
+      }
     }
     for (auto& k : k16) {
       uint32_t slot = trc_key8_slot(k.first ^ (k.second * 0x9E3779B97F4A7C15ULL), s16 - 1);

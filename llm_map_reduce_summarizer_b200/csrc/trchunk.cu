@@ -804,6 +804,11 @@ extern "C" int trc_load_vocab(trc_ctx* ctx, const uint8_t* token_bytes, const in
   ctx->T.tok8_mask = (uint32_t)V.tok8.size() - 1; ctx->T.tok16_mask = (uint32_t)(V.tok16.size() / 2) - 1;
   ctx->T.hot8_size = (uint32_t)V.hot8.size();
   for (int k = 0; k < 4; ++k) ctx->T.sp_first[k] = V.sp_first[k];
+  {
+    int nset = 0, which = 0x100;
+    for (int b = 0; b < 256; ++b) if ((V.sp_first[b >> 6] >> (b & 63)) & 1ULL) { ++nset; which = b; }
+    ctx->T.sp_single = (nset == 1 && which >= 1 && which < 0x7f) ? (uint32_t)which : 0x100u;
+  }
   ctx->d_byte_id = (uint32_t*)byte_id;
   ctx->T.n_tok = V.n_tok; ctx->T.n_sp = V.n_sp;
   ctx->T.tokhash_mask = (uint32_t)V.tokhash.size() - 1;
@@ -935,14 +940,16 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       const int64_t ntiles = (n + FUSE_SEGS - 1) / FUSE_SEGS;
       FuseArgs A;
       unsigned long long* fz;
-      ALLOC(fz, unsigned long long, 2 * ntiles + 24);
-      CK(cudaMemsetAsync(fz, 0, 8 * (size_t)(2 * ntiles + 24), st));
-      A.tile_counter = fz; A.wl_cnt = fz + 2; A.totals = (int64_t*)(fz + 4); A.desc_bytes = fz + 24; A.desc_kept = fz + 24 + ntiles;
+      ALLOC(fz, unsigned long long, 2 * ntiles + 32);
+      CK(cudaMemsetAsync(fz, 0, 8 * (size_t)(2 * ntiles + 32), st));
+      A.tile_counter = fz; A.wl_cnt = fz + 2; A.totals = (int64_t*)(fz + 4); A.desc_bytes = fz + 32; A.desc_kept = fz + 32 + ntiles;
       static const bool want_phases = getenv("TRCHUNK_PHASES") != nullptr;
       A.phase = want_phases ? fz + 8 : nullptr;
       A.text_bytes = braw; A.seg_special = seg_special;
       A.wl_cap = ccap / (TRC_SHORT_SPAN + 1) + 1;
       ALLOC(A.wl, LongEntry, A.wl_cap);
+      A.sl_cap = 2 * n + 1024; A.sl_cnt = fz + 7;
+      ALLOC(A.sl, SlowWord, A.sl_cap);
       static bool attr_done[64] = {false};
       if (!attr_done[ctx->device & 63]) {
         CK(cudaFuncSetAttribute(k_clean_tok_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FuseSmem)));
@@ -961,16 +968,23 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       ctx->launches++;
       CK(cudaGetLastError());
       unsigned long long h[6];
-      if ((rc = read_back(ctx, st, fz + 2, 32, h))) return rc;      // wl count, wl scratch, n_kept, bclean
+      if ((rc = read_back(ctx, st, fz + 2, 48, h))) return rc;      // wl count, wl scratch, n_kept, bclean, -, slow words
       nk = (int64_t)h[2]; bclean = (int64_t)h[3];
       D.n_kept = nk;
+      {
+        int64_t nslow = (int64_t)h[5] < A.sl_cap ? (int64_t)h[5] : A.sl_cap;   // entries past the capacity were counted in the kernel
+        if (nslow > 0) {
+          LAUNCH(k_count_slow_words, nslow, 128, D, ctx->T, ctx->d_byte_id, A.sl, nslow, A.wl, A.wl_cnt, A.wl_cap);
+          if ((rc = read_back(ctx, st, fz + 2, 16, h))) return rc;  // long spans found by the slow words
+        }
+      }
       if (want_phases) {
         unsigned long long ph[16];
-        if ((rc = read_back(ctx, st, fz + 8, 9 * 8, ph))) return rc;
-        unsigned long long tot = 0; for (int k = 0; k < 9; ++k) tot += ph[k];
-        fprintf(stderr, "[trchunk phases %%] load %.1f  P1 %.1f  P2 %.1f  P3+scan %.1f  lookback %.1f  scatter+copy %.1f  words %.1f  tokenize %.1f  outputs %.1f\n",
+        if ((rc = read_back(ctx, st, fz + 8, 12 * 8, ph))) return rc;
+        unsigned long long tot = 0; for (int k = 0; k < 11; ++k) tot += ph[k];
+        fprintf(stderr, "[trchunk phases %%] load %.1f  classify %.1f  dup %.1f  codes+scan %.1f  publish %.1f  scatter %.1f  words %.1f  tok-fast %.1f  resolve+copy %.1f  tok-slow %.1f  outputs %.1f\n",
                 100.0 * ph[0] / tot, 100.0 * ph[1] / tot, 100.0 * ph[2] / tot, 100.0 * ph[3] / tot, 100.0 * ph[4] / tot, 100.0 * ph[5] / tot,
-                100.0 * ph[6] / tot, 100.0 * ph[7] / tot, 100.0 * ph[8] / tot);
+                100.0 * ph[6] / tot, 100.0 * ph[9] / tot, 100.0 * ph[10] / tot, 100.0 * ph[7] / tot, 100.0 * ph[8] / tot);
       }
       if (h[0] > 0) {
         uint32_t* scratch;
