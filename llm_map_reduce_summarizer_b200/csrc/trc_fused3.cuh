@@ -25,14 +25,14 @@ struct F3Smem {
   } y;
   union alignas(16) {                         // bit masks (sp w ct lt ep bd drop ds lead); after the word list: slow words
     uint8_t m[F3_MASKS][F3_MSTRIDE];
-    uint16_t slow[F3_WORD_CAP];
+    uint16_t slow[2 * F3_WORD_CAP];           // slow words, then cache-miss words
   } z;
   alignas(16) uint8_t out[F3_OUT_CAP + 32];
   uint64_t hot8[TRC_HOT8];
   uint16_t cand[F3_CAND_CAP];
   uint16_t pre_o[F3_NCELL + 32], pre_s[F3_NCELL + 32];   // per cell: output bytes / spaces before it, inside its step
   uint16_t st_o[F3_NSTEP + 1], st_s[F3_NSTEP + 1], st_t[F3_NSTEP + 1];
-  uint16_t step_seg[F3_NSTEP];
+  uint16_t blk_seg[F3_IN_CAP / 64];         // segment of the first byte of every 64-byte block
   uint16_t sg_o[F3_SEGS + 1], sg_s[F3_SEGS + 1], sg_t[F3_SEGS + 1];   // step-relative prefixes at segment starts
   uint16_t spb[F3_SEGS + 1], ctb[F3_SEGS + 1];
   int32_t rel[F3_SEGS + 1];
@@ -40,7 +40,7 @@ struct F3Smem {
   int32_t len[F3_SEGS], koff[F3_SEGS], tok[F3_SEGS], spmin[F3_SEGS];
   int32_t wsum[3][F3_NW];
   int32_t tot[3];
-  int32_t ncand, nslow, has_sp;
+  int32_t ncand, nslow, nmiss, has_sp;
   unsigned int tile;
   long long gbase, kbase, slbase;
 };
@@ -74,7 +74,7 @@ __device__ __forceinline__ void f3_scan3(F3Smem& S, int lane, int wid, int32_t v
 
 // segment of tile byte k, starting the search at the first segment of k's step
 __device__ __forceinline__ int f3_seg_of(const F3Smem& S, int ns, int32_t k) {
-  int i = S.step_seg[k >> 8];
+  int i = S.blk_seg[k >> 6];
   while (i + 1 < ns && S.rel[i + 1] <= k) ++i;
   return i;
 }
@@ -84,8 +84,10 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
   extern __shared__ __align__(16) unsigned char fuse_raw[];
   F3Smem& S = *reinterpret_cast<F3Smem*>(fuse_raw);
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  for (int k = tid; k < TRC_HOT8; k += F3_T) S.hot8[k] = T.hot8_src[k];
-  TrcFast F; F.acls = T.acls; F.hot8 = S.hot8; F.hot8_mask = TRC_HOT8 - 1;
+  // S.hot8 is used as a WORD cache here: packed bytes of a word of <= 7 bytes (space included) | tokens << 56.
+  // Exact (the key is the whole word), filled on the fly, kept across tiles.
+  for (int k = tid; k < TRC_HOT8; k += F3_T) S.hot8[k] = 0ULL;
+  TrcFast F; F.acls = T.acls; F.hot8 = nullptr; F.hot8_mask = 0;
   SwMasks M;
   M.sp = S.z.m[0]; M.w = S.z.m[1]; M.ct = S.z.m[2]; M.lt = S.z.m[3]; M.ep = S.z.m[4]; M.bd = S.z.m[5]; M.drop = S.z.m[6]; M.ds = S.z.m[7];
   uint8_t* const mlead = S.z.m[8];
@@ -130,10 +132,10 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
         const int32_t a = S.rel[tid], b = S.rel[tid + 1];
         if (b > a) {
           sw_or_bit(M.bd, a);
-          for (int32_t s = (a + 255) >> 8; (s << 8) < b; ++s) S.step_seg[s] = (uint16_t)tid;
+          for (int32_t s = (a + 63) >> 6; (s << 6) < b; ++s) S.blk_seg[s] = (uint16_t)tid;
         }
       }
-      if (tid == 0) S.step_seg[0] = 0;
+      if (tid == 0) S.blk_seg[0] = 0;
       // ---- A: ASCII classes of every cell
       for (int st = wid; st < nstep; st += F3_NW) {
         const int c = (st << 5) + lane;
@@ -387,8 +389,35 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
       FUSE_PH(6);
       if (tid == 0) S.nslow = 0;
       __syncthreads();
-      uint16_t* slow = S.z.slow;                 // the masks are dead
+      uint16_t* slow = S.z.slow;                 // the masks are dead: two word lists live there
+      uint16_t* miss = S.z.slow + F3_WORD_CAP;
+      if (tid == 0) S.nmiss = 0;
+      __syncthreads();
+      // pass 1 (uniform): probe the word cache; misses and words longer than 7 bytes are queued
       for (int32_t w = tid; w < tot_words; w += F3_T) {
+        const int seg = S.y.w.wseg[w];
+        const int32_t st = S.y.w.wstart[w];
+        const int32_t sl = S.loff[seg];
+        const int32_t en = (w + 1 < tot_words && S.y.w.wseg[w + 1] == seg) ? (int32_t)S.y.w.wstart[w + 1] : sl + S.len[seg];
+        const int vs = st == sl ? 1 : 0, Lw = en - st + vs;
+        bool hit = false;
+        if (Lw <= 7) {
+          const uint32_t* p32 = reinterpret_cast<const uint32_t*>(S.out + (st & ~3));
+          const unsigned sh = (unsigned)(st & 3) * 8u;
+          const uint32_t w0 = p32[0], w1 = p32[1], w2 = p32[2];
+          uint64_t lo = (uint64_t)__funnelshift_r(w0, w1, sh) | ((uint64_t)__funnelshift_r(w1, w2, sh) << 32);
+          if (vs) lo = (lo << 8) | (uint64_t)' ';
+          lo &= (1ULL << (8 * Lw)) - 1;
+          const uint64_t ce = S.hot8[trc_key8_slot(lo, TRC_HOT8 - 1)];
+          if ((ce & 0x00ffffffffffffffULL) == lo) { atomicAdd(&S.tok[seg], (int32_t)(ce >> 56)); hit = true; }
+        }
+        if (!hit) miss[atomicAdd(&S.nmiss, 1)] = (uint16_t)w;
+      }
+      __syncthreads();
+      // pass 2 (dense): packed-word matcher for the queued words; what it cannot decide goes to the slow list
+      const int32_t nmiss = S.nmiss;
+      for (int32_t q = tid; q < nmiss; q += F3_T) {
+        const int32_t w = miss[q];
         const int seg = S.y.w.wseg[w];
         const int32_t st = S.y.w.wstart[w];
         const int32_t sl = S.loff[seg];
@@ -405,6 +434,7 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
           if (vs) { hi = (hi << 8) | (lo >> 56); lo = (lo << 8) | (uint64_t)' '; }
           if (Lw < 8) { lo &= (1ULL << (8 * Lw)) - 1; hi = 0; } else if (Lw == 8) hi = 0; else if (Lw < 16) hi &= (1ULL << (8 * (Lw - 8))) - 1;
           done = trc_count_word16(T, F, lo, hi, Lw, &c);
+          if (done && Lw <= 7) S.hot8[trc_key8_slot(lo, TRC_HOT8 - 1)] = lo | ((uint64_t)c << 56);
         }
         if (!done) done = trc_count_word_fast(T, F, S.out + st, n, vs, &c);
         if (done) atomicAdd(&S.tok[seg], (int32_t)c);

@@ -104,13 +104,26 @@ TRC_HD uint32_t sw_dup_candidates(const SwMasks& M, int32_t c, uint32_t valid) {
   return wstart & after_ws & ~(uint32_t)M.bd[c] & valid & 0xffu;
 }
 
+// Number of consecutive set bits of a mask array starting at bit k (a byte of the array at a time).
+TRC_HD int32_t sw_run_up(const uint8_t* arr, int32_t k, int32_t limit) {
+  int32_t e = k;
+  while (e < limit) {
+    const uint32_t x = (uint32_t)arr[e >> 3] >> (e & 7);
+    const int room = 8 - (e & 7);
+    const uint32_t inv = ~x & ((1u << room) - 1u);
+    if (inv) { e += (int32_t)trc_ctz32(inv); break; }
+    e += room;
+  }
+  return e < limit ? e : limit;
+}
+
 // The rule of cp_mark_dup on mask arrays: byte k starts a \w-run after whitespace inside segment [a,b).
 TRC_HD void sw_mark_dup(const uint8_t* in, const SwMasks& M, int32_t k, int32_t a, int32_t b) {
   int32_t p = k;
   while (p > a && sw_bit(M.sp, p - 1)) --p;                 // start of the whitespace run
   if (p == a || !sw_bit(M.w, p - 1)) return;                // ... which must follow a \w character
-  int32_t e = k;
-  while (e < b && sw_bit(M.w, e)) ++e;
+  const int32_t e = sw_run_up(M.w, k, b);
+  if (in[e - 1] != in[p - 1]) return;                       // equal words end with the same byte: rejects most
   int32_t L = e - k;
   if (p - L < a) return;
   if (p - L > a && sw_bit(M.w, p - L - 1)) return;          // previous \w-run is longer

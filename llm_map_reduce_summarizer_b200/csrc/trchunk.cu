@@ -937,7 +937,8 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
     ALLOC(D.C, uint8_t, ccap);
     if (n == 0) { CK(cudaMemsetAsync(D.coff, 0, 8, st)); CK(cudaMemsetAsync(D.kdoc_off, 0, 8 * (size_t)(nd + 1), st)); }
     else {
-      const int64_t ntiles = (n + FUSE_SEGS - 1) / FUSE_SEGS;
+      const int64_t tile_segs = ctx->fused_gen >= 3 ? F3_SEGS : FUSE_SEGS;
+      const int64_t ntiles = (n + tile_segs - 1) / tile_segs;
       FuseArgs A;
       unsigned long long* fz;
       ALLOC(fz, unsigned long long, 2 * ntiles + 32);
