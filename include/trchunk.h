@@ -131,6 +131,9 @@ enum {
   TRC_A_CDOC_OFF,     /* int64 [n_doc+1]     chunk range of every document                                 */
   TRC_A_CCHARS,       /* int32 [n_seg]       code points of the cleaned text of every RAW segment          */
   TRC_A_SENT,         /* trc_sent [n_sent]   sentence / clause records of the sentence path                */
+  TRC_A_PDST,         /* int64 [n_kept]      offset inside TRC_A_TWC where every piece starts: its "[ts] " marker  */
+                      /*                     if it has one, then its cleaned text (-1: the piece                  */
+                      /*                     belongs to a sentence-path item; use TRC_A_CLEAN for it)             */
   TRC_A__COUNT
 };
 int trc_get_array(trc_ctx* ctx, int which, void* dst, int64_t dst_bytes, int32_t memory, int64_t* nbytes,

@@ -604,9 +604,47 @@ __global__ void k_item_layout(TrcDev D) { GSTRIDE(t, D.n_items) trc_item_layout(
 #ifdef TRC_HOSTSIM
 __global__ void k_emit_pieces_flat(TrcDev D) { GSTRIDE(j, D.n_kept) trc_emit_piece_flat(D, j, 0, 1); }
 #else
-__global__ void k_emit_pieces_flat(TrcDev D) {   // 8 lanes per piece
-  for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; (q >> 3) < D.n_kept; q += (int64_t)gridDim.x * blockDim.x)
-    trc_emit_piece_flat(D, q >> 3, (int)(q & 7), 8);
+// 8 lanes per piece.  The body is copied in 4-byte words aligned to the DESTINATION (two aligned source
+// words + a funnel shift per destination word); head, tail and the "[ts] " prefix go byte by byte.
+__global__ void k_emit_pieces_flat(TrcDev D) {
+  for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; (q >> 3) < D.n_kept; q += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t j = q >> 3;
+    const int lane = (int)(q & 7);
+    const int64_t d = D.pdst[j];
+    if (d < 0) continue;
+    const uint8_t f = D.pflag[j];
+    uint8_t* dst = D.twc + d;
+    int64_t o = 0;
+    if (f & 1) {
+      const double st = D.start[D.k2r[j]];
+      o = trc_ts_len(st) + 3;
+      if (lane == 0) {
+        uint8_t buf[TRC_TS_MAX + 4];
+        int tl = trc_fmt_ts(st, buf + 1);
+        buf[0] = '['; buf[tl + 1] = ']'; buf[tl + 2] = ' ';
+        for (int k = 0; k < tl + 3; ++k) dst[k] = buf[k];
+      }
+    }
+    const int64_t c0 = D.coff[j];
+    const int64_t len = D.coff[j + 1] - c0;
+    const uint8_t* src = D.C + c0;
+    uint8_t* db = dst + o;
+    if ((f & 2) && lane == 7) db[len] = ' ';
+    if (len < 24) { for (int64_t k = lane; k < len; k += 8) db[k] = src[k]; continue; }
+    const int head = (int)((4 - ((uintptr_t)db & 3)) & 3);            // bytes until db is 4-byte aligned
+    if (lane < head) db[lane] = src[lane];
+    const int64_t nw = (len - head) >> 2;                              // whole destination words
+    const uint8_t* s0 = src + head;
+    const unsigned sh = (unsigned)((uintptr_t)s0 & 3) * 8u;
+    const uint32_t* sw = reinterpret_cast<const uint32_t*>((uintptr_t)s0 & ~(uintptr_t)3);
+    uint32_t* dw = reinterpret_cast<uint32_t*>(db + head);
+    for (int64_t k = lane; k < nw; k += 8) {
+      const uint32_t a = sw[k], b = sh ? sw[k + 1] : 0u;
+      dw[k] = __funnelshift_r(a, b, sh);
+    }
+    const int64_t done = head + (nw << 2);
+    if (lane < len - done) db[done + lane] = src[done + lane];
+  }
 }
 #endif
 
@@ -1214,6 +1252,7 @@ extern "C" int trc_chunk(trc_ctx* ctx, const int32_t* doc_max_tokens, int32_t co
   set_arr(ctx, TRC_A_CHUNKS, D.chunks, (int64_t)sizeof(TrcChunk) * nc); set_arr(ctx, TRC_A_SPK_LIST, D.spk_list, 4 * ni);
   set_arr(ctx, TRC_A_TWC, D.twc, btwc); set_arr(ctx, TRC_A_CDOC_OFF, D.cdoc_off, 8 * (nd + 1));
   set_arr(ctx, TRC_A_SENT, ctx->SS.recs, (int64_t)sizeof(TrcSent) * ctx->SS.n_recs);
+  set_arr(ctx, TRC_A_PDST, D.pdst, 8 * nk);
   ctx->counts[TRC_N_SENT] = ctx->SS.n_recs;
   ctx->have_chunk = true;
   return TRC_OK;
