@@ -100,7 +100,7 @@ int trc_chunk(trc_ctx* ctx, const int32_t* doc_max_tokens, int32_t context_token
 /* Counters of the current batch. */
 enum {
   TRC_N_SEG = 0, TRC_N_KEPT, TRC_N_GROUPS, TRC_N_ITEMS, TRC_N_SUBS, TRC_N_CHUNKS, TRC_B_RAW, TRC_B_CLEAN,
-  TRC_B_MERGED, TRC_B_TWC, TRC_TOKENS, TRC_N_DOC, TRC_N_LONG_SPANS, TRC_N_ERR_DOCS, TRC_N_SENT, TRC_N_COUNTERS = 24
+  TRC_B_MERGED, TRC_B_TWC, TRC_TOKENS, TRC_N_DOC, TRC_N_LONG_SPANS, TRC_N_ERR_DOCS, TRC_N_SENT, TRC_N_GIANTS, TRC_N_COUNTERS = 24
 };
 int trc_get_counts(trc_ctx* ctx, int64_t* counts /* TRC_N_COUNTERS */);
 

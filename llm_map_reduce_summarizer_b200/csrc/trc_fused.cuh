@@ -44,6 +44,11 @@ struct FuseSmem {
 };
 static_assert(sizeof(FuseSmem) <= 115200, "two CTAs per SM");
 
+struct GiantView {                  // what the fused kernel needs about pre-processed giant segments (trc_giant.cuh)
+  const int32_t* of_seg;            // per raw segment: giant index or -1; nullptr when the batch has no giants
+  const int64_t* toff; const uint8_t* text; const int32_t* chars; const uint32_t* tok; const long long* spw;
+};
+
 struct SlowWord { int64_t pos; int32_t len_vs; int32_t unit; };   // byte offset in the cleaned text, length | vs << 31, kept segment
 
 struct FuseArgs {
@@ -56,6 +61,7 @@ struct FuseArgs {
   LongEntry* wl; unsigned long long* wl_cnt; int64_t wl_cap;
   unsigned long long* phase;        // optional: cycles per phase summed over CTAs (diagnostics, TRCHUNK_PHASES=1)
   SlowWord* sl; unsigned long long* sl_cnt; int64_t sl_cap;   // words left to the generic matcher (k_count_slow_words)
+  GiantView G;
 };
 #define FUSE_PH(i) do { if (A.phase && tid == 0) { long long now_ = clock64(); atomicAdd(&A.phase[i], (unsigned long long)(now_ - ph_t)); ph_t = now_; } } while (0)
 

@@ -112,6 +112,7 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
     int32_t tot_out = 0, tot_words = 0, tot_kept = 0;
     long long gbase = 0, kbase = 0;
     bool fast_out = false;
+    int32_t gq = -1;
     if (fast_in) {
       const int ncell = (span + 7) >> 3, nstep = (span + 255) >> 8;
       M.ncell = ncell;
@@ -361,17 +362,22 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
         }
       }
     } else {
-      // ================= slow lane: sequential per-segment routines on global memory =================
+      // ================= slow lane: sequential per-segment routines on global memory; giants come pre-cleaned =====
       const uint8_t* src = D.text + base;
       int32_t a = 0, b = 0;
       if (tid < ns) {
         a = S.rel[tid]; b = S.rel[tid + 1];
-        TrcCleanOut r = trc_clean_segment<false>(T, src + a, b - a, nullptr);
-        mylen = (int32_t)r.bytes; mychars = (int32_t)r.chars; mykeep = r.bytes > 0;
+        gq = A.G.of_seg ? A.G.of_seg[s0 + tid] : -1;
+        if (gq >= 0) { mylen = (int32_t)(A.G.toff[gq + 1] - A.G.toff[gq]); mychars = A.G.chars[gq]; mykeep = mylen > 0; }
+        else {
+          TrcCleanOut r = trc_clean_segment<false>(T, src + a, b - a, nullptr);
+          mylen = (int32_t)r.bytes; mychars = (int32_t)r.chars; mykeep = r.bytes > 0;
+        }
       }
       int32_t d1;
       f3_scan3(S, lane, wid, mylen, mykeep, 0, &loff, &koff, &d1);
       tot_out = S.tot[0]; tot_kept = S.tot[1];
+      if (tid < F3_SEGS) { S.loff[tid] = loff; S.spmin[tid] = tid < ns ? gq : -1; S.len[tid] = mylen; }
       if (wid == 0) {
         long long gb = fuse_lookback(A.desc_bytes, tile, tot_out, lane);
         long long kb = fuse_lookback(A.desc_kept, tile, tot_kept, lane);
@@ -379,7 +385,15 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
       }
       __syncthreads();
       gbase = S.gbase; kbase = S.kbase;
-      if (tid < ns && mylen > 0) trc_clean_segment<true>(T, src + a, b - a, D.C + gbase + loff);
+      if (tid < ns && mylen > 0 && gq < 0) trc_clean_segment<true>(T, src + a, b - a, D.C + gbase + loff);
+      for (int i = 0; i < ns; ++i) {          // giants: the whole CTA copies their cleaned text
+        const int32_t q = S.spmin[i];
+        if (q < 0) continue;
+        const uint8_t* gsrc = A.G.text + A.G.toff[q];
+        uint8_t* gdst = D.C + gbase + S.loff[i];
+        const int32_t gl = S.len[i];
+        for (int32_t k = tid; k < gl; k += F3_T) gdst[k] = gsrc[k];
+      }
     }
     if (tid < F3_SEGS) S.tok[tid] = 0;
     __syncthreads();
@@ -484,6 +498,10 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
         });
         atomicAdd(&S.tok[seg], (int32_t)c);
       }
+    } else if (tid < ns && mylen > 0 && gq >= 0) {
+      S.tok[tid] = (int32_t)A.G.tok[gq];
+      const long long v = A.G.spw[gq];
+      mysp = v == 0x7fffffffffffffffLL ? -1 : (int32_t)(v & 15);
     } else if (tid < ns && mylen > 0) {
       const int64_t j = kbase + koff;
       const uint8_t* p = D.C + gbase + loff;

@@ -1,0 +1,126 @@
+// Segments too large for a fused tile ("giants": a monologue of tens of KB in one segment, config 4).
+// They are cleaned and tokenised BEFORE the fused kernel by byte-parallel grid kernels over global memory
+// (the per-byte local rules of trc_clean_par.cuh, preprocessor.py:38,69-89), so that the fused kernel's
+// slow lane only has to copy their cleaned text and take over their counts instead of walking tens of KB
+// in one thread.  Tokens: every space of the cleaned text starts a word; words are counted as units
+// (big_chunkeroosky.py:83 via DESIGN.md §3) and summed per giant.
+#pragma once
+
+#define TRC_GIANT_MIN 4096          // raw bytes; larger segments are pre-processed here
+
+struct GiantState {
+  const int32_t* list;              // raw segment index of every giant (ascending)
+  const int64_t* boff;              // prefix of their raw lengths, ng+1
+  int64_t ng, gb;                   // giants, raw bytes
+  uint8_t* cls; uint8_t* code;      // per raw byte
+  int32_t* fns;                     // first non-space byte per giant
+  int64_t* pk;                      // per raw byte: output bytes | code points << 32   (scanned in place -> opk)
+  int64_t* opk;                     // exclusive scan of pk, gb+1
+  uint8_t* text;                    // cleaned text of all giants back to back
+  int64_t* toff;                    // cleaned offset of every giant, ng+1
+  int32_t* chars;                   // cleaned code points
+  uint32_t* tok;                    // tokens of " " + cleaned text
+  long long* spw;                   // first special-token hit: (word << 4 | k), or LLONG_MAX
+  const int32_t* of_seg;            // per raw segment: giant index or -1 (n entries)
+};
+
+__global__ void k_giant_flag(TrcDev D, int32_t* flag) { GSTRIDE(i, D.n) flag[i] = (D.seg_off[i + 1] - D.seg_off[i]) > TRC_GIANT_MIN; }
+__global__ void k_giant_list(TrcDev D, const int32_t* __restrict__ flag, const int64_t* __restrict__ scan, int32_t* list, int64_t* len,
+                             int32_t* of_seg) {
+  GSTRIDE(i, D.n) {
+    if (flag[i]) { int64_t q = scan[i]; list[q] = (int32_t)i; len[q] = D.seg_off[i + 1] - D.seg_off[i]; of_seg[i] = (int32_t)q; }
+    else of_seg[i] = -1;
+  }
+}
+__device__ __forceinline__ int64_t giant_of_byte(const GiantState& G, int64_t p) {
+  int64_t lo = 0, hi = G.ng;
+  while (hi - lo > 1) { int64_t mid = (lo + hi) >> 1; if (G.boff[mid] <= p) lo = mid; else hi = mid; }
+  return lo;
+}
+__global__ void k_giant_classify(TrcDev D, TrcTables T, GiantState G) {
+  GSTRIDE(p, G.gb) {
+    const int64_t q = giant_of_byte(G, p);
+    const int64_t s = D.seg_off[G.list[q]];
+    const int32_t n = (int32_t)(G.boff[q + 1] - G.boff[q]);
+    cp_classify(T, D.text + s, G.cls + G.boff[q], G.code + G.boff[q], (int32_t)(p - G.boff[q]), n);
+  }
+}
+__global__ void k_giant_fns(GiantState G) {
+  GSTRIDE(q, G.ng) G.fns[q] = cp_first_nonspace(G.cls + G.boff[q], 0, (int32_t)(G.boff[q + 1] - G.boff[q]));
+}
+__global__ void k_giant_markdup(TrcDev D, GiantState G) {
+  GSTRIDE(p, G.gb) {
+    const int64_t q = giant_of_byte(G, p);
+    const int32_t k = (int32_t)(p - G.boff[q]), n = (int32_t)(G.boff[q + 1] - G.boff[q]);
+    const uint8_t* cls = G.cls + G.boff[q];
+    if (cp_dup_candidate(cls, k, 0)) cp_mark_dup(D.text + D.seg_off[G.list[q]], cls, G.code + G.boff[q], k, 0, n);
+  }
+}
+__global__ void k_giant_code(TrcDev D, GiantState G) {
+  GSTRIDE(p, G.gb) {
+    const int64_t q = giant_of_byte(G, p);
+    const int32_t k = (int32_t)(p - G.boff[q]), n = (int32_t)(G.boff[q + 1] - G.boff[q]);
+    const uint8_t* cls = G.cls + G.boff[q];
+    const uint32_t r = cp_code(D.text + D.seg_off[G.list[q]], cls, G.code + G.boff[q], k, 0, n, G.fns[q]);
+    const int64_t ch = (r == 3) ? 2 : ((r == 2 || (r == 1 && !(cls[k] & CP_CONT))) ? 1 : 0);
+    G.pk[p] = (int64_t)cp_outlen(r) | (ch << 32);
+  }
+}
+__global__ void k_giant_offsets(GiantState G) {
+  GSTRIDE(q, G.ng + 1) {
+    const int64_t v = G.opk[G.boff[q]];
+    G.toff[q] = v & 0xffffffffLL;
+    if (q > 0) G.chars[q - 1] = (int32_t)((v >> 32) - (G.opk[G.boff[q - 1]] >> 32));
+    if (q < G.ng) { G.tok[q] = 0; G.spw[q] = 0x7fffffffffffffffLL; }
+  }
+}
+__global__ void k_giant_scatter(TrcDev D, GiantState G) {
+  GSTRIDE(p, G.gb) {
+    const uint8_t r = G.code[p];
+    if (!r) continue;
+    const int64_t q = giant_of_byte(G, p);
+    const int64_t o = G.opk[p] & 0xffffffffLL;
+    const uint8_t b = D.text[D.seg_off[G.list[q]] + (p - G.boff[q])];
+    if (r == 1) G.text[o] = b; else if (r == 2) G.text[o] = ' '; else { G.text[o] = ' '; G.text[o + 1] = b; }
+  }
+}
+// words of the cleaned giants: a word starts at every space and at every giant's first byte
+__global__ void k_giant_wflag(GiantState G, int64_t gc, int32_t* wflag, const int64_t* __restrict__ toff) {
+  GSTRIDE(x, gc) wflag[x] = G.text[x] == ' ';
+}
+__global__ void k_giant_first(GiantState G, int32_t* wflag) { GSTRIDE(q, G.ng) if (G.toff[q + 1] > G.toff[q]) wflag[G.toff[q]] = 1; }
+__global__ void k_giant_words(GiantState G, int64_t gc, const int32_t* __restrict__ wflag, const int64_t* __restrict__ wscan, int64_t* ustart) {
+  GSTRIDE(x, gc) if (wflag[x]) ustart[wscan[x]] = x;
+}
+__global__ void k_giant_wends(GiantState G, int64_t nw, int64_t gc, const int64_t* __restrict__ ustart, int64_t* uend, int32_t* wgiant, uint8_t* wfirst) {
+  GSTRIDE(w, nw) {
+    const int64_t x = ustart[w];
+    int64_t lo = 0, hi = G.ng;                       // giant of cleaned byte x
+    while (hi - lo > 1) { int64_t mid = (lo + hi) >> 1; if (G.toff[mid] <= x) lo = mid; else hi = mid; }
+    while (lo + 1 < G.ng && G.toff[lo + 1] <= x) ++lo;   // skip blank giants that share the offset
+    const int64_t gend = G.toff[lo + 1];
+    const int64_t nx = w + 1 < nw ? ustart[w + 1] : gc;
+    uend[w] = nx < gend ? nx : gend;
+    wgiant[w] = (int32_t)lo;
+    wfirst[w] = x == G.toff[lo] && G.text[x] != ' ';
+  }
+}
+// first word of every giant (it gets the virtual leading space) as its own unit list
+__global__ void k_giant_firstunits(GiantState G, const int64_t* __restrict__ wscan, const int64_t* __restrict__ uend, int64_t* fs, int64_t* fe) {
+  GSTRIDE(q, G.ng) {
+    const int64_t x = G.toff[q];
+    fs[q] = x;
+    fe[q] = G.toff[q + 1] > x ? uend[wscan[x]] : x;
+  }
+}
+__global__ void k_giant_sum(GiantState G, int64_t nw, const int32_t* __restrict__ wgiant, const uint32_t* __restrict__ c0,
+                            const uint8_t* __restrict__ wfirst, const int32_t* __restrict__ sp) {
+  GSTRIDE(w, nw) {
+    const int32_t q = wgiant[w];
+    if (!wfirst[w]) atomicAdd(&G.tok[q], c0[w]);
+    if (sp[w] >= 0) atomicMin(&G.spw[q], (long long)((w << 4) | sp[w]));
+  }
+}
+__global__ void k_giant_sum_first(GiantState G, const uint32_t* __restrict__ c1) {
+  GSTRIDE(q, G.ng) if (G.toff[q + 1] > G.toff[q]) atomicAdd(&G.tok[q], c1[q]);
+}

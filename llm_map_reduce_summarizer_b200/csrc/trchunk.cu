@@ -462,6 +462,7 @@ __global__ void __launch_bounds__(LONG_T) k_bpe_long(TrcTables T, const uint32_t
 
 #endif
 #ifndef TRC_HOSTSIM
+#include "trc_giant.cuh"
 #include "trc_fused.cuh"
 #include "trc_fused3.cuh"
 #endif
@@ -750,6 +751,65 @@ static int count_units(trc_ctx* ctx, cudaStream_t st, const uint8_t* bytes, cons
 
 #include "trc_sent_kernels.cuh"
 
+#ifndef TRC_HOSTSIM
+// Pre-pass for segments larger than a fused tile (trc_giant.cuh).  Leaves *V empty when there are none.
+static int giant_stage(trc_ctx* ctx, cudaStream_t st, int64_t braw, GiantView* V) {
+  TrcDev& D = ctx->D;
+  const int64_t n = D.n;
+  int rc;
+  int32_t* gflag; int64_t* gscan;
+  ALLOC(gflag, int32_t, n); ALLOC(gscan, int64_t, n + 1);
+  LAUNCH(k_giant_flag, n, 256, D, gflag);
+  if ((rc = scan_excl(ctx, st, gflag, gscan, n))) return rc;
+  int64_t ng = 0;
+  if ((rc = read_back(ctx, st, gscan + n, 8, &ng))) return rc;
+  if (ng == 0) return TRC_OK;
+  GiantState G{};
+  int32_t* list; int64_t* len; int32_t* of_seg; int64_t* boff;
+  ALLOC(list, int32_t, ng); ALLOC(len, int64_t, ng); ALLOC(of_seg, int32_t, n); ALLOC(boff, int64_t, ng + 1);
+  LAUNCH(k_giant_list, n, 256, D, gflag, gscan, list, len, of_seg);
+  if ((rc = scan_excl(ctx, st, len, boff, ng))) return rc;
+  int64_t gb = 0;
+  if ((rc = read_back(ctx, st, boff + ng, 8, &gb))) return rc;
+  if (gb >= (1LL << 31)) { ctx->err = "more than 2 GiB of oversized segments in one batch"; return TRC_EUNSUPPORTED; }
+  G.list = list; G.boff = boff; G.ng = ng; G.gb = gb; G.of_seg = of_seg;
+  ALLOC(G.cls, uint8_t, gb); ALLOC(G.code, uint8_t, gb); ALLOC(G.fns, int32_t, ng); ALLOC(G.pk, int64_t, gb); ALLOC(G.opk, int64_t, gb + 1);
+  ALLOC(G.toff, int64_t, ng + 1); ALLOC(G.chars, int32_t, ng); ALLOC(G.tok, uint32_t, ng); ALLOC(G.spw, long long, ng);
+  LAUNCH(k_giant_classify, gb, 256, D, ctx->T, G);
+  LAUNCH(k_giant_fns, ng, 64, G);
+  LAUNCH(k_giant_markdup, gb, 256, D, G);
+  LAUNCH(k_giant_code, gb, 256, D, G);
+  if ((rc = scan_excl(ctx, st, G.pk, G.opk, gb))) return rc;
+  int64_t packed = 0;
+  if ((rc = read_back(ctx, st, G.opk + gb, 8, &packed))) return rc;
+  const int64_t gc = packed & 0xffffffffLL;
+  ALLOC(G.text, uint8_t, gc);
+  LAUNCH(k_giant_offsets, ng + 1, 128, G);
+  LAUNCH(k_giant_scatter, gb, 256, D, G);
+  // words of the cleaned giants -> token counts
+  int32_t* wflag; int64_t* wscan;
+  ALLOC(wflag, int32_t, gc); ALLOC(wscan, int64_t, gc + 1);
+  LAUNCH(k_giant_wflag, gc, 256, G, gc, wflag, G.toff);
+  LAUNCH(k_giant_first, ng, 64, G, wflag);
+  if ((rc = scan_excl(ctx, st, wflag, wscan, gc))) return rc;
+  int64_t nw = 0;
+  if (gc) { if ((rc = read_back(ctx, st, wscan + gc, 8, &nw))) return rc; }
+  int64_t* ustart; int64_t* uend; int32_t* wgiant; uint8_t* wfirst; uint32_t* c0; int32_t* sp; int64_t* fs; int64_t* fe; uint32_t* c1;
+  ALLOC(ustart, int64_t, nw); ALLOC(uend, int64_t, nw); ALLOC(wgiant, int32_t, nw); ALLOC(wfirst, uint8_t, nw);
+  ALLOC(c0, uint32_t, nw); ALLOC(sp, int32_t, nw); ALLOC(fs, int64_t, ng); ALLOC(fe, int64_t, ng); ALLOC(c1, uint32_t, ng);
+  LAUNCH(k_giant_words, gc, 256, G, gc, wflag, wscan, ustart);
+  LAUNCH(k_giant_wends, nw, 256, G, nw, gc, ustart, uend, wgiant, wfirst);
+  LAUNCH(k_giant_firstunits, ng, 64, G, wscan, uend, fs, fe);
+  if ((rc = count_units(ctx, st, G.text, ustart, uend, nw, gc, 0, c0, sp, false))) return rc;
+  if ((rc = count_units(ctx, st, G.text, fs, fe, ng, gc, 1, c1, nullptr, false))) return rc;
+  LAUNCH(k_giant_sum, nw, 256, G, nw, wgiant, c0, wfirst, sp);
+  LAUNCH(k_giant_sum_first, ng, 64, G, c1);
+  V->of_seg = of_seg; V->toff = G.toff; V->text = G.text; V->chars = G.chars; V->tok = G.tok; V->spw = G.spw;
+  ctx->counts[TRC_N_GIANTS] = ng;
+  return TRC_OK;
+}
+#endif
+
 // =====================================================================================================
 // C ABI
 // =====================================================================================================
@@ -989,6 +1049,8 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       ALLOC(A.wl, LongEntry, A.wl_cap);
       A.sl_cap = 2 * n + 1024; A.sl_cnt = fz + 7;
       ALLOC(A.sl, SlowWord, A.sl_cap);
+      A.G = GiantView{};
+      if (ctx->fused_gen >= 3) { if ((rc = giant_stage(ctx, st, braw, &A.G))) return rc; }
       static bool attr_done[64] = {false};
       if (!attr_done[ctx->device & 63]) {
         CK(cudaFuncSetAttribute(k_clean_tok_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FuseSmem)));
