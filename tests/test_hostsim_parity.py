@@ -126,3 +126,16 @@ def test_combine_helpers(hostsim_engine):
                 one = PP.create_combined_segment(unmerged[:4], pres)
             assert one["original_segments"] == min(4, len(unmerged)) and one["is_combined"] is True
             assert one["text"].count(unmerged[0]["text"]) >= 1
+
+
+def test_token_counter_service(hostsim_engine):
+    import pytest
+    from llm_map_reduce_summarizer_b200.token_counter import TokenCounter
+    E.set_default_engine(hostsim_engine)
+    enc = TK.encoding()
+    tc = TokenCounter()
+    texts = ["A short summary.", "", "Bullet points:\n- one\n- two\n\nDone.", "naïve café 你好 123456", "x" * 300]
+    assert tc.count_batch(texts) == [len(enc.encode(t)) for t in texts]
+    assert tc.total(texts) == sum(len(enc.encode(t)) for t in texts)
+    with pytest.raises(ValueError):
+        tc.count("bad <|endoftext|> text")
