@@ -149,6 +149,7 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
         M.sp[c] = (uint8_t)cl.sp; M.w[c] = (uint8_t)cl.w; M.ct[c] = (uint8_t)cl.ct; M.lt[c] = (uint8_t)cl.lt; M.ep[c] = (uint8_t)cl.ep;
         mlead[c] = (uint8_t)cl.lead;
       }
+      if (tid < 8) { M.w[(nstep << 5) + tid] = 0; M.sp[(nstep << 5) + tid] = 0; }   // window reads may look two cells past the tile
       __syncthreads();
       // ---- A2: multi-byte characters (code point lookup by the owner of the lead byte)
       for (int st = wid; st < nstep; st += F3_NW) {
@@ -166,6 +167,14 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
         if (k0 < al) valid &= (al - k0 >= 8) ? 0u : (0xffu << (al - k0));
         if (k0 + 8 > span) valid &= (span <= k0) ? 0u : (0xffu >> (k0 + 8 - span));
         uint32_t cand = (c < ncell) ? sw_dup_candidates(M, c, valid & 0xffu) : 0u;
+        {                                        // most candidates fail a two-byte test and never reach the list
+          uint32_t t = cand;
+          while (t) {
+            const int bit = __ffs(t) - 1;
+            t &= t - 1;
+            if (sw_dup_quick_reject(S.y.in, M, k0 + bit, span)) cand &= ~(1u << bit);
+          }
+        }
         const int cnt = __popc(cand);
         int x = cnt;
 #pragma unroll

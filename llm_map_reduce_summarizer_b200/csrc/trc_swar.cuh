@@ -104,6 +104,20 @@ TRC_HD uint32_t sw_dup_candidates(const SwMasks& M, int32_t c, uint32_t valid) {
   return wstart & after_ws & ~(uint32_t)M.bd[c] & valid & 0xffu;
 }
 
+// Cheap necessary condition for sw_mark_dup at candidate byte k (a \w-run start after whitespace): when the
+// separator is a single whitespace byte and the run ends within 16 bytes inside its segment, equal words
+// must end with the same byte.  Returns true when the candidate can be discarded.
+TRC_HD bool sw_dup_quick_reject(const uint8_t* in, const SwMasks& M, int32_t k, int32_t lim) {
+  const int32_t c = k >> 3, bit = k & 7;
+  if (k < 2 || sw_bit(M.sp, k - 2) || sw_bit(M.ct, k - 1)) return false;        // longer / multi-byte separator: undecided
+  const uint32_t wwin = ((uint32_t)M.w[c] | ((uint32_t)M.w[c + 1] << 8) | ((uint32_t)M.w[c + 2] << 16)) >> bit;
+  const uint32_t L = trc_ctz32(~wwin);
+  if (L >= 16 || k + (int32_t)L > lim) return false;                            // bytes past lim belong to the next tile
+  const uint32_t bwin = ((uint32_t)M.bd[c] | ((uint32_t)M.bd[c + 1] << 8) | ((uint32_t)M.bd[c + 2] << 16)) >> bit;
+  if (bwin & ((1u << L) - 1u) & ~1u) return false;                             // a segment starts inside the run
+  return in[k + L - 1] != in[k - 2];
+}
+
 // Number of consecutive set bits of a mask array starting at bit k (a byte of the array at a time).
 TRC_HD int32_t sw_run_up(const uint8_t* arr, int32_t k, int32_t limit) {
   int32_t e = k;

@@ -284,7 +284,7 @@ static void hostsim_clean_par_count(TrcDev D, TrcTables T, int32_t* keep, uint8_
 // The 8-byte-cell (SWAR) formulation, whole batch as one tile: validates the bit logic of trc_swar.cuh.
 static void hostsim_clean_swar(TrcDev D, TrcTables T, int32_t* keep, uint8_t* code, int64_t braw) {
   const int32_t nb = (int32_t)braw, ncell = (nb + 7) / 8 + 1;
-  std::vector<uint8_t> buf(8 * (size_t)ncell + 8, 0), arr(8 * (size_t)ncell + 64, 0), leadv(ncell, 0);
+  std::vector<uint8_t> buf(8 * (size_t)ncell + 8, 0), arr(8 * (size_t)ncell + 128, 0), leadv(ncell, 0);
   if (nb) memcpy(buf.data(), D.text, nb);
   SwMasks M; M.ncell = ncell;
   M.sp = arr.data(); M.w = M.sp + ncell + 4; M.ct = M.w + ncell + 4; M.lt = M.ct + ncell + 4; M.ep = M.lt + ncell + 4;
@@ -305,6 +305,7 @@ static void hostsim_clean_swar(TrcDev D, TrcTables T, int32_t* keep, uint8_t* co
       cand &= cand - 1;
       int32_t k = c * 8 + bit;
       if (k >= nb) continue;
+      if (sw_dup_quick_reject(buf.data(), M, k, (int32_t)nb)) continue;
       while (seg + 1 < D.n && D.seg_off[seg + 1] <= k) ++seg;
       sw_mark_dup(buf.data(), M, k, (int32_t)D.seg_off[seg], (int32_t)D.seg_off[seg + 1]);
     }
