@@ -281,41 +281,62 @@ static void hostsim_clean_par_count(TrcDev D, TrcTables T, int32_t* keep, uint8_
     D.clen[i] = len; D.cchars[i] = chars; keep[i] = len > 0;
   }
 }
-// The 8-byte-cell (SWAR) formulation, whole batch as one tile: validates the bit logic of trc_swar.cuh.
-static void hostsim_clean_swar(TrcDev D, TrcTables T, int32_t* keep, uint8_t* code, int64_t braw) {
-  const int32_t nb = (int32_t)braw, ncell = (nb + 7) / 8 + 1;
-  std::vector<uint8_t> buf(8 * (size_t)ncell + 8, 0), arr(8 * (size_t)ncell + 128, 0), leadv(ncell, 0);
-  if (nb) memcpy(buf.data(), D.text, nb);
-  SwMasks M; M.ncell = ncell;
-  M.sp = arr.data(); M.w = M.sp + ncell + 4; M.ct = M.w + ncell + 4; M.lt = M.ct + ncell + 4; M.ep = M.lt + ncell + 4;
-  M.bd = M.ep + ncell + 4; M.drop = M.bd + ncell + 4; M.ds = M.drop + ncell + 4;
-  for (int64_t i = 0; i < D.n; ++i) if (D.seg_off[i + 1] > D.seg_off[i]) sw_or_bit(M.bd, (int32_t)D.seg_off[i]);
-  for (int32_t c = 0; c < ncell; ++c) {
-    uint64_t x; memcpy(&x, buf.data() + 8 * (size_t)c, 8);
-    SwCell cl = sw_classify(x);
-    M.sp[c] = (uint8_t)cl.sp; M.w[c] = (uint8_t)cl.w; M.ct[c] = (uint8_t)cl.ct; M.lt[c] = (uint8_t)cl.lt; M.ep[c] = (uint8_t)cl.ep;
-    leadv[c] = (uint8_t)cl.lead;
-  }
-  for (int32_t c = 0; c < ncell; ++c) if (leadv[c]) sw_fix_multibyte(T, buf.data(), M, c, leadv[c], nb);
-  int64_t seg = 0;
-  for (int32_t c = 0; c < ncell; ++c) {
-    uint32_t cand = sw_dup_candidates(M, c, 0xffu);
-    while (cand) {
-      int bit = 0; while (!((cand >> bit) & 1u)) ++bit;
-      cand &= cand - 1;
-      int32_t k = c * 8 + bit;
-      if (k >= nb) continue;
-      if (sw_dup_quick_reject(buf.data(), M, k, (int32_t)nb)) continue;
-      while (seg + 1 < D.n && D.seg_off[seg + 1] <= k) ++seg;
-      sw_mark_dup(buf.data(), M, k, (int32_t)D.seg_off[seg], (int32_t)D.seg_off[seg + 1]);
+// The 8-byte-cell (SWAR) formulation, tiled exactly like k_clean_tok_fused3 (tiles of `tile_segs` segments
+// starting at a 16-byte aligned base, 16-byte loads that pull in bytes of the neighbouring tiles, mask bytes
+// the kernel never writes poisoned with 0xff): validates the bit logic of trc_swar.cuh and its tile edges.
+// tile_segs <= 0: the whole batch as one tile.
+static void hostsim_clean_swar(TrcDev D, TrcTables T, int32_t* keep, uint8_t* code, int64_t braw, int64_t tile_segs) {
+  if (tile_segs <= 0) tile_segs = D.n > 0 ? D.n : 1;
+  std::vector<uint8_t> buf, arr, leadv;
+  for (int64_t s0 = 0; s0 < D.n; s0 += tile_segs) {
+    const int64_t ns = (D.n - s0) < tile_segs ? (D.n - s0) : tile_segs;
+    const int64_t raw0 = D.seg_off[s0], raw1 = D.seg_off[s0 + ns];
+    const int32_t al = (int32_t)(raw0 & 15);
+    const int64_t base = raw0 - al;
+    const int32_t span = (int32_t)(raw1 - base);
+    const int32_t ncell = (span + 7) >> 3, nstep = (span + 255) >> 8, stride = nstep * 32 + 8;
+    buf.assign((size_t)nstep * 256 + 32, 0);
+    for (int32_t k = 0; k < span; k += 16)
+      for (int q = 0; q < 16; ++q) buf[k + q] = base + k + q < braw ? D.text[base + k + q] : 0;
+    arr.assign((size_t)stride * 8, 0xff);
+    leadv.assign((size_t)nstep * 32, 0);
+    SwMasks M; M.ncell = ncell;
+    M.sp = arr.data(); M.w = M.sp + stride; M.ct = M.w + stride; M.lt = M.ct + stride; M.ep = M.lt + stride;
+    M.bd = M.ep + stride; M.drop = M.bd + stride; M.ds = M.drop + stride;
+    memset(M.bd, 0, (size_t)stride * 3);
+    for (int q = 0; q < 8; ++q) { M.w[nstep * 32 + q] = 0; M.sp[nstep * 32 + q] = 0; }
+    for (int64_t i = s0; i < s0 + ns; ++i) if (D.seg_off[i + 1] > D.seg_off[i]) sw_or_bit(M.bd, (int32_t)(D.seg_off[i] - base));
+    for (int32_t c = 0; c < nstep * 32; ++c) {
+      uint64_t x; memcpy(&x, buf.data() + 8 * (size_t)c, 8);
+      SwCell cl = sw_classify(x);
+      M.sp[c] = (uint8_t)cl.sp; M.w[c] = (uint8_t)cl.w; M.ct[c] = (uint8_t)cl.ct; M.lt[c] = (uint8_t)cl.lt; M.ep[c] = (uint8_t)cl.ep;
+      leadv[c] = (uint8_t)cl.lead;
     }
-  }
-  for (int32_t c = 0; c < ncell; ++c) {
-    SwCodes r = sw_cell_codes(buf.data(), M, c, 0, nb);
-    for (int bit = 0; bit < 8; ++bit) {
-      int32_t k = c * 8 + bit;
-      if (k >= nb) break;
-      code[k] = ((r.ins >> bit) & 1u) ? 3 : (((r.space >> bit) & 1u) ? 2 : (((r.copy >> bit) & 1u) ? 1 : 0));
+    for (int32_t c = 0; c < nstep * 32; ++c) if (leadv[c]) sw_fix_multibyte(T, buf.data(), M, c, leadv[c], span);
+    int64_t seg = s0;
+    for (int32_t c = 0; c < ncell; ++c) {
+      const int32_t k0 = c << 3;
+      uint32_t valid = 0xffu;
+      if (k0 < al) valid &= (al - k0 >= 8) ? 0u : (0xffu << (al - k0));
+      if (k0 + 8 > span) valid &= (span <= k0) ? 0u : (0xffu >> (k0 + 8 - span));
+      uint32_t cand = sw_dup_candidates(M, c, valid & 0xffu);
+      while (cand) {
+        int bit = 0; while (!((cand >> bit) & 1u)) ++bit;
+        cand &= cand - 1;
+        const int32_t k = k0 + bit;
+        if (sw_dup_quick_reject(buf.data(), M, k, span)) continue;
+        while (seg + 1 < s0 + ns && D.seg_off[seg + 1] - base <= k) ++seg;
+        sw_mark_dup(buf.data(), M, k, (int32_t)(D.seg_off[seg] - base), (int32_t)(D.seg_off[seg + 1] - base));
+      }
+    }
+    for (int32_t c = 0; c < ncell; ++c) {
+      SwCodes r = sw_cell_codes(buf.data(), M, c, al, span);
+      for (int bit = 0; bit < 8; ++bit) {
+        const int32_t k = c * 8 + bit;
+        if (k < al) continue;
+        if (k >= span) break;
+        code[base + k] = ((r.ins >> bit) & 1u) ? 3 : (((r.space >> bit) & 1u) ? 2 : (((r.copy >> bit) & 1u) ? 1 : 0));
+      }
     }
   }
   for (int64_t i = 0; i < D.n; ++i) {
@@ -1117,7 +1138,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   if (hs_par) {
     ALLOC(hs_cls, uint8_t, braw); ALLOC(hs_code, uint8_t, braw);
     if (hs_mode && hs_mode[0] == 'p') hostsim_clean_par_count(D, ctx->T, keep, hs_cls, hs_code);
-    else hostsim_clean_swar(D, ctx->T, keep, hs_code, braw);
+    else { const char* ts = getenv("TRCHUNK_HOSTSIM_TILE"); hostsim_clean_swar(D, ctx->T, keep, hs_code, braw, ts ? atoll(ts) : 256); }   // 256 = F3_SEGS
   } else
 #endif
   LAUNCH(k_clean_count, n, 128, D, ctx->T, keep);

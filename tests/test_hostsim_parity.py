@@ -3,6 +3,7 @@ golden vectors and the oracle.  CPU only; the GPU parity tests proper are tests/
 import json
 
 import numpy as np
+import pytest
 
 import parity_common as pc
 from conftest import load_golden
@@ -36,6 +37,20 @@ def test_kats(hostsim_engine):
 def test_fuzz_cases(hostsim_engine):
     n = pc.check_fuzz_cases(hostsim_engine, load_golden("fuzz_cases.json.gz"), require_all=True)
     assert n == 160
+
+
+@pytest.mark.parametrize("tile", ["1", "3", "0"])
+def test_fuzz_cases_tile_edges(hostsim_engine, monkeypatch, tile):
+    """The cleaner's tile edges: tiles of 1 and 3 segments put every segment boundary on a tile boundary, with
+    the neighbouring tiles' bytes visible past the span, as in the fused kernel; 0 = one tile per batch."""
+    monkeypatch.setenv("TRCHUNK_HOSTSIM_TILE", tile)
+    cases = load_golden("fuzz_cases.json.gz")
+    assert pc.check_fuzz_cases(hostsim_engine, cases[::2], require_all=True) == 80
+    b, mt, _ = synth.config(5, 0.004)
+    hostsim_engine.preprocess(b)
+    P = hostsim_engine.fetch_processed()
+    for x in range(b.n_doc):
+        assert json.dumps(E.build_processed(b, P, x)) == json.dumps(OP.preprocess(synth.doc_to_segments(b, x))), x
 
 
 def test_token_counts_vs_corebpe(hostsim_engine):
