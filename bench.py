@@ -20,8 +20,9 @@ sys.path.insert(0, ROOT)
 METRIC = "transcript tokens/sec preprocess+chunk"
 UNIT = "tokens/s"
 # every array a caller needs to rebuild the processed segments and the chunks: the cleaned piece texts are
-# slices of TWC (PDST + COFF lengths), so the separate cleaned-text buffer is not copied back
-OUT_ARRAYS = [("K2R", "<i4"), ("COFF", "<i8"), ("PDST", "<i8"), ("GSTART", "<i4"), ("POFF", "<i8"), ("GTS", "u1"),
+# slices of TWC (PDST + COFF lengths) and so are the merged texts (ITEM_DST; a piece's offset inside its merged
+# text is PDST minus that), so neither the cleaned-text buffer nor the merged-text offsets are copied back
+OUT_ARRAYS = [("K2R", "<i4"), ("COFF", "<i8"), ("PDST", "<i8"), ("GSTART", "<i4"), ("GTS", "u1"),
               ("GTOK", "<i8"), ("ITEM_GROUP", "<i4"), ("ITEM_SUB", "<i4"), ("ITEM_TOK", "<i4"), ("ITEM_LEN", "<i8"),
               ("ITEM_DST", "<i8"), ("SUBS", None), ("CHUNKS", None), ("SPK_LIST", "<i4"), ("TWC", "u1"), ("DOC_ERR", "<i4"),
               ("GDOC_OFF", "<i8"), ("CDOC_OFF", "<i8")]
@@ -161,6 +162,7 @@ def main():
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--cpu-sample-mb", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-contexts", type=int, default=4, help="contexts (host threads) that take batches in turn in the end-to-end leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
     if args.impl == "reference":
@@ -265,11 +267,11 @@ def main():
                              "frac": (pipe_gbs / peak) if pipe_gbs else None},
                 "kernels_ms_per_step": {k: v[0] / args.steps for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0])}}
 
-    # end to end through the C ABI with host buffers: two contexts on two host threads alternate batches, so
+    # end to end through the C ABI with host buffers: a few contexts on their own host threads take batches in turn, so
     # one batch's D2H overlaps the next one's H2D and kernels (every step still pays its own copies)
-    eng2 = E.Engine(local)
-    workers = [(eng, torch.cuda.Stream()), (eng2, torch.cuda.Stream())]
-    pin_outs = [dict(), dict()]
+    nctx = max(1, args.e2e_contexts)
+    workers = [(eng if wi == 0 else E.Engine(local), torch.cuda.Stream()) for wi in range(nctx)]
+    pin_outs = [dict() for _ in range(nctx)]
 
     def e2e_worker(wi, nsteps, res):
         en, stream = workers[wi]
@@ -290,15 +292,15 @@ def main():
         res[wi] = total
 
     def step_e2e_pair(nsteps):
-        res = [0, 0]
-        ts = [threading.Thread(target=e2e_worker, args=(wi, (nsteps + 1 - wi) // 2, res)) for wi in range(2)]
+        res = [0] * nctx
+        ts = [threading.Thread(target=e2e_worker, args=(wi, (nsteps + nctx - 1 - wi) // nctx, res)) for wi in range(nctx)]
         for t in ts:
             t.start()
         for t in ts:
             t.join()
         return max(res)
 
-    d2h = step_e2e_pair(4)
+    d2h = step_e2e_pair(2 * nctx)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     t0 = time.perf_counter()
@@ -315,8 +317,8 @@ def main():
     h2d = int(sum(getattr(b, k).nbytes for k in ("text", "seg_off", "start", "end", "speaker", "doc_off", "spk_bytes", "spk_off")))
     e2e = {"value": tokens_all * args.steps / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps,
-           "api": "trc_preprocess + trc_chunk + trc_get_array (C ABI, pinned host buffers); two contexts on two host "
-                  "threads alternate batches; timed with the host clock around K steps"}
+           "api": "trc_preprocess + trc_chunk + trc_get_array (C ABI, pinned host buffers); %d contexts on %d host "
+                  "threads take batches in turn; timed with the host clock around K steps" % (nctx, nctx)}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -18,6 +18,9 @@ static inline cudaError_t cudaMalloc(void* pp, size_t n) { *(void**)pp = malloc(
 template <class T> static inline cudaError_t cudaMalloc(T** pp, size_t n) { *pp = (T*)malloc(n ? n : 1); return *pp ? 0 : 2; }
 static inline cudaError_t cudaFree(void* p) { free(p); return 0; }
 template <class T> static inline cudaError_t cudaMallocHost(T** pp, size_t n) { *pp = (T*)malloc(n); return 0; }
+enum { cudaHostAllocMapped = 2 };
+static inline cudaError_t cudaHostAlloc(void** pp, size_t n, int) { *pp = malloc(n); return 0; }
+static inline cudaError_t cudaHostGetDevicePointer(void** d, void* h, int) { *d = h; return 0; }
 static inline cudaError_t cudaFreeHost(void* p) { free(p); return 0; }
 static inline cudaError_t cudaMemcpy(void* d, const void* s, size_t n, cudaMemcpyKind) { memcpy(d, s, n); return 0; }
 static inline cudaError_t cudaMemcpyAsync(void* d, const void* s, size_t n, cudaMemcpyKind, cudaStream_t) { memcpy(d, s, n); return 0; }

@@ -85,7 +85,8 @@ struct trc_ctx {
   bool use_fused = true;          // single-pass clean+tokenise kernel (TRCHUNK_NO_FUSED=1 selects the v1 kernels)
   int fused_gen = 3;              // TRCHUNK_FUSED=2 selects the byte-per-lane kernel, 3 the 8-byte-cell kernel
   int64_t counts[TRC_N_COUNTERS] = {0};
-  int64_t* h_pin = nullptr;        // pinned scratch for small D2H reads (64 int64)
+  int64_t* h_pin = nullptr;        // mapped pinned scratch for small counter reads (64 int64)
+  void* d_pin = nullptr;           // its device address
   int64_t launches = 0;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   bool ev_pre = false, ev_chunk = false;
@@ -718,12 +719,24 @@ static void prof_collect(trc_ctx* ctx) {
 #endif
 #define LAUNCH_W(kern, nwarps, ...) LAUNCH(kern, (nwarps) * 32, 256, __VA_ARGS__)
 
+// Small counter reads.  A tiny kernel stores the words into mapped pinned memory instead of a D2H copy: a copy
+// would queue on the copy engine behind the bulk result transfers of other contexts working on the same GPU
+// (several contexts take batches in turn in a serving loop, bench.py's end-to-end leg) and stall this one.
+#ifndef TRC_HOSTSIM
+__global__ void k_read_back(const uint32_t* __restrict__ src, uint32_t* __restrict__ dst, int nwords) {
+  for (int k = threadIdx.x; k < nwords; k += blockDim.x) dst[k] = src[k];
+}
+#endif
 static int read_back(trc_ctx* ctx, cudaStream_t st, const void* dsrc, size_t bytes, void* hdst) {
-  // small counter reads: via pinned scratch, then one stream synchronise
-  if (bytes > 64 * sizeof(int64_t)) { ctx->err = "read_back too large"; return TRC_EINVAL; }
-  CK(cudaMemcpyAsync(ctx->h_pin, dsrc, bytes, cudaMemcpyDeviceToHost, st));
+  if (bytes > 64 * sizeof(int64_t) || (bytes & 3)) { ctx->err = "read_back size"; return TRC_EINVAL; }
+#ifdef TRC_HOSTSIM
+  memcpy(hdst, dsrc, bytes);
+#else
+  k_read_back<<<1, 64, 0, st>>>((const uint32_t*)dsrc, (uint32_t*)ctx->d_pin, (int)(bytes >> 2));
+  CK(cudaGetLastError());
   CK(cudaStreamSynchronize(st));
   memcpy(hdst, ctx->h_pin, bytes);
+#endif
   return TRC_OK;
 }
 
@@ -847,7 +860,8 @@ extern "C" int trc_create(int device, trc_ctx** out) {
   trc_ctx* ctx = new trc_ctx();
   ctx->device = device;
   if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
-      cudaMallocHost(&ctx->h_pin, 64 * sizeof(int64_t)) != cudaSuccess) { delete ctx; return TRC_ECUDA; }
+      cudaHostAlloc((void**)&ctx->h_pin, 64 * sizeof(int64_t), cudaHostAllocMapped) != cudaSuccess ||
+      cudaHostGetDevicePointer(&ctx->d_pin, ctx->h_pin, 0) != cudaSuccess) { delete ctx; return TRC_ECUDA; }
   for (int k = 0; k < 4; ++k) cudaEventCreate(&ctx->ev[k]);
   { const char* e = getenv("TRCHUNK_NO_FUSED"); ctx->use_fused = !(e && e[0] == '1'); }
   { const char* e = getenv("TRCHUNK_FUSED"); if (e && e[0] == '2') ctx->fused_gen = 2; }
