@@ -100,7 +100,8 @@ int trc_chunk(trc_ctx* ctx, const int32_t* doc_max_tokens, int32_t context_token
 /* Counters of the current batch. */
 enum {
   TRC_N_SEG = 0, TRC_N_KEPT, TRC_N_GROUPS, TRC_N_ITEMS, TRC_N_SUBS, TRC_N_CHUNKS, TRC_B_RAW, TRC_B_CLEAN,
-  TRC_B_MERGED, TRC_B_TWC, TRC_TOKENS, TRC_N_DOC, TRC_N_LONG_SPANS, TRC_N_ERR_DOCS, TRC_N_SENT, TRC_N_GIANTS, TRC_N_COUNTERS = 24
+  TRC_B_MERGED, TRC_B_TWC, TRC_TOKENS, TRC_N_DOC, TRC_N_LONG_SPANS, TRC_N_ERR_DOCS, TRC_N_SENT, TRC_N_GIANTS,
+  TRC_N_AGG, TRC_N_AGG_MEM, TRC_B_AGG, TRC_N_COUNTERS = 24
 };
 int trc_get_counts(trc_ctx* ctx, int64_t* counts /* TRC_N_COUNTERS */);
 
@@ -134,6 +135,11 @@ enum {
   TRC_A_PDST,         /* int64 [n_kept]      offset inside TRC_A_TWC where every piece starts: its "[ts] " marker  */
                       /*                     if it has one, then its cleaned text (-1: the piece                  */
                       /*                     belongs to a sentence-path item; use TRC_A_CLEAN for it)             */
+  TRC_A_AGG,          /* trc_agg [n_agg]     time-interval segments of trc_aggregate, documents back to back      */
+  TRC_A_AGG_MEM,      /* trc_agg_mem [n_agg_mem]  their member segments, every interval sorted by start (stable)  */
+  TRC_A_AGG_PIECE,    /* int32 []            kept-segment indices: the components that survive in a member        */
+  TRC_A_AGG_TEXT,     /* uint8 [B_agg]       the aggregated texts back to back                                    */
+  TRC_A_AGG_DOC_OFF,  /* int64 [n_doc+1]     trc_agg range of every document                                      */
   TRC_A__COUNT
 };
 int trc_get_array(trc_ctx* ctx, int which, void* dst, int64_t dst_bytes, int32_t memory, int64_t* nbytes,
@@ -164,6 +170,36 @@ typedef struct {            /* sentence (kind 1) / clause (kind 2) of an over-bu
   int32_t parent, ncl;
   int64_t cl0;
 } trc_sent;
+
+/* Fixed time intervals over the merged segments of the current batch: replaces aggregate_by_time_interval
+ * (preprocessor.py:217-324; preprocess_transcript calls it when time_interval_seconds is set, :62-65).
+ * Runs after trc_preprocess on the resident batch.  Interval i of a document spans
+ * [start_time + i*interval_seconds, min(that + interval_seconds, end_time)) with start_time / end_time the
+ * first segment's start / the last one's end (:232-242); a segment belongs to every interval it starts in or
+ * spans (:253-256); a combined segment keeps only the components that do (:262-287, its text is rebuilt as
+ * "[ts] text" joined by spaces) and is left out when none does; an interval's text is its members sorted by
+ * start, "[ts speaker] text" joined by blank lines (:302-307); empty intervals produce nothing (:292).
+ * The 'speaker' field of an interval (:311) is a join over a Python set, whose order depends on the
+ * interpreter's string hashing: the host builds it from the member records.
+ * Results: TRC_A_AGG / TRC_A_AGG_MEM / TRC_A_AGG_PIECE / TRC_A_AGG_TEXT / TRC_A_AGG_DOC_OFF and the counters
+ * TRC_N_AGG, TRC_N_AGG_MEM, TRC_B_AGG.  interval_seconds must be a non-zero number (Python raises
+ * ZeroDivisionError, :236); a non-positive quotient yields no intervals, as range() does. */
+int trc_aggregate(trc_ctx* ctx, double interval_seconds, void* stream);
+
+typedef struct {
+  int32_t doc, interval_index;
+  double start, end;          /* interval_start, interval_end (:241-242) */
+  int64_t mem0, mem1;         /* members [mem0, mem1) in TRC_A_AGG_MEM */
+  int64_t text_off, text_len; /* 'text' in TRC_A_AGG_TEXT */
+  uint8_t ts[48];             /* start_formatted / end_formatted, 24-byte slots [len][chars] */
+} trc_agg;
+
+typedef struct {
+  int32_t group, n_pieces;    /* merged segment (index into the document-ordered processed list of the batch);
+                                 surviving components, 0 for a segment without 'segment_timestamps' */
+  int64_t piece0;             /* components [piece0, piece0+n_pieces) in TRC_A_AGG_PIECE, sorted by start (stable) */
+  int64_t text_off, text_len; /* the member's text (what 'segment_timestamps'[k]['text'] holds, :318) in TRC_A_AGG_TEXT */
+} trc_agg_mem;
 
 /* Token counting service: counts[i] = len(encode([" "] + bytes[off[i] .. off[i+1]))) for n strings.
  * Replaces len(self.tokenizer.encode(x)) (big_chunkeroosky.py:83,298,370,510).  special[i] (may be

@@ -7,10 +7,11 @@ DEFAULT_LIB = os.path.join(_HERE, "libtrchunk.so")
 
 TRC_MEM_HOST, TRC_MEM_DEVICE = 0, 1
 COUNTERS = ["n_seg", "n_kept", "n_groups", "n_items", "n_subs", "n_chunks", "b_raw", "b_clean", "b_merged", "b_twc",
-            "tokens", "n_doc", "n_long_spans", "n_err_docs", "n_sent", "n_giants"]
+            "tokens", "n_doc", "n_long_spans", "n_err_docs", "n_sent", "n_giants", "n_agg", "n_agg_mem", "b_agg"]
 N_COUNTERS = 24
 ARRAYS = ["K2R", "COFF", "CLEAN", "CTOK", "GSTART", "POFF", "MERGED", "GTS", "GTOK", "ITEM_GROUP", "ITEM_SUB", "ITEM_TOK",
-          "ITEM_LEN", "ITEM_DST", "SUBS", "CHUNKS", "SPK_LIST", "TWC", "DOC_ERR", "GDOC_OFF", "CDOC_OFF", "CCHARS", "SENT", "PDST"]
+          "ITEM_LEN", "ITEM_DST", "SUBS", "CHUNKS", "SPK_LIST", "TWC", "DOC_ERR", "GDOC_OFF", "CDOC_OFF", "CCHARS", "SENT", "PDST",
+          "AGG", "AGG_MEM", "AGG_PIECE", "AGG_TEXT", "AGG_DOC_OFF"]
 A = {n: i for i, n in enumerate(ARRAYS)}
 ERRORS = {-1: "TRC_ECUDA", -2: "TRC_EINVAL", -3: "TRC_ENOVOCAB", -4: "TRC_EUNSUPPORTED"}
 
@@ -35,9 +36,12 @@ CHUNK_DTYPE = [("item0", "<i4"), ("item1", "<i4"), ("doc", "<i4"), ("chunk_index
 SENT_DTYPE = [("group", "<i4"), ("kind", "<i4"), ("off", "<i8"), ("len", "<i8"), ("chars", "<i4"), ("tok", "<i4"),
               ("start", "<f8"), ("end", "<f8"), ("sub", "<i4"), ("last_in_sub", "<i4"), ("off_in_sub", "<i8"),
               ("parent", "<i4"), ("ncl", "<i4"), ("cl0", "<i8")]
+AGG_DTYPE = [("doc", "<i4"), ("interval_index", "<i4"), ("start", "<f8"), ("end", "<f8"), ("mem0", "<i8"), ("mem1", "<i8"),
+             ("text_off", "<i8"), ("text_len", "<i8"), ("ts", "u1", (48,))]
+AGG_MEM_DTYPE = [("group", "<i4"), ("n_pieces", "<i4"), ("piece0", "<i8"), ("text_off", "<i8"), ("text_len", "<i8")]
 
 EXPORTS = ["trc_create", "trc_destroy", "trc_last_error", "trc_load_tables", "trc_load_vocab", "trc_preprocess",
-           "trc_chunk", "trc_get_counts", "trc_get_array", "trc_count_tokens", "trc_last_stage_ms", "trc_kernel_launches", "trc_set_profiling",
+           "trc_chunk", "trc_aggregate", "trc_get_counts", "trc_get_array", "trc_count_tokens", "trc_last_stage_ms", "trc_kernel_launches", "trc_set_profiling",
            "trc_get_profile", "trc_bpe_span_count_static"]
 
 
@@ -58,6 +62,7 @@ def load_library(path=None):
     lib.trc_load_vocab.argtypes = [vp, vp, vp, vp, i32, vp, vp, i32]
     lib.trc_preprocess.argtypes = [vp, C.POINTER(Batch), vp]
     lib.trc_chunk.argtypes = [vp, vp, i32, i32, vp]
+    lib.trc_aggregate.argtypes = [vp, C.c_double, vp]
     lib.trc_get_counts.argtypes = [vp, vp]
     lib.trc_get_array.argtypes = [vp, C.c_int, vp, i64, i32, C.POINTER(i64), vp]
     lib.trc_count_tokens.argtypes = [vp, vp, vp, i64, i32, i32, vp, vp, vp]

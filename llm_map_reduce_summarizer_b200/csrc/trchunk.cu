@@ -1249,6 +1249,18 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   return TRC_OK;
 }
 
+#include "trc_agg.cuh"
+static_assert(sizeof(TrcAggRec) == sizeof(trc_agg) && sizeof(TrcAggMemRec) == sizeof(trc_agg_mem), "aggregate record layouts");
+
+extern "C" int trc_aggregate(trc_ctx* ctx, double interval_seconds, void* stream) {
+  if (!ctx) return TRC_EINVAL;
+  if (!ctx->have_pre) { ctx->err = "trc_aggregate needs a preceding trc_preprocess"; return TRC_EINVAL; }
+  if (!(interval_seconds == interval_seconds) || interval_seconds == 0.0) { ctx->err = "interval_seconds must be a non-zero number"; return TRC_EINVAL; }
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : ctx->own_stream;
+  return aggregate_stage(ctx, st, interval_seconds);
+}
+
 extern "C" int trc_chunk(trc_ctx* ctx, const int32_t* doc_max_tokens, int32_t context_tokens, int32_t add_context, void* stream) {
   if (!ctx || !doc_max_tokens) return TRC_EINVAL;
   if (!ctx->have_pre) { ctx->err = "trc_chunk needs a preceding trc_preprocess"; return TRC_EINVAL; }

@@ -74,15 +74,17 @@ class ProcessedBatch(PackedBatch):
     groups = None
 
 
-def pack_processed(segments):
+def pack_processed(segments, for_aggregate=False):
     """One transcript given as processed-segment dicts (the output format of preprocess_transcript,
-    preprocessor.py:45-52,203-213) -> ProcessedBatch."""
+    preprocessor.py:45-52,203-213) -> ProcessedBatch.  The chunker looks at the components of a segment when
+    it has 'segment_timestamps' AND is_combined (big_chunkeroosky.py:281), the interval aggregation whenever
+    it has 'segment_timestamps' (preprocessor.py:262): for_aggregate selects the latter."""
     texts, starts, ends, spk_names, group_off, gs, ge, full = [], [], [], [], [0], [], [], []
     for seg in segments:
         sp = seg["speaker"]
         if not isinstance(sp, str):
             raise TypeError("speaker must be a str (the reference's header join fails otherwise)")
-        if "segment_timestamps" in seg and seg.get("is_combined", False):
+        if "segment_timestamps" in seg and (for_aggregate or seg.get("is_combined", False)):
             pieces = seg["segment_timestamps"]
             if len(pieces) < 2:
                 raise NotImplementedError("combined segment with fewer than two segment_timestamps entries")
@@ -201,6 +203,15 @@ class Engine:
             raise ValueError("doc_max_tokens must have one entry per document")
         self._check(self.lib.trc_chunk(self.h, mt.ctypes.data, int(context_tokens), 1 if add_context else 0, stream))
 
+    def aggregate(self, interval_seconds, stream=None):
+        """Fixed time intervals over the resident batch's merged segments (preprocessor.py:217-324)."""
+        self._check(self.lib.trc_aggregate(self.h, float(interval_seconds), stream))
+
+    def fetch_aggregated(self):
+        return {"agg": self.array("AGG", N.AGG_DTYPE), "mem": self.array("AGG_MEM", N.AGG_MEM_DTYPE),
+                "piece": self.array("AGG_PIECE", "<i4"), "text": self.array("AGG_TEXT", "u1"),
+                "adoc_off": self.array("AGG_DOC_OFF", "<i8")}
+
     def counts(self):
         c = np.zeros(N.N_COUNTERS, dtype=np.int64)
         self._check(self.lib.trc_get_counts(self.h, c.ctypes.data))
@@ -312,6 +323,36 @@ def build_processed(batch, P, doc=0, piece_dicts=None):
             d["segment_timestamps"] = [{"start": starts[int(k2r[j])], "end": ends[int(k2r[j])],
                                         "text": clean.get(int(coff[j]), int(coff[j + 1]))} for j in range(a, b)]
         out.append(d)
+    return out
+
+
+def build_aggregated(batch, P, AG, processed, interval_seconds, doc=0):
+    """Time-interval dicts of document `doc` in the reference's format (preprocessor.py:305-319).  `processed`
+    is the document's processed list (its start / end / speaker objects are reused as they are)."""
+    g0 = int(P["gdoc_off"][doc])
+    a0, a1 = int(AG["adoc_off"][doc]), int(AG["adoc_off"][doc + 1])
+    text = _Text(AG["text"])
+    mem = AG["mem"]
+    start_time, end_time = processed[0]["start"], processed[-1]["end"]
+    out = []
+    for rec in AG["agg"][a0:a1]:
+        i = int(rec["interval_index"])
+        lo = start_time + (i * interval_seconds)                      # :241-242, on the caller's own number types
+        hi = min(lo + interval_seconds, end_time)
+        if float(lo) != float(rec["start"]) or float(hi) != float(rec["end"]):
+            raise NotImplementedError("interval bounds beyond exact fp64 integer arithmetic")
+        ts = rec["ts"].tobytes()
+        members = mem[int(rec["mem0"]):int(rec["mem1"])]
+        segs = [processed[int(m["group"]) - g0] for m in members]
+        who = set(processed[g]["speaker"] for g in sorted(int(m["group"]) - g0 for m in members))   # :296 (input order)
+        out.append({"start": lo, "end": hi, "start_formatted": ts[1:1 + ts[0]].decode("ascii"),
+                    "end_formatted": ts[25:25 + ts[24]].decode("ascii"),
+                    "speaker": ", ".join(who) if len(who) > 1 else next(iter(who)),
+                    "text": text.get(int(rec["text_off"]), int(rec["text_off"] + rec["text_len"])),
+                    "is_aggregated": True, "interval_index": i, "original_segments": len(members),
+                    "segment_timestamps": [{"start": s["start"], "end": s["end"], "speaker": s["speaker"],
+                                            "text": text.get(int(m["text_off"]), int(m["text_off"] + m["text_len"]))}
+                                           for s, m in zip(segs, members)]})
     return out
 
 

@@ -3,10 +3,10 @@
 `preprocess_transcript`, `clean_text`, `format_timestamp`, `combine_same_speaker_segments` and
 `create_combined_segment` keep the reference's names, arguments, printed lines and dict formats; the
 work runs in the CUDA kernels of libtrchunk.so (stage P, include/trchunk.h: trc_preprocess).
-`aggregate_by_time_interval` (preprocessor.py:217-324) is outside the hot path (main.py never passes
-time_interval_seconds) and raises NotImplementedError rather than running on the CPU.
+`aggregate_by_time_interval` (preprocessor.py:217-324) runs on the device too (trc_aggregate).
 `extract_speakers` / `get_transcript_duration` (:326-361) are trivial host accessors.
 """
+import math
 from typing import Any, Dict, List, Optional, Tuple
 
 from . import engine as _eng
@@ -97,8 +97,42 @@ def create_combined_segment(segments: List[Dict[Any, Any]], preserve_timestamps:
 
 
 def aggregate_by_time_interval(segments: List[Dict[Any, Any]], interval_seconds: int) -> List[Dict[Any, Any]]:
-    """preprocessor.py:217-324 - not on the hot path (SURVEY.md §8f 'next')."""
-    raise NotImplementedError("aggregate_by_time_interval is outside the accelerated path (SURVEY.md §8f)")
+    """preprocessor.py:217-324: the interval membership tests, the two sorts and the text assembly run in
+    trc_aggregate; this wrapper prints the reference's lines and builds the dicts."""
+    if not segments:
+        return []
+    start_time, end_time = segments[0]["start"], segments[-1]["end"]
+    num_intervals = math.ceil((end_time - start_time) / interval_seconds)                        # :236
+    h = getattr(segments, "_trc", None)
+    if h is not None and len(segments) == len(h["ids"]) and all(id(d) == i for d, i in zip(segments, h["ids"])):
+        eng, batch = h["engine"], h["batch"]
+        if eng.batch_serial != h["serial"]:
+            h["serial"] = eng.preprocess(batch, want_merged_text=True, **h["params"])
+        P = h["P"]
+    else:
+        eng = _eng.default_engine()
+        batch = _eng.pack_processed(segments, for_aggregate=True)
+        P = None
+        for preserve in (True, False):           # how the combined texts were joined (:190-200) does not matter here,
+            eng.preprocess(batch, merge_same_speaker=True, max_segment_duration=None,   # but start/end must be the pieces'
+                           preserve_timestamps=preserve, want_merged_text=True)
+            if int(eng.array("DOC_ERR", "<i4")[0]) != -1:
+                P = eng.fetch_processed()
+                break
+        if P is None:
+            raise NotImplementedError("processed segments whose own start/end/text differ from what their "
+                                      "segment_timestamps imply are outside the device path")
+    gts = P["gts"].tobytes()
+    o = (len(segments) - 1) * 48
+    print(f"Creating {num_intervals} time intervals of {interval_seconds} seconds each")        # :240
+    print(f"Total time range: {gts[1:1 + gts[0]].decode('ascii')} - {gts[o + 25:o + 25 + gts[o + 24]].decode('ascii')} "
+          f"({end_time - start_time:.2f}s)")                                                     # :241
+    out = []
+    if num_intervals > 0:
+        eng.aggregate(interval_seconds)
+        out = _eng.build_aggregated(batch, P, eng.fetch_aggregated(), segments, interval_seconds, 0)
+    print(f"Created {len(out)} time-interval segments (some intervals may be empty)")           # :323
+    return out
 
 
 def extract_speakers(segments: List[Dict[Any, Any]]) -> List[str]:

@@ -88,8 +88,6 @@ def group_bounds(segs, max_duration):
 
 def preprocess(segments, merge_same_speaker=True, time_interval_seconds=None, max_segment_duration=120,
                preserve_timestamps=True):
-    if time_interval_seconds:
-        raise NotImplementedError("aggregate_by_time_interval is outside the hot path (SURVEY.md §8f)")
     P = _props()
     proc = []
     for seg in segments:
@@ -100,8 +98,13 @@ def preprocess(segments, merge_same_speaker=True, time_interval_seconds=None, ma
                      "start_formatted": format_ts(seg.get("start", 0)),
                      "end_formatted": format_ts(seg.get("end", 0)),
                      "speaker": seg.get("speaker", ""), "text": clean_text(raw)})
-    if not (merge_same_speaker and proc):
+    if not proc:
         return proc
+    out = _merge(proc, max_segment_duration, preserve_timestamps) if merge_same_speaker else proc
+    return aggregate(out, time_interval_seconds) if time_interval_seconds else out
+
+
+def _merge(proc, max_segment_duration, preserve_timestamps):
     out = []
     for a, b in group_bounds(proc, max_segment_duration):
         if b - a == 1:
@@ -117,4 +120,47 @@ def preprocess(segments, merge_same_speaker=True, time_interval_seconds=None, ma
                     "speaker": grp[0]["speaker"], "text": text, "is_combined": True,
                     "original_segments": b - a,
                     "segment_timestamps": [{"start": g["start"], "end": g["end"], "text": g["text"]} for g in grp]})
+    return out
+
+
+def _in_interval(lo, hi, s, e):
+    """preprocessor.py:253-256 / :270-273: starts inside [lo, hi), or starts at/before lo and ends after lo."""
+    return (lo <= s < hi) or (s <= lo and e > lo)
+
+
+def aggregate(segments, interval_seconds):
+    """preprocessor.py:217-324 (aggregate_by_time_interval), prints left out.  The joined speaker string takes
+    the iteration order of a Python set of str, like the reference (:296,:311) - identical inside one process."""
+    import math
+    if not segments:
+        return []
+    t0, t1 = segments[0]["start"], segments[-1]["end"]
+    out = []
+    for i in range(math.ceil((t1 - t0) / interval_seconds)):
+        lo = t0 + (i * interval_seconds)
+        hi = min(lo + interval_seconds, t1)
+        members = []
+        for seg in segments:
+            if not _in_interval(lo, hi, seg["start"], seg["end"]):
+                continue
+            if "segment_timestamps" not in seg:
+                members.append(dict(seg))
+                continue
+            kept = [ts for ts in seg["segment_timestamps"] if _in_interval(lo, hi, ts["start"], ts["end"])]
+            if kept:
+                m = dict(seg)
+                m["segment_timestamps"] = kept
+                m["text"] = " ".join("[" + format_ts(ts["start"]) + "] " + ts["text"]
+                                     for ts in sorted(kept, key=lambda ts: ts["start"]))
+                members.append(m)
+        if not members:
+            continue
+        who = set(m["speaker"] for m in members)
+        ordered = sorted(members, key=lambda m: m["start"])
+        out.append({"start": lo, "end": hi, "start_formatted": format_ts(lo), "end_formatted": format_ts(hi),
+                    "speaker": ", ".join(who) if len(who) > 1 else next(iter(who)),
+                    "text": "\n\n".join("[" + format_ts(m["start"]) + " " + m["speaker"] + "] " + m["text"] for m in ordered),
+                    "is_aggregated": True, "interval_index": i, "original_segments": len(members),
+                    "segment_timestamps": [{"start": m["start"], "end": m["end"], "speaker": m["speaker"], "text": m["text"]}
+                                           for m in ordered]})
     return out

@@ -94,3 +94,56 @@ def sentence_fuzz(eng, n_cases, seed):
         assert same(list(proc), op), "case %d preprocess" % it
         assert same(chunks, oc), "case %d: %s" % (it, first_diff(chunks, oc))
     return n_cases
+
+
+def agg_norm(agg):
+    """Time-interval segments with the 'speaker' join (a Python set's iteration order, preprocessor.py:296,311:
+    it differs from process to process) reduced to the set it was joined from."""
+    out = []
+    for a in agg:
+        names = set(t["speaker"] for t in a["segment_timestamps"])
+        b = dict(a)
+        if len(names) > 1:
+            assert len(a["speaker"]) == sum(map(len, names)) + 2 * (len(names) - 1) and all(n in a["speaker"] for n in names)
+            b["speaker"] = sorted(names)
+        else:
+            assert a["speaker"] == next(iter(names))
+        out.append(b)
+    return out
+
+
+def check_agg_cases(eng, cases, foreign=False):
+    """Drop-in preprocess_transcript(time_interval_seconds=...) against the reference's outputs; foreign=True
+    feeds aggregate_by_time_interval a plain deep copy of the oracle's processed list instead."""
+    import copy
+    from oracle import preprocess as OP
+    for i, cs in enumerate(cases):
+        kw = cs["kw"]
+        E.set_default_engine(eng)
+        with quiet():
+            if foreign:
+                proc = OP.preprocess(cs["segments"], kw["merge"], None, kw["max_dur"], kw["preserve"])
+                got = PP.aggregate_by_time_interval(copy.deepcopy(proc), kw["interval"]) if proc else []
+            else:
+                got = PP.preprocess_transcript(cs["segments"], kw["merge"], kw["interval"], kw["max_dur"], kw["preserve"])
+        assert same(agg_norm(got), agg_norm(cs["agg"])), "case %d: %s" % (i, first_diff(agg_norm(got), agg_norm(cs["agg"])))
+    return len(cases)
+
+
+def check_agg_batch(eng, batch, interval, docs):
+    """Engine.aggregate on a multi-document batch against the oracle, document by document (same process, so
+    the speaker joins agree too)."""
+    from llm_map_reduce_summarizer_b200 import synth
+    from oracle import preprocess as OP
+    eng.preprocess(batch)
+    P = eng.fetch_processed()
+    eng.aggregate(interval)
+    AG = eng.fetch_aggregated()
+    c = eng.counts()
+    assert c["n_agg"] == len(AG["agg"]) and c["n_agg_mem"] == len(AG["mem"]) and c["b_agg"] == len(AG["text"])
+    for x in docs:
+        segs = synth.doc_to_segments(batch, x)
+        want = OP.preprocess(segs, True, interval)
+        proc = E.build_processed(batch, P, x)
+        got = E.build_aggregated(batch, P, AG, proc, interval, x) if proc else []
+        assert same(got, want), "doc %d: %s" % (x, first_diff(got, want))

@@ -169,3 +169,15 @@ def test_foreign_processed_lists(gpu_engine):
     bad[0]["text"] = bad[0]["text"] + " edited"
     with quiet(), pytest.raises(NotImplementedError):
         c.chunk_transcript(bad)
+
+
+def test_aggregate_by_time_interval(gpu_engine):
+    """preprocessor.py:217-324 on the device, against the reference's outputs and the oracle."""
+    g = load_golden("agg_cases.json.gz")["fuzz"]
+    assert pc.check_agg_cases(gpu_engine, g) == 90
+    assert pc.check_agg_cases(gpu_engine, g[::3], foreign=True) == 30
+    b, _, _ = synth.config(3, 0.02)
+    for iv in (60, 300, 7.5):
+        pc.check_agg_batch(gpu_engine, b, iv, range(0, b.n_doc, 2))
+    b, _, _ = synth.config(2, 0.2)
+    pc.check_agg_batch(gpu_engine, b, 30, range(b.n_doc))

@@ -154,3 +154,20 @@ def test_token_counter_service(hostsim_engine):
     assert tc.total(texts) == sum(len(enc.encode(t)) for t in texts)
     with pytest.raises(ValueError):
         tc.count("bad <|endoftext|> text")
+
+
+def test_aggregate_by_time_interval(hostsim_engine):
+    g = load_golden("agg_cases.json.gz")["fuzz"]
+    assert pc.check_agg_cases(hostsim_engine, g) == 90
+    assert pc.check_agg_cases(hostsim_engine, g[::3], foreign=True) == 30
+    b, _, _ = synth.config(3, 0.002)
+    for iv in (60, 300, 7.5, 100000):
+        pc.check_agg_batch(hostsim_engine, b, iv, range(b.n_doc))
+    # error behaviour of the reference's own expression (:236)
+    E.set_default_engine(hostsim_engine)
+    with pytest.raises(ZeroDivisionError):
+        PP.aggregate_by_time_interval([{"start": 0, "end": 5, "speaker": "A", "text": "x"}], 0)
+    with pc.quiet():
+        assert PP.aggregate_by_time_interval([{"start": 0, "end": 5, "speaker": "A", "text": "x"}], -3) == []
+        assert PP.aggregate_by_time_interval([], 10) == []
+        assert PP.preprocess_transcript([{"start": 0, "end": 5, "speaker": "A", "text": " "}], True, 10) == []

@@ -52,6 +52,26 @@ def test_fuzz_cases():
         assert json.dumps(chunks) == json.dumps(cs["chunks"]), i
 
 
+def test_aggregate_cases():
+    """aggregate_by_time_interval (preprocessor.py:217-324) against the reference's outputs."""
+    import parity_common as pc
+    g = load_golden("agg_cases.json.gz")
+    nonempty = multi = 0
+    for i, cs in enumerate(g["fuzz"]):
+        kw = cs["kw"]
+        got = OP.preprocess(cs["segments"], kw["merge"], kw["interval"], kw["max_dur"], kw["preserve"])
+        assert pc.same(pc.agg_norm(got), pc.agg_norm(cs["agg"])), i
+        nonempty += bool(got)
+        multi += sum(1 for a in got if a["original_segments"] > 1)
+    assert nonempty > 60 and multi > 200
+    segs = load_golden("example_segments.json.gz")
+    for iv, e in g["example"].items():
+        out = OP.preprocess(segs, True, float(iv) if "." in iv else int(iv))
+        for o in out:
+            o["speaker"] = sorted(o["speaker"].split(", "))
+        assert len(out) == e["n"] and sha(out) == e["sha256"], iv
+
+
 def test_python_bpe_restatement_matches_corebpe():
     ranks = TK.load_ranks()
     enc = TK.encoding()

@@ -87,6 +87,28 @@ def main():
             chunks, err = None, "ValueError"
         cases.append({"segments": s, "kw": kw, "proc": proc, "chunks": chunks, "error": err})
     dump_gz(os.path.join(G, "fuzz_cases.json.gz"), cases)
+
+    # aggregate_by_time_interval (preprocessor.py:217-324) through preprocess_transcript(time_interval_seconds=...).
+    # The 'speaker' of an interval is a join over a Python set (hash order, differs between processes): the
+    # fixture keeps the reference's string and tests compare it as a set of names.
+    import contextlib, io
+    rng = random.Random(20261107)
+    agg = []
+    for it in range(90):
+        s = fuzzgen.rand_transcript(rng, long_p=0.05)
+        kw = dict(interval=rng.choice([1, 5, 10, 30, 60, 300, 7.5, 0.5, 100000, 3]), merge=rng.random() < 0.7,
+                  max_dur=rng.choice([1, 30, 120, None]), preserve=rng.random() < 0.8)
+        with contextlib.redirect_stdout(io.StringIO()):
+            out = rp.preprocess_transcript(s, kw["merge"], kw["interval"], kw["max_dur"], kw["preserve"])
+        agg.append({"segments": s, "kw": kw, "agg": out})
+    ex_agg = {}
+    for iv in (60, 300, 45.5):
+        with contextlib.redirect_stdout(io.StringIO()):
+            out = rp.preprocess_transcript(segs, True, iv)
+        for o in out:
+            o["speaker"] = sorted(o["speaker"].split(", "))
+        ex_agg[str(iv)] = {"n": len(out), "sha256": sha(out)}
+    dump_gz(os.path.join(G, "agg_cases.json.gz"), {"fuzz": agg, "example": ex_agg})
     print("golden written:", os.listdir(G))
 
 
