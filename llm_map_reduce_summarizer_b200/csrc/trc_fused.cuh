@@ -62,6 +62,9 @@ struct FuseArgs {
   unsigned long long* phase;        // optional: cycles per phase summed over CTAs (diagnostics, TRCHUNK_PHASES=1)
   SlowWord* sl; unsigned long long* sl_cnt; int64_t sl_cap;   // words left to the generic matcher (k_count_slow_words)
   GiantView G;
+  // word memo of the launch (k_clean_tok_fused3): packed word of <= 15 bytes -> token count, write-once entries of
+  // two 64-bit words {bytes 0..7, bytes 8..14 | (count+1) << 56}, claimed through memo_lock; cleared before every launch
+  unsigned long long* memo; uint32_t* memo_lock; uint32_t memo_mask;
 };
 #define FUSE_PH(i) do { if (A.phase && tid == 0) { long long now_ = clock64(); atomicAdd(&A.phase[i], (unsigned long long)(now_ - ph_t)); ph_t = now_; } } while (0)
 

@@ -79,6 +79,30 @@ __device__ __forceinline__ int f3_seg_of(const F3Smem& S, int ns, int32_t k) {
   return i;
 }
 
+#define F3_MATCH_T 128     // threads that run the packed-word matcher when only a few words are queued
+#define F3_MEMO_SLOW 254   // count value that marks a word the packed matcher cannot decide (-> slow list)
+// ---- word memo (FuseArgs::memo).  An entry only ever goes from {0, 0} to its final value, one aligned 64-bit
+// store per half, so whatever mixture of old and new halves a reader sees, it matches only a fully written entry:
+// the second half carries count+1 in its top byte (0 = not written) and keys whose first half is 0 stay out.
+__device__ __forceinline__ uint32_t f3_memo_slot(uint64_t lo, uint64_t hi, uint32_t mask) {
+  uint32_t x = (uint32_t)lo ^ ((uint32_t)(lo >> 32) * 0x9E3779B1u) ^ ((uint32_t)hi * 0x85EBCA77u) ^ ((uint32_t)(hi >> 32) * 0xC2B2AE3Du);
+  x *= 0x85EBCA6Bu; x ^= x >> 15; x *= 0xC2B2AE35u; x ^= x >> 13;
+  return x & mask;
+}
+__device__ __forceinline__ int f3_memo_get(const FuseArgs& A, uint64_t lo, uint64_t hi) {
+  if (!A.memo || lo == 0) return -1;
+  const ulonglong2 e = __ldcg(reinterpret_cast<const ulonglong2*>(A.memo) + f3_memo_slot(lo, hi, A.memo_mask));
+  if (e.x == lo && (e.y & 0x00ffffffffffffffULL) == hi && (e.y >> 56)) return (int)(e.y >> 56) - 1;
+  return -1;
+}
+__device__ __forceinline__ void f3_memo_put(const FuseArgs& A, uint64_t lo, uint64_t hi, uint32_t c) {
+  if (!A.memo || lo == 0 || c > (uint32_t)F3_MEMO_SLOW) return;
+  const uint32_t slot = f3_memo_slot(lo, hi, A.memo_mask);
+  if (atomicCAS(&A.memo_lock[slot], 0u, 1u) != 0u) return;       // write-once: the first word to claim a slot keeps it
+  st_relaxed(&A.memo[2 * (size_t)slot], lo);
+  st_relaxed(&A.memo[2 * (size_t)slot + 1], hi | ((uint64_t)(c + 1u) << 56));
+}
+
 __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTables T, const uint32_t* __restrict__ byte_id, FuseArgs A,
                                                               int64_t ntiles) {
   extern __shared__ __align__(16) unsigned char fuse_raw[];
@@ -431,52 +455,96 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
           uint64_t lo = (uint64_t)__funnelshift_r(w0, w1, sh) | ((uint64_t)__funnelshift_r(w1, w2, sh) << 32);
           if (vs) lo = (lo << 8) | (uint64_t)' ';
           lo &= (1ULL << (8 * Lw)) - 1;
-          const uint64_t ce = S.hot8[trc_key8_slot(lo, TRC_HOT8 - 1)];
-          if ((ce & 0x00ffffffffffffffULL) == lo) { atomicAdd(&S.tok[seg], (int32_t)(ce >> 56)); hit = true; }
-        }
-        if (!hit) miss[atomicAdd(&S.nmiss, 1)] = (uint16_t)w;
-      }
-      __syncthreads();
-      // pass 2 (dense): packed-word matcher for the queued words; what it cannot decide goes to the slow list
-      const int32_t nmiss = S.nmiss;
-      for (int32_t q = tid; q < nmiss; q += F3_T) {
-        const int32_t w = miss[q];
-        const int seg = S.y.w.wseg[w];
-        const int32_t st = S.y.w.wstart[w];
-        const int32_t sl = S.loff[seg];
-        const int32_t en = (w + 1 < tot_words && S.y.w.wseg[w + 1] == seg) ? (int32_t)S.y.w.wstart[w + 1] : sl + S.len[seg];
-        uint32_t c = 0;
-        const int vs = st == sl ? 1 : 0, n = en - st, Lw = n + vs;
-        bool done = false;
-        if (Lw <= 16) {
+          const uint32_t slot = trc_key8_slot(lo, TRC_HOT8 - 1);
+          const uint64_t ce = S.hot8[slot];
+          int mc = -1;
+          if ((ce & 0x00ffffffffffffffULL) == lo) mc = (int)(ce >> 56);
+          else {
+            mc = f3_memo_get(A, lo, 0);
+            if (mc >= 0) S.hot8[slot] = lo | ((uint64_t)mc << 56);
+          }
+          if (mc >= 0) { hit = true; if (mc == F3_MEMO_SLOW) slow[atomicAdd(&S.nslow, 1)] = (uint16_t)w; else atomicAdd(&S.tok[seg], mc); }
+        } else if (Lw <= 15) {
           const uint32_t* p32 = reinterpret_cast<const uint32_t*>(S.out + (st & ~3));
           const unsigned sh = (unsigned)(st & 3) * 8u;
           const uint32_t w0 = p32[0], w1 = p32[1], w2 = p32[2], w3 = p32[3], w4 = p32[4];
           uint64_t lo = (uint64_t)__funnelshift_r(w0, w1, sh) | ((uint64_t)__funnelshift_r(w1, w2, sh) << 32);
           uint64_t hi = (uint64_t)__funnelshift_r(w2, w3, sh) | ((uint64_t)__funnelshift_r(w3, w4, sh) << 32);
           if (vs) { hi = (hi << 8) | (lo >> 56); lo = (lo << 8) | (uint64_t)' '; }
-          if (Lw < 8) { lo &= (1ULL << (8 * Lw)) - 1; hi = 0; } else if (Lw == 8) hi = 0; else if (Lw < 16) hi &= (1ULL << (8 * (Lw - 8))) - 1;
-          done = trc_count_word16(T, F, lo, hi, Lw, &c);
-          if (done && Lw <= 7) S.hot8[trc_key8_slot(lo, TRC_HOT8 - 1)] = lo | ((uint64_t)c << 56);
+          if (Lw == 8) hi = 0; else hi &= (1ULL << (8 * (Lw - 8))) - 1;
+          const int mc = f3_memo_get(A, lo, hi);
+          if (mc >= 0) { hit = true; if (mc == F3_MEMO_SLOW) slow[atomicAdd(&S.nslow, 1)] = (uint16_t)w; else atomicAdd(&S.tok[seg], mc); }
         }
-        if (!done) done = trc_count_word_fast(T, F, S.out + st, n, vs, &c);
-        if (done) atomicAdd(&S.tok[seg], (int32_t)c);
-        else slow[atomicAdd(&S.nslow, 1)] = (uint16_t)w;
+        if (!hit) miss[atomicAdd(&S.nmiss, 1)] = (uint16_t)w;
       }
       __syncthreads();
+      FUSE_PH(11);
+      // pass 2 (dense): packed-word matcher for the queued words; what it cannot decide goes to the slow list
+      const int32_t nmiss = S.nmiss;
+      auto match_words = [&](int32_t first, int32_t stride) {
+        for (int32_t q = first; q < nmiss; q += stride) {
+          const int32_t w = miss[q];
+          const int seg = S.y.w.wseg[w];
+          const int32_t st = S.y.w.wstart[w];
+          const int32_t sl = S.loff[seg];
+          const int32_t en = (w + 1 < tot_words && S.y.w.wseg[w + 1] == seg) ? (int32_t)S.y.w.wstart[w + 1] : sl + S.len[seg];
+          uint32_t c = 0;
+          const int vs = st == sl ? 1 : 0, n = en - st, Lw = n + vs;
+          bool done = false;
+          if (Lw <= 16) {
+            const uint32_t* p32 = reinterpret_cast<const uint32_t*>(S.out + (st & ~3));
+            const unsigned sh = (unsigned)(st & 3) * 8u;
+            const uint32_t w0 = p32[0], w1 = p32[1], w2 = p32[2], w3 = p32[3], w4 = p32[4];
+            uint64_t lo = (uint64_t)__funnelshift_r(w0, w1, sh) | ((uint64_t)__funnelshift_r(w1, w2, sh) << 32);
+            uint64_t hi = (uint64_t)__funnelshift_r(w2, w3, sh) | ((uint64_t)__funnelshift_r(w3, w4, sh) << 32);
+            if (vs) { hi = (hi << 8) | (lo >> 56); lo = (lo << 8) | (uint64_t)' '; }
+            if (Lw < 8) { lo &= (1ULL << (8 * Lw)) - 1; hi = 0; } else if (Lw == 8) hi = 0; else if (Lw < 16) hi &= (1ULL << (8 * (Lw - 8))) - 1;
+            done = trc_count_word16(T, F, lo, hi, Lw, &c);       // what it cannot decide needs the generic matcher: remembered too
+            if (Lw <= 7) S.hot8[trc_key8_slot(lo, TRC_HOT8 - 1)] = lo | ((uint64_t)(done ? c : (uint32_t)F3_MEMO_SLOW) << 56);
+            if (Lw <= 15) f3_memo_put(A, lo, hi, done ? c : (uint32_t)F3_MEMO_SLOW);
+          } else done = trc_count_word_fast(T, F, S.out + st, n, vs, &c);
+          if (A.phase && Lw > 15) atomicAdd(&A.phase[15], 1ULL);
+          if (done) atomicAdd(&S.tok[seg], (int32_t)c);
+          else slow[atomicAdd(&S.nslow, 1)] = (uint16_t)w;
+        }
+      };
+      // Few queued words (the usual case once the memo is warm): the matcher is a latency chain on a handful of
+      // lanes, so four warps run it while the other twelve resolve the look-back and copy the cleaned tile out.
+      const bool split = nmiss <= 2 * F3_MATCH_T;
+      if (split) {
+        if (wid < F3_MATCH_T / 32) match_words(tid, F3_MATCH_T);
+        else {
+          if (wid == F3_MATCH_T / 32) {
+            long long gb = fuse_resolve(A.desc_bytes, tile, tot_out, lane);
+            long long kb = fuse_resolve(A.desc_kept, tile, tot_kept, lane);
+            if (lane == 0) { S.gbase = gb; S.kbase = kb; }
+          }
+          asm volatile("bar.sync 1, %0;" ::"n"(F3_T - F3_MATCH_T) : "memory");
+          uint8_t* dstg = D.C + S.gbase;
+          for (int32_t k = tid - F3_MATCH_T; k < tot_out; k += F3_T - F3_MATCH_T) dstg[k] = S.out[k];
+        }
+        __syncthreads();
+      } else {
+        match_words(tid, F3_T);
+        __syncthreads();
+      }
+      if (A.phase && tid == 0) {               // diagnostics: how the words split over the passes
+        atomicAdd(&A.phase[12], (unsigned long long)tot_words); atomicAdd(&A.phase[13], (unsigned long long)nmiss);
+        atomicAdd(&A.phase[14], (unsigned long long)S.nslow);
+      }
       FUSE_PH(9);
-      // the global offsets are needed from here on (long-span work list, outputs): predecessors published long ago
-      if (wid == 0) {
-        long long gb = fuse_resolve(A.desc_bytes, tile, tot_out, lane);
-        long long kb = fuse_resolve(A.desc_kept, tile, tot_kept, lane);
-        if (lane == 0) { S.gbase = gb; S.kbase = kb; }
-      }
-      __syncthreads();
-      gbase = S.gbase; kbase = S.kbase;
-      {                                        // the cleaned tile leaves shared memory once, coalesced
-        uint8_t* dstg = D.C + gbase;
+      if (!split) {
+        // the global offsets are needed from here on (long-span work list, outputs): predecessors published long ago
+        if (wid == 0) {
+          long long gb = fuse_resolve(A.desc_bytes, tile, tot_out, lane);
+          long long kb = fuse_resolve(A.desc_kept, tile, tot_kept, lane);
+          if (lane == 0) { S.gbase = gb; S.kbase = kb; }
+        }
+        __syncthreads();
+        uint8_t* dstg = D.C + S.gbase;         // the cleaned tile leaves shared memory once, coalesced
         for (int32_t k = tid; k < tot_out; k += F3_T) dstg[k] = S.out[k];
       }
+      gbase = S.gbase; kbase = S.kbase;
       FUSE_PH(10);
       const int32_t nslow = S.nslow;
       // words for the generic matcher: handed to k_count_slow_words (full occupancy) unless its list is full

@@ -87,6 +87,8 @@ struct trc_ctx {
   int64_t counts[TRC_N_COUNTERS] = {0};
   int64_t* h_pin = nullptr;        // mapped pinned scratch for small counter reads (64 int64)
   void* d_pin = nullptr;           // its device address
+  unsigned long long* d_memo = nullptr;   // word memo of the fused kernel (FuseArgs::memo): entries, then claim words
+  bool use_memo = true;
   int64_t launches = 0;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   bool ev_pre = false, ev_chunk = false;
@@ -485,6 +487,7 @@ __global__ void __launch_bounds__(LONG_T) k_bpe_long(TrcTables T, const uint32_t
 
 #endif
 #ifndef TRC_HOSTSIM
+#define TRC_MEMO_LOG2 18
 #include "trc_giant.cuh"
 #include "trc_fused.cuh"
 #include "trc_fused3.cuh"
@@ -865,6 +868,7 @@ extern "C" int trc_create(int device, trc_ctx** out) {
   for (int k = 0; k < 4; ++k) cudaEventCreate(&ctx->ev[k]);
   { const char* e = getenv("TRCHUNK_NO_FUSED"); ctx->use_fused = !(e && e[0] == '1'); }
   { const char* e = getenv("TRCHUNK_FUSED"); if (e && e[0] == '2') ctx->fused_gen = 2; }
+  { const char* e = getenv("TRCHUNK_NO_MEMO"); ctx->use_memo = !(e && e[0] == '1'); }
   *out = ctx;
   return TRC_OK;
 }
@@ -878,6 +882,7 @@ extern "C" void trc_destroy(trc_ctx* ctx) {
   if (ctx->d_props) cudaFree(ctx->d_props);
   if (ctx->d_acls) cudaFree(ctx->d_acls);
   if (ctx->h_pin) cudaFreeHost(ctx->h_pin);
+  if (ctx->d_memo) cudaFree(ctx->d_memo);
   for (int k = 0; k < 4; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
   delete ctx;
@@ -1085,6 +1090,13 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       ALLOC(A.wl, LongEntry, A.wl_cap);
       A.sl_cap = 2 * n + 1024; A.sl_cnt = fz + 7;
       ALLOC(A.sl, SlowWord, A.sl_cap);
+      A.memo = nullptr; A.memo_lock = nullptr; A.memo_mask = 0;
+      if (ctx->use_memo && ctx->fused_gen >= 3) {
+        const size_t ents = (size_t)1 << TRC_MEMO_LOG2, bytes = ents * 16 + ents * 4;
+        if (!ctx->d_memo) CK(cudaMalloc(&ctx->d_memo, bytes));
+        CK(cudaMemsetAsync(ctx->d_memo, 0, bytes, st));
+        A.memo = ctx->d_memo; A.memo_lock = (uint32_t*)(ctx->d_memo + 2 * ents); A.memo_mask = (uint32_t)(ents - 1);
+      }
       A.G = GiantView{};
       if (ctx->fused_gen >= 3) { if ((rc = giant_stage(ctx, st, braw, &A.G))) return rc; }
       static bool attr_done[64] = {false};
@@ -1117,11 +1129,12 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       }
       if (want_phases) {
         unsigned long long ph[16];
-        if ((rc = read_back(ctx, st, fz + 8, 12 * 8, ph))) return rc;
-        unsigned long long tot = 0; for (int k = 0; k < 11; ++k) tot += ph[k];
-        fprintf(stderr, "[trchunk phases %%] load %.1f  classify %.1f  dup %.1f  codes+scan %.1f  publish %.1f  scatter %.1f  words %.1f  tok-fast %.1f  resolve+copy %.1f  tok-slow %.1f  outputs %.1f\n",
+        if ((rc = read_back(ctx, st, fz + 8, 16 * 8, ph))) return rc;
+        fprintf(stderr, "[trchunk words] %llu in word lists, %llu past the word cache, %llu to the slow list, %llu matcher words longer than 15 bytes\n", ph[12], ph[13], ph[14], ph[15]);
+        unsigned long long tot = 0; for (int k = 0; k < 12; ++k) tot += ph[k];
+        fprintf(stderr, "[trchunk phases %%] load %.1f  classify %.1f  dup %.1f  codes+scan %.1f  publish %.1f  scatter %.1f  words %.1f  tok-cache %.1f  tok-match %.1f  resolve+copy %.1f  tok-slow %.1f  outputs %.1f\n",
                 100.0 * ph[0] / tot, 100.0 * ph[1] / tot, 100.0 * ph[2] / tot, 100.0 * ph[3] / tot, 100.0 * ph[4] / tot, 100.0 * ph[5] / tot,
-                100.0 * ph[6] / tot, 100.0 * ph[9] / tot, 100.0 * ph[10] / tot, 100.0 * ph[7] / tot, 100.0 * ph[8] / tot);
+                100.0 * ph[6] / tot, 100.0 * ph[11] / tot, 100.0 * ph[9] / tot, 100.0 * ph[10] / tot, 100.0 * ph[7] / tot, 100.0 * ph[8] / tot);
       }
       if (h[0] > 0) {
         uint32_t* scratch;
