@@ -162,6 +162,7 @@ def main():
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--cpu-sample-mb", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-parts", type=int, default=1, help="sub-batches a step's documents are cut into in the end-to-end leg")
     ap.add_argument("--e2e-contexts", type=int, default=4, help="contexts (host threads) that take batches in turn in the end-to-end leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
@@ -195,11 +196,6 @@ def main():
     def step_resident():
         eng.preprocess(b, want_merged_text=False, stream=sp, device_ptrs=ptrs)
         eng.chunk(mt, stream=sp)
-
-    # pinned host staging for the e2e path
-    pin_in = {k: torch.from_numpy(getattr(b, k)).pin_memory() for k in ("text", "seg_off", "start", "end", "speaker", "doc_off")}
-    hb = E.PackedBatch(pin_in["text"].numpy(), pin_in["seg_off"].numpy(), pin_in["start"].numpy(), pin_in["end"].numpy(),
-                       pin_in["speaker"].numpy(), pin_in["doc_off"].numpy(), b.speakers, None)
 
     def barrier():
         torch.cuda.synchronize()
@@ -267,20 +263,39 @@ def main():
                              "frac": (pipe_gbs / peak) if pipe_gbs else None},
                 "kernels_ms_per_step": {k: v[0] / args.steps for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0])}}
 
-    # end to end through the C ABI with host buffers: a few contexts on their own host threads take batches in turn, so
-    # one batch's D2H overlaps the next one's H2D and kernels (every step still pays its own copies)
-    nctx = max(1, args.e2e_contexts)
+    # end to end through the C ABI with host buffers.  The step's documents are independent, so the host side works
+    # like a serving loop: the batch is cut into a few sub-batches (by documents, balanced by bytes) and a few
+    # contexts, each on its own host thread and stream, take sub-batches in turn - one sub-batch's result download
+    # overlaps the next one's upload and kernels.  Every step still uploads all of its inputs from pinned host
+    # memory and downloads all of its result arrays.
+    from llm_map_reduce_summarizer_b200 import shard as SH, synth
+    nctx, nparts = max(1, args.e2e_contexts), max(1, args.e2e_parts)
+    bounds = SH.shard_ranges(b, nparts)
+    parts = []
+    for (x0, x1) in bounds:
+        sb = synth.sub_batch(b, x0, x1)
+        pin = {k: torch.from_numpy(np.ascontiguousarray(getattr(sb, k))).pin_memory()
+               for k in ("text", "seg_off", "start", "end", "speaker", "doc_off")}
+        parts.append((E.PackedBatch(pin["text"].numpy(), pin["seg_off"].numpy(), pin["start"].numpy(), pin["end"].numpy(),
+                                    pin["speaker"].numpy(), pin["doc_off"].numpy(), b.speakers, None),
+                      np.ascontiguousarray(mt[x0:x1]), pin))
     workers = [(eng if wi == 0 else E.Engine(local), torch.cuda.Stream()) for wi in range(nctx)]
     pin_outs = [dict() for _ in range(nctx)]
+    qlock = threading.Lock()
 
-    def e2e_worker(wi, nsteps, res):
+    def e2e_worker(wi, state, res):
         en, stream = workers[wi]
         torch.cuda.set_device(local)
         po = pin_outs[wi]
-        total = 0
-        for _ in range(nsteps):
-            en.preprocess(hb, want_merged_text=False, stream=stream.cuda_stream)
-            en.chunk(mt, stream=stream.cuda_stream)
+        while True:
+            with qlock:
+                item = state[0]
+                if item >= state[1]:
+                    return
+                state[0] = item + 1
+            hb_, mt_, _ = parts[item % nparts]
+            en.preprocess(hb_, want_merged_text=False, stream=stream.cuda_stream)
+            en.chunk(mt_, stream=stream.cuda_stream)
             total = 0
             for name, _ in OUT_ARRAYS:
                 nb = en.array_into(name, None, 0)
@@ -289,18 +304,19 @@ def main():
                 if nb:
                     en.array_into(name, po[name].data_ptr(), po[name].numel(), N.TRC_MEM_HOST, stream.cuda_stream)
                 total += nb
-        res[wi] = total
+            with qlock:
+                res[item % nparts] = total
 
     def step_e2e_pair(nsteps):
-        res = [0] * nctx
-        ts = [threading.Thread(target=e2e_worker, args=(wi, (nsteps + nctx - 1 - wi) // nctx, res)) for wi in range(nctx)]
+        res, state = [0] * nparts, [0, nsteps * nparts]
+        ts = [threading.Thread(target=e2e_worker, args=(wi, state, res)) for wi in range(nctx)]
         for t in ts:
             t.start()
         for t in ts:
             t.join()
-        return max(res)
+        return sum(res)
 
-    d2h = step_e2e_pair(2 * nctx)
+    d2h = step_e2e_pair(max(2, (2 * nctx + nparts - 1) // nparts))
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     t0 = time.perf_counter()
@@ -314,11 +330,13 @@ def main():
         t = torch.tensor([ms_e2e], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_e2e = float(t.item())
-    h2d = int(sum(getattr(b, k).nbytes for k in ("text", "seg_off", "start", "end", "speaker", "doc_off", "spk_bytes", "spk_off")))
+    h2d = int(sum(v.numel() * v.element_size() for _, _, pin in parts for v in pin.values())
+              + nparts * (b.spk_bytes.nbytes + b.spk_off.nbytes))
     e2e = {"value": tokens_all * args.steps / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps,
-           "api": "trc_preprocess + trc_chunk + trc_get_array (C ABI, pinned host buffers); %d contexts on %d host "
-                  "threads take batches in turn; timed with the host clock around K steps" % (nctx, nctx)}
+           "api": "trc_preprocess + trc_chunk + trc_get_array (C ABI, pinned host buffers); every step's documents go "
+                  "through as %d sub-batches taken in turn by %d contexts on %d host threads; timed with the host "
+                  "clock around K steps" % (nparts, nctx, nctx)}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
