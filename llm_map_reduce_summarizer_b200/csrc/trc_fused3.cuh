@@ -16,6 +16,7 @@
 #define F3_NSTEP (F3_IN_CAP / 256)
 #define F3_MASKS 9
 #define F3_MSTRIDE (F3_NCELL + 8)
+#define F3_HINT_LOG2 4
 
 struct F3Smem {
   union alignas(16) {                         // raw tile; after the scatter: sorted word list
@@ -32,7 +33,7 @@ struct F3Smem {
   uint16_t cand[F3_CAND_CAP];
   uint16_t pre_o[F3_NCELL + 32], pre_s[F3_NCELL + 32];   // per cell: output bytes / spaces before it, inside its step
   uint16_t st_o[F3_NSTEP + 1], st_s[F3_NSTEP + 1], st_t[F3_NSTEP + 1];
-  uint16_t blk_seg[F3_IN_CAP / 64];         // segment of the first byte of every 64-byte block
+  uint16_t blk_seg[F3_IN_CAP >> F3_HINT_LOG2];   // segment of the first byte of every 16-byte block
   uint16_t sg_o[F3_SEGS + 1], sg_s[F3_SEGS + 1], sg_t[F3_SEGS + 1];   // step-relative prefixes at segment starts
   uint16_t spb[F3_SEGS + 1], ctb[F3_SEGS + 1];
   int32_t rel[F3_SEGS + 1];
@@ -42,6 +43,7 @@ struct F3Smem {
   int32_t tot[3];
   int32_t ncand, nslow, nmiss, has_sp;
   unsigned int tile;
+  int32_t doc0;                             // document of the tile's first segment
   long long gbase, kbase, slbase;
 };
 static_assert(sizeof(F3Smem) <= 115200, "two CTAs per SM");
@@ -74,9 +76,29 @@ __device__ __forceinline__ void f3_scan3(F3Smem& S, int lane, int wid, int32_t v
 
 // segment of tile byte k, starting the search at the first segment of k's step
 __device__ __forceinline__ int f3_seg_of(const F3Smem& S, int ns, int32_t k) {
-  int i = S.blk_seg[k >> 6];
+  int i = S.blk_seg[k >> F3_HINT_LOG2];
   while (i + 1 < ns && S.rel[i + 1] <= k) ++i;
   return i;
+}
+
+// Copies n bytes of the shared tile (src 16-byte aligned, readable a few words past n) to global memory with
+// 16-byte stores aligned to the DESTINATION: five aligned shared words and four funnel shifts per store; the
+// bytes before the first and after the last aligned 16 go one by one.  Threads t of nt cooperate.
+__device__ __forceinline__ void f3_copy_out(uint8_t* dstg, const uint8_t* src, int32_t n, int t, int nt) {
+  const int head = (int)((16 - ((uintptr_t)dstg & 15)) & 15);
+  if (n < 64 + head) { for (int32_t k = t; k < n; k += nt) dstg[k] = src[k]; return; }
+  if (t < head) dstg[t] = src[t];
+  const int32_t nq = (n - head) >> 4;
+  const uint32_t* sw = reinterpret_cast<const uint32_t*>(src) + (head >> 2);
+  const unsigned sh = (unsigned)(head & 3) * 8u;
+  uint4* dq = reinterpret_cast<uint4*>(dstg + head);
+  for (int32_t i = t; i < nq; i += nt) {
+    const uint32_t* w = sw + 4 * i;
+    const uint32_t a = w[0], b = w[1], c = w[2], d = w[3], e = w[4];
+    dq[i] = make_uint4(__funnelshift_r(a, b, sh), __funnelshift_r(b, c, sh), __funnelshift_r(c, d, sh), __funnelshift_r(d, e, sh));
+  }
+  const int32_t done = head + (nq << 4);
+  if (t < n - done) dstg[done + t] = src[done + t];
 }
 
 #define F3_MATCH_T 128     // threads that run the packed-word matcher when only a few words are queued
@@ -125,6 +147,19 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
     if ((int64_t)tile >= ntiles) break;
     const int64_t s0 = (int64_t)tile * F3_SEGS;
     const int ns = (int)((D.n - s0) < F3_SEGS ? (D.n - s0) : F3_SEGS);
+    if (wid == F3_NW - 1) {                   // document of the first segment: one 32-ary search per tile, under the tile load
+      int64_t lo = 0, hi = D.n_doc;           // doc_off[lo] <= s0 < doc_off[hi]
+      while (hi - lo > 1) {
+        const int64_t step = (hi - lo + 31) >> 5;
+        const int64_t pv = lo + step * (lane + 1);
+        const bool le = pv < hi && D.doc_off[pv] <= s0;
+        const int cnt = __popc(__ballot_sync(0xffffffffu, le));       // doc_off is sorted: the lanes that say yes are a prefix
+        const int64_t nhi = lo + step * (cnt + 1);
+        lo += step * cnt;
+        if (nhi < hi) hi = nhi;
+      }
+      if (lane == 0) S.doc0 = (int32_t)lo;
+    }
     const int64_t raw0 = D.seg_off[s0], raw1 = D.seg_off[s0 + ns];
     const int al = (int)(raw0 & 15);
     const int64_t base = raw0 - al;
@@ -157,7 +192,7 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
         const int32_t a = S.rel[tid], b = S.rel[tid + 1];
         if (b > a) {
           sw_or_bit(M.bd, a);
-          for (int32_t s = (a + 63) >> 6; (s << 6) < b; ++s) S.blk_seg[s] = (uint16_t)tid;
+          for (int32_t s = (a + (1 << F3_HINT_LOG2) - 1) >> F3_HINT_LOG2; (s << F3_HINT_LOG2) < b; ++s) S.blk_seg[s] = (uint16_t)tid;
         }
       }
       if (tid == 0) S.blk_seg[0] = 0;
@@ -332,6 +367,12 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
           if (!(cp | se)) continue;
           int32_t pos = S.st_o[st] + S.pre_o[c];
           const unsigned long long x = S.y.in64[c];
+          if (in == 0u && (cp | se) == 0xffu) {   // the common cell: every byte yields exactly one byte
+            uint8_t* d8 = dst + pos;
+#pragma unroll
+            for (int bit = 0; bit < 8; ++bit) d8[bit] = ((se >> bit) & 1u) ? (uint8_t)' ' : (uint8_t)(x >> (8 * bit));
+            continue;
+          }
 #pragma unroll
           for (int bit = 0; bit < 8; ++bit) {
             if ((in >> bit) & 1u) dst[pos++] = ' ';
@@ -353,7 +394,7 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
         __syncthreads();
         gbase = S.gbase; kbase = S.kbase;
         uint8_t* dstg = D.C + gbase;
-        for (int32_t k = tid; k < tot_out; k += F3_T) dstg[k] = S.out[k];
+        f3_copy_out(dstg, S.out, tot_out, tid, F3_T);
       }
       (void)resolved_early;
       if (fast_out) {
@@ -520,8 +561,7 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
             if (lane == 0) { S.gbase = gb; S.kbase = kb; }
           }
           asm volatile("bar.sync 1, %0;" ::"n"(F3_T - F3_MATCH_T) : "memory");
-          uint8_t* dstg = D.C + S.gbase;
-          for (int32_t k = tid - F3_MATCH_T; k < tot_out; k += F3_T - F3_MATCH_T) dstg[k] = S.out[k];
+          f3_copy_out(D.C + S.gbase, S.out, tot_out, tid - F3_MATCH_T, F3_T - F3_MATCH_T);
         }
         __syncthreads();
       } else {
@@ -541,8 +581,7 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
           if (lane == 0) { S.gbase = gb; S.kbase = kb; }
         }
         __syncthreads();
-        uint8_t* dstg = D.C + S.gbase;         // the cleaned tile leaves shared memory once, coalesced
-        for (int32_t k = tid; k < tot_out; k += F3_T) dstg[k] = S.out[k];
+        f3_copy_out(D.C + S.gbase, S.out, tot_out, tid, F3_T);   // the cleaned tile leaves shared memory once, coalesced
       }
       gbase = S.gbase; kbase = S.kbase;
       FUSE_PH(10);
@@ -601,8 +640,12 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
         const int64_t j = kbase + koff;
         const int64_t i = s0 + tid;
         D.k2r[j] = (int32_t)i; D.coff[j] = gbase + loff; D.ctok[j] = (uint32_t)S.tok[tid]; A.seg_special[j] = mysp;
-        int64_t lo = 0, hi = D.n_doc;
-        while (hi - lo > 1) { int64_t mid = (lo + hi) >> 1; if (D.doc_off[mid] <= i) lo = mid; else hi = mid; }
+        int64_t lo = S.doc0;                  // documents are rarely shorter than a few segments: walk, then search
+        for (int q = 0; q < 4 && D.doc_off[lo + 1] <= i; ++q) ++lo;
+        if (D.doc_off[lo + 1] <= i) {
+          int64_t hi = D.n_doc;
+          while (hi - lo > 1) { int64_t mid = (lo + hi) >> 1; if (D.doc_off[mid] <= i) lo = mid; else hi = mid; }
+        }
         D.sdoc[j] = (int32_t)lo;
       }
     }
