@@ -481,42 +481,50 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
       uint16_t* miss = S.z.slow + F3_WORD_CAP;
       if (tid == 0) S.nmiss = 0;
       __syncthreads();
-      // pass 1 (uniform): probe the word cache; misses and words longer than 7 bytes are queued
-      for (int32_t w = tid; w < tot_words; w += F3_T) {
-        const int seg = S.y.w.wseg[w];
+      // pass 1 (uniform): probe the word cache, then the launch memo (L2); what neither knows is queued.  Two words
+      // per thread and round, so that the two memo loads are in flight together.
+      auto p1_key = [&](int32_t w, uint64_t& lo, uint64_t& hi, int& seg, int& mc, uint32_t& slot8) -> bool {
+        mc = -1; seg = -1; lo = hi = 0; slot8 = 0xffffffffu;
+        if (w >= tot_words) return false;
+        seg = S.y.w.wseg[w];
         const int32_t st = S.y.w.wstart[w];
         const int32_t sl = S.loff[seg];
         const int32_t en = (w + 1 < tot_words && S.y.w.wseg[w + 1] == seg) ? (int32_t)S.y.w.wstart[w + 1] : sl + S.len[seg];
         const int vs = st == sl ? 1 : 0, Lw = en - st + vs;
-        bool hit = false;
+        if (Lw > 15) return false;
+        const uint32_t* p32 = reinterpret_cast<const uint32_t*>(S.out + (st & ~3));
+        const unsigned sh = (unsigned)(st & 3) * 8u;
+        const uint32_t w0 = p32[0], w1 = p32[1], w2 = p32[2], w3 = p32[3], w4 = p32[4];
+        lo = (uint64_t)__funnelshift_r(w0, w1, sh) | ((uint64_t)__funnelshift_r(w1, w2, sh) << 32);
+        hi = (uint64_t)__funnelshift_r(w2, w3, sh) | ((uint64_t)__funnelshift_r(w3, w4, sh) << 32);
+        if (vs) { hi = (hi << 8) | (lo >> 56); lo = (lo << 8) | (uint64_t)' '; }
+        if (Lw < 8) { lo &= (1ULL << (8 * Lw)) - 1; hi = 0; } else if (Lw == 8) hi = 0; else hi &= (1ULL << (8 * (Lw - 8))) - 1;
         if (Lw <= 7) {
-          const uint32_t* p32 = reinterpret_cast<const uint32_t*>(S.out + (st & ~3));
-          const unsigned sh = (unsigned)(st & 3) * 8u;
-          const uint32_t w0 = p32[0], w1 = p32[1], w2 = p32[2];
-          uint64_t lo = (uint64_t)__funnelshift_r(w0, w1, sh) | ((uint64_t)__funnelshift_r(w1, w2, sh) << 32);
-          if (vs) lo = (lo << 8) | (uint64_t)' ';
-          lo &= (1ULL << (8 * Lw)) - 1;
-          const uint32_t slot = trc_key8_slot(lo, TRC_HOT8 - 1);
-          const uint64_t ce = S.hot8[slot];
-          int mc = -1;
-          if ((ce & 0x00ffffffffffffffULL) == lo) mc = (int)(ce >> 56);
-          else {
-            mc = f3_memo_get(A, lo, 0);
-            if (mc >= 0) S.hot8[slot] = lo | ((uint64_t)mc << 56);
-          }
-          if (mc >= 0) { hit = true; if (mc == F3_MEMO_SLOW) slow[atomicAdd(&S.nslow, 1)] = (uint16_t)w; else atomicAdd(&S.tok[seg], mc); }
-        } else if (Lw <= 15) {
-          const uint32_t* p32 = reinterpret_cast<const uint32_t*>(S.out + (st & ~3));
-          const unsigned sh = (unsigned)(st & 3) * 8u;
-          const uint32_t w0 = p32[0], w1 = p32[1], w2 = p32[2], w3 = p32[3], w4 = p32[4];
-          uint64_t lo = (uint64_t)__funnelshift_r(w0, w1, sh) | ((uint64_t)__funnelshift_r(w1, w2, sh) << 32);
-          uint64_t hi = (uint64_t)__funnelshift_r(w2, w3, sh) | ((uint64_t)__funnelshift_r(w3, w4, sh) << 32);
-          if (vs) { hi = (hi << 8) | (lo >> 56); lo = (lo << 8) | (uint64_t)' '; }
-          if (Lw == 8) hi = 0; else hi &= (1ULL << (8 * (Lw - 8))) - 1;
-          const int mc = f3_memo_get(A, lo, hi);
-          if (mc >= 0) { hit = true; if (mc == F3_MEMO_SLOW) slow[atomicAdd(&S.nslow, 1)] = (uint16_t)w; else atomicAdd(&S.tok[seg], mc); }
+          slot8 = trc_key8_slot(lo, TRC_HOT8 - 1);
+          const uint64_t ce = S.hot8[slot8];
+          if ((ce & 0x00ffffffffffffffULL) == lo) { mc = (int)(ce >> 56); return false; }
         }
-        if (!hit) miss[atomicAdd(&S.nmiss, 1)] = (uint16_t)w;
+        return A.memo != nullptr && lo != 0;
+      };
+      auto p1_fin = [&](int32_t w, uint64_t lo, uint64_t hi, int seg, int mc, uint32_t slot8, bool asked, const ulonglong2& e) {
+        if (seg < 0) return;
+        if (asked && e.x == lo && (e.y & 0x00ffffffffffffffULL) == hi && (e.y >> 56)) {
+          mc = (int)(e.y >> 56) - 1;
+          if (slot8 != 0xffffffffu) S.hot8[slot8] = lo | ((uint64_t)mc << 56);
+        }
+        if (mc < 0) miss[atomicAdd(&S.nmiss, 1)] = (uint16_t)w;
+        else if (mc == F3_MEMO_SLOW) slow[atomicAdd(&S.nslow, 1)] = (uint16_t)w;
+        else atomicAdd(&S.tok[seg], mc);
+      };
+      for (int32_t wb = tid; wb < tot_words; wb += 2 * F3_T) {
+        uint64_t lo0, hi0, lo1, hi1; int sg0, sg1, mc0, mc1; uint32_t s80, s81;
+        const bool ask0 = p1_key(wb, lo0, hi0, sg0, mc0, s80);
+        const bool ask1 = p1_key(wb + F3_T, lo1, hi1, sg1, mc1, s81);
+        ulonglong2 e0 = make_ulonglong2(0, 0), e1 = make_ulonglong2(0, 0);
+        if (ask0) e0 = __ldcg(reinterpret_cast<const ulonglong2*>(A.memo) + f3_memo_slot(lo0, hi0, A.memo_mask));
+        if (ask1) e1 = __ldcg(reinterpret_cast<const ulonglong2*>(A.memo) + f3_memo_slot(lo1, hi1, A.memo_mask));
+        p1_fin(wb, lo0, hi0, sg0, mc0, s80, ask0, e0);
+        p1_fin(wb + F3_T, lo1, hi1, sg1, mc1, s81, ask1, e1);
       }
       __syncthreads();
       FUSE_PH(11);
