@@ -81,7 +81,7 @@ TRC_HD void sw_or_bit(uint8_t* arr, int32_t k) { sw_or_bits(arr, k >> 3, 1u << (
 // byte of the character (they may spill into the next cell).  `in` is tile-relative, hi = end of the tile.
 TRC_HD void sw_fix_multibyte(const TrcTables& T, const uint8_t* in, const SwMasks& M, int32_t cell, uint32_t lead, int32_t hi) {
   while (lead) {
-    int bit = 0; while (!((lead >> bit) & 1u)) ++bit;
+    const int bit = (int)trc_ctz32(lead);
     lead &= lead - 1;
     int32_t k = cell * 8 + bit;
     int len;
@@ -168,7 +168,7 @@ TRC_HD SwCodes sw_cell_codes(const uint8_t* in, const SwMasks& M, int32_t c, int
   {
     uint32_t t = mb;
     while (t) {
-      int bit = 0; while (!((t >> bit) & 1u)) ++bit;
+      const int bit = (int)trc_ctz32(t);
       t &= t - 1;
       int32_t k = k0 + bit;
       uint8_t ch = in[k];
