@@ -162,6 +162,7 @@ def main():
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--cpu-sample-mb", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-repeats", type=int, default=3, help="repetitions of the K-step end-to-end leg (median reported)")
     ap.add_argument("--e2e-parts", type=int, default=1, help="sub-batches a step's documents are cut into in the end-to-end leg")
     ap.add_argument("--e2e-contexts", type=int, default=4, help="contexts (host threads) that take batches in turn in the end-to-end leg")
     args = ap.parse_args()
@@ -256,8 +257,15 @@ def main():
     ach = kb / (per_launch_ms / 1e3) / 1e9 if per_launch_ms > 0 else 0.0
     A = algorithmic_bytes(counts)
     pipe_gbs = A * args.steps / (ms / 1e3) / 1e9 if world == 1 else None
+    traffic = None
+    try:        # DRAM bytes of that kernel from the committed ncu --set full capture (same workload only)
+        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(tname)
+        if tr and tr.get("config") == args.config and tr.get("scale") == args.scale:
+            traffic = tr["dram_bytes_per_launch"]
+    except Exception:
+        pass
     roofline = {"bound": "hbm", "kernel": tname, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": kb,
+                "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": kb,
                 "kernel_ms_per_launch": per_launch_ms, "kernel_share_of_step": tms / tot_ms,
                 "pipeline": {"algorithmic_bytes_per_step": A, "achieved_gbs": pipe_gbs,
                              "frac": (pipe_gbs / peak) if pipe_gbs else None},
@@ -317,23 +325,27 @@ def main():
         return sum(res)
 
     d2h = step_e2e_pair(max(2, (2 * nctx + nparts - 1) // nparts))
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    t0 = time.perf_counter()
-    e0.record(st)
-    step_e2e_pair(args.steps)
-    torch.cuda.synchronize()
-    e1.record(st)
-    barrier()
-    ms_e2e = (time.perf_counter() - t0) * 1e3        # host clock: the work runs on the workers' own streams
-    if world > 1:
-        t = torch.tensor([ms_e2e], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_e2e = float(t.item())
+    # K steps, timed with the host clock (the work runs on the workers' own streams), max over ranks; repeated a few
+    # times because the PCIe leg shares the host with other tenants: the median run is reported, all runs are listed
+    runs = []
+    for _ in range(max(1, args.e2e_repeats)):
+        barrier()
+        t0 = time.perf_counter()
+        step_e2e_pair(args.steps)
+        torch.cuda.synchronize()
+        barrier()
+        ms_run = (time.perf_counter() - t0) * 1e3
+        if world > 1:
+            t = torch.tensor([ms_run], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms_run = float(t.item())
+        runs.append(ms_run)
+    ms_e2e = sorted(runs)[len(runs) // 2]
     h2d = int(sum(v.numel() * v.element_size() for _, _, pin in parts for v in pin.values())
               + nparts * (b.spk_bytes.nbytes + b.spk_off.nbytes))
     e2e = {"value": tokens_all * args.steps / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps,
+           "ms_per_step_runs": [r / args.steps for r in runs],
            "api": "trc_preprocess + trc_chunk + trc_get_array (C ABI, pinned host buffers); every step's documents go "
                   "through as %d sub-batches taken in turn by %d contexts on %d host threads; timed with the host "
                   "clock around K steps" % (nparts, nctx, nctx)}

@@ -736,6 +736,7 @@ static int read_back(trc_ctx* ctx, cudaStream_t st, const void* dsrc, size_t byt
   memcpy(hdst, dsrc, bytes);
 #else
   k_read_back<<<1, 64, 0, st>>>((const uint32_t*)dsrc, (uint32_t*)ctx->d_pin, (int)(bytes >> 2));
+  ctx->launches++;
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(st));
   memcpy(hdst, ctx->h_pin, bytes);
