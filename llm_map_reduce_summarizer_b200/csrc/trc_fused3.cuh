@@ -602,10 +602,14 @@ __global__ void __launch_bounds__(F3_T, 2) k_clean_tok_fused3(TrcDev D, TrcTable
       // words for the generic matcher: handed to k_count_slow_words (full occupancy) unless its list is full
       if (tid == 0) {
         unsigned long long b0 = nslow ? atomicAdd(A.sl_cnt, (unsigned long long)nslow) : 0ULL;
-        S.slbase = ((int64_t)b0 + nslow <= A.sl_cap) ? (long long)b0 : -1LL;
+        S.slbase = ((int64_t)b0 + nslow <= A.sl_cap) ? (long long)b0 : ((int64_t)b0 < A.sl_cap ? -2LL - (long long)b0 : -1LL);
       }
       __syncthreads();
       const long long slbase = S.slbase;
+      if (slbase < -1) {                       // the reservation ran over the end of the list: its part inside the list
+        SlowWord e; e.pos = 0; e.len_vs = 0; e.unit = 0;   // becomes empty words, the tile counts its words inline
+        for (int64_t q = -2 - slbase + tid; q < A.sl_cap; q += F3_T) A.sl[q] = e;
+      }
       for (int32_t q = tid; q < nslow; q += F3_T) {
         const int32_t w = slow[q];
         const int seg = S.y.w.wseg[w];

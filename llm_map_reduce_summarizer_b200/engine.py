@@ -120,7 +120,9 @@ def pack_processed(segments, for_aggregate=False):
 class Engine:
     """One context on one GPU.  Not thread-safe (one engine per thread / per rank)."""
 
-    def __init__(self, device=0, lib_path=None, tokenizer_name="cl100k_base"):
+    def __init__(self, device=0, lib_path=None, tokenizer_name="cl100k_base", rank_table=None):
+        """rank_table: optional (name, tokens: list[bytes], ranks: list[int]) instead of the table
+        `tokenizer_name` resolves to (any byte-pair table whose ranks are its merge priorities)."""
         self.lib = N.load_library(lib_path)
         h = C.c_void_p()
         rc = self.lib.trc_create(int(device), C.byref(h))
@@ -132,7 +134,7 @@ class Engine:
         self.device = device
         props = _vocab.load_props()
         self._check(self.lib.trc_load_tables(self.h, props.ctypes.data))
-        self.vocab_name, toks, ranks = _vocab.load_rank_table(tokenizer_name)
+        self.vocab_name, toks, ranks = rank_table if rank_table is not None else _vocab.load_rank_table(tokenizer_name)
         tb, to = _vocab.pack_strings(toks)
         rk = np.array(ranks, dtype=np.int32)
         self.specials = list(_vocab.SPECIALS)

@@ -25,6 +25,11 @@ def quiet():
         yield
 
 
+def hostsim_library():
+    from llm_map_reduce_summarizer_b200 import build
+    return build.build_hostsim()
+
+
 @pytest.fixture(scope="session")
 def hostsim_engine():
     """TEST INFRASTRUCTURE: the product sources compiled by g++ (tests/hostsim), so the CPU suite can

@@ -147,3 +147,53 @@ def check_agg_batch(eng, batch, interval, docs):
         proc = E.build_processed(batch, P, x)
         got = E.build_aggregated(batch, P, AG, proc, interval, x) if proc else []
         assert same(got, want), "doc %d: %s" % (x, first_diff(got, want))
+
+
+def small_rank_tables():
+    """Other byte-pair tables for the table-driven kernels: the 256 single bytes (every token is one byte, SURVEY.md
+    Appendix C.2) and the first 1 200 ranks of the repo table (a prefix of a BPE table is a BPE table; nearly every
+    word then needs byte-pair merging, long spans included)."""
+    from oracle import tokenizer as TK
+    full = TK.load_ranks()
+    by_rank = sorted(full.items(), key=lambda kv: kv[1])
+    out = []
+    for name, n in (("bytes256", 256), ("prefix1200", 1200)):
+        sub = dict(by_rank[:n])
+        assert all(len(t) == 1 for t, r in by_rank[:256])
+        out.append((name, sub))
+    return out
+
+
+def check_other_vocab(make_engine, name, ranks, n_cases=25, seed=3):
+    """Drop-in vs oracle under the rank table `ranks` (dict bytes -> rank)."""
+    import random
+    import fuzzgen
+    from oracle import chunker as OC, preprocess as OP, tokenizer as TK
+    toks = sorted(ranks, key=lambda t: ranks[t])
+    eng = make_engine((name, toks, [ranks[t] for t in toks]))
+    enc = TK.encoding(ranks, name)
+    count = lambda s_: len(enc.encode(s_))
+    strs = ["", " ", "hello world", "a" * 120, "ab" * 70 + " x", "!" * 90, "don't stop-me now", "naïve café 你好", "1234567 89",
+            "The quick brown fox jumps over the lazy dog.", "  lead", "trail  ", "x\ny\r\n z", "supercalifragilisticexpialidocious"]
+    cnt, _ = eng.count_tokens(strs)
+    for s_, c in zip(strs, cnt):
+        assert c == len(enc.encode_ordinary(s_)), (name, s_)
+    rng = random.Random(seed)
+    done = 0
+    for it in range(n_cases):
+        segs = fuzzgen.rand_transcript(rng, long_p=0.1)
+        mt = rng.choice([170, 260, 400, 4000])
+        merge = rng.random() < 0.8
+        want_p = OP.preprocess(segs, merge)
+        try:
+            want_c = OC.ChunkerOracle(mt, count=count).chunk(want_p)
+        except ValueError:
+            want_c = "ValueError"
+        try:
+            got_p, got_c = run_dropin(eng, segs, mt, merge)
+        except ValueError:
+            got_p, got_c = want_p, "ValueError"
+        assert same(list(got_p), want_p), (name, it)
+        assert same(got_c, want_c), (name, it, first_diff(got_c, want_c) if isinstance(want_c, list) and isinstance(got_c, list) else (got_c, want_c))
+        done += 1
+    return done

@@ -181,3 +181,25 @@ def test_aggregate_by_time_interval(gpu_engine):
         pc.check_agg_batch(gpu_engine, b, iv, range(0, b.n_doc, 2))
     b, _, _ = synth.config(2, 0.2)
     pc.check_agg_batch(gpu_engine, b, 30, range(b.n_doc))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("table", pc.small_rank_tables(), ids=lambda t: t[0])
+def test_other_rank_tables(table):
+    """The kernels are table driven: the same parity under two other byte-pair tables (nearly every
+    word needs byte-pair merging under the small one: slow-word kernel, long-span kernel, memo of failures)."""
+    name, ranks = table
+    assert pc.check_other_vocab(lambda rt: E.Engine(0, rank_table=rt), name, ranks, n_cases=40) == 40
+    # and a synthetic batch through the fused kernel, token totals against the oracle tokenizer
+    from oracle import tokenizer as TK
+    toks = sorted(ranks, key=lambda t: ranks[t])
+    eng = E.Engine(0, rank_table=(name, toks, [ranks[t] for t in toks]))
+    b, mt, _ = synth.config(3, 0.01)
+    eng.preprocess(b)
+    P = eng.fetch_processed()
+    enc = TK.encoding(ranks, name)
+    clean = P["clean"].tobytes()
+    coff = P["coff"]
+    for j in range(0, len(P["k2r"]), 7):
+        t = clean[int(coff[j]):int(coff[j + 1])].decode("utf-8")
+        assert int(P["ctok"][j]) == len(enc.encode_ordinary(" " + t)), (name, j)

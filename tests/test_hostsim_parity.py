@@ -171,3 +171,11 @@ def test_aggregate_by_time_interval(hostsim_engine):
         assert PP.aggregate_by_time_interval([{"start": 0, "end": 5, "speaker": "A", "text": "x"}], -3) == []
         assert PP.aggregate_by_time_interval([], 10) == []
         assert PP.preprocess_transcript([{"start": 0, "end": 5, "speaker": "A", "text": " "}], True, 10) == []
+
+
+@pytest.mark.parametrize("table", pc.small_rank_tables(), ids=lambda t: t[0])
+def test_other_rank_tables(table):
+    """The kernels are table driven: the same parity under two other byte-pair tables."""
+    import conftest
+    name, ranks = table
+    assert pc.check_other_vocab(lambda rt: E.Engine(0, lib_path=conftest.hostsim_library(), rank_table=rt), name, ranks) == 25
