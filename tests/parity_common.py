@@ -197,3 +197,41 @@ def check_other_vocab(make_engine, name, ranks, n_cases=25, seed=3):
         assert same(got_c, want_c), (name, it, first_diff(got_c, want_c) if isinstance(want_c, list) and isinstance(got_c, list) else (got_c, want_c))
         done += 1
     return done
+
+
+def dense_tile_docs():
+    """Transcripts that overrun the fused kernel's per-tile capacities (trc_fused3.cuh: word list, duplicate-candidate
+    list, output buffer, input buffer) so that every overflow path runs: one-letter words, repeated words, a missing
+    space after every second byte, and segments sized around the input capacity of a 256-segment tile."""
+    import random
+    rng = random.Random(99)
+    docs = []
+    def doc(texts, spk=2):
+        return [{"start": 1.5 * i, "end": 1.5 * i + 1.5, "speaker": "S%d" % (i // 7 % spk), "text": t} for i, t in enumerate(texts)]
+    docs.append(doc([" ".join(rng.choice("abcdefgh") for _ in range(35)) for _ in range(600)]))            # ~9k words per tile
+    docs.append(doc([" ".join(["go"] * rng.randint(20, 34)) + " x" for _ in range(600)]))                   # every word a duplicate
+    docs.append(doc([".".join(rng.choice("abcXYZ") for _ in range(36)) for _ in range(600)]))               # output 1.5x the input
+    docs.append(doc(["w" * 71 for _ in range(300)] + ["v" * 72 for _ in range(300)] + ["u" * 73 for _ in range(300)]))   # at / over the input capacity
+    docs.append(doc([("é " * 30).strip() for _ in range(300)] + ["你好 你好 " * 9 for _ in range(300)]))     # multi-byte everywhere
+    docs.append(doc([("ab " * 20) + "\t\n " * 5 + ("cd  " * 5) for _ in range(520)]))                      # whitespace runs
+    return docs
+
+
+def check_dense_tiles(eng):
+    from llm_map_reduce_summarizer_b200 import engine as E2
+    from oracle import chunker as OC, preprocess as OP
+    docs = dense_tile_docs()
+    b = E2.pack_documents(docs)
+    import numpy as np
+    mt = np.array([4000, 700, 4000, 2000, 4000, 1000], dtype=np.int32)
+    eng.preprocess(b)
+    eng.chunk(mt)
+    P, R = eng.fetch_processed(), eng.fetch_chunks()
+    for x, segs in enumerate(docs):
+        op = OP.preprocess(segs)
+        oc = OC.ChunkerOracle(int(mt[x])).chunk(op)
+        pp = E2.build_processed(b, P, x)
+        assert same(pp, op), "doc %d processed: %s" % (x, first_diff(pp, op))
+        got = E2.build_chunks(eng, b, P, R, pp, x)
+        assert same(got, oc), "doc %d chunks: %s" % (x, first_diff(got, oc))
+    return len(docs)

@@ -203,3 +203,8 @@ def test_other_rank_tables(table):
     for j in range(0, len(P["k2r"]), 7):
         t = clean[int(coff[j]):int(coff[j + 1])].decode("utf-8")
         assert int(P["ctok"][j]) == len(enc.encode_ordinary(" " + t)), (name, j)
+
+
+def test_dense_tiles(gpu_engine):
+    """Tiles that overrun the fused kernel's word / candidate / output / input capacities (overflow paths)."""
+    assert pc.check_dense_tiles(gpu_engine) == 6

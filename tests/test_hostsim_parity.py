@@ -179,3 +179,8 @@ def test_other_rank_tables(table):
     import conftest
     name, ranks = table
     assert pc.check_other_vocab(lambda rt: E.Engine(0, lib_path=conftest.hostsim_library(), rank_table=rt), name, ranks) == 25
+
+
+def test_dense_tiles(hostsim_engine):
+    """Tiles that overrun the fused kernel's word / candidate / output / input capacities (overflow paths)."""
+    assert pc.check_dense_tiles(hostsim_engine) == 6
