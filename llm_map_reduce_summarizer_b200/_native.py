@@ -3,7 +3,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-DEFAULT_LIB = os.path.join(_HERE, "libtrchunk.so")
+DEFAULT_LIB = os.environ.get("TRCHUNK_LIB") or os.path.join(_HERE, "libtrchunk.so")
 
 TRC_MEM_HOST, TRC_MEM_DEVICE = 0, 1
 COUNTERS = ["n_seg", "n_kept", "n_groups", "n_items", "n_subs", "n_chunks", "b_raw", "b_clean", "b_merged", "b_twc",
@@ -62,7 +62,8 @@ def load_library(path=None):
     lib.trc_load_vocab.argtypes = [vp, vp, vp, vp, i32, vp, vp, i32]
     lib.trc_preprocess.argtypes = [vp, C.POINTER(Batch), vp]
     lib.trc_chunk.argtypes = [vp, vp, i32, i32, vp]
-    lib.trc_aggregate.argtypes = [vp, C.c_double, vp]
+    if hasattr(lib, "trc_aggregate"):
+        lib.trc_aggregate.argtypes = [vp, C.c_double, vp]
     lib.trc_get_counts.argtypes = [vp, vp]
     lib.trc_get_array.argtypes = [vp, C.c_int, vp, i64, i32, C.POINTER(i64), vp]
     lib.trc_count_tokens.argtypes = [vp, vp, vp, i64, i32, i32, vp, vp, vp]
