@@ -113,14 +113,16 @@ __global__ void k_giant_firstunits(GiantState G, const int64_t* __restrict__ wsc
     fe[q] = G.toff[q + 1] > x ? uend[wscan[x]] : x;
   }
 }
-__global__ void k_giant_sum(GiantState G, int64_t nw, const int32_t* __restrict__ wgiant, const uint32_t* __restrict__ c0,
-                            const uint8_t* __restrict__ wfirst, const int32_t* __restrict__ sp) {
+// final count of every word (the first word of a giant takes the count made with the virtual leading space);
+// special-token hits are rare and go through an atomic
+__global__ void k_giant_wcount(GiantState G, int64_t nw, const int32_t* __restrict__ wgiant, const uint32_t* __restrict__ c0,
+                               const uint32_t* __restrict__ c1, const uint8_t* __restrict__ wfirst, const int32_t* __restrict__ sp, int32_t* wc) {
   GSTRIDE(w, nw) {
     const int32_t q = wgiant[w];
-    if (!wfirst[w]) atomicAdd(&G.tok[q], c0[w]);
+    wc[w] = (int32_t)(wfirst[w] ? c1[q] : c0[w]);
     if (sp[w] >= 0) atomicMin(&G.spw[q], (long long)((w << 4) | sp[w]));
   }
 }
-__global__ void k_giant_sum_first(GiantState G, const uint32_t* __restrict__ c1) {
-  GSTRIDE(q, G.ng) if (G.toff[q + 1] > G.toff[q]) atomicAdd(&G.tok[q], c1[q]);
+__global__ void k_giant_totals(GiantState G, const int64_t* __restrict__ wscan, const int64_t* __restrict__ wpre) {
+  GSTRIDE(q, G.ng) G.tok[q] = (uint32_t)(wpre[wscan[G.toff[q + 1]]] - wpre[wscan[G.toff[q]]]);
 }

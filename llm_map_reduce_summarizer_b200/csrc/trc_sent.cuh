@@ -34,6 +34,16 @@ struct TrcSentState {
   const int64_t* sent_off;    // first sentence record of each, n_rl+1
 };
 
+// Per-word token counts of the oversized segments (trc_giant.cuh), kept from stage P: every space of a cleaned
+// text starts a word and words are tokenised independently, so the tokens of " " + sentence are a
+// difference of the running sum over its words whenever the sentence begins and ends at word edges.
+struct TrcWordSums {
+  const int32_t* of_seg;      // per raw segment: giant index or -1; nullptr: none
+  const int64_t* toff;        // cleaned offset of every giant inside the giants' text buffer
+  const int64_t* wscan;       // words that start before byte x of that buffer
+  const int64_t* wpre;        // tokens of the words before word w
+};
+
 TRC_HD bool pk_nonword(uint8_t c) {
   return c == ')' || c == '"' || c == ';' || c == '}' || c == ']' || c == '*' || c == ':' || c == '@' || c == '\'' ||
          c == '(' || c == '{' || c == '[' || c == '?' || c == '!';

@@ -97,12 +97,37 @@ __global__ void k_sent_times(TrcDev D, TrcSentState S, const int64_t* __restrict
   }
 }
 
-__global__ void k_sent_tok(TrcDev D, TrcTables T, TrcSentState S, const uint32_t* __restrict__ cnt, int32_t* ncl) {
+// Sentences of an oversized segment whose token counts are differences of the per-word running sum of stage P
+// (TrcWordSums): wsum[r] >= 0 and the unit range is emptied so that the generic counter skips them; the others
+// (segment not pre-tokenised, or a sentence edge inside a word, e.g. a closing quote followed by "--") keep -1.
+__global__ void k_sent_wordsum(TrcDev D, TrcSentState S, TrcWordSums W, int64_t* ustart, int64_t* uend, int64_t* wsum) {
+  GSTRIDE(r, S.n_sent) {
+    const TrcSent& R = S.recs[r];
+    int64_t v = -1;
+    if (W.of_seg && R.len > 0) {
+      const int32_t j = D.gstart[R.group];
+      const int32_t q = W.of_seg[D.k2r[j]];
+      if (q >= 0) {
+        const int64_t c0 = D.coff[j], c1 = D.coff[j + 1], a = R.off, b = R.off + R.len;
+        const bool left = a == c0 || D.C[a - 1] == ' ', right = b == c1 || D.C[b] == ' ';
+        if (left && right && D.C[a] != ' ') {
+          const int64_t ga = W.toff[q] + (a - c0), gb = ga + R.len;      // the same bytes inside the giants' buffer
+          const int64_t w0 = W.wscan[a == c0 ? ga : ga - 1], w1 = W.wscan[gb];
+          v = W.wpre[w1] - W.wpre[w0];
+          uend[r] = ustart[r];
+        }
+      }
+    }
+    wsum[r] = v;
+  }
+}
+
+__global__ void k_sent_tok(TrcDev D, TrcTables T, TrcSentState S, const uint32_t* __restrict__ cnt, const int64_t* __restrict__ wsum, int32_t* ncl) {
   GSTRIDE(r, S.n_sent) {
     TrcSent& R = S.recs[r];
     int32_t n = 0;
     if (R.len > 0) {
-      R.tok = 2 + trc_ts_tokens(T, R.start) + (int32_t)cnt[r];
+      R.tok = 2 + trc_ts_tokens(T, R.start) + (wsum[r] >= 0 ? (int32_t)wsum[r] : (int32_t)cnt[r]);
       int64_t E = D.doc_E[D.sdoc[D.gstart[R.group]]];
       if (R.tok > E) n = pk_clauses(D.C, R.off, R.off + R.len, [](int32_t, int64_t, int64_t) {});
     }
@@ -275,8 +300,11 @@ static int sentence_stage_count(trc_ctx* ctx, cudaStream_t st, int32_t* nsub_g, 
   LAUNCH(k_sent_build, S.n_sent, 128, D, S, bscan, brk_pos, chars64);
   if ((rc = scan_excl(ctx, st, chars64, cscan, S.n_sent))) return rc;
   LAUNCH(k_sent_times, S.n_sent, 128, D, S, cscan, ustart, uend);
+  int64_t* wsum;
+  ALLOC(wsum, int64_t, S.n_sent);
+  LAUNCH(k_sent_wordsum, S.n_sent, 128, D, S, ctx->WS, ustart, uend, wsum);
   if ((rc = count_units(ctx, st, D.C, ustart, uend, S.n_sent, total, 1, cnt, nullptr, false))) return rc;
-  LAUNCH(k_sent_tok, S.n_sent, 128, D, ctx->T, S, cnt, ncl);
+  LAUNCH(k_sent_tok, S.n_sent, 128, D, ctx->T, S, cnt, wsum, ncl);
   if ((rc = scan_excl(ctx, st, ncl, clscan, S.n_sent))) return rc;
   int64_t ncls = 0;
   if ((rc = read_back(ctx, st, clscan + S.n_sent, 8, &ncls))) return rc;

@@ -101,6 +101,7 @@ struct trc_ctx {
   std::vector<ProfAcc> prof_acc;
   // sentence path
   TrcSentState SS{};
+  TrcWordSums WS{};
   // result array table
   struct Arr { const void* p; int64_t bytes; } arr[TRC_A__COUNT] = {};
 };
@@ -841,8 +842,13 @@ static int giant_stage(trc_ctx* ctx, cudaStream_t st, int64_t braw, GiantView* V
   LAUNCH(k_giant_firstunits, ng, 64, G, wscan, uend, fs, fe);
   if ((rc = count_units(ctx, st, G.text, ustart, uend, nw, gc, 0, c0, sp, false))) return rc;
   if ((rc = count_units(ctx, st, G.text, fs, fe, ng, gc, 1, c1, nullptr, false))) return rc;
-  LAUNCH(k_giant_sum, nw, 256, G, nw, wgiant, c0, wfirst, sp);
-  LAUNCH(k_giant_sum_first, ng, 64, G, c1);
+  // running sum of the per-word counts: totals per giant are differences, and so are the sentences of the chunk stage
+  int32_t* wc; int64_t* wpre;
+  ALLOC(wc, int32_t, nw); ALLOC(wpre, int64_t, nw + 1);
+  LAUNCH(k_giant_wcount, nw, 256, G, nw, wgiant, c0, c1, wfirst, sp, wc);
+  if ((rc = scan_excl(ctx, st, wc, wpre, nw))) return rc;
+  LAUNCH(k_giant_totals, ng, 64, G, wscan, wpre);
+  ctx->WS.of_seg = of_seg; ctx->WS.toff = G.toff; ctx->WS.wscan = wscan; ctx->WS.wpre = wpre;
   V->of_seg = of_seg; V->toff = G.toff; V->text = G.text; V->chars = G.chars; V->tok = G.tok; V->spw = G.spw;
   ctx->counts[TRC_N_GIANTS] = ng;
   return TRC_OK;
@@ -1017,6 +1023,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   cudaStream_t st = stream ? (cudaStream_t)stream : ctx->own_stream;
   ctx->arena.reset();
   ctx->have_pre = ctx->have_chunk = false;
+  ctx->WS = TrcWordSums{};
   for (auto& a : ctx->arr) a = {nullptr, 0};
   for (auto& c : ctx->counts) c = 0;
   TrcDev& D = ctx->D;
