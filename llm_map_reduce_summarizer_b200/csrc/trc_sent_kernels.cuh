@@ -170,71 +170,117 @@ struct SubAcc {
   int64_t tok, text_len; int32_t r0, r1, n; double start, end; int32_t start_src;
 };
 
+// The greedy below is sequential per segment, but a thread that walks 80-byte records one by one waits a memory
+// round trip per record.  On the device a WARP runs it: the lanes load 32 consecutive records at once and hand
+// them around with shuffles while every lane executes the same (uniform) loop; lane 0 does the writes.
+struct SentLite { int64_t len, cl0; double start, end; int32_t tok, ncl; };
+TRC_HD SentLite sent_lite(const TrcSent& R) { SentLite o; o.len = R.len; o.cl0 = R.cl0; o.start = R.start; o.end = R.end; o.tok = R.tok; o.ncl = R.ncl; return o; }
+struct SentFetchDirect {
+  const TrcSent* recs;
+  TRC_HD SentLite operator()(int64_t r) { return sent_lite(recs[r]); }
+};
+#ifndef TRC_HOSTSIM
+struct SentFetchWarp {
+  const TrcSent* recs; int64_t hi; int lane; int64_t win0; SentLite mine;
+  __device__ SentLite operator()(int64_t r) {
+    if (r < win0 || r >= win0 + 32) {
+      win0 = r;
+      const int64_t x = r + lane;
+      if (x < hi) mine = sent_lite(recs[x]);
+    }
+    const int src = (int)(r - win0);
+    SentLite o;
+    o.len = __shfl_sync(0xffffffffu, mine.len, src); o.cl0 = __shfl_sync(0xffffffffu, mine.cl0, src);
+    o.start = __shfl_sync(0xffffffffu, mine.start, src); o.end = __shfl_sync(0xffffffffu, mine.end, src);
+    o.tok = __shfl_sync(0xffffffffu, mine.tok, src); o.ncl = __shfl_sync(0xffffffffu, mine.ncl, src);
+    return o;
+  }
+};
+#endif
+
 template <bool WRITE>
-TRC_HD void sg_flush(const TrcDev& D, TrcSentState& S, TrcSub* out, int32_t& ns, int64_t sub_base, int32_t g, int32_t kind, SubAcc& a) {
-  if (WRITE) {
+TRC_HD void sg_flush(TrcSentState& S, TrcSub* out, int32_t& ns, int32_t g, int32_t kind, SubAcc& a, bool wr) {
+  if (WRITE && wr) {
     TrcSub& s = out[ns];
     s.group = g; s.kind = kind; s.r0 = a.r0; s.r1 = a.r1; s.start_src = a.start_src; s.end_src = -1; s.tok = (int32_t)a.tok; s.pad = 0;
     s.start = a.start; s.end = a.end; s.text_len = a.text_len;
-    for (int32_t r = a.r0; r <= a.r1; ++r) if (S.recs[r].sub == -2) S.recs[r].sub = (int32_t)(sub_base + ns);
-    for (int32_t r = a.r1; r >= a.r0; --r) if (S.recs[r].sub == (int32_t)(sub_base + ns)) { S.recs[r].last_in_sub = 1; break; }
+    S.recs[a.r1].last_in_sub = 1;
   }
   ++ns;
 }
+// Appends record r to the sub-chunk under construction, which will be flushed as number ns (nothing else is
+// flushed between a sub-chunk's first append and its own flush).
 template <bool WRITE>
-TRC_HD void sg_append(TrcSentState& S, SubAcc& a, int32_t r, const TrcSent& R) {
+TRC_HD void sg_append(TrcSentState& S, SubAcc& a, int32_t r, const SentLite& R, int64_t sub_index, bool wr) {
   int64_t piece = 1 + trc_ts_len(R.start) + 2 + R.len;
   if (a.n == 0) { a.r0 = r; a.text_len = 0; }
-  if (WRITE) { S.recs[r].sub = -2; S.recs[r].off_in_sub = a.n ? a.text_len + 1 : 0; }
+  if (WRITE && wr) { S.recs[r].sub = (int32_t)sub_index; S.recs[r].off_in_sub = a.n ? a.text_len + 1 : 0; }
   a.text_len += piece + (a.n ? 1 : 0);
   a.tok += R.tok; a.r1 = r; a.n += 1; a.end = R.end;
 }
 
-template <bool WRITE>
-TRC_HD int32_t trc_split_sentences(const TrcDev& D, TrcSentState S, int64_t q, TrcSub* out, int64_t sub_base) {
+template <bool WRITE, class Fetch>
+TRC_HD int32_t trc_split_sentences(const TrcDev& D, TrcSentState S, int64_t q, TrcSub* out, int64_t sub_base, Fetch&& fetch, bool wr) {
   int32_t g = S.rl_groups[q];
   int32_t j = D.gstart[g];
   int64_t E = D.doc_E[D.sdoc[j]];
   int32_t ns = 0;
   SubAcc cur; cur.tok = 0; cur.text_len = 0; cur.n = 0; cur.r0 = cur.r1 = -1; cur.start = D.start[D.k2r[j]]; cur.end = 0; cur.start_src = j;
   for (int64_t r = S.sent_off[q]; r < S.sent_off[q + 1]; ++r) {
-    const TrcSent R = S.recs[r];
+    const SentLite R = fetch(r);
     if (R.len == 0) continue;
     if (R.tok > E) {
       // clause sub-chunks of this sentence (:437-542)
       SubAcc cl; cl.tok = 0; cl.text_len = 0; cl.n = 0; cl.r0 = cl.r1 = -1; cl.start = R.start; cl.end = 0; cl.start_src = -1;
       // an existing sub-chunk is closed first (:378-381), but it is appended BEFORE the clause chunks
-      if (cur.tok > 0) { cur.end = R.start; sg_flush<WRITE>(D, S, out, ns, sub_base, g, 1, cur); }
+      if (cur.tok > 0) { cur.end = R.start; sg_flush<WRITE>(S, out, ns, g, 1, cur, wr); }
       for (int64_t c = R.cl0; c < R.cl0 + R.ncl; ++c) {
-        const TrcSent C = S.recs[c];
+        const SentLite C = sent_lite(S.recs[c]);
         if (C.len == 0) continue;
         if (cl.tok + C.tok > E && cl.tok > 0) {
-          sg_flush<WRITE>(D, S, out, ns, sub_base, g, 2, cl);
+          sg_flush<WRITE>(S, out, ns, g, 2, cl, wr);
           cl.tok = 0; cl.text_len = 0; cl.n = 0; cl.start = C.start; cl.start_src = -1;
         }
-        sg_append<WRITE>(S, cl, (int32_t)c, C);
+        sg_append<WRITE>(S, cl, (int32_t)c, C, sub_base + ns, wr);
       }
-      if (cl.tok > 0) sg_flush<WRITE>(D, S, out, ns, sub_base, g, 2, cl);
+      if (cl.tok > 0) sg_flush<WRITE>(S, out, ns, g, 2, cl, wr);
       cur.tok = 0; cur.text_len = 0; cur.n = 0; cur.start = R.end; cur.start_src = -1;     // :387-399
     } else if (cur.tok + R.tok > E && cur.tok > 0) {
       cur.end = R.start;                                                                   // :404
-      sg_flush<WRITE>(D, S, out, ns, sub_base, g, 1, cur);
+      sg_flush<WRITE>(S, out, ns, g, 1, cur, wr);
       cur.tok = 0; cur.text_len = 0; cur.n = 0; cur.start = R.start; cur.start_src = -1;   // :409-421
-      sg_append<WRITE>(S, cur, (int32_t)r, R);
+      sg_append<WRITE>(S, cur, (int32_t)r, R, sub_base + ns, wr);
     } else {
-      sg_append<WRITE>(S, cur, (int32_t)r, R);                                             // :423-429
+      sg_append<WRITE>(S, cur, (int32_t)r, R, sub_base + ns, wr);                          // :423-429
     }
   }
-  if (cur.tok > 0) sg_flush<WRITE>(D, S, out, ns, sub_base, g, 1, cur);
+  if (cur.tok > 0) sg_flush<WRITE>(S, out, ns, g, 1, cur, wr);
   return ns;
 }
 
+#ifdef TRC_HOSTSIM
 __global__ void k_sent_greedy_count(TrcDev D, TrcSentState S, int32_t* nsub_g) {
-  GSTRIDE(q, S.n_rl) nsub_g[S.rl_groups[q]] = trc_split_sentences<false>(D, S, q, nullptr, 0);
+  GSTRIDE(q, S.n_rl) nsub_g[S.rl_groups[q]] = trc_split_sentences<false>(D, S, q, nullptr, 0, SentFetchDirect{S.recs}, true);
 }
 __global__ void k_sent_greedy_write(TrcDev D, TrcSentState S) {
-  GSTRIDE(q, S.n_rl) { int64_t base = D.sub_off[S.rl_groups[q]]; trc_split_sentences<true>(D, S, q, D.subs + base, base); }
+  GSTRIDE(q, S.n_rl) { int64_t base = D.sub_off[S.rl_groups[q]]; trc_split_sentences<true>(D, S, q, D.subs + base, base, SentFetchDirect{S.recs}, true); }
 }
+#else
+__global__ void k_sent_greedy_count(TrcDev D, TrcSentState S, int32_t* nsub_g) {
+  WSTRIDE(q, S.n_rl) {
+    SentFetchWarp f; f.recs = S.recs; f.hi = S.sent_off[q + 1]; f.lane = TRC_LANE; f.win0 = -64;
+    const int32_t n = trc_split_sentences<false>(D, S, q, nullptr, 0, f, TRC_LANE == 0);
+    if (TRC_LANE == 0) nsub_g[S.rl_groups[q]] = n;
+  }
+}
+__global__ void k_sent_greedy_write(TrcDev D, TrcSentState S) {
+  WSTRIDE(q, S.n_rl) {
+    SentFetchWarp f; f.recs = S.recs; f.hi = S.sent_off[q + 1]; f.lane = TRC_LANE; f.win0 = -64;
+    int64_t base = D.sub_off[S.rl_groups[q]];
+    trc_split_sentences<true>(D, S, q, D.subs + base, base, f, TRC_LANE == 0);
+  }
+}
+#endif
 
 // K6 for sentence/clause records: "[ts] text" (+ joining space) into the item text; warp per record
 __global__ void k_emit_sent_recs(TrcDev D, TrcSentState S) {
@@ -319,12 +365,12 @@ static int sentence_stage_count(trc_ctx* ctx, cudaStream_t st, int32_t* nsub_g, 
     if ((rc = count_units(ctx, st, D.C, cus, cue, ncls, total, 1, ccnt, nullptr, false))) return rc;
     LAUNCH(k_clause_tok, ncls, 128, ctx->T, S, ccnt, ncls);
   }
-  LAUNCH(k_sent_greedy_count, (int64_t)nraw, 64, D, S, nsub_g);
+  LAUNCH_W(k_sent_greedy_count, (int64_t)nraw, D, S, nsub_g);
   return TRC_OK;
 }
 
 static int sentence_stage_write(trc_ctx* ctx, cudaStream_t st, const int32_t*) {
-  LAUNCH(k_sent_greedy_write, ctx->SS.n_rl, 64, ctx->D, ctx->SS);
+  LAUNCH_W(k_sent_greedy_write, ctx->SS.n_rl, ctx->D, ctx->SS);
   return TRC_OK;
 }
 static int sentence_stage_emit(trc_ctx* ctx, cudaStream_t st) {
