@@ -76,6 +76,13 @@ TRC_HD uint32_t trc_key8_slot(uint64_t key, uint32_t mask) {   // cheap 32-bit m
   return x & mask;
 }
 
+TRC_HD uint32_t trc_popc32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+  return (uint32_t)__popc(x);
+#else
+  return (uint32_t)__builtin_popcount(x);
+#endif
+}
 TRC_HD uint32_t trc_ctz32(uint32_t x) {
 #if defined(__CUDA_ARCH__)
   return (uint32_t)(__ffs((int)x) - 1);

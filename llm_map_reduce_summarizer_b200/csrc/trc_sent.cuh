@@ -9,6 +9,7 @@
 #pragma once
 #include "trc_common.cuh"
 #include "trc_format.cuh"
+#include "trc_swar.cuh"
 
 struct TrcSent {          // one sentence (kind 1) or clause (kind 2) of an over-budget raw segment
   int32_t group;
@@ -183,41 +184,114 @@ TRC_HD void pk_realign(const uint8_t* s, int64_t a, int64_t b, int64_t* k_out, i
   }
 }
 
-TRC_HD int32_t pk_count_chars(const uint8_t* s, int64_t a, int64_t b) {
-  int32_t c = 0;
-  for (int64_t i = a; i < b; ++i) c += (s[i] & 0xC0) != 0x80;
-  return c;
-}
 TRC_HD bool pk_clause_punct(uint8_t c) { return c == ',' || c == '.' || c == ';' || c == ':' || c == '?' || c == '!'; }
 
-// Clause splitter for one over-budget sentence s[a,b) (:455-472).  emit(k, ca, cb) receives the raw
-// clause ranges in order (before strip); returns the count.
-template <class Emit>
-TRC_HD int32_t pk_clauses(const uint8_t* s, int64_t a, int64_t b, Emit&& emit) {
-  int32_t n = 0;
-  int64_t i = a;
-  while (i < b && pk_clause_punct(s[i])) ++i;       // a leading punctuation run matches nothing
-  int64_t cs = i;
-  while (i < b) {
-    while (i < b && !pk_clause_punct(s[i])) ++i;
-    if (i >= b) break;                              // trailing text without punctuation is dropped (:455-456)
-    while (i < b && pk_clause_punct(s[i])) ++i;
-    emit(n, cs, i); ++n;
-    cs = i;
-  }
-  if (n) return n;
-  // no clause boundary: groups of 20 whitespace-separated words (:459-472)
-  i = a;
-  while (i < b) {
-    while (i < b && s[i] == ' ') ++i;
-    if (i >= b) break;
-    int64_t gs = i, ge = i; int w = 0;
-    while (i < b && w < 20) {
-      while (i < b && s[i] != ' ') ++i;
-      ge = i; ++w;
-      while (i < b && s[i] == ' ') ++i;
-    }
-    emit(n, gs, ge); ++n;
-  }
-  return n;
+// ---- eight bytes at a time -----------------------------------------------------------------------------------
+// An over-budget sentence can be tens of KB (config 4); one thread walks it, so the walk reads aligned 64-bit
+// words and works on 8-bit masks: clause punctuation, space, UTF-8 continuation bytes.
+struct PkWord { uint32_t p, sp, cont; };
+TRC_HD uint64_t pk_eq8(uint64_t x, uint8_t c) {                // 0x80 in every byte of x that equals c (exact)
+  const uint64_t t = x ^ (SW_L * c);
+  return ~(((t & ~SW_H) + ~SW_H) | t | ~SW_H);
 }
+// word W (bytes 8W .. 8W+7) of the 8-byte aligned buffer sb, restricted to [a, b); bytes outside count as spaces
+TRC_HD PkWord pk_word(const uint8_t* sb, int64_t W, int64_t a, int64_t b) {
+  uint64_t x;
+#if defined(__CUDA_ARCH__)
+  x = *reinterpret_cast<const unsigned long long*>(sb + 8 * W);
+#else
+  memcpy(&x, sb + 8 * W, 8);
+#endif
+  const int64_t k0 = 8 * W;
+  uint32_t valid = 0xffu;
+  if (k0 < a) valid &= (a - k0 >= 8) ? 0u : (0xffu << (a - k0));
+  if (k0 + 8 > b) valid &= (b <= k0) ? 0u : (0xffu >> (k0 + 8 - b));
+  valid &= 0xffu;
+  PkWord o;
+  o.p = sw_pack(pk_eq8(x, ',') | pk_eq8(x, '.') | pk_eq8(x, ';') | pk_eq8(x, ':') | pk_eq8(x, '?') | pk_eq8(x, '!')) & valid;
+  o.sp = (sw_pack(pk_eq8(x, ' ')) | ~valid) & 0xffu;
+  o.cont = sw_pack((x & SW_H) & ~((x << 1) & SW_H)) & valid;
+  return o;
+}
+struct PkBuf { const uint8_t* sb; int64_t mis; };              // aligned view of s: position k of s is byte k + mis of sb
+TRC_HD PkBuf pk_buf(const uint8_t* s) { PkBuf o; o.mis = (int64_t)((uintptr_t)s & 7); o.sb = s - o.mis; return o; }
+
+TRC_HD int32_t pk_count_chars(const uint8_t* s, int64_t a, int64_t b) {
+  if (b <= a) return 0;
+  if (b - a < 16) { int32_t c = 0; for (int64_t i = a; i < b; ++i) c += (s[i] & 0xC0) != 0x80; return c; }
+  const PkBuf B = pk_buf(s);
+  const int64_t a2 = a + B.mis, b2 = b + B.mis;
+  int32_t cont = 0;
+  for (int64_t W = a2 >> 3; W <= (b2 - 1) >> 3; ++W) cont += (int32_t)trc_popc32(pk_word(B.sb, W, a2, b2).cont);
+  return (int32_t)(b - a) - cont;
+}
+
+// Clause splitter for one over-budget sentence s[a,b) (:455-472): the matches of ([^,.;:?!]+[,.;:?!]+), i.e. one
+// clause per punctuation run that has something in front of it (a leading run matches nothing, text after the last
+// run is dropped, :455-456); when there is none, groups of 20 space-separated words (:459-472).
+// emit(k, ca, cb) receives the raw clause ranges in order (before strip); returns the count.  COUNT only counts.
+template <bool COUNT, class Emit>
+TRC_HD int32_t pk_clauses_t(const uint8_t* s, int64_t a, int64_t b, Emit&& emit) {
+  if (b <= a) return 0;
+  const PkBuf B = pk_buf(s);
+  const int64_t a2 = a + B.mis, b2 = b + B.mis, W0 = a2 >> 3, W1 = (b2 - 1) >> 3;
+  const bool lead = pk_clause_punct(s[a]);
+  int32_t ends = 0, words = 0;
+  {
+    PkWord cur = pk_word(B.sb, W0, a2, b2);
+    uint32_t prev_sp = 1u;
+    for (int64_t W = W0; W <= W1; ++W) {
+      PkWord nx; nx.p = 0; nx.sp = 0xffu; nx.cont = 0;
+      if (W < W1) nx = pk_word(B.sb, W + 1, a2, b2);
+      ends += (int32_t)trc_popc32(cur.p & ~((cur.p >> 1) | ((nx.p & 1u) << 7)));
+      words += (int32_t)trc_popc32(~cur.sp & 0xffu & ((cur.sp << 1) | prev_sp));
+      prev_sp = (cur.sp >> 7) & 1u;
+      cur = nx;
+    }
+  }
+  const int32_t ncl = ends - (lead ? 1 : 0);
+  const int32_t n = ncl > 0 ? ncl : (words + 19) / 20;
+  if (COUNT) return n;
+  int32_t k = 0;
+  PkWord cur = pk_word(B.sb, W0, a2, b2);
+  if (ncl > 0) {
+    int64_t cs = a;
+    bool skip = lead;                                    // the leading run's end only moves the start
+    for (int64_t W = W0; W <= W1; ++W) {
+      PkWord nx; nx.p = 0; nx.sp = 0xffu; nx.cont = 0;
+      if (W < W1) nx = pk_word(B.sb, W + 1, a2, b2);
+      uint32_t e = cur.p & ~((cur.p >> 1) | ((nx.p & 1u) << 7));
+      while (e) {
+        const int bit = (int)trc_ctz32(e);
+        e &= e - 1;
+        const int64_t ce = 8 * W + bit + 1 - B.mis;
+        if (skip) skip = false; else { emit(k, cs, ce); ++k; }
+        cs = ce;
+      }
+      cur = nx;
+    }
+    return k;
+  }
+  uint32_t prev_sp = 1u;
+  int64_t gs = a; int32_t w = 0;                         // w: words seen so far
+  for (int64_t W = W0; W <= W1; ++W) {
+    PkWord nx; nx.p = 0; nx.sp = 0xffu; nx.cont = 0;
+    if (W < W1) nx = pk_word(B.sb, W + 1, a2, b2);
+    const uint32_t ws = ~cur.sp & 0xffu & ((cur.sp << 1) | prev_sp);                // first byte of a word
+    const uint32_t we = ~cur.sp & 0xffu & ((cur.sp >> 1) | ((nx.sp & 1u) << 7));    // last byte of a word
+    uint32_t ev = ws | we;
+    while (ev) {
+      const int bit = (int)trc_ctz32(ev);
+      ev &= ev - 1;
+      const int64_t pos = 8 * W + bit - B.mis;
+      if ((ws >> bit) & 1u) { if (w % 20 == 0) gs = pos; ++w; }
+      if (((we >> bit) & 1u) && (w % 20 == 0 || w == words)) { emit(k, gs, pos + 1); ++k; }
+    }
+    prev_sp = (cur.sp >> 7) & 1u;
+    cur = nx;
+  }
+  return k;
+}
+template <class Emit>
+TRC_HD int32_t pk_clauses(const uint8_t* s, int64_t a, int64_t b, Emit&& emit) { return pk_clauses_t<false>(s, a, b, emit); }
+TRC_HD int32_t pk_clause_count(const uint8_t* s, int64_t a, int64_t b) { return pk_clauses_t<true>(s, a, b, [](int32_t, int64_t, int64_t) {}); }

@@ -129,7 +129,7 @@ __global__ void k_sent_tok(TrcDev D, TrcTables T, TrcSentState S, const uint32_t
     if (R.len > 0) {
       R.tok = 2 + trc_ts_tokens(T, R.start) + (wsum[r] >= 0 ? (int32_t)wsum[r] : (int32_t)cnt[r]);
       int64_t E = D.doc_E[D.sdoc[D.gstart[R.group]]];
-      if (R.tok > E) n = pk_clauses(D.C, R.off, R.off + R.len, [](int32_t, int64_t, int64_t) {});
+      if (R.tok > E) n = pk_clause_count(D.C, R.off, R.off + R.len);
     }
     R.ncl = n; ncl[r] = n;
   }
