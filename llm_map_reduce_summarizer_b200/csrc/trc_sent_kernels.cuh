@@ -97,37 +97,51 @@ __global__ void k_sent_times(TrcDev D, TrcSentState S, const int64_t* __restrict
   }
 }
 
-// Sentences of an oversized segment whose token counts are differences of the per-word running sum of stage P
-// (TrcWordSums): wsum[r] >= 0 and the unit range is emptied so that the generic counter skips them; the others
-// (segment not pre-tokenised, or a sentence edge inside a word, e.g. a closing quote followed by "--") keep -1.
-__global__ void k_sent_wordsum(TrcDev D, TrcSentState S, TrcWordSums W, int64_t* ustart, int64_t* uend, int64_t* wsum) {
-  GSTRIDE(r, S.n_sent) {
-    const TrcSent& R = S.recs[r];
-    int64_t v = -1;
+// Token count of " " + record text, split three ways.  For a record of an oversized segment the words that lie
+// completely inside it are a difference of the per-word running sum of stage P (TrcWordSums) -> wsum.  A record
+// edge inside a word (a closing quote followed by "--", a clause cut at the dot of "3.5") leaves a partial word:
+// the head [a, first space) is counted as its own unit with the virtual leading space, the tail [last space, b)
+// as a unit that starts with its real space.  Records of segments that were not pre-tokenised are one head unit.
+// Empty unit ranges are skipped by the generic counter; their counts are ignored.
+__global__ void k_sent_wordsum(TrcDev D, TrcSentState S, TrcWordSums W, int64_t rec0, int64_t nrec, int64_t* hs, int64_t* he,
+                               int64_t* ts, int64_t* te, int64_t* wsum) {
+  GSTRIDE(r, nrec) {                           // records rec0 .. rec0+nrec (sentences, or the clause records behind them)
+    const TrcSent& R = S.recs[rec0 + r];
+    const int64_t a = R.off, b = R.off + R.len;
+    int64_t h0 = a, h1 = b, t0 = b, t1 = b, v = 0;
     if (W.of_seg && R.len > 0) {
       const int32_t j = D.gstart[R.group];
       const int32_t q = W.of_seg[D.k2r[j]];
       if (q >= 0) {
-        const int64_t c0 = D.coff[j], c1 = D.coff[j + 1], a = R.off, b = R.off + R.len;
+        const int64_t c0 = D.coff[j], c1 = D.coff[j + 1], gshift = W.toff[q] - c0;   // position x of C is x + gshift of the giants' buffer
         const bool left = a == c0 || D.C[a - 1] == ' ', right = b == c1 || D.C[b] == ' ';
-        if (left && right && D.C[a] != ' ') {
-          const int64_t ga = W.toff[q] + (a - c0), gb = ga + R.len;      // the same bytes inside the giants' buffer
-          const int64_t w0 = W.wscan[a == c0 ? ga : ga - 1], w1 = W.wscan[gb];
+        int64_t m0 = a, m1 = b;
+        bool whole = false;                      // no usable word edge inside: the record is one generic unit
+        if (!left) { while (m0 < b && D.C[m0] != ' ') ++m0; if (m0 >= b) whole = true; }
+        if (!whole && !right) { m1 = b - 1; while (m1 >= m0 && D.C[m1] != ' ') --m1; if (m1 < m0) whole = true; }
+        if (!whole) {
+          h1 = left ? a : m0;                    // head: [a, first space) when the left edge is inside a word
+          if (!right) t0 = m1;                   // tail: [last space, b) when the right edge is inside a word
+          const int64_t w0 = W.wscan[(left ? (a == c0 ? a : a - 1) : m0) + gshift], w1 = W.wscan[m1 + gshift];
           v = W.wpre[w1] - W.wpre[w0];
-          uend[r] = ustart[r];
         }
       }
     }
-    wsum[r] = v;
+    hs[r] = h0; he[r] = h1; ts[r] = t0; te[r] = t1; wsum[r] = v;
   }
 }
+TRC_HD int32_t sent_unit_tokens(int64_t r, const int64_t* hs, const int64_t* he, const int64_t* ts, const int64_t* te, const int64_t* wsum,
+                                const uint32_t* hc, const uint32_t* tc) {
+  return (int32_t)wsum[r] + (he[r] > hs[r] ? (int32_t)hc[r] : 0) + (te[r] > ts[r] ? (int32_t)tc[r] : 0);
+}
 
-__global__ void k_sent_tok(TrcDev D, TrcTables T, TrcSentState S, const uint32_t* __restrict__ cnt, const int64_t* __restrict__ wsum, int32_t* ncl) {
+__global__ void k_sent_tok(TrcDev D, TrcTables T, TrcSentState S, const int64_t* hs, const int64_t* he, const int64_t* ts, const int64_t* te,
+                           const int64_t* wsum, const uint32_t* hc, const uint32_t* tc, int32_t* ncl) {
   GSTRIDE(r, S.n_sent) {
     TrcSent& R = S.recs[r];
     int32_t n = 0;
     if (R.len > 0) {
-      R.tok = 2 + trc_ts_tokens(T, R.start) + (wsum[r] >= 0 ? (int32_t)wsum[r] : (int32_t)cnt[r]);
+      R.tok = 2 + trc_ts_tokens(T, R.start) + sent_unit_tokens(r, hs, he, ts, te, wsum, hc, tc);
       int64_t E = D.doc_E[D.sdoc[D.gstart[R.group]]];
       if (R.tok > E) n = pk_clause_count(D.C, R.off, R.off + R.len);
     }
@@ -161,8 +175,12 @@ __global__ void k_clause_build(TrcDev D, TrcSentState S, const int64_t* __restri
     });
   }
 }
-__global__ void k_clause_tok(TrcTables T, TrcSentState S, const uint32_t* __restrict__ cnt, int64_t n_cl) {
-  GSTRIDE(u, n_cl) { TrcSent& R = S.recs[S.n_sent + u]; R.tok = R.len > 0 ? 2 + trc_ts_tokens(T, R.start) + (int32_t)cnt[u] : 0; }
+__global__ void k_clause_tok(TrcTables T, TrcSentState S, const int64_t* hs, const int64_t* he, const int64_t* ts, const int64_t* te,
+                             const int64_t* wsum, const uint32_t* hc, const uint32_t* tc, int64_t n_cl) {
+  GSTRIDE(u, n_cl) {
+    TrcSent& R = S.recs[S.n_sent + u];
+    R.tok = R.len > 0 ? 2 + trc_ts_tokens(T, R.start) + sent_unit_tokens(u, hs, he, ts, te, wsum, hc, tc) : 0;
+  }
 }
 
 // ---- nested greedy, one thread per over-budget raw segment -----------------------------------------------
@@ -346,11 +364,12 @@ static int sentence_stage_count(trc_ctx* ctx, cudaStream_t st, int32_t* nsub_g, 
   LAUNCH(k_sent_build, S.n_sent, 128, D, S, bscan, brk_pos, chars64);
   if ((rc = scan_excl(ctx, st, chars64, cscan, S.n_sent))) return rc;
   LAUNCH(k_sent_times, S.n_sent, 128, D, S, cscan, ustart, uend);
-  int64_t* wsum;
-  ALLOC(wsum, int64_t, S.n_sent);
-  LAUNCH(k_sent_wordsum, S.n_sent, 128, D, S, ctx->WS, ustart, uend, wsum);
+  int64_t* wsum; int64_t* tst; int64_t* ten; uint32_t* tcnt;
+  ALLOC(wsum, int64_t, S.n_sent); ALLOC(tst, int64_t, S.n_sent); ALLOC(ten, int64_t, S.n_sent); ALLOC(tcnt, uint32_t, S.n_sent);
+  LAUNCH(k_sent_wordsum, S.n_sent, 128, D, S, ctx->WS, (int64_t)0, S.n_sent, ustart, uend, tst, ten, wsum);
   if ((rc = count_units(ctx, st, D.C, ustart, uend, S.n_sent, total, 1, cnt, nullptr, false))) return rc;
-  LAUNCH(k_sent_tok, S.n_sent, 128, D, ctx->T, S, cnt, wsum, ncl);
+  if (ctx->WS.of_seg) { if ((rc = count_units(ctx, st, D.C, tst, ten, S.n_sent, total, 0, tcnt, nullptr, false))) return rc; }
+  LAUNCH(k_sent_tok, S.n_sent, 128, D, ctx->T, S, ustart, uend, tst, ten, wsum, cnt, tcnt, ncl);
   if ((rc = scan_excl(ctx, st, ncl, clscan, S.n_sent))) return rc;
   int64_t ncls = 0;
   if ((rc = read_back(ctx, st, clscan + S.n_sent, 8, &ncls))) return rc;
@@ -362,8 +381,12 @@ static int sentence_stage_count(trc_ctx* ctx, cudaStream_t st, int32_t* nsub_g, 
     int64_t* cus; int64_t* cue; uint32_t* ccnt;
     ALLOC(cus, int64_t, ncls); ALLOC(cue, int64_t, ncls); ALLOC(ccnt, uint32_t, ncls);
     LAUNCH(k_clause_build, S.n_sent, 64, D, S, clscan, cus, cue);
+    int64_t* cwsum; int64_t* cts; int64_t* cte; uint32_t* ctc;
+    ALLOC(cwsum, int64_t, ncls); ALLOC(cts, int64_t, ncls); ALLOC(cte, int64_t, ncls); ALLOC(ctc, uint32_t, ncls);
+    LAUNCH(k_sent_wordsum, ncls, 128, D, S, ctx->WS, S.n_sent, ncls, cus, cue, cts, cte, cwsum);
     if ((rc = count_units(ctx, st, D.C, cus, cue, ncls, total, 1, ccnt, nullptr, false))) return rc;
-    LAUNCH(k_clause_tok, ncls, 128, ctx->T, S, ccnt, ncls);
+    if (ctx->WS.of_seg) { if ((rc = count_units(ctx, st, D.C, cts, cte, ncls, total, 0, ctc, nullptr, false))) return rc; }
+    LAUNCH(k_clause_tok, ncls, 128, ctx->T, S, cus, cue, cts, cte, cwsum, ccnt, ctc, ncls);
   }
   LAUNCH_W(k_sent_greedy_count, (int64_t)nraw, D, S, nsub_g);
   return TRC_OK;
