@@ -76,6 +76,14 @@ TRC_HD uint32_t trc_key8_slot(uint64_t key, uint32_t mask) {   // cheap 32-bit m
   return x & mask;
 }
 
+// Sum over the lanes of a warp (device); the host test build runs one "lane", so the value is already the sum.
+TRC_HD int64_t trc_lanes_sum(int64_t v) {
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+#endif
+  return v;
+}
 TRC_HD uint32_t trc_popc32(uint32_t x) {
 #if defined(__CUDA_ARCH__)
   return (uint32_t)__popc(x);

@@ -142,18 +142,20 @@ TRC_HD void trc_emit_merged(const TrcDev& D, int64_t j, int lane, int nl) {
 // formatted = "[" ts(start) "] " speaker ": " text        (big_chunkeroosky.py:244-265)
 // tokens    = count("[ts]") + count(" speaker:") + count(" " + text), exact because the pre-tokeniser
 //             always has match boundaries after "]" and after ":" (DESIGN.md §3).
-TRC_HD void trc_group_stats(const TrcDev& D, const TrcTables& T, int64_t g) {
+TRC_HD void trc_group_stats(const TrcDev& D, const TrcTables& T, int64_t g, int lane, int nl) {   // lanes share the pieces
   int32_t a = D.gstart[g], b = D.gstart[g + 1];
   int32_t ra = D.k2r[a], rb = D.k2r[b - 1];
   double st = D.start[ra];
-  int64_t tok = 2 + trc_ts_tokens(T, st) + D.spk_tok[D.spk[ra]];
-  if (b - a == 1) tok += D.ctok[a];
+  int64_t part = 0;
+  if (b - a == 1) { if (lane == 0) part = D.ctok[a]; }
   else {
-    for (int32_t j = a; j < b; ++j) {
-      tok += D.ctok[j];
-      if (D.preserve) tok += T.cnt_space_lbracket + trc_ts_tokens(T, D.start[D.k2r[j]]) + 1;
+    for (int32_t j = a + lane; j < b; j += nl) {
+      part += D.ctok[j];
+      if (D.preserve) part += T.cnt_space_lbracket + trc_ts_tokens(T, D.start[D.k2r[j]]) + 1;
     }
   }
+  const int64_t tok = 2 + trc_ts_tokens(T, st) + D.spk_tok[D.spk[ra]] + (nl > 1 ? trc_lanes_sum(part) : part);
+  if (lane != 0) return;
   D.gtok[g] = tok;
   int64_t mlen = D.poff[b] - D.poff[a];
   int32_t s = D.spk[ra];
@@ -170,17 +172,36 @@ TRC_HD int32_t trc_piece_tokens(const TrcDev& D, const TrcTables& T, int32_t j) 
   return 2 + trc_ts_tokens(T, D.start[D.k2r[j]]) + (int32_t)D.ctok[j];
 }
 
-template <bool WRITE>
-TRC_HD int32_t trc_split_combined(const TrcDev& D, const TrcTables& T, int64_t g, TrcSub* out) {
+// The greedy is sequential, but the piece token counts are not: `tokens(j)` may hand out counts that the lanes of a
+// warp computed 32 at a time (PieceTokWarp); every lane runs the same loop and `wr` picks the lane that writes.
+struct PieceTokDirect {
+  const TrcDev* D; const TrcTables* T;
+  TRC_HD int64_t operator()(int32_t j) { return trc_piece_tokens(*D, *T, j); }
+};
+#ifndef TRC_HOSTSIM
+struct PieceTokWarp {
+  const TrcDev* D; const TrcTables* T; int32_t hi; int lane; int32_t win0; int32_t mine;
+  __device__ int64_t operator()(int32_t j) {
+    if (j < win0 || j >= win0 + 32) {
+      win0 = j;
+      const int32_t x = j + lane;
+      if (x < hi) mine = trc_piece_tokens(*D, *T, x);
+    }
+    return (int64_t)__shfl_sync(0xffffffffu, mine, j - win0);
+  }
+};
+#endif
+template <bool WRITE, class Tokens>
+TRC_HD int32_t trc_split_combined(const TrcDev& D, int64_t g, TrcSub* out, Tokens&& tokens, bool wr) {
   int32_t a = D.gstart[g], b = D.gstart[g + 1];
   int64_t E = D.doc_E[D.sdoc[a]];
   int32_t ns = 0;
   int64_t cur = 0;
   int32_t first = a;
   for (int32_t j = a; j < b; ++j) {
-    int64_t p = trc_piece_tokens(D, T, j);
+    int64_t p = tokens(j);
     if (cur + p > E && cur > 0) {
-      if (WRITE) {
+      if (WRITE && wr) {
         TrcSub& s = out[ns];
         s.group = (int32_t)g; s.kind = 0; s.r0 = first; s.r1 = j - 1; s.start_src = first; s.end_src = j - 1;
         s.tok = (int32_t)cur; s.pad = 0;
@@ -192,7 +213,7 @@ TRC_HD int32_t trc_split_combined(const TrcDev& D, const TrcTables& T, int64_t g
     cur += p;
   }
   if (cur > 0) {
-    if (WRITE) {
+    if (WRITE && wr) {
       TrcSub& s = out[ns];
       s.group = (int32_t)g; s.kind = 0; s.r0 = first; s.r1 = b - 1; s.start_src = first; s.end_src = b - 1;
       s.tok = (int32_t)cur; s.pad = 0;

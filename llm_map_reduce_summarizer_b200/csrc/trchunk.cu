@@ -572,19 +572,44 @@ __global__ void k_piece_len(TrcDev D, int32_t* plen_sub) {
   }
 }
 __global__ void k_emit_merged(TrcDev D) { WSTRIDE(j, D.n_kept) trc_emit_merged(D, j, TRC_LANE, TRC_NL); }
-__global__ void k_group_stats(TrcDev D, TrcTables T) { GSTRIDE(g, D.m) trc_group_stats(D, T, g); }
+__global__ void k_group_stats(TrcDev D, TrcTables T) { WSTRIDE(g, D.m) trc_group_stats(D, T, g, TRC_LANE, TRC_NL); }
+__global__ void k_group_stats_t(TrcDev D, TrcTables T) { GSTRIDE(g, D.m) trc_group_stats(D, T, g, 0, 1); }   // short groups: a thread each
 
 // ---- chunk stage
+// warp per merged segment (the sub-chunk greedy of an over-budget combined segment walks thousands of pieces)
+#ifdef TRC_HOSTSIM
+#define TRC_PIECE_TOKENS(hi_) PieceTokDirect{&D, &T}
+#else
+#define TRC_PIECE_TOKENS(hi_) PieceTokWarp{&D, &T, (hi_), (int)TRC_LANE, -64, 0}
+#endif
 __global__ void k_large_count(TrcDev D, TrcTables T, int32_t* nsub_g, int32_t* n_raw_large) {
+  WSTRIDE(g, D.m) {
+    int32_t a = D.gstart[g];
+    bool large = D.gtok[g] > (int64_t)D.doc_E[D.sdoc[a]];
+    int32_t ns = 0;
+    if (large) {
+      if (D.gstart[g + 1] - a > 1) ns = trc_split_combined<false>(D, g, nullptr, TRC_PIECE_TOKENS(D.gstart[g + 1]), TRC_LANE == 0);
+      else { ns = -1; if (TRC_LANE == 0) atomicAdd(n_raw_large, 1); }   // sentence path: counted by the sentence stage
+    }
+    if (TRC_LANE == 0) nsub_g[g] = ns;
+  }
+}
+__global__ void k_large_count_t(TrcDev D, TrcTables T, int32_t* nsub_g, int32_t* n_raw_large) {   // short groups: a thread each
   GSTRIDE(g, D.m) {
     int32_t a = D.gstart[g];
     bool large = D.gtok[g] > (int64_t)D.doc_E[D.sdoc[a]];
     int32_t ns = 0;
     if (large) {
-      if (D.gstart[g + 1] - a > 1) ns = trc_split_combined<false>(D, T, g, nullptr);
-      else { ns = -1; atomicAdd(n_raw_large, 1); }   // sentence path: counted by the sentence stage
+      if (D.gstart[g + 1] - a > 1) ns = trc_split_combined<false>(D, g, nullptr, PieceTokDirect{&D, &T}, true);
+      else { ns = -1; atomicAdd(n_raw_large, 1); }
     }
     nsub_g[g] = ns;
+  }
+}
+__global__ void k_large_write_t(TrcDev D, TrcTables T, const int32_t* __restrict__ nsub_g) {
+  GSTRIDE(g, D.m) {
+    int32_t a = D.gstart[g];
+    if (nsub_g[g] > 0 && D.gstart[g + 1] - a > 1) trc_split_combined<true>(D, g, D.subs + D.sub_off[g], PieceTokDirect{&D, &T}, true);
   }
 }
 __global__ void k_nitems(TrcDev D, const int32_t* __restrict__ nsub_g) {
@@ -595,9 +620,10 @@ __global__ void k_nitems(TrcDev D, const int32_t* __restrict__ nsub_g) {
   }
 }
 __global__ void k_large_write(TrcDev D, TrcTables T, const int32_t* __restrict__ nsub_g) {
-  GSTRIDE(g, D.m) {
+  WSTRIDE(g, D.m) {
     int32_t a = D.gstart[g];
-    if (nsub_g[g] > 0 && D.gstart[g + 1] - a > 1) trc_split_combined<true>(D, T, g, D.subs + D.sub_off[g]);
+    if (nsub_g[g] > 0 && D.gstart[g + 1] - a > 1)
+      trc_split_combined<true>(D, g, D.subs + D.sub_off[g], TRC_PIECE_TOKENS(D.gstart[g + 1]), TRC_LANE == 0);
   }
 }
 __global__ void k_build_items(TrcDev D) {
@@ -1242,7 +1268,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   }
   // P5: group token totals, formatted lengths, formatted timestamps
   ALLOC(D.gts, uint8_t, m * 48); ALLOC(D.gtok, int64_t, m); ALLOC(D.glen, int64_t, m);
-  LAUNCH(k_group_stats, m, 128, D, ctx->T);
+  if (nk >= 64 * m) LAUNCH_W(k_group_stats, m, D, ctx->T); else LAUNCH(k_group_stats_t, m, 128, D, ctx->T);
   if (modeB && B->group_off) {
     if (m != B->n_groups) { ctx->err = "group_off does not describe the pieces"; return TRC_EINVAL; }
     const double* d_gs; const double* d_ge; const uint8_t* d_full; const int64_t* d_foff;
@@ -1306,7 +1332,7 @@ extern "C" int trc_chunk(trc_ctx* ctx, const int32_t* doc_max_tokens, int32_t co
   ALLOC(nsub_g, int32_t, m); ALLOC(d_nraw, int32_t, 1); ALLOC(D.sub_off, int64_t, m + 1);
   ALLOC(D.nitems_g, int32_t, m); ALLOC(D.item_off, int64_t, m + 1);
   CK(cudaMemsetAsync(d_nraw, 0, 4, st));
-  LAUNCH(k_large_count, m, 128, D, ctx->T, nsub_g, d_nraw);
+  if (nk >= 64 * m) LAUNCH_W(k_large_count, m, D, ctx->T, nsub_g, d_nraw); else LAUNCH(k_large_count_t, m, 128, D, ctx->T, nsub_g, d_nraw);
   int32_t nraw = 0;
   if (m) { if ((rc = read_back(ctx, st, d_nraw, 4, &nraw))) return rc; }
   ctx->SS = TrcSentState{};
@@ -1323,7 +1349,7 @@ extern "C" int trc_chunk(trc_ctx* ctx, const int32_t* doc_max_tokens, int32_t co
   D.n_subs = nsub; D.n_items = ni;
   ctx->counts[TRC_N_SUBS] = nsub; ctx->counts[TRC_N_ITEMS] = ni;
   ALLOC(D.subs, TrcSub, nsub);
-  LAUNCH(k_large_write, m, 128, D, ctx->T, nsub_g);
+  if (nk >= 64 * m) LAUNCH_W(k_large_write, m, D, ctx->T, nsub_g); else LAUNCH(k_large_write_t, m, 128, D, ctx->T, nsub_g);
   if (nraw > 0) { if ((rc = sentence_stage_write(ctx, st, nsub_g))) return rc; }
   // C2: items
   ALLOC(D.it_group, int32_t, ni); ALLOC(D.it_sub, int32_t, ni); ALLOC(D.it_tok, int32_t, ni); ALLOC(D.it_len, int64_t, ni);
