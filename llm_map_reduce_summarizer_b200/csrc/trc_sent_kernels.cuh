@@ -136,14 +136,18 @@ TRC_HD int32_t sent_unit_tokens(int64_t r, const int64_t* hs, const int64_t* he,
 }
 
 __global__ void k_sent_tok(TrcDev D, TrcTables T, TrcSentState S, const int64_t* hs, const int64_t* he, const int64_t* ts, const int64_t* te,
-                           const int64_t* wsum, const uint32_t* hc, const uint32_t* tc, int32_t* ncl) {
+                           const int64_t* wsum, const uint32_t* hc, const uint32_t* tc, int32_t* ncl,
+                           int64_t* ob_list, unsigned long long* ob_cnt) {
   GSTRIDE(r, S.n_sent) {
     TrcSent& R = S.recs[r];
     int32_t n = 0;
     if (R.len > 0) {
       R.tok = 2 + trc_ts_tokens(T, R.start) + sent_unit_tokens(r, hs, he, ts, te, wsum, hc, tc);
       int64_t E = D.doc_E[D.sdoc[D.gstart[R.group]]];
-      if (R.tok > E) n = pk_clause_count(D.C, R.off, R.off + R.len);
+      if (R.tok > E) {
+        if (ob_list) ob_list[atomicAdd(ob_cnt, 1ULL)] = r;       // over budget: its clauses are counted by a warp (k_clause_count_w)
+        else n = pk_clause_count(D.C, R.off, R.off + R.len);
+      }
     }
     R.ncl = n; ncl[r] = n;
   }
@@ -175,6 +179,144 @@ __global__ void k_clause_build(TrcDev D, TrcSentState S, const int64_t* __restri
     });
   }
 }
+#ifndef TRC_HOSTSIM
+// ---- the same clause splitting (pk_clauses_t) by a warp per over-budget sentence ---------------------------------
+// An over-budget sentence can be tens of KB; lanes take consecutive 8-byte words, neighbours exchange the edge
+// bits with shuffles, clause / word indices are warp prefix sums.  Counting first (the records need their number),
+// then the raw clause ranges, then one thread per clause for strip / code points / times.
+struct PkWarpWord { PkWord w; uint32_t nxp, nxsp, prevsp; };
+__device__ __forceinline__ PkWarpWord pk_warp_word(const PkBuf& B, int64_t base, int64_t W1, int64_t a2, int64_t b2, int lane, uint32_t carry_sp) {
+  const int64_t W = base + lane;
+  PkWarpWord o;
+  o.w.p = 0; o.w.sp = 0xffu; o.w.cont = 0;
+  if (W <= W1) o.w = pk_word(B.sb, W, a2, b2);
+  o.nxp = __shfl_down_sync(0xffffffffu, o.w.p, 1);
+  o.nxsp = __shfl_down_sync(0xffffffffu, o.w.sp, 1);
+  if (lane == 31) { o.nxp = 0; o.nxsp = 0xffu; if (W + 1 <= W1) { const PkWord x = pk_word(B.sb, W + 1, a2, b2); o.nxp = x.p; o.nxsp = x.sp; } }
+  o.prevsp = __shfl_up_sync(0xffffffffu, o.w.sp, 1);
+  if (lane == 0) o.prevsp = carry_sp;
+  return o;
+}
+__device__ __forceinline__ int32_t pk_warp_excl(int32_t v, int lane, int32_t* total) {
+  int32_t x = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const int32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+  *total = __shfl_sync(0xffffffffu, x, 31);
+  return x - v;
+}
+__global__ void k_clause_count_w(TrcDev D, TrcSentState S, const int64_t* __restrict__ ob, int64_t nob, int32_t* ncl, int32_t* ob_words) {
+  WSTRIDE(i, nob) {
+    const int lane = TRC_LANE;
+    const int64_t r = ob[i];
+    TrcSent& R = S.recs[r];
+    const PkBuf B = pk_buf(D.C);
+    const int64_t a2 = R.off + B.mis, b2 = R.off + R.len + B.mis, W0 = a2 >> 3, W1 = (b2 - 1) >> 3;
+    int64_t ends = 0, words = 0;
+    uint32_t carry = 0xffu;
+    for (int64_t base = W0; base <= W1; base += 32) {
+      const PkWarpWord x = pk_warp_word(B, base, W1, a2, b2, lane, carry);
+      ends += __popc(x.w.p & ~((x.w.p >> 1) | ((x.nxp & 1u) << 7)));
+      words += __popc(~x.w.sp & 0xffu & ((x.w.sp << 1) | ((x.prevsp >> 7) & 1u)));
+      carry = __shfl_sync(0xffffffffu, x.w.sp, 31);
+    }
+    ends = trc_lanes_sum(ends); words = trc_lanes_sum(words);
+    const int32_t nc = (int32_t)ends - (pk_clause_punct(D.C[R.off]) ? 1 : 0);
+    const int32_t n = nc > 0 ? nc : (int32_t)((words + 19) / 20);
+    if (lane == 0) { R.ncl = n; ncl[r] = n; ob_words[i] = nc > 0 ? -1 : (int32_t)words; }
+  }
+}
+// raw clause ranges [rs[u], re[u]) of every clause record u (before strip)
+__global__ void k_clause_ranges_w(TrcDev D, TrcSentState S, const int64_t* __restrict__ ob, int64_t nob, const int32_t* __restrict__ ob_words,
+                                  const int64_t* __restrict__ clscan, int64_t* rs, int64_t* re) {
+  WSTRIDE(i, nob) {
+    const int lane = TRC_LANE;
+    const int64_t r = ob[i];
+    TrcSent& R = S.recs[r];
+    if (R.ncl == 0) continue;
+    const int64_t u0 = clscan[r];
+    const int32_t n = R.ncl, words = ob_words[i];
+    if (lane == 0) R.cl0 = S.n_sent + u0;
+    const PkBuf B = pk_buf(D.C);
+    const int64_t a = R.off, a2 = a + B.mis, b2 = a + R.len + B.mis, W0 = a2 >> 3, W1 = (b2 - 1) >> 3;
+    uint32_t carry = 0xffu;
+    int32_t kbase = 0;
+    if (words < 0) {                                       // punctuation runs end the clauses
+      const int32_t lead = pk_clause_punct(D.C[a]) ? 1 : 0;
+      if (!lead && lane == 0) rs[u0] = a;
+      for (int64_t base = W0; base <= W1; base += 32) {
+        const PkWarpWord x = pk_warp_word(B, base, W1, a2, b2, lane, carry);
+        uint32_t e = x.w.p & ~((x.w.p >> 1) | ((x.nxp & 1u) << 7));
+        int32_t tot;
+        int32_t k = kbase + pk_warp_excl(__popc(e), lane, &tot) - lead;
+        while (e) {
+          const int bit = __ffs(e) - 1;
+          e &= e - 1;
+          const int64_t ce = 8 * (base + lane) + bit + 1 - B.mis;
+          if (k >= 0 && k < n) re[u0 + k] = ce;
+          if (k + 1 < n) rs[u0 + k + 1] = ce;               // also the leading run's end (k == -1): start of clause 0
+          ++k;
+        }
+        kbase += tot;
+        carry = __shfl_sync(0xffffffffu, x.w.sp, 31);
+      }
+    } else {                                               // groups of 20 words
+      for (int64_t base = W0; base <= W1; base += 32) {
+        const PkWarpWord x = pk_warp_word(B, base, W1, a2, b2, lane, carry);
+        const uint32_t ws = ~x.w.sp & 0xffu & ((x.w.sp << 1) | ((x.prevsp >> 7) & 1u));
+        const uint32_t we = ~x.w.sp & 0xffu & ((x.w.sp >> 1) | ((x.nxsp & 1u) << 7));
+        int32_t tot;
+        const int32_t w0 = kbase + pk_warp_excl(__popc(ws), lane, &tot);   // words that start before this lane's word
+        uint32_t t = ws;
+        while (t) {
+          const int bit = __ffs(t) - 1;
+          t &= t - 1;
+          const int32_t idx = w0 + __popc(ws & ((1u << bit) - 1u));
+          if (idx % 20 == 0) rs[u0 + idx / 20] = 8 * (base + lane) + bit - B.mis;
+        }
+        t = we;
+        while (t) {
+          const int bit = __ffs(t) - 1;
+          t &= t - 1;
+          const int32_t idx = w0 + __popc(ws & ((2u << bit) - 1u)) - 1;   // the word that ends here
+          if ((idx + 1) % 20 == 0 || idx + 1 == words) re[u0 + idx / 20] = 8 * (base + lane) + bit + 1 - B.mis;
+        }
+        kbase += tot;
+        carry = __shfl_sync(0xffffffffu, x.w.sp, 31);
+      }
+    }
+  }
+}
+__global__ void k_clause_recs(TrcDev D, TrcSentState S, const int64_t* __restrict__ clscan, int64_t n_cl, const int64_t* __restrict__ rs,
+                              const int64_t* __restrict__ re, int64_t* chars64) {
+  GSTRIDE(u, n_cl) {
+    const int64_t r = rl_find(clscan, S.n_sent, u);
+    const TrcSent& P = S.recs[r];
+    const uint8_t* s = D.C;
+    int64_t ca = rs[u], cb = re[u];
+    while (ca < cb && s[ca] == ' ') ++ca;
+    while (cb > ca && s[cb - 1] == ' ') --cb;
+    TrcSent& R = S.recs[S.n_sent + u];
+    R.group = P.group; R.kind = 2; R.off = ca; R.len = cb - ca; R.chars = pk_count_chars(s, ca, cb);
+    R.tok = 0; R.sub = -1; R.last_in_sub = 0; R.off_in_sub = 0; R.parent = (int32_t)r; R.ncl = 0; R.cl0 = 0; R.start = 0; R.end = 0;
+    chars64[u] = R.chars;
+  }
+}
+__global__ void k_clause_times(TrcSentState S, const int64_t* __restrict__ clscan, int64_t n_cl, const int64_t* __restrict__ ccs,
+                               int64_t* ustart, int64_t* uend) {
+  GSTRIDE(u, n_cl) {
+    TrcSent& R = S.recs[S.n_sent + u];
+    const TrcSent& P = S.recs[R.parent];
+    const double span = P.end - P.start;
+    const double tpc = P.chars > 0 ? span / (double)P.chars : 0.0;
+    const int64_t done = ccs[u] - ccs[clscan[R.parent]];
+    const double m1 = tpc * (double)done;
+    R.start = P.start + m1;
+    const double m2 = tpc * (double)R.chars;
+    R.end = R.start + m2;
+    ustart[u] = R.off; uend[u] = R.off + R.len;
+  }
+}
+#endif
 __global__ void k_clause_tok(TrcTables T, TrcSentState S, const int64_t* hs, const int64_t* he, const int64_t* ts, const int64_t* te,
                              const int64_t* wsum, const uint32_t* hc, const uint32_t* tc, int64_t n_cl) {
   GSTRIDE(u, n_cl) {
@@ -369,7 +511,20 @@ static int sentence_stage_count(trc_ctx* ctx, cudaStream_t st, int32_t* nsub_g, 
   LAUNCH(k_sent_wordsum, S.n_sent, 128, D, S, ctx->WS, (int64_t)0, S.n_sent, ustart, uend, tst, ten, wsum);
   if ((rc = count_units(ctx, st, D.C, ustart, uend, S.n_sent, total, 1, cnt, nullptr, false))) return rc;
   if (ctx->WS.of_seg) { if ((rc = count_units(ctx, st, D.C, tst, ten, S.n_sent, total, 0, tcnt, nullptr, false))) return rc; }
-  LAUNCH(k_sent_tok, S.n_sent, 128, D, ctx->T, S, ustart, uend, tst, ten, wsum, cnt, tcnt, ncl);
+#ifdef TRC_HOSTSIM
+  LAUNCH(k_sent_tok, S.n_sent, 128, D, ctx->T, S, ustart, uend, tst, ten, wsum, cnt, tcnt, ncl, (int64_t*)nullptr, (unsigned long long*)nullptr);
+#else
+  int64_t* ob; unsigned long long* ob_cnt; int32_t* ob_words = nullptr;
+  ALLOC(ob, int64_t, S.n_sent); ALLOC(ob_cnt, unsigned long long, 1);
+  CK(cudaMemsetAsync(ob_cnt, 0, 8, st));
+  LAUNCH(k_sent_tok, S.n_sent, 128, D, ctx->T, S, ustart, uend, tst, ten, wsum, cnt, tcnt, ncl, ob, ob_cnt);
+  int64_t nob = 0;
+  if ((rc = read_back(ctx, st, ob_cnt, 8, &nob))) return rc;
+  if (nob > 0) {
+    ALLOC(ob_words, int32_t, nob);
+    LAUNCH_W(k_clause_count_w, nob, D, S, ob, nob, ncl, ob_words);
+  }
+#endif
   if ((rc = scan_excl(ctx, st, ncl, clscan, S.n_sent))) return rc;
   int64_t ncls = 0;
   if ((rc = read_back(ctx, st, clscan + S.n_sent, 8, &ncls))) return rc;
@@ -380,7 +535,18 @@ static int sentence_stage_count(trc_ctx* ctx, cudaStream_t st, int32_t* nsub_g, 
     S.recs = recs; S.n_recs = S.n_sent + ncls;
     int64_t* cus; int64_t* cue; uint32_t* ccnt;
     ALLOC(cus, int64_t, ncls); ALLOC(cue, int64_t, ncls); ALLOC(ccnt, uint32_t, ncls);
+#ifdef TRC_HOSTSIM
     LAUNCH(k_clause_build, S.n_sent, 64, D, S, clscan, cus, cue);
+#else
+    {
+      int64_t* rs; int64_t* re; int64_t* cch; int64_t* ccs;
+      ALLOC(rs, int64_t, ncls); ALLOC(re, int64_t, ncls); ALLOC(cch, int64_t, ncls); ALLOC(ccs, int64_t, ncls + 1);
+      LAUNCH_W(k_clause_ranges_w, nob, D, S, ob, nob, ob_words, clscan, rs, re);
+      LAUNCH(k_clause_recs, ncls, 128, D, S, clscan, ncls, rs, re, cch);
+      if ((rc = scan_excl(ctx, st, cch, ccs, ncls))) return rc;
+      LAUNCH(k_clause_times, ncls, 128, S, clscan, ncls, ccs, cus, cue);
+    }
+#endif
     int64_t* cwsum; int64_t* cts; int64_t* cte; uint32_t* ctc;
     ALLOC(cwsum, int64_t, ncls); ALLOC(cts, int64_t, ncls); ALLOC(cte, int64_t, ncls); ALLOC(ctc, uint32_t, ncls);
     LAUNCH(k_sent_wordsum, ncls, 128, D, S, ctx->WS, S.n_sent, ncls, cus, cue, cts, cte, cwsum);

@@ -62,8 +62,10 @@ def check_fuzz_cases(eng, cases, require_all=True, foreign=False):
     return n_ok
 
 
-def sentence_fuzz(eng, n_cases, seed):
-    """Over-budget un-merged segments: Punkt sentences, clause splits, 20-word splits, nested greedy."""
+def sentence_fuzz(eng, n_cases, seed, giant=False):
+    """Over-budget un-merged segments: Punkt sentences, clause splits, 20-word splits, nested greedy.
+    giant=True: segments of 5-10 KB, i.e. larger than a fused tile's share (pre-tokenised word by word in stage P;
+    sentence and clause token counts are then differences of the per-word running sum, partial edge words apart)."""
     import random
     import fuzzgen
     from oracle import chunker as OC, preprocess as OP
@@ -76,7 +78,7 @@ def sentence_fuzz(eng, n_cases, seed):
         segs = []
         t = 0.0
         for k in range(nseg):
-            words = [rng.choice(fuzzgen.WORDS + extra) for _ in range(rng.randint(30, 260))]
+            words = [rng.choice(fuzzgen.WORDS + extra) for _ in range(rng.randint(900, 1800) if giant else rng.randint(30, 260))]
             if rng.random() < 0.15:
                 words = [w.strip(",.;:?!") or "w" for w in words]          # forces the 20-word path
             elif rng.random() < 0.2:
@@ -85,7 +87,7 @@ def sentence_fuzz(eng, n_cases, seed):
             segs.append({"start": t if rng.random() < 0.5 else int(t), "end": t + d, "text": " ".join(words),
                          "speaker": rng.choice(["A", "B", ""])})
             t += d
-        mt = rng.choice([158, 165, 180, 220, 300])
+        mt = rng.choice([158, 165, 180, 220, 300] + ([600, 1500] if giant else []))
         op = OP.preprocess(segs, rng.random() < 0.5)
         merge = "is_combined" in json.dumps(op)
         proc, chunks = run_dropin(eng, segs, mt, merge=merge)

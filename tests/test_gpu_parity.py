@@ -136,6 +136,7 @@ def test_idempotent_rerun(gpu_engine):
 
 def test_sentence_path_fuzz(gpu_engine):
     pc.sentence_fuzz(gpu_engine, 300, 1234)
+    pc.sentence_fuzz(gpu_engine, 40, 77, giant=True)
 
 
 def test_config4_monologues(gpu_engine):

@@ -92,6 +92,7 @@ def test_empty_inputs(hostsim_engine):
 
 def test_sentence_path_fuzz(hostsim_engine):
     pc.sentence_fuzz(hostsim_engine, 300, 99)
+    pc.sentence_fuzz(hostsim_engine, 10, 77, giant=True)
 
 
 def test_foreign_processed_lists(hostsim_engine):
