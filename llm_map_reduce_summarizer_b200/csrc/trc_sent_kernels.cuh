@@ -19,26 +19,69 @@ TRC_HD int64_t rl_find(const int64_t* boff, int64_t n, int64_t pos) {   // last 
   return lo;
 }
 
-// one thread per text byte of the over-budget raw segments: Punkt break decision
-__global__ void k_punkt_breaks(TrcDev D, TrcTables T, TrcSentState S, int64_t total, int32_t* brk) {
-  GSTRIDE(p, total) {
-    int64_t q = rl_find(S.rl_boff, S.n_rl, p);
-    int32_t j = D.gstart[S.rl_groups[q]];
-    const uint8_t* s = D.C + D.coff[j];
-    int64_t n = D.coff[j + 1] - D.coff[j];
-    int64_t i = p - S.rl_boff[q];
-    brk[p] = pk_sentend(s[i]) && pk_is_break(T, s, n, i);
-    // domain check (only ever fails for text that did not come through clean_text): the sentence path
-    // assumes single U+0020 between words and no leading/trailing whitespace
-    uint8_t c = s[i];
-    bool bad = false;
-    if (c == ' ') bad = (i == 0 || i + 1 == n || s[i + 1] == ' ');
-    else if (c < 0x80) bad = (T.props[c] & TRC_P_SPACE) != 0;
-    else if (c >= 0xC0) { int l; uint32_t cp = trc_decode(s, i, n, &l); bad = (T.props[cp] & TRC_P_SPACE) != 0; }
-    if (bad) D.doc_err[D.sdoc[j]] = -1;
+// Punkt break decision for every text byte of the over-budget raw segments, a thread per 8 bytes.  Ordinary
+// cells (inside one segment, ASCII, no control bytes) are handled on bit masks: only the '.', '?' and '!' bytes
+// go through the context test; the domain check of the sentence path (single U+0020 between words, no leading /
+// trailing whitespace - it only ever fails for text that did not come through clean_text) is two mask tests.
+TRC_HD void pk_break_byte(const TrcDev& D, const TrcTables& T, const uint8_t* s, int64_t n, int64_t i, int32_t j, uint8_t* out) {
+  *out = pk_sentend(s[i]) && pk_is_break(T, s, n, i);
+  uint8_t c = s[i];
+  bool bad = false;
+  if (c == ' ') bad = (i == 0 || i + 1 == n || s[i + 1] == ' ');
+  else if (c < 0x80) bad = (T.props[c] & TRC_P_SPACE) != 0;
+  else if (c >= 0xC0) { int l; uint32_t cp = trc_decode(s, i, n, &l); bad = (T.props[cp] & TRC_P_SPACE) != 0; }
+  if (bad) D.doc_err[D.sdoc[j]] = -1;
+}
+TRC_HD void pk_break_cell(const TrcDev& D, const TrcTables& T, const TrcSentState& S, int64_t total, int64_t cell, uint8_t* brk) {
+  const int64_t p0 = cell * 8;
+  int64_t q = rl_find(S.rl_boff, S.n_rl, p0);
+  if (p0 + 16 <= S.rl_boff[q + 1]) {                        // (two aligned words are read: both inside the segment)
+    const int32_t j = D.gstart[S.rl_groups[q]];
+    const int64_t c0 = D.coff[j], n = D.coff[j + 1] - c0, i = p0 - S.rl_boff[q];
+    const PkBuf B = pk_buf(D.C);
+    const int64_t c = c0 + i + B.mis;
+    uint64_t lo, hi;
+#if defined(__CUDA_ARCH__)
+    lo = *reinterpret_cast<const unsigned long long*>(B.sb + (c & ~7LL)); hi = *reinterpret_cast<const unsigned long long*>(B.sb + (c & ~7LL) + 8);
+#else
+    memcpy(&lo, B.sb + (c & ~7LL), 8); memcpy(&hi, B.sb + (c & ~7LL) + 8, 8);
+#endif
+    const unsigned sh = (unsigned)(c & 7) * 8u;
+    const uint64_t x = sh ? (lo >> sh) | (hi << (64 - sh)) : lo;
+    const uint8_t nextb = i + 8 < n ? (uint8_t)((sh ? hi >> sh : hi) & 0xff) : (uint8_t)'x';
+    const uint64_t sp = pk_eq8(x, ' ');
+    const uint64_t low = ~(((x & ~SW_H) | SW_H) - SW_L * 0x21) & SW_H;       // ASCII bytes below 0x21
+    if (!((x & SW_H) | (low & ~sp))) {
+      uint64_t bad = sp & ((sp >> 8) | (nextb == ' ' ? (0x80ULL << 56) : 0ULL));   // two spaces in a row
+      if (i == 0) bad |= sp & 0x80ULL;                                              // leading space
+      if (n - i <= 8) bad |= sp & (0x80ULL << (8 * (n - 1 - i)));                   // trailing space
+      if (bad) D.doc_err[D.sdoc[j]] = -1;
+      uint32_t se = sw_pack(pk_eq8(x, '.') | pk_eq8(x, '?') | pk_eq8(x, '!'));
+      uint64_t flags = 0;
+      const uint8_t* s = D.C + c0;
+      while (se) {
+        const int k = (int)trc_ctz32(se);
+        se &= se - 1;
+        if (pk_is_break(T, s, n, i + k)) flags |= 1ULL << (8 * k);
+      }
+#if defined(__CUDA_ARCH__)
+      *reinterpret_cast<unsigned long long*>(brk + p0) = flags;
+#else
+      memcpy(brk + p0, &flags, 8);
+#endif
+      return;
+    }
+  }
+  for (int64_t p = p0; p < p0 + 8 && p < total; ++p) {      // cell across a segment edge, or with unusual bytes
+    while (p >= S.rl_boff[q + 1]) ++q;
+    const int32_t j = D.gstart[S.rl_groups[q]];
+    pk_break_byte(D, T, D.C + D.coff[j], D.coff[j + 1] - D.coff[j], p - S.rl_boff[q], j, brk + p);
   }
 }
-__global__ void k_brk_pos(const int32_t* __restrict__ brk, const int64_t* __restrict__ bscan, int64_t total, int64_t* pos) {
+__global__ void k_punkt_breaks(TrcDev D, TrcTables T, TrcSentState S, int64_t total, uint8_t* brk) {
+  GSTRIDE(cell, (total + 7) / 8) pk_break_cell(D, T, S, total, cell, brk);
+}
+__global__ void k_brk_pos(const uint8_t* __restrict__ brk, const int64_t* __restrict__ bscan, int64_t total, int64_t* pos) {
   GSTRIDE(p, total) if (brk[p]) pos[bscan[p]] = p;
 }
 __global__ void k_sent_counts(TrcSentState S, const int64_t* __restrict__ bscan, int32_t* ns) {
@@ -484,9 +527,9 @@ static int sentence_stage_count(trc_ctx* ctx, cudaStream_t st, int32_t* nsub_g, 
   if ((rc = read_back(ctx, st, rl_boff + nraw, 8, &total))) return rc;
   S.rl_groups = rl_groups; S.n_rl = nraw; S.rl_boff = rl_boff;
   // Punkt breaks
-  int32_t* brk; int64_t* bscan;
-  ALLOC(brk, int32_t, total); ALLOC(bscan, int64_t, total + 1);
-  LAUNCH(k_punkt_breaks, total, 128, D, ctx->T, S, total, brk);
+  uint8_t* brk; int64_t* bscan;
+  ALLOC(brk, uint8_t, total + 8); ALLOC(bscan, int64_t, total + 1);
+  LAUNCH(k_punkt_breaks, (total + 7) / 8, 128, D, ctx->T, S, total, brk);
   if ((rc = scan_excl(ctx, st, brk, bscan, total))) return rc;
   int64_t nbrk = 0;
   if ((rc = read_back(ctx, st, bscan + total, 8, &nbrk))) return rc;
