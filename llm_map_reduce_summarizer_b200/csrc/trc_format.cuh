@@ -15,6 +15,11 @@ TRC_HD void trc_ts_split(double x, int64_t* h, int* m, int* s) {
   else if (x >= 9.2e18) t = INT64_MAX;
   else if (x <= -9.2e18) t = INT64_MIN + 1;
   else t = (int64_t)x;
+  if (t >= 0 && t < 2147483648LL) {             // the usual case in 32-bit arithmetic (divisions by constants: multiply + shift)
+    const uint32_t u = (uint32_t)t, hq = u / 3600u, r32 = u - hq * 3600u, mq = r32 / 60u;
+    *h = (int64_t)hq; *m = (int)mq; *s = (int)(r32 - mq * 60u);
+    return;
+  }
   int64_t hh = t / 3600, r = t % 3600;
   if (r < 0) { r += 3600; hh -= 1; }
   *h = hh; *m = (int)(r / 60); *s = (int)(r % 60);
@@ -22,6 +27,7 @@ TRC_HD void trc_ts_split(double x, int64_t* h, int* m, int* s) {
 
 TRC_HD int trc_udigits(uint64_t v, char* tmp) {  // writes reversed digits, returns count
   int n = 0;
+  if (v < 4294967296ULL) { uint32_t u = (uint32_t)v; do { const uint32_t q = u / 10u; tmp[n++] = (char)('0' + (u - q * 10u)); u = q; } while (u); return n; }
   do { tmp[n++] = (char)('0' + (v % 10)); v /= 10; } while (v);
   return n;
 }
