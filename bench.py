@@ -22,7 +22,9 @@ UNIT = "tokens/s"
 # every array a caller needs to rebuild the processed segments and the chunks: the cleaned piece texts are
 # slices of TWC (PDST + COFF lengths) and so are the merged texts (ITEM_DST; a piece's offset inside its merged
 # text is PDST minus that), so neither the cleaned-text buffer nor the merged-text offsets are copied back
-OUT_ARRAYS = [("K2R", "<i4"), ("COFF", "<i8"), ("PDST", "<i8"), ("GSTART", "<i4"), ("GTS", "u1"),
+# CLEN32 carries the piece lengths (COFF's differences); K2R is the identity when no segment was blank, which the
+# counters of the call say, so it is only downloaded when segments were dropped
+OUT_ARRAYS = [("K2R", "<i4"), ("CLEN32", "<i4"), ("PDST", "<i8"), ("GSTART", "<i4"), ("GTS", "u1"),
               ("GTOK", "<i8"), ("ITEM_GROUP", "<i4"), ("ITEM_SUB", "<i4"), ("ITEM_TOK", "<i4"), ("ITEM_LEN", "<i8"),
               ("ITEM_DST", "<i8"), ("SUBS", None), ("CHUNKS", None), ("SPK_LIST", "<i4"), ("TWC", "u1"), ("DOC_ERR", "<i4"),
               ("GDOC_OFF", "<i8"), ("CDOC_OFF", "<i8")]
@@ -311,7 +313,10 @@ def main():
             en.preprocess(hb_, want_merged_text=False, stream=stream.cuda_stream)
             en.chunk(mt_, stream=stream.cuda_stream)
             total = 0
+            cn = en.counts()
             for name, _ in OUT_ARRAYS:
+                if name == "K2R" and cn["n_kept"] == cn["n_seg"]:
+                    continue
                 nb = en.array_into(name, None, 0)
                 if name not in po or po[name].numel() < nb:
                     po[name] = torch.empty(max(nb, 1) + max(nb, 1) // 8, dtype=torch.uint8).pin_memory()

@@ -140,6 +140,8 @@ enum {
   TRC_A_AGG_PIECE,    /* int32 []            kept-segment indices: the components that survive in a member        */
   TRC_A_AGG_TEXT,     /* uint8 [B_agg]       the aggregated texts back to back                                    */
   TRC_A_AGG_DOC_OFF,  /* int64 [n_doc+1]     trc_agg range of every document                                      */
+  TRC_A_CLEN32,       /* int32 [n_kept]      byte length of every kept segment's cleaned text (== differences of       */
+                      /*                     TRC_A_COFF; half the bytes for callers that download results over PCIe)  */
   TRC_A__COUNT
 };
 int trc_get_array(trc_ctx* ctx, int which, void* dst, int64_t dst_bytes, int32_t memory, int64_t* nbytes,

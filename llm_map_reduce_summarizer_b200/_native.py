@@ -11,7 +11,7 @@ COUNTERS = ["n_seg", "n_kept", "n_groups", "n_items", "n_subs", "n_chunks", "b_r
 N_COUNTERS = 24
 ARRAYS = ["K2R", "COFF", "CLEAN", "CTOK", "GSTART", "POFF", "MERGED", "GTS", "GTOK", "ITEM_GROUP", "ITEM_SUB", "ITEM_TOK",
           "ITEM_LEN", "ITEM_DST", "SUBS", "CHUNKS", "SPK_LIST", "TWC", "DOC_ERR", "GDOC_OFF", "CDOC_OFF", "CCHARS", "SENT", "PDST",
-          "AGG", "AGG_MEM", "AGG_PIECE", "AGG_TEXT", "AGG_DOC_OFF"]
+          "AGG", "AGG_MEM", "AGG_PIECE", "AGG_TEXT", "AGG_DOC_OFF", "CLEN32"]
 A = {n: i for i, n in enumerate(ARRAYS)}
 ERRORS = {-1: "TRC_ECUDA", -2: "TRC_EINVAL", -3: "TRC_ENOVOCAB", -4: "TRC_EUNSUPPORTED"}
 

@@ -549,6 +549,7 @@ __global__ void k_verify_groups(TrcDev D, TrcTables T, const double* __restrict_
   }
 }
 
+__global__ void k_clen32(const int64_t* __restrict__ coff, int64_t nk, int32_t* out) { GSTRIDE(j, nk) out[j] = (int32_t)(coff[j + 1] - coff[j]); }
 __global__ void k_merge_next(TrcDev D) { GSTRIDE(j, D.n_kept) trc_merge_next(D, j); }
 __global__ void k_orbit(const int64_t* __restrict__ range_off, const int32_t* __restrict__ nxt, int32_t* flag, int64_t n_doc) {
   GSTRIDE(x, n_doc) trc_orbit_walk(range_off, nxt, flag, x);
@@ -1292,6 +1293,12 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   set_arr(ctx, TRC_A_POFF, D.poff, 8 * (nk + 1)); set_arr(ctx, TRC_A_GTS, D.gts, 48 * m); set_arr(ctx, TRC_A_GTOK, D.gtok, 8 * m);
   set_arr(ctx, TRC_A_DOC_ERR, D.doc_err, 4 * nd); set_arr(ctx, TRC_A_GDOC_OFF, D.gdoc_off, 8 * (nd + 1));
   set_arr(ctx, TRC_A_CCHARS, D.cchars, 4 * n);
+  {
+    int32_t* clen32;
+    ALLOC(clen32, int32_t, nk);
+    LAUNCH(k_clen32, nk, 256, D.coff, nk, clen32);
+    set_arr(ctx, TRC_A_CLEN32, clen32, 4 * nk);
+  }
   ctx->have_pre = true;
   return TRC_OK;
 }

@@ -103,6 +103,7 @@ def test_full_size_properties(gpu_engine):
     R = e.fetch_chunks()
     ch = R["chunks"]
     assert c["n_doc"] == b.n_doc and c["n_kept"] <= c["n_seg"]
+    assert (e.array("CLEN32", "<i4") == np.diff(e.array("COFF", "<i8"))).all()
     # every item lands in exactly one chunk, chunks tile the item list, token sums agree
     assert (ch["item0"][1:] == ch["item1"][:-1]).all() and ch["item0"][0] == 0 and ch["item1"][-1] == c["n_items"]
     assert int(ch["token_count"].sum()) == int(R["item_tok"].sum()) == c["tokens"]

@@ -74,6 +74,7 @@ def test_synthetic_docs_vs_oracle(hostsim_engine):
         e.preprocess(b)
         e.chunk(mt)
         P, R = e.fetch_processed(), e.fetch_chunks()
+        assert (e.array("CLEN32", "<i4") == np.diff(P["coff"])).all()
         for x in range(b.n_doc):
             segs = synth.doc_to_segments(b, x)
             op = OP.preprocess(segs)
