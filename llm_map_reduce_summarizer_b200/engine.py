@@ -38,33 +38,37 @@ class PackedBatch:
         return len(self.doc_off) - 1
 
 
+def _finite_f64(values):
+    arr = np.fromiter(map(float, values), dtype=np.float64, count=len(values))
+    if arr.size and not np.isfinite(arr).all():
+        if np.isnan(arr).any():
+            raise ValueError("cannot convert float NaN to integer")
+        raise OverflowError("cannot convert float infinity to integer")
+    return arr
+
+
 def pack_documents(docs):
     """list of transcripts (each a list of {start,end,text,speaker} dicts) -> PackedBatch.
     Mirrors the defaults of preprocessor.py:46-50 (`segment.get(key, default)`)."""
     texts, starts, ends, spk_names, doc_off = [], [], [], [], [0]
     for segs in docs:
-        for seg in segs:
-            t = seg.get("text", "")
-            t.strip                                    # same AttributeError as the reference for non-str text
-            texts.append(t.encode("utf-8"))           # lone surrogates raise UnicodeEncodeError (unsupported)
-            starts.append(seg.get("start", 0))
-            ends.append(seg.get("end", 0))
-            s = seg.get("speaker", "")
-            if not isinstance(s, str):
-                raise TypeError("speaker must be a str (the reference's header join fails otherwise)")
-            spk_names.append(s)
+        texts += [seg.get("text", "") for seg in segs]
+        starts += [seg.get("start", 0) for seg in segs]
+        ends += [seg.get("end", 0) for seg in segs]
+        spk_names += [seg.get("speaker", "") for seg in segs]
         doc_off.append(len(texts))
+    for t in texts:
+        if type(t) is not str:
+            t.strip                                    # same AttributeError as the reference for non-str text
+    for s in spk_names:
+        if type(s) is not str and not isinstance(s, str):
+            raise TypeError("speaker must be a str (the reference's header join fails otherwise)")
+    enc = [t.encode("utf-8") for t in texts]          # lone surrogates raise UnicodeEncodeError (unsupported)
     names = sorted(set(spk_names) | {""})
     ids = {s: i for i, s in enumerate(names)}
-    buf, off = _vocab.pack_strings(texts)
-    st = np.array([float(x) for x in starts], dtype=np.float64)
-    en = np.array([float(x) for x in ends], dtype=np.float64)
-    for arr in (st, en):
-        if arr.size and not np.isfinite(arr).all():
-            if np.isnan(arr).any():
-                raise ValueError("cannot convert float NaN to integer")
-            raise OverflowError("cannot convert float infinity to integer")
-    spk = np.array([ids[s] for s in spk_names], dtype=np.int32)
+    buf, off = _vocab.pack_strings(enc)
+    st, en = _finite_f64(starts), _finite_f64(ends)
+    spk = np.fromiter(map(ids.__getitem__, spk_names), dtype=np.int32, count=len(spk_names))
     return PackedBatch(buf, off, st, en, spk, np.array(doc_off, dtype=np.int64), names, (starts, ends))
 
 
@@ -285,6 +289,14 @@ class Engine:
                 "cdoc_off": self.array("CDOC_OFF", "<i8"), "sent": self.array("SENT", N.SENT_DTYPE)}
 
 
+def _text_of(arrays, key):
+    """The _Text view of arrays[key], built once per fetched result (documents of a batch share it)."""
+    t = arrays.get("_text_" + key)
+    if t is None:
+        t = arrays["_text_" + key] = _Text(arrays[key])
+    return t
+
+
 class _Text:
     """Slices of a UTF-8 byte buffer as str; ASCII buffers are decoded once."""
 
@@ -300,17 +312,24 @@ def build_processed(batch, P, doc=0, piece_dicts=None):
     """Processed-segment dicts of document `doc` in the reference's format (preprocessor.py:45-52,203-213).
     piece_dicts: the caller's own processed dicts when the pieces came in already processed; a group of
     one is then returned as that very object (preprocessor.py:181-183)."""
-    starts, ends = batch.originals if batch.originals is not None else (batch.start.tolist(), batch.end.tolist())
-    k2r, coff, gstart, poff, gts = P["k2r"], P["coff"], P["gstart"], P["poff"], P["gts"]
-    clean, merged = _Text(P["clean"]), _Text(P["merged"])
-    gts_b = gts.tobytes()
-    out = []
+    if batch.originals is None:                               # synthetic batches: the float64 arrays are the times
+        batch.originals = (batch.start.tolist(), batch.end.tolist())
+    starts, ends = batch.originals
     g0, g1 = int(P["gdoc_off"][doc]), int(P["gdoc_off"][doc + 1])
+    gstart = P["gstart"][g0:g1 + 1].tolist()                 # plain lists: element access on numpy arrays is slow
+    p0, p1 = (gstart[0], gstart[-1]) if g1 > g0 else (0, 0)
+    k2r = P["k2r"][p0:p1].tolist()
+    coff = P["coff"][p0:p1 + 1].tolist()
+    poff = P["poff"][p0:p1 + 1].tolist()
+    clean, merged = _text_of(P, "clean"), _text_of(P, "merged")
+    gts_b = P["gts"].tobytes()
+    out = []
     names = batch.speakers
     spk = batch.speaker
+    cget, mget = clean.get, merged.get
     for g in range(g0, g1):
-        a, b = int(gstart[g]), int(gstart[g + 1])
-        ra, rb = int(k2r[a]), int(k2r[b - 1])
+        a, b = gstart[g - g0] - p0, gstart[g - g0 + 1] - p0
+        ra, rb = k2r[a], k2r[b - 1]
         if piece_dicts is not None and b - a == 1:
             out.append(piece_dicts[ra])
             continue
@@ -318,12 +337,12 @@ def build_processed(batch, P, doc=0, piece_dicts=None):
         sf = gts_b[o + 1:o + 1 + gts_b[o]].decode("ascii")
         ef = gts_b[o + 25:o + 25 + gts_b[o + 24]].decode("ascii")
         d = {"start": starts[ra], "end": ends[rb], "start_formatted": sf, "end_formatted": ef,
-             "speaker": names[spk[ra]], "text": merged.get(int(poff[a]), int(poff[b]))}
+             "speaker": names[spk[ra]], "text": mget(poff[a], poff[b])}
         if b - a > 1:
             d["is_combined"] = True
             d["original_segments"] = b - a
-            d["segment_timestamps"] = [{"start": starts[int(k2r[j])], "end": ends[int(k2r[j])],
-                                        "text": clean.get(int(coff[j]), int(coff[j + 1]))} for j in range(a, b)]
+            d["segment_timestamps"] = [{"start": starts[r], "end": ends[r], "text": cget(coff[j], coff[j + 1])}
+                                       for j, r in zip(range(a, b), k2r[a:b])]
         out.append(d)
     return out
 
@@ -333,7 +352,7 @@ def build_aggregated(batch, P, AG, processed, interval_seconds, doc=0):
     is the document's processed list (its start / end / speaker objects are reused as they are)."""
     g0 = int(P["gdoc_off"][doc])
     a0, a1 = int(AG["adoc_off"][doc]), int(AG["adoc_off"][doc + 1])
-    text = _Text(AG["text"])
+    text = _text_of(AG, "text")
     mem = AG["mem"]
     start_time, end_time = processed[0]["start"], processed[-1]["end"]
     out = []
@@ -377,10 +396,12 @@ def build_chunks(engine, batch, P, R, processed, doc=0):
         raise special_token_error(engine, err - 1)
     if err < 0:
         raise NotImplementedError("document uses a construct outside the supported domain")
-    starts, ends = batch.originals if batch.originals is not None else (batch.start.tolist(), batch.end.tolist())
+    if batch.originals is None:
+        batch.originals = (batch.start.tolist(), batch.end.tolist())
+    starts, ends = batch.originals
     k2r, gstart = P["k2r"], P["gstart"]
     g0 = int(P["gdoc_off"][doc])
-    twc = _Text(R["twc"])
+    twc = _text_of(R, "twc")
     ch = R["chunks"]
     subs = R["subs"]
     names = batch.speakers

@@ -51,6 +51,6 @@ def pack_strings(strs):
     """list[bytes] -> (uint8 buffer, int64 offsets)."""
     off = np.zeros(len(strs) + 1, dtype=np.int64)
     if strs:
-        off[1:] = np.cumsum([len(s) for s in strs])
+        off[1:] = np.cumsum(np.fromiter(map(len, strs), dtype=np.int64, count=len(strs)))
     buf = np.frombuffer(b"".join(strs), dtype=np.uint8).copy() if strs else np.zeros(0, dtype=np.uint8)
     return buf, off
