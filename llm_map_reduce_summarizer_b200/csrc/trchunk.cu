@@ -772,6 +772,26 @@ static int read_back(trc_ctx* ctx, cudaStream_t st, const void* dsrc, size_t byt
   return TRC_OK;
 }
 
+// Two 8-byte counters in one round trip (either pointer may be null: its value is then 0).
+#ifndef TRC_HOSTSIM
+__global__ void k_read_back2(const unsigned long long* a, const unsigned long long* b, unsigned long long* dst) {
+  if (threadIdx.x == 0) dst[0] = a ? *a : 0ULL;
+  if (threadIdx.x == 1) dst[1] = b ? *b : 0ULL;
+}
+#endif
+static int read_back2(trc_ctx* ctx, cudaStream_t st, const void* a, const void* b, int64_t out[2]) {
+#ifdef TRC_HOSTSIM
+  out[0] = a ? *(const int64_t*)a : 0; out[1] = b ? *(const int64_t*)b : 0;
+#else
+  k_read_back2<<<1, 32, 0, st>>>((const unsigned long long*)a, (const unsigned long long*)b, (unsigned long long*)ctx->d_pin);
+  ctx->launches++;
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(st));
+  out[0] = ctx->h_pin[0]; out[1] = ctx->h_pin[1];
+#endif
+  return TRC_OK;
+}
+
 template <class Tp>
 static int to_device(trc_ctx* ctx, cudaStream_t st, const Tp* src, int64_t count, int memory, const Tp** out) {
   if (memory == TRC_MEM_DEVICE) { *out = src; return TRC_OK; }
@@ -1061,9 +1081,9 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   int64_t braw = 0, bspk = 0;
   if (B->memory == TRC_MEM_HOST) { braw = n ? B->seg_off[n] : 0; bspk = B->spk_off[B->n_spk]; }
   else {
-    int64_t t[1];
-    if (n) { if ((rc = read_back(ctx, st, B->seg_off + n, 8, t))) return rc; braw = t[0]; }
-    if ((rc = read_back(ctx, st, B->spk_off + B->n_spk, 8, t))) return rc; bspk = t[0];
+    int64_t t2[2];
+    if ((rc = read_back2(ctx, st, n ? B->seg_off + n : nullptr, B->spk_off + B->n_spk, t2))) return rc;
+    braw = t2[0]; bspk = t2[1];
   }
   if ((rc = to_device(ctx, st, B->text, braw, B->memory, &D.text))) return rc;
   if ((rc = to_device(ctx, st, B->seg_off, n + 1, B->memory, &D.seg_off))) return rc;
@@ -1208,8 +1228,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   if ((rc = scan_excl(ctx, st, D.clen, D.cscan, n))) return rc;
   int64_t h2[2] = {0, 0};
   if (n) {
-    if ((rc = read_back(ctx, st, D.kscan + n, 8, &h2[0]))) return rc;
-    if ((rc = read_back(ctx, st, D.cscan + n, 8, &h2[1]))) return rc;
+    if ((rc = read_back2(ctx, st, D.kscan + n, D.cscan + n, h2))) return rc;
   }
   nk = h2[0]; bclean = h2[1];
   D.n_kept = nk;
@@ -1244,10 +1263,9 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
     LAUNCH(k_orbit, nd, 64, D.kdoc_off, D.mnxt, D.gflag, nd);
   }
   if ((rc = scan_excl(ctx, st, D.gflag, D.gscan, nk))) return rc;
-  int64_t m = 0;
-  if (nk) { if ((rc = read_back(ctx, st, D.gscan + nk, 8, &m))) return rc; }
-  D.m = m; ctx->counts[TRC_N_GROUPS] = m;
-  ALLOC(D.gstart, int32_t, m + 1); ALLOC(D.gdoc_off, int64_t, nd + 1);
+  // (the number of merged segments is only needed on the host after the piece layout: gstart is sized by its
+  // bound n_kept + 1 and one round trip returns both totals)
+  ALLOC(D.gstart, int32_t, nk + 1); ALLOC(D.gdoc_off, int64_t, nd + 1);
   if (nk == 0) { CK(cudaMemsetAsync(D.gstart, 0, 4, st)); CK(cudaMemsetAsync(D.gdoc_off, 0, 8 * (size_t)(nd + 1), st)); }
   LAUNCH(k_scatter_starts, nk, 256, D.gflag, D.gscan, D.gstart, nk);
   if (nk) LAUNCH(k_map_off, nd + 1, 256, D.kdoc_off, D.gscan, D.gdoc_off, nd + 1);
@@ -1259,8 +1277,9 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   LAUNCH(k_piece_len, nk, 256, D, plen_sub);
   if ((rc = scan_excl(ctx, st, D.plen, D.poff, nk))) return rc;
   if (!D.preserve) { if ((rc = scan_excl(ctx, st, plen_sub, D.poffs, nk))) return rc; }
-  int64_t bm = 0;
-  if (nk) { if ((rc = read_back(ctx, st, D.poff + nk, 8, &bm))) return rc; }
+  int64_t m = 0, bm = 0;
+  if (nk) { int64_t t2[2]; if ((rc = read_back2(ctx, st, D.gscan + nk, D.poff + nk, t2))) return rc; m = t2[0]; bm = t2[1]; }
+  D.m = m; ctx->counts[TRC_N_GROUPS] = m;
   ctx->counts[TRC_B_MERGED] = bm;
   if (B->want_merged_text || modeB) {
     ALLOC(D.M, uint8_t, bm);
@@ -1349,8 +1368,7 @@ extern "C" int trc_chunk(trc_ctx* ctx, const int32_t* doc_max_tokens, int32_t co
   if ((rc = scan_excl(ctx, st, D.nitems_g, D.item_off, m))) return rc;
   int64_t h2[2] = {0, 0};
   if (m) {
-    if ((rc = read_back(ctx, st, D.sub_off + m, 8, &h2[0]))) return rc;
-    if ((rc = read_back(ctx, st, D.item_off + m, 8, &h2[1]))) return rc;
+    if ((rc = read_back2(ctx, st, D.sub_off + m, D.item_off + m, h2))) return rc;
   }
   const int64_t nsub = h2[0], ni = h2[1];
   D.n_subs = nsub; D.n_items = ni;
@@ -1395,8 +1413,7 @@ extern "C" int trc_chunk(trc_ctx* ctx, const int32_t* doc_max_tokens, int32_t co
   LAUNCH(k_chunk_record, nc, 64, D);
   if ((rc = scan_excl(ctx, st, D.twc_len, D.twc_scan, nc))) return rc;
   int64_t h3[2] = {0, 0};
-  if (nc) { if ((rc = read_back(ctx, st, D.twc_scan + nc, 8, &h3[0]))) return rc; }
-  if (ni) { if ((rc = read_back(ctx, st, D.W + ni, 8, &h3[1]))) return rc; }
+  if (nc || ni) { if ((rc = read_back2(ctx, st, nc ? D.twc_scan + nc : nullptr, ni ? D.W + ni : nullptr, h3))) return rc; }
   const int64_t btwc = h3[0];
   ctx->counts[TRC_B_TWC] = btwc; ctx->counts[TRC_TOKENS] = h3[1];
   ALLOC(D.twc, uint8_t, btwc);
