@@ -210,3 +210,19 @@ def test_other_rank_tables(table):
 def test_dense_tiles(gpu_engine):
     """Tiles that overrun the fused kernel's word / candidate / output / input capacities (overflow paths)."""
     assert pc.check_dense_tiles(gpu_engine) == 6
+
+
+@pytest.mark.parametrize("env", ["TRCHUNK_FUSED=2", "TRCHUNK_NO_FUSED=1", "TRCHUNK_NO_MEMO=1"])
+def test_alternate_kernel_paths(monkeypatch, env):
+    """The older kernel generations kept for A/B runs and the fused kernel without its word memo:
+    the switches are read when a context is created."""
+    k, v = env.split("=")
+    monkeypatch.setenv(k, v)
+    eng = E.Engine(0)
+    try:
+        b, mt, _ = synth.config(5, 0.01)
+        _check_docs(eng, b, mt, range(0, b.n_doc, 2))
+        assert pc.check_dense_tiles(eng) == 6
+        pc.sentence_fuzz(eng, 30, 5)
+    finally:
+        eng.close()
