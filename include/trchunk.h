@@ -203,6 +203,23 @@ typedef struct {
   int64_t text_off, text_len; /* the member's text (what 'segment_timestamps'[k]['text'] holds, :318) in TRC_A_AGG_TEXT */
 } trc_agg_mem;
 
+/* Ingest (host side): n_doc transcripts as JSON text (document x = json[doc_off[x] .. doc_off[x+1])) -> the packed
+ * batch layout above, without building Python objects.  Replaces json.load + transcript_data.get('segments', [])
+ * (main.py:337-339, :133) and the per-segment segment.get(...) defaults (preprocessor.py:46-50): missing text /
+ * speaker -> "", missing start / end -> the int 0, a repeated key keeps its last value, unknown members are
+ * validated and skipped.  Numbers go through strtod / strtoll (correctly rounded, as Python's float() / int());
+ * start_kind / end_kind say which Python type json.load would have produced (0 float, 1 int, 2 bool).  Invalid
+ * JSON, invalid UTF-8, and inputs the reference itself fails on at first use (segment not an object, text or
+ * speaker not a string, null / string / NaN / Infinity times, lone surrogates) or that do not fit the layout
+ * (integer times beyond 2^53, which float64 cannot hold exactly) are errors: err receives a message with the document and byte offset.
+ * Documents are parsed in parallel on n_threads host threads.  The result owns its arrays; trc_ingest_view fills a
+ * trc_batch (memory = TRC_MEM_HOST, merge parameters untouched) whose pointers stay valid until trc_ingest_free. */
+typedef struct trc_ingest trc_ingest;
+int trc_ingest_json(const uint8_t* json, const int64_t* doc_off, int64_t n_doc, int32_t n_threads, trc_ingest** out,
+                    char* err, int64_t err_cap);
+int trc_ingest_view(const trc_ingest* r, trc_batch* batch, const uint8_t** start_kind, const uint8_t** end_kind);
+void trc_ingest_free(trc_ingest* r);
+
 /* Token counting service: counts[i] = len(encode([" "] + bytes[off[i] .. off[i+1]))) for n strings.
  * Replaces len(self.tokenizer.encode(x)) (big_chunkeroosky.py:83,298,370,510).  special[i] (may be
  * NULL) receives the index of a special-token literal found in string i, or -1. */

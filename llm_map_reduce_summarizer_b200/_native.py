@@ -42,7 +42,7 @@ AGG_MEM_DTYPE = [("group", "<i4"), ("n_pieces", "<i4"), ("piece0", "<i8"), ("tex
 
 EXPORTS = ["trc_create", "trc_destroy", "trc_last_error", "trc_load_tables", "trc_load_vocab", "trc_preprocess",
            "trc_chunk", "trc_aggregate", "trc_get_counts", "trc_get_array", "trc_count_tokens", "trc_last_stage_ms", "trc_kernel_launches", "trc_set_profiling",
-           "trc_get_profile", "trc_bpe_span_count_static"]
+           "trc_get_profile", "trc_bpe_span_count_static", "trc_ingest_json", "trc_ingest_view", "trc_ingest_free"]
 
 
 def load_library(path=None):
@@ -71,6 +71,11 @@ def load_library(path=None):
     lib.trc_kernel_launches.argtypes = [vp, C.POINTER(i64)]
     lib.trc_set_profiling.argtypes = [vp, i32]
     lib.trc_get_profile.argtypes = [vp, C.c_char_p, i64]
+    if hasattr(lib, "trc_ingest_json"):
+        lib.trc_ingest_json.argtypes = [vp, vp, i64, i32, C.POINTER(vp), C.c_char_p, i64]
+        lib.trc_ingest_view.argtypes = [vp, C.POINTER(Batch), C.POINTER(vp), C.POINTER(vp)]
+        lib.trc_ingest_free.argtypes = [vp]
+        lib.trc_ingest_free.restype = None
     if hasattr(lib, "trc_bpe_span_count_static"):
         lib.trc_bpe_span_count_static.argtypes = [vp, vp, i64, vp, vp]
     return lib

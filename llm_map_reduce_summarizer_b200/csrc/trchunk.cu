@@ -20,6 +20,7 @@
 #include "trc_stages.cuh"
 #include "trc_sent.cuh"
 #include "trc_vocab_host.h"
+#include "trc_ingest_host.h"
 
 static_assert(sizeof(TrcSub) == sizeof(trc_sub), "trc_sub layout");
 static_assert(sizeof(TrcChunk) == sizeof(trc_chunk_rec), "trc_chunk_rec layout");
@@ -1438,6 +1439,33 @@ extern "C" int trc_chunk(trc_ctx* ctx, const int32_t* doc_max_tokens, int32_t co
   ctx->have_chunk = true;
   return TRC_OK;
 }
+
+extern "C" int trc_ingest_json(const uint8_t* json, const int64_t* doc_off, int64_t n_doc, int32_t n_threads, trc_ingest** out,
+                               char* err, int64_t err_cap) {
+  if (!json || !doc_off || n_doc < 0 || !out) return TRC_EINVAL;
+  *out = nullptr;
+  trc_ingest* R = new trc_ingest();
+  std::string e;
+  try { e = trc_ingest_run(json, doc_off, n_doc, n_threads, R); } catch (const std::exception& x) { e = std::string("ingest: ") + x.what(); }
+  if (!e.empty()) {
+    delete R;
+    if (err && err_cap > 0) { size_t k = e.size() < (size_t)err_cap - 1 ? e.size() : (size_t)err_cap - 1; memcpy(err, e.data(), k); err[k] = 0; }
+    return TRC_EINVAL;
+  }
+  *out = R;
+  return TRC_OK;
+}
+extern "C" int trc_ingest_view(const trc_ingest* R, trc_batch* B, const uint8_t** start_kind, const uint8_t** end_kind) {
+  if (!R || !B) return TRC_EINVAL;
+  B->text = R->text.data(); B->seg_off = R->seg_off.data(); B->start = R->start.data(); B->end = R->end.data();
+  B->speaker = R->speaker.data(); B->n_seg = (int64_t)R->start.size(); B->doc_off = R->doc_off.data();
+  B->n_doc = (int64_t)R->doc_off.size() - 1; B->spk_bytes = R->spk_bytes.data(); B->spk_off = R->spk_off.data();
+  B->n_spk = (int32_t)R->n_spk; B->memory = TRC_MEM_HOST;
+  if (start_kind) *start_kind = R->start_kind.data();
+  if (end_kind) *end_kind = R->end_kind.data();
+  return TRC_OK;
+}
+extern "C" void trc_ingest_free(trc_ingest* R) { delete R; }
 
 extern "C" int trc_get_counts(trc_ctx* ctx, int64_t* counts) {
   if (!ctx || !counts) return TRC_EINVAL;

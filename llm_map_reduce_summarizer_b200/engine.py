@@ -72,6 +72,76 @@ def pack_documents(docs):
     return PackedBatch(buf, off, st, en, spk, np.array(doc_off, dtype=np.int64), names, (starts, ends))
 
 
+class IngestedBatch(PackedBatch):
+    """A batch parsed from JSON text by trc_ingest_json (include/trchunk.h).  The arrays are views of the
+    library's buffers (freed with this object); the start / end objects json.load would have produced (float,
+    int or bool) are only materialised when dicts are built."""
+
+    def __init__(self, lib, handle, view, start_kind, end_kind):
+        self._lib, self._handle = lib, handle
+        self._originals = None
+        n, nd, ns = view.n_seg, view.n_doc, view.n_spk
+
+        def arr(ptr, count, dtype):
+            if count == 0 or not ptr:
+                return np.zeros(0, dtype=dtype)
+            ct = {np.uint8: C.c_uint8, np.int64: C.c_int64, np.float64: C.c_double, np.int32: C.c_int32}[dtype]
+            return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(ct)), shape=(count,))
+        seg_off = arr(view.seg_off, n + 1, np.int64)
+        spk_off = arr(view.spk_off, ns + 1, np.int64)
+        sb = arr(view.spk_bytes, int(spk_off[-1]), np.uint8).tobytes()
+        speakers = [sb[int(spk_off[k]):int(spk_off[k + 1])].decode("utf-8") for k in range(ns)]
+        super().__init__(arr(view.text, int(seg_off[-1]), np.uint8), seg_off, arr(view.start, n, np.float64),
+                         arr(view.end, n, np.float64), arr(view.speaker, n, np.int32), arr(view.doc_off, nd + 1, np.int64),
+                         speakers, None)
+        self.start_kind, self.end_kind = arr(start_kind, n, np.uint8), arr(end_kind, n, np.uint8)
+
+    @staticmethod
+    def _objects(values, kinds):
+        out = values.tolist()
+        for k in np.flatnonzero(kinds).tolist():           # ints and bools are the exception in transcripts
+            out[k] = int(out[k]) if kinds[k] == 1 else bool(out[k])
+        return out
+
+    @property
+    def originals(self):
+        if self._originals is None:
+            self._originals = (self._objects(self.start, self.start_kind), self._objects(self.end, self.end_kind))
+        return self._originals
+
+    @originals.setter
+    def originals(self, v):
+        if v is not None:
+            self._originals = v
+
+    def __del__(self):
+        try:
+            if self._handle:
+                self._lib.trc_ingest_free(self._handle)
+                self._handle = None
+        except Exception:
+            pass
+
+
+def ingest_json(docs, n_threads=None, lib=None):
+    """Transcripts as JSON text (list of bytes / str, each {"segments": [...]} as main.py:337-339 loads it) ->
+    IngestedBatch, parsed by the library on host threads.  Raises ValueError with the library's message for
+    anything json.load or the reference's first use of a field would reject."""
+    lib = lib or default_engine().lib
+    raw = [d.encode("utf-8") if isinstance(d, str) else bytes(d) for d in docs]
+    buf, off = _vocab.pack_strings(raw)
+    h = C.c_void_p()
+    err = C.create_string_buffer(512)
+    nt = n_threads or min(len(raw), os.cpu_count() or 1) or 1
+    rc = lib.trc_ingest_json(buf.ctypes.data, off.ctypes.data, len(raw), int(nt), C.byref(h), err, len(err))
+    if rc != 0:
+        raise ValueError("trc_ingest_json: " + err.value.decode("utf-8", "replace"))
+    view = N.Batch()
+    sk, ek = C.c_void_p(), C.c_void_p()
+    lib.trc_ingest_view(h, C.byref(view), C.byref(sk), C.byref(ek))
+    return IngestedBatch(lib, h, view, sk.value, ek.value)
+
+
 class ProcessedBatch(PackedBatch):
     """Already processed segments (big_chunkeroosky.py:46 accepts any such list): the PIECES are the packed
     segments; `groups` holds the C ABI's extra arrays (include/trchunk.h: trc_batch.already_processed)."""
