@@ -140,6 +140,8 @@ enum {
   TRC_A_AGG_PIECE,    /* int32 []            kept-segment indices: the components that survive in a member        */
   TRC_A_AGG_TEXT,     /* uint8 [B_agg]       the aggregated texts back to back                                    */
   TRC_A_AGG_DOC_OFF,  /* int64 [n_doc+1]     trc_agg range of every document                                      */
+  TRC_A_PROMPTS,      /* uint8 []            prompts of trc_assemble_prompts, chunks back to back                 */
+  TRC_A_PROMPT_OFF,   /* int64 [n_chunks+1]  their offsets                                                        */
   TRC_A_CLEN32,       /* int32 [n_kept]      byte length of every kept segment's cleaned text (== differences of       */
                       /*                     TRC_A_COFF; half the bytes for callers that download results over PCIe)  */
   TRC_A__COUNT
@@ -202,6 +204,13 @@ typedef struct {
   int64_t piece0;             /* components [piece0, piece0+n_pieces) in TRC_A_AGG_PIECE, sorted by start (stable) */
   int64_t text_off, text_len; /* the member's text (what 'segment_timestamps'[k]['text'] holds, :318) in TRC_A_AGG_TEXT */
 } trc_agg_mem;
+
+/* Prompt assembly from the device buffers: prompt(c) = lit[0] + twc(c) + lit[1] + twc(c) + ... + lit[n_lit-1] for
+ * every chunk c, where twc(c) is the chunk's text_with_context.  Replaces prompt_template.format(transcript=
+ * chunk['text_with_context'], summary_type=...) (llm_executor.py:187-190): the caller formats the template once
+ * with a placeholder for the transcript and passes the literal pieces around it (n_lit >= 1; lit_off has n_lit+1
+ * entries; host pointers).  Runs after trc_chunk; results: TRC_A_PROMPTS / TRC_A_PROMPT_OFF. */
+int trc_assemble_prompts(trc_ctx* ctx, const uint8_t* lit_bytes, const int64_t* lit_off, int32_t n_lit, void* stream);
 
 /* Ingest (host side): n_doc transcripts as JSON text (document x = json[doc_off[x] .. doc_off[x+1])) -> the packed
  * batch layout above, without building Python objects.  Replaces json.load + transcript_data.get('segments', [])

@@ -11,7 +11,7 @@ COUNTERS = ["n_seg", "n_kept", "n_groups", "n_items", "n_subs", "n_chunks", "b_r
 N_COUNTERS = 24
 ARRAYS = ["K2R", "COFF", "CLEAN", "CTOK", "GSTART", "POFF", "MERGED", "GTS", "GTOK", "ITEM_GROUP", "ITEM_SUB", "ITEM_TOK",
           "ITEM_LEN", "ITEM_DST", "SUBS", "CHUNKS", "SPK_LIST", "TWC", "DOC_ERR", "GDOC_OFF", "CDOC_OFF", "CCHARS", "SENT", "PDST",
-          "AGG", "AGG_MEM", "AGG_PIECE", "AGG_TEXT", "AGG_DOC_OFF", "CLEN32"]
+          "AGG", "AGG_MEM", "AGG_PIECE", "AGG_TEXT", "AGG_DOC_OFF", "PROMPTS", "PROMPT_OFF", "CLEN32"]
 A = {n: i for i, n in enumerate(ARRAYS)}
 ERRORS = {-1: "TRC_ECUDA", -2: "TRC_EINVAL", -3: "TRC_ENOVOCAB", -4: "TRC_EUNSUPPORTED"}
 
@@ -42,7 +42,7 @@ AGG_MEM_DTYPE = [("group", "<i4"), ("n_pieces", "<i4"), ("piece0", "<i8"), ("tex
 
 EXPORTS = ["trc_create", "trc_destroy", "trc_last_error", "trc_load_tables", "trc_load_vocab", "trc_preprocess",
            "trc_chunk", "trc_aggregate", "trc_get_counts", "trc_get_array", "trc_count_tokens", "trc_last_stage_ms", "trc_kernel_launches", "trc_set_profiling",
-           "trc_get_profile", "trc_bpe_span_count_static", "trc_ingest_json", "trc_ingest_view", "trc_ingest_free"]
+           "trc_get_profile", "trc_bpe_span_count_static", "trc_ingest_json", "trc_ingest_view", "trc_ingest_free", "trc_assemble_prompts"]
 
 
 def load_library(path=None):
@@ -71,6 +71,8 @@ def load_library(path=None):
     lib.trc_kernel_launches.argtypes = [vp, C.POINTER(i64)]
     lib.trc_set_profiling.argtypes = [vp, i32]
     lib.trc_get_profile.argtypes = [vp, C.c_char_p, i64]
+    if hasattr(lib, "trc_assemble_prompts"):
+        lib.trc_assemble_prompts.argtypes = [vp, vp, vp, i32, vp]
     if hasattr(lib, "trc_ingest_json"):
         lib.trc_ingest_json.argtypes = [vp, vp, i64, i32, C.POINTER(vp), C.c_char_p, i64]
         lib.trc_ingest_view.argtypes = [vp, C.POINTER(Batch), C.POINTER(vp), C.POINTER(vp)]

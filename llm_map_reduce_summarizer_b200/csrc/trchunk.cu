@@ -1326,6 +1326,56 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
 #include "trc_agg.cuh"
 static_assert(sizeof(TrcAggRec) == sizeof(trc_agg) && sizeof(TrcAggMemRec) == sizeof(trc_agg_mem), "aggregate record layouts");
 
+// ---- prompt assembly (llm_executor.py:187-190): lit[0] + twc(c) + lit[1] + twc(c) + ... + lit[n_lit-1] per chunk
+__global__ void k_prompt_len(TrcDev D, int64_t lit_total, int32_t n_lit, int64_t* plen) {
+  GSTRIDE(c, D.n_chunks) plen[c] = lit_total + (int64_t)(n_lit - 1) * D.twc_len[c];
+}
+__global__ void k_prompt_write(TrcDev D, const uint8_t* __restrict__ lit, const int64_t* __restrict__ lit_off, int32_t n_lit,
+                               const int64_t* __restrict__ poff, uint8_t* out) {
+  WSTRIDE(c, D.n_chunks) {
+    const int lane = TRC_LANE, nl = TRC_NL;
+    uint8_t* dst = out + poff[c];
+    const uint8_t* src = D.twc + D.twc_scan[c];
+    const int64_t tl = D.twc_len[c];
+    for (int32_t k = 0; k < n_lit; ++k) {
+      const int64_t a = lit_off[k], L = lit_off[k + 1] - a;
+      for (int64_t q = lane; q < L; q += nl) dst[q] = lit[a + q];
+      dst += L;
+      if (k + 1 < n_lit) { for (int64_t q = lane; q < tl; q += nl) dst[q] = src[q]; dst += tl; }
+    }
+  }
+}
+extern "C" int trc_assemble_prompts(trc_ctx* ctx, const uint8_t* lit_bytes, const int64_t* lit_off, int32_t n_lit, void* stream) {
+  if (!ctx || !lit_off || n_lit < 1 || (!lit_bytes && lit_off[n_lit] > 0)) return TRC_EINVAL;
+  if (!ctx->have_chunk) { ctx->err = "trc_assemble_prompts needs a preceding trc_chunk"; return TRC_EINVAL; }
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : ctx->own_stream;
+  TrcDev& D = ctx->D;
+  int rc;
+  const int64_t nc = D.n_chunks, lt = lit_off[n_lit] - lit_off[0];
+  const uint8_t* d_lit; const int64_t* d_loff;
+  if ((rc = to_device(ctx, st, lit_bytes ? lit_bytes + lit_off[0] : (const uint8_t*)"", lt > 0 ? lt : 1, TRC_MEM_HOST, &d_lit))) return rc;
+  std::vector<int64_t> rel((size_t)n_lit + 1);
+  for (int32_t k = 0; k <= n_lit; ++k) rel[(size_t)k] = lit_off[k] - lit_off[0];
+  int64_t* loff;
+  ALLOC(loff, int64_t, n_lit + 1);
+  CK(cudaMemcpyAsync(loff, rel.data(), 8 * (size_t)(n_lit + 1), cudaMemcpyHostToDevice, st));
+  CK(cudaStreamSynchronize(st));                        // rel is a local vector
+  d_loff = loff;
+  int64_t* plen; int64_t* poff;
+  ALLOC(plen, int64_t, nc); ALLOC(poff, int64_t, nc + 1);
+  LAUNCH(k_prompt_len, nc, 256, D, lt, n_lit, plen);
+  if ((rc = scan_excl(ctx, st, plen, poff, nc))) return rc;
+  int64_t total = 0;
+  if (nc) { if ((rc = read_back(ctx, st, poff + nc, 8, &total))) return rc; }
+  uint8_t* out;
+  ALLOC(out, uint8_t, total);
+  LAUNCH_W(k_prompt_write, nc, D, d_lit, d_loff, n_lit, poff, out);
+  set_arr(ctx, TRC_A_PROMPTS, out, total);
+  set_arr(ctx, TRC_A_PROMPT_OFF, poff, 8 * (nc + 1));
+  return TRC_OK;
+}
+
 extern "C" int trc_aggregate(trc_ctx* ctx, double interval_seconds, void* stream) {
   if (!ctx) return TRC_EINVAL;
   if (!ctx->have_pre) { ctx->err = "trc_aggregate needs a preceding trc_preprocess"; return TRC_EINVAL; }

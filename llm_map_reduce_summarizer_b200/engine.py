@@ -288,6 +288,25 @@ class Engine:
                 "piece": self.array("AGG_PIECE", "<i4"), "text": self.array("AGG_TEXT", "u1"),
                 "adoc_off": self.array("AGG_DOC_OFF", "<i8")}
 
+    def assemble_prompts(self, prompt_template, **fields):
+        """prompt_template.format(transcript=chunk['text_with_context'], **fields) for every chunk of the resident
+        batch (llm_executor.py:187-190), assembled on the device: returns (uint8 buffer, int64 offsets[n_chunks+1]).
+        The template is formatted once on the host with a placeholder for the transcript; the device copies the
+        literal pieces and the chunk texts."""
+        import string
+        for _, name, spec, conv in string.Formatter().parse(prompt_template):
+            if name is not None and name.split(".")[0].split("[")[0] == "transcript" and (name != "transcript" or spec or conv):
+                raise NotImplementedError("only a plain {transcript} field is assembled on the device")
+        mark = "\x00\x01trc-transcript\x01\x00"
+        if mark in prompt_template or any(mark in str(v) for v in fields.values()):
+            raise ValueError("template contains the internal placeholder")
+        lits = [x.encode("utf-8") for x in prompt_template.format(transcript=mark, **fields).split(mark)]
+        buf, off = _vocab.pack_strings(lits)
+        if buf.size == 0:
+            buf = np.zeros(1, dtype=np.uint8)
+        self._check(self.lib.trc_assemble_prompts(self.h, buf.ctypes.data, off.ctypes.data, len(lits), None))
+        return self.array("PROMPTS", "u1"), self.array("PROMPT_OFF", "<i8")
+
     def counts(self):
         c = np.zeros(N.N_COUNTERS, dtype=np.int64)
         self._check(self.lib.trc_get_counts(self.h, c.ctypes.data))

@@ -237,3 +237,29 @@ def check_dense_tiles(eng):
         got = E2.build_chunks(eng, b, P, R, pp, x)
         assert same(got, oc), "doc %d chunks: %s" % (x, first_diff(got, oc))
     return len(docs)
+
+
+def check_prompts(eng):
+    from llm_map_reduce_summarizer_b200 import synth
+    b, mt, _ = synth.config(5, 0.004)
+    eng.preprocess(b)
+    eng.chunk(mt)
+    R = eng.fetch_chunks()
+    twc = R["twc"].tobytes()
+    ch = R["chunks"]
+    texts = []
+    for c in ch:
+        n = int(c["text_len"]) + (int(c["hdr_len"]) + 2 if c["hdr_len"] > 0 else 0)
+        texts.append(twc[int(c["twc_off"]):int(c["twc_off"]) + n].decode("utf-8"))
+    for tpl, kw in (("Summarise ({summary_type}):\n\n{transcript}\n\nEnd {{braces}} é.", {"summary_type": "brief"}),
+                    ("{transcript}", {}), ("no field at all", {}), ("{transcript}|{transcript}|{x}", {"x": 3}), ("", {})):
+        buf, off = eng.assemble_prompts(tpl, **kw)
+        raw = buf.tobytes()
+        assert len(off) == len(ch) + 1
+        for k, t in enumerate(texts):
+            assert raw[int(off[k]):int(off[k + 1])].decode("utf-8") == tpl.format(transcript=t, **kw), (tpl, k)
+    import pytest
+    with pytest.raises(NotImplementedError):
+        eng.assemble_prompts("{transcript!r}")
+    with pytest.raises(KeyError):
+        eng.assemble_prompts("{transcript} {missing}")

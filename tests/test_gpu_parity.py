@@ -226,3 +226,7 @@ def test_alternate_kernel_paths(monkeypatch, env):
         pc.sentence_fuzz(eng, 30, 5)
     finally:
         eng.close()
+
+
+def test_prompt_assembly(gpu_engine):
+    pc.check_prompts(gpu_engine)

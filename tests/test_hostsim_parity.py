@@ -186,3 +186,8 @@ def test_other_rank_tables(table):
 def test_dense_tiles(hostsim_engine):
     """Tiles that overrun the fused kernel's word / candidate / output / input capacities (overflow paths)."""
     assert pc.check_dense_tiles(hostsim_engine) == 6
+
+
+def test_prompt_assembly(hostsim_engine):
+    """llm_executor.py:187-190: prompt_template.format(transcript=chunk['text_with_context'], summary_type=...)."""
+    pc.check_prompts(hostsim_engine)
