@@ -673,12 +673,22 @@ __global__ void k_emit_pieces_flat(TrcDev D) {
     int64_t o = 0;
     if (f & 1) {
       const double st = D.start[D.k2r[j]];
-      o = trc_ts_len(st) + 3;
-      if (lane == 0) {
-        uint8_t buf[TRC_TS_MAX + 4];
-        int tl = trc_fmt_ts(st, buf + 1);
-        buf[0] = '['; buf[tl + 1] = ']'; buf[tl + 2] = ' ';
-        for (int k = 0; k < tl + 3; ++k) dst[k] = buf[k];
+      int64_t h; int m, sec;
+      trc_ts_split(st, &h, &m, &sec);
+      if (h <= 0) {                          // "[MM:SS] " is exactly eight bytes: every lane of the group writes one of them
+        const unsigned long long pre = (unsigned long long)'[' | ((unsigned long long)('0' + m / 10) << 8) | ((unsigned long long)('0' + m % 10) << 16) |
+                                       ((unsigned long long)':' << 24) | ((unsigned long long)('0' + sec / 10) << 32) |
+                                       ((unsigned long long)('0' + sec % 10) << 40) | ((unsigned long long)']' << 48) | ((unsigned long long)' ' << 56);
+        dst[lane] = (uint8_t)(pre >> (8 * lane));
+        o = 8;
+      } else {
+        o = trc_ts_len(st) + 3;
+        if (lane == 0) {
+          uint8_t buf[TRC_TS_MAX + 4];
+          int tl = trc_fmt_ts(st, buf + 1);
+          buf[0] = '['; buf[tl + 1] = ']'; buf[tl + 2] = ' ';
+          for (int k = 0; k < tl + 3; ++k) dst[k] = buf[k];
+        }
       }
     }
     const int64_t c0 = D.coff[j];
