@@ -164,6 +164,7 @@ def main():
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--cpu-sample-mb", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-offsets64", action="store_true", help="upload the int64 segment offsets instead of int32 lengths")
     ap.add_argument("--e2e-repeats", type=int, default=3, help="repetitions of the K-step end-to-end leg (median reported)")
     ap.add_argument("--e2e-parts", type=int, default=1, help="sub-batches a step's documents are cut into in the end-to-end leg")
     ap.add_argument("--e2e-contexts", type=int, default=4, help="contexts (host threads) that take batches in turn in the end-to-end leg")
@@ -286,6 +287,8 @@ def main():
         sb = synth.sub_batch(b, x0, x1)
         pin = {k: torch.from_numpy(np.ascontiguousarray(getattr(sb, k))).pin_memory()
                for k in ("text", "seg_off", "start", "end", "speaker", "doc_off")}
+        # the segment lengths go up as int32 (trc_batch.seg_len32) instead of the int64 offsets
+        pin["seg_len32"] = torch.from_numpy(np.diff(sb.seg_off).astype(np.int32)).pin_memory()
         parts.append((E.PackedBatch(pin["text"].numpy(), pin["seg_off"].numpy(), pin["start"].numpy(), pin["end"].numpy(),
                                     pin["speaker"].numpy(), pin["doc_off"].numpy(), b.speakers, None),
                       np.ascontiguousarray(mt[x0:x1]), pin))
@@ -309,8 +312,8 @@ def main():
                     if item >= state[1]:
                         return
                     state[0] = item + 1
-            hb_, mt_, _ = parts[item % nparts]
-            en.preprocess(hb_, want_merged_text=False, stream=stream.cuda_stream)
+            hb_, mt_, pin_ = parts[item % nparts]
+            en.preprocess(hb_, want_merged_text=False, stream=stream.cuda_stream, seg_len32=None if args.e2e_offsets64 else pin_["seg_len32"].numpy())
             en.chunk(mt_, stream=stream.cuda_stream)
             total = 0
             cn = en.counts()
@@ -355,7 +358,7 @@ def main():
             ms_run = float(t.item())
         runs.append(ms_run)
     ms_e2e = sorted(runs)[len(runs) // 2]
-    h2d = int(sum(v.numel() * v.element_size() for _, _, pin in parts for v in pin.values())
+    h2d = int(sum(v.numel() * v.element_size() for _, _, pin in parts for k, v in pin.items() if k != "seg_off")
               + nparts * (b.spk_bytes.nbytes + b.spk_off.nbytes))
     e2e = {"value": tokens_all * args.steps / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps,

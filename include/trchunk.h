@@ -84,6 +84,10 @@ typedef struct {
   const double* group_end;     /* n_groups */
   const uint8_t* full_text;    /* the segments' own text, back to back */
   const int64_t* full_off;     /* n_groups + 1 */
+  /* --- optional compact form of seg_off for callers that upload over PCIe: n_seg byte lengths (each < 2^31) and
+   * the total text size; seg_off may then be NULL and is rebuilt on the device by a prefix sum. */
+  const int32_t* seg_len32;    /* n_seg, or NULL */
+  int64_t text_bytes;          /* bytes of `text`; read only when seg_len32 is given */
 } trc_batch;
 
 /* Stage P: preprocessor.preprocess_transcript (preprocessor.py:15-67) for every document of the batch:

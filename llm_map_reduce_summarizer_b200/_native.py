@@ -24,7 +24,8 @@ class Batch(C.Structure):
                 ("preserve_timestamps", C.c_int32), ("want_merged_text", C.c_int32),
                 ("already_processed", C.c_int32), ("reserved_", C.c_int32), ("group_off", C.c_void_p),
                 ("n_groups", C.c_int64), ("group_start", C.c_void_p), ("group_end", C.c_void_p),
-                ("full_text", C.c_void_p), ("full_off", C.c_void_p)]
+                ("full_text", C.c_void_p), ("full_off", C.c_void_p),
+                ("seg_len32", C.c_void_p), ("text_bytes", C.c_int64)]
 
 
 SUB_DTYPE = [("group", "<i4"), ("kind", "<i4"), ("r0", "<i4"), ("r1", "<i4"), ("start_src", "<i4"), ("end_src", "<i4"),

@@ -1090,20 +1090,36 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   CK(cudaEventRecord(ctx->ev[0], st));
   const int64_t n = B->n_seg, nd = B->n_doc;
   int64_t braw = 0, bspk = 0;
-  if (B->memory == TRC_MEM_HOST) { braw = n ? B->seg_off[n] : 0; bspk = B->spk_off[B->n_spk]; }
-  else {
+  const bool len32 = B->seg_len32 != nullptr && B->seg_off == nullptr;
+  if (!len32 && !B->seg_off) { ctx->err = "seg_off (or seg_len32 + text_bytes) is required"; return TRC_EINVAL; }
+  if (len32 && B->already_processed) { ctx->err = "seg_len32 is not accepted together with already_processed"; return TRC_EINVAL; }
+  if (len32 && B->memory == TRC_MEM_HOST) { braw = B->text_bytes; bspk = B->spk_off[B->n_spk]; }
+  else if (B->memory == TRC_MEM_HOST) { braw = n ? B->seg_off[n] : 0; bspk = B->spk_off[B->n_spk]; }
+  else if (len32) {
+    int64_t t2[2];
+    if ((rc = read_back2(ctx, st, nullptr, B->spk_off + B->n_spk, t2))) return rc;
+    braw = B->text_bytes; bspk = t2[1];
+  } else {
     int64_t t2[2];
     if ((rc = read_back2(ctx, st, n ? B->seg_off + n : nullptr, B->spk_off + B->n_spk, t2))) return rc;
     braw = t2[0]; bspk = t2[1];
   }
   if ((rc = to_device(ctx, st, B->text, braw, B->memory, &D.text))) return rc;
-  if ((rc = to_device(ctx, st, B->seg_off, n + 1, B->memory, &D.seg_off))) return rc;
+  const int32_t* d_len32 = nullptr;
+  if (len32) { if ((rc = to_device(ctx, st, B->seg_len32, n, B->memory, &d_len32))) return rc; }
+  else if ((rc = to_device(ctx, st, B->seg_off, n + 1, B->memory, &D.seg_off))) return rc;
   if ((rc = to_device(ctx, st, B->start, n, B->memory, &D.start))) return rc;
   if ((rc = to_device(ctx, st, B->end, n, B->memory, &D.end))) return rc;
   if ((rc = to_device(ctx, st, B->speaker, n, B->memory, &D.spk))) return rc;
   if ((rc = to_device(ctx, st, B->doc_off, nd + 1, B->memory, &D.doc_off))) return rc;
   if ((rc = to_device(ctx, st, B->spk_bytes, bspk, B->memory, &D.spk_bytes))) return rc;
   if ((rc = to_device(ctx, st, B->spk_off, (int64_t)B->n_spk + 1, B->memory, &D.spk_off))) return rc;
+  if (len32) {     // lengths in, offsets by a prefix sum - after the last upload, so that the copies stay back to back
+    int64_t* soff;
+    ALLOC(soff, int64_t, n + 1);
+    if ((rc = scan_excl(ctx, st, d_len32, soff, n))) return rc;
+    D.seg_off = soff;
+  }
   D.n = n; D.n_doc = nd; D.n_spk = B->n_spk;
   D.merge = B->merge_same_speaker; D.has_cap = B->has_max_duration; D.cap = B->max_duration; D.preserve = B->preserve_timestamps;
   ctx->counts[TRC_N_SEG] = n; ctx->counts[TRC_N_DOC] = nd; ctx->counts[TRC_B_RAW] = braw;

@@ -238,12 +238,17 @@ class Engine:
 
     # ---- stages ---------------------------------------------------------------------------------------
     def preprocess(self, batch, merge_same_speaker=True, max_segment_duration=120, preserve_timestamps=True,
-                   want_merged_text=True, stream=None, device_ptrs=None):
+                   want_merged_text=True, stream=None, device_ptrs=None, seg_len32=None):
         """Stage P on a PackedBatch (host arrays), or on device pointers when `device_ptrs` is given
-        (dict with the trc_batch pointer fields as ints)."""
+        (dict with the trc_batch pointer fields as ints).  seg_len32: int32 array of the segments' byte lengths
+        to upload instead of the int64 offsets (half the bytes over PCIe)."""
         b = N.Batch()
         if device_ptrs is None:
             b.text, b.seg_off = batch.text.ctypes.data, batch.seg_off.ctypes.data
+            if seg_len32 is not None:
+                if seg_len32.dtype != np.int32 or seg_len32.shape != (batch.n_seg,):
+                    raise ValueError("seg_len32 must be int32[n_seg]")
+                b.seg_off, b.seg_len32, b.text_bytes = None, seg_len32.ctypes.data, int(batch.text.size)
             b.start, b.end, b.speaker = batch.start.ctypes.data, batch.end.ctypes.data, batch.speaker.ctypes.data
             b.doc_off = batch.doc_off.ctypes.data
             b.spk_bytes, b.spk_off = batch.spk_bytes.ctypes.data, batch.spk_off.ctypes.data

@@ -263,3 +263,17 @@ def check_prompts(eng):
         eng.assemble_prompts("{transcript!r}")
     with pytest.raises(KeyError):
         eng.assemble_prompts("{transcript} {missing}")
+
+
+def check_len32_input(eng):
+    """trc_batch.seg_len32: int32 lengths uploaded instead of the int64 offsets give the same batch."""
+    import numpy as np
+    from llm_map_reduce_summarizer_b200 import synth
+    b, mt, _ = synth.config(5, 0.004)
+    eng.preprocess(b)
+    eng.chunk(mt)
+    want = {k: eng.array(k, "u1").tobytes() for k in ("CLEAN", "COFF", "K2R", "CTOK", "GSTART", "TWC", "CHUNKS")}
+    eng.preprocess(b, seg_len32=np.diff(b.seg_off).astype(np.int32))
+    eng.chunk(mt)
+    for k, v in want.items():
+        assert eng.array(k, "u1").tobytes() == v, k

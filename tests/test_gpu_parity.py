@@ -230,3 +230,7 @@ def test_alternate_kernel_paths(monkeypatch, env):
 
 def test_prompt_assembly(gpu_engine):
     pc.check_prompts(gpu_engine)
+
+
+def test_len32_input(gpu_engine):
+    pc.check_len32_input(gpu_engine)

@@ -191,3 +191,7 @@ def test_dense_tiles(hostsim_engine):
 def test_prompt_assembly(hostsim_engine):
     """llm_executor.py:187-190: prompt_template.format(transcript=chunk['text_with_context'], summary_type=...)."""
     pc.check_prompts(hostsim_engine)
+
+
+def test_len32_input(hostsim_engine):
+    pc.check_len32_input(hostsim_engine)
