@@ -277,3 +277,46 @@ def check_len32_input(eng):
     eng.chunk(mt)
     for k, v in want.items():
         assert eng.array(k, "u1").tobytes() == v, k
+
+
+def check_edge_batches(eng):
+    """Ragged and extreme batches in ONE call: empty documents, all-blank documents, one 300 KB segment, thousands of
+    speakers, a 1 KB speaker name, NUL bytes, only multi-byte whitespace - every document against the oracle."""
+    import random
+    import numpy as np
+    from llm_map_reduce_summarizer_b200 import engine as E2
+    from oracle import chunker as OC, preprocess as OP
+    rng = random.Random(17)
+    words = ["alpha", "beta,", "gamma.", "delta", "it's", "3.5", "go", "go", "é", "naïve", "ok!", "so;", "and"]
+    def seg(t, text, spk):
+        return {"start": t, "end": t + 2.5, "text": text, "speaker": spk}
+    docs = [
+        [],
+        [seg(0, "", "A"), seg(1, " \t\n", "B"), seg(2, "\u00a0\u2003", "A")],
+        [seg(0, " ".join(rng.choice(words) for _ in range(60000)), "MONO")],
+        [seg(i * 2.5, "word%d same same" % i, "speaker_%05d" % (i * 7919 % 3001)) for i in range(3001)],
+        [seg(0, "hello there", "N" * 1000), seg(3, "again again", "N" * 1000), seg(6, "x", "")],
+        [seg(0, "nul\x00inside \x00 \x00", "A"), seg(1, "\x00", "A")],
+        [seg(0, "\u3000\u2028lead", "A"), seg(1, "trail\u2029\u3000", "A"), seg(2, "a\u00a0\u00a0b", "B")],
+        [],
+        [seg(5, "last one.", "Z")],
+    ]
+    b = E2.pack_documents(docs)
+    mt = np.array([4000, 4000, 2000, 300, 4000, 4000, 4000, 4000, 200], dtype=np.int32)
+    eng.preprocess(b)
+    eng.chunk(mt)
+    P, R = eng.fetch_processed(), eng.fetch_chunks()
+    for x, segs in enumerate(docs):
+        op = OP.preprocess(segs)
+        oc = OC.ChunkerOracle(int(mt[x])).chunk(op)
+        pp = E2.build_processed(b, P, x)
+        assert same(pp, op), "doc %d processed: %s" % (x, first_diff(pp, op))
+        got = E2.build_chunks(eng, b, P, R, pp, x)
+        assert same(got, oc), "doc %d chunks: %s" % (x, first_diff(got, oc))
+    # an entirely empty batch
+    e0 = E2.pack_documents([[], []])
+    eng.preprocess(e0)
+    eng.chunk(np.array([4000, 4000], dtype=np.int32))
+    c = eng.counts()
+    assert c["n_seg"] == 0 and c["n_chunks"] == 0 and c["tokens"] == 0
+    return len(docs)

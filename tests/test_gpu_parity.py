@@ -234,3 +234,7 @@ def test_prompt_assembly(gpu_engine):
 
 def test_len32_input(gpu_engine):
     pc.check_len32_input(gpu_engine)
+
+
+def test_edge_batches(gpu_engine):
+    assert pc.check_edge_batches(gpu_engine) == 9

@@ -195,3 +195,7 @@ def test_prompt_assembly(hostsim_engine):
 
 def test_len32_input(hostsim_engine):
     pc.check_len32_input(hostsim_engine)
+
+
+def test_edge_batches(hostsim_engine):
+    assert pc.check_edge_batches(hostsim_engine) == 9
