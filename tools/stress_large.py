@@ -34,3 +34,14 @@ for x in (0, b.n_doc // 2, b.n_doc - 1):
     pp = E.build_processed(sb, P, 0)
     assert json.dumps(pp) == json.dumps(op) and json.dumps(E.build_chunks(e, sb, P, R, pp, 0)) == json.dumps(oc), x
 print("sample documents match the oracle", flush=True)
+# the same documents taken out of the WHOLE batch's result arrays (offsets beyond 2^31 for scale >= 20)
+t = time.time(); e.preprocess(b, want_merged_text=True); e.chunk(mt)
+P, R = e.fetch_processed(), e.fetch_chunks()
+print("whole batch fetched in %.1fs (TWC %.2f GB)" % (time.time() - t, len(R["twc"]) / 1e9), flush=True)
+for x in (0, b.n_doc // 3, b.n_doc // 2, b.n_doc - 2, b.n_doc - 1):
+    segs = synth.doc_to_segments(b, x)
+    op = OP.preprocess(segs); oc = OC.ChunkerOracle(int(mt[x])).chunk(op)
+    pp = E.build_processed(b, P, x)
+    assert json.dumps(pp) == json.dumps(op), x
+    assert json.dumps(E.build_chunks(e, b, P, R, pp, x)) == json.dumps(oc), x
+print("documents inside the whole batch match the oracle (last chunk at byte %d of TWC)" % int(R["chunks"]["twc_off"][-1]), flush=True)
