@@ -72,6 +72,8 @@ struct LongEntry { int64_t unit, lstart, len, scratch_off; };
 struct trc_ctx {
   int device = 0;
   cudaStream_t own_stream = nullptr;
+  cudaStream_t aux_stream = nullptr;   // side stream: the slow-word kernel runs beside the merge kernels
+  cudaEvent_t ev_aux[2] = {nullptr, nullptr};
   std::string err;
   bool have_tables = false, have_vocab = false;
   TrcTables T{};
@@ -928,6 +930,9 @@ extern "C" int trc_create(int device, trc_ctx** out) {
   trc_ctx* ctx = new trc_ctx();
   ctx->device = device;
   if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&ctx->aux_stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&ctx->ev_aux[0], cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&ctx->ev_aux[1], cudaEventDisableTiming) != cudaSuccess ||
       cudaHostAlloc((void**)&ctx->h_pin, 64 * sizeof(int64_t), cudaHostAllocMapped) != cudaSuccess ||
       cudaHostGetDevicePointer(&ctx->d_pin, ctx->h_pin, 0) != cudaSuccess) { delete ctx; return TRC_ECUDA; }
   for (int k = 0; k < 4; ++k) cudaEventCreate(&ctx->ev[k]);
@@ -950,6 +955,8 @@ extern "C" void trc_destroy(trc_ctx* ctx) {
   if (ctx->d_memo) cudaFree(ctx->d_memo);
   for (int k = 0; k < 4; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+  if (ctx->aux_stream) cudaStreamDestroy(ctx->aux_stream);
+  for (int k = 0; k < 2; ++k) if (ctx->ev_aux[k]) cudaEventDestroy(ctx->ev_aux[k]);
   delete ctx;
 }
 
@@ -1133,6 +1140,9 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   D.spk_tok = spk_tok;
 
   int64_t nk = 0, bclean = 0;
+  bool slow_pending = false;                 // k_count_slow_words in flight on the side stream
+  unsigned long long j_h0 = 0, j_h1 = 0; unsigned long long* j_fz = nullptr; LongEntry* j_wl = nullptr;
+  (void)slow_pending; (void)j_h0; (void)j_h1; (void)j_fz; (void)j_wl;
   int32_t* seg_special = nullptr;
   ALLOC(D.doc_err, int32_t, nd); ALLOC(D.doc_err_seg, int64_t, nd);
   CK(cudaMemsetAsync(D.doc_err, 0, 4 * (size_t)(nd > 0 ? nd : 1), st));
@@ -1204,9 +1214,15 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       D.n_kept = nk;
       {
         int64_t nslow = (int64_t)h[5] < A.sl_cap ? (int64_t)h[5] : A.sl_cap;   // entries past the capacity were counted in the kernel
-        if (nslow > 0) {
-          LAUNCH(k_count_slow_words, nslow, 128, D, ctx->T, ctx->d_byte_id, A.sl, nslow, A.wl, A.wl_cnt, A.wl_cap);
-          if ((rc = read_back(ctx, st, fz + 2, 16, h))) return rc;  // long spans found by the slow words
+        if (nslow > 0) {       // on the side stream: nothing before the per-group token totals needs these counts
+          CK(cudaEventRecord(ctx->ev_aux[0], st));
+          CK(cudaStreamWaitEvent(ctx->aux_stream, ctx->ev_aux[0], 0));
+          prof_begin(ctx, ctx->aux_stream, "k_count_slow_words");
+          k_count_slow_words<<<grid_for(nslow, 128), 128, 0, ctx->aux_stream>>>(D, ctx->T, ctx->d_byte_id, A.sl, nslow, A.wl, A.wl_cnt, A.wl_cap);
+          prof_end(ctx, ctx->aux_stream);
+          ctx->launches++;
+          CK(cudaGetLastError());
+          slow_pending = true;
         }
       }
       if (want_phases) {
@@ -1218,17 +1234,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
                 100.0 * ph[0] / tot, 100.0 * ph[1] / tot, 100.0 * ph[2] / tot, 100.0 * ph[3] / tot, 100.0 * ph[4] / tot, 100.0 * ph[5] / tot,
                 100.0 * ph[6] / tot, 100.0 * ph[11] / tot, 100.0 * ph[9] / tot, 100.0 * ph[10] / tot, 100.0 * ph[7] / tot, 100.0 * ph[8] / tot);
       }
-      if (h[0] > 0) {
-        uint32_t* scratch;
-        ALLOC(scratch, uint32_t, 4 * (int64_t)h[1]);
-        int lblocks = (int)(h[0] < 148 * 8 ? h[0] : 148 * 8);
-        prof_begin(ctx, st, "k_bpe_long");
-        k_bpe_long<<<lblocks, LONG_T, 0, st>>>(ctx->T, ctx->d_byte_id, D.C, D.coff, D.coff + 1, 1, D.ctok, A.wl, (int64_t)h[0], scratch, (int64_t)h[1]);
-        prof_end(ctx, st);
-        ctx->launches++;
-        CK(cudaGetLastError());
-        ctx->counts[TRC_N_LONG_SPANS] += (int64_t)h[0];
-      }
+      j_h0 = h[0]; j_h1 = h[1]; j_fz = fz; j_wl = A.wl;       // long spans: launched at the join below
       LAUNCH(k_doc_ranges, nd + 1, 128, D.sdoc, nk, D.kdoc_off, nd);
     }
     ctx->counts[TRC_N_KEPT] = nk; ctx->counts[TRC_B_CLEAN] = bclean;
@@ -1313,6 +1319,27 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
     LAUNCH_W(k_emit_merged, nk, D);
     set_arr(ctx, TRC_A_MERGED, D.M, bm);
   }
+#ifndef TRC_HOSTSIM
+  // join: the slow words' counts (side stream) and the long spans both feed ctok, which the group totals read
+  if (slow_pending) {
+    unsigned long long h[2];
+    if ((rc = read_back(ctx, ctx->aux_stream, j_fz + 2, 16, h))) return rc;    // long spans found by the slow words included
+    j_h0 = h[0]; j_h1 = h[1];
+    CK(cudaEventRecord(ctx->ev_aux[1], ctx->aux_stream));
+    CK(cudaStreamWaitEvent(st, ctx->ev_aux[1], 0));
+  }
+  if (j_h0 > 0) {
+    uint32_t* scratch;
+    ALLOC(scratch, uint32_t, 4 * (int64_t)j_h1);
+    int lblocks = (int)(j_h0 < 148 * 8 ? j_h0 : 148 * 8);
+    prof_begin(ctx, st, "k_bpe_long");
+    k_bpe_long<<<lblocks, LONG_T, 0, st>>>(ctx->T, ctx->d_byte_id, D.C, D.coff, D.coff + 1, 1, D.ctok, j_wl, (int64_t)j_h0, scratch, (int64_t)j_h1);
+    prof_end(ctx, st);
+    ctx->launches++;
+    CK(cudaGetLastError());
+    ctx->counts[TRC_N_LONG_SPANS] += (int64_t)j_h0;
+  }
+#endif
   // P5: group token totals, formatted lengths, formatted timestamps
   ALLOC(D.gts, uint8_t, m * 48); ALLOC(D.gtok, int64_t, m); ALLOC(D.glen, int64_t, m);
   if (nk >= 64 * m) LAUNCH_W(k_group_stats, m, D, ctx->T); else LAUNCH(k_group_stats_t, m, 128, D, ctx->T);
