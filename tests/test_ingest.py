@@ -147,3 +147,39 @@ def test_ingested_batch_through_the_path(hostsim_engine):
         except ValueError:
             continue
         assert pc.same(E.build_chunks(hostsim_engine, b, P, R, pp, x), oc), x
+
+
+def test_mutated_documents_are_never_misread(lib):
+    """Soundness under random damage: whenever the ingest ACCEPTS a mutated document, json.loads accepts it too and
+    the packed batch is identical (it may refuse more than Python does, never read something else)."""
+    rng = random.Random(2024)
+    base = []
+    for it in range(25):
+        segs = fuzzgen.rand_transcript(rng, nseg=rng.randint(1, 6))
+        for s in segs:
+            if rng.random() < 0.3:
+                s["start"] = int(s["start"])
+            if rng.random() < 0.2:
+                s["extra"] = {"k": [1, "two", None, True, 3.5e-2]}
+        base.append(variants(rng, segs))
+    alphabet = list('{}[]",:\\ntrufalse0123456789.-+eE \n') + ["\\u00e9", "\\ud83d", "\\ude00", "é", "null", "true", '"text"', '"start"', '"segments"']
+    accepted = 0
+    for trial in range(4000):
+        raw = rng.choice(base)
+        for _ in range(rng.randint(1, 3)):
+            k = rng.randrange(len(raw) + 1)
+            r = rng.random()
+            if r < 0.35:
+                raw = raw[:k] + raw[k + rng.randint(1, 4):]
+            elif r < 0.7:
+                raw = raw[:k] + rng.choice(alphabet) + raw[k:]
+            else:
+                raw = raw[:k] + rng.choice(alphabet) + raw[k + 1:]
+        try:
+            got = E.ingest_json([raw], lib=lib)
+        except ValueError:
+            continue
+        accepted += 1
+        segs = json.loads(raw).get("segments", [])          # must not raise
+        same_batch(got, E.pack_documents([list(segs)]))
+    assert accepted > 300
