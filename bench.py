@@ -97,7 +97,7 @@ class ClockSampler:
 
 
 def oracle_docs(args_tuple):
-    """Worker: reference-equivalent CPU path (oracle) on a list of documents; returns tokens."""
+    """Worker: the oracle PORT of the path (oracle/preprocess.py + oracle/chunker.py) on a list of documents."""
     docs, mts = args_tuple
     from oracle import chunker as OC, preprocess as OP
     tok = 0
@@ -106,6 +106,14 @@ def oracle_docs(args_tuple):
         ch = OC.ChunkerOracle(int(mt)).chunk(proc)
         tok += sum(c["token_count"] for c in ch)
     return tok
+
+
+def reference_docs(args_tuple):
+    """Worker: the UNMODIFIED reference (oracle/_ref copies of preprocessor.py + big_chunkeroosky.py,
+    main.py:139-149's three calls) on a list of documents."""
+    docs, mts = args_tuple
+    from oracle import refimpl
+    return refimpl.run_docs(docs, mts)[0]
 
 
 def cpu_sample(b, mt, max_docs, max_bytes):
@@ -120,36 +128,110 @@ def cpu_sample(b, mt, max_docs, max_bytes):
     return docs, mts, nbytes
 
 
+def workload_config(args, b, mt, desc, table):
+    """The `config` object of the JSON line.  Both arms print exactly this (it only depends on the synthetic
+    workload and the rank table, not on what ran), so the driver can tell that they measured the same thing."""
+    in_bytes = int(b.text.nbytes + 4 * b.n_seg + 8 * b.n_seg + 8 * b.n_seg + 4 * b.n_seg)
+    return {"workload": "config %d: %s" % (args.config, desc), "scale": args.scale,
+            "docs_per_gpu": int(b.n_doc), "segments_per_gpu": int(b.n_seg), "raw_text_bytes_per_gpu": int(b.text.nbytes),
+            "max_tokens_per_chunk": [int(x) for x in np.unique(np.asarray(mt))],
+            "rank_table": table,
+            "l2": "inputs larger than L2 (text + segment arrays > 126 MB)" if in_bytes > 126e6
+                  else "inputs smaller than L2: numbers are L2-warm",
+            "merged_text": "not materialised in the timed step (want_merged_text=0): merged texts are slices of the "
+                           "text_with_context stream, which is written in full",
+            "parallelism": "documents sharded by rank, no collective"}
+
+
+def table_name():
+    from llm_map_reduce_summarizer_b200 import vocab
+    return vocab.resolve_table_name()
+
+
+def pool_rate(fn, docs, mts, procs, warmup, steps):
+    """tokens/s of `fn` over the sample with `procs` worker processes (documents dealt round robin)."""
+    import multiprocessing as mp
+    parts = [(docs[i::procs], mts[i::procs]) for i in range(procs)] if len(docs) >= procs else [(docs, mts)]
+    # modules and the rank table are loaded once, before the fork (the GPU arm does not time its vocabulary load either)
+    from oracle import tokenizer as TK
+    TK.encoding()
+    if fn is reference_docs:
+        from oracle import refimpl
+        refimpl.load()
+    else:
+        from oracle import chunker, preprocess  # noqa: F401
+    ctx = mp.get_context("fork")
+    with ctx.Pool(len(parts)) as pool:
+        for _ in range(warmup):
+            pool.map(fn, parts)
+        t0 = time.perf_counter()
+        tok = 0
+        for _ in range(steps):
+            tok = sum(pool.map(fn, parts))
+        dt = time.perf_counter() - t0
+    return tok * steps / dt, dt / steps, len(parts), tok
+
+
+def hostsim_rate(b, mt, max_bytes):
+    """this repo's own stage code compiled by g++ (tests/hostsim, one host thread) on the sample.
+    Test build only - reported as a native-CPU comparator, never loaded by the product."""
+    try:
+        from llm_map_reduce_summarizer_b200 import build, engine as E, synth, shard as SH
+        lib = build.build_hostsim()
+        x1, nbytes = 0, 0
+        while x1 < b.n_doc and nbytes < max_bytes:
+            nbytes += int(b.seg_off[b.doc_off[x1 + 1]] - b.seg_off[b.doc_off[x1]])
+            x1 += 1
+        sb = synth.sub_batch(b, 0, x1)
+        eng = E.Engine(0, lib)
+        t0 = time.perf_counter()
+        eng.preprocess(sb, want_merged_text=False)
+        eng.chunk(np.ascontiguousarray(mt[:x1]))
+        dt = time.perf_counter() - t0
+        tok = eng.counts()["tokens"]
+        eng.close()
+        return {"value": tok / dt, "unit": UNIT, "cores": 1, "sample": "%d documents, %.1f MB" % (x1, nbytes / 1e6)}
+    except Exception as e:      # the comparator is optional
+        return {"unavailable": str(e)[:200]}
+
+
 def run_reference(args):
-    """--impl reference: the reference's own CPU implementation is pure Python + tiktoken's Rust CoreBPE;
-    /root/reference does not exist on the GPU box, so this arm times the oracle port of it (same Python
-    control flow, the same real CoreBPE, Punkt restated) on all host cores, one process per core."""
+    """--impl reference: the reference's own CPU implementation of the path on the box's host cores.
+    oracle/_ref holds byte-identical copies of /root/reference/preprocessor.py and big_chunkeroosky.py (staged by
+    __graft_entry__.build() in the build container, shipped like the built .so); they run unmodified, one process
+    per host core over a stated sample of the SAME synthetic workload, with tiktoken's Rust CoreBPE on the same rank
+    table as the GPU arm and the nltk shim for Punkt.  Falls back to the oracle port (kind "port") only when the
+    copies are missing."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import multiprocessing as mp
+    from oracle import refimpl
     b, mt, desc = workload(args, 0)
     cores = os.cpu_count() or 1
     docs, mts, nbytes = cpu_sample(b, mt, 100000, args.cpu_sample_mb * 1e6)
-    parts = [(docs[i::cores], mts[i::cores]) for i in range(cores)] if len(docs) >= cores else [(docs, mts)]
-    used = len(parts)
-    ctx = mp.get_context("fork")
-    with ctx.Pool(used) as pool:
-        for _ in range(args.warmup):
-            pool.map(oracle_docs, parts)
-        t0 = time.perf_counter()
-        tok = 0
-        for _ in range(args.steps):
-            tok = sum(pool.map(oracle_docs, parts))
-        dt = time.perf_counter() - t0
-    val = tok * args.steps / dt
+    is_ref = refimpl.available()
+    fn = reference_docs if is_ref else oracle_docs
+    val, sec, used, tok = pool_rate(fn, docs, mts, cores, args.warmup, args.steps)
+    extra = {}
+    if not args.no_cpu_baseline:
+        # BASELINE.md 4: the other CPU legs, each on the same sample, one pass
+        other = oracle_docs if is_ref else None
+        if other:
+            v2, _, u2, _ = pool_rate(other, docs, mts, cores, 0, 1)
+            extra["oracle_port"] = {"value": v2, "unit": UNIT, "cores": u2}
+        v1, _, _, _ = pool_rate(fn, docs[:max(1, len(docs) // max(cores, 1))], mts[:max(1, len(docs) // max(cores, 1))], 1, 0, 1)
+        extra["single_process"] = {"value": v1, "unit": UNIT, "cores": 1}
+        extra["own_cpp_build"] = hostsim_rate(b, mt, args.cpu_sample_mb * 1e6 / 4)
+    sample = ("%d of %d documents (%.1f MB of %.1f MB raw text, %d tokens) per step, %s, one process per core"
+              % (len(docs), b.n_doc, nbytes / 1e6, b.text.nbytes / 1e6, tok,
+                 "unmodified reference preprocessor.py + big_chunkeroosky.py (tiktoken CoreBPE, nltk shim)" if is_ref
+                 else "oracle port (Python + tiktoken CoreBPE)"))
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": 1e3 * sec, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": "config %d: %s" % (args.config, desc), "scale": args.scale},
-            "cpu_baseline": {"value": val, "unit": UNIT, "cores": used, "kind": "port",
-                             "sample": "%d documents / %.1f MB of the workload per step, oracle port (Python + tiktoken CoreBPE), "
-                                       "one process per core" % (len(docs), nbytes / 1e6)},
+            "config": workload_config(args, b, mt, desc, table_name()),
+            "cpu_baseline": dict({"value": val, "unit": UNIT, "cores": used, "kind": "reference" if is_ref else "port",
+                                  "sample": sample}, **extra),
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
@@ -369,24 +451,28 @@ def main():
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        # the reference's own code (oracle/_ref, unmodified) on ONE host core over a bounded sample of this workload
+        from oracle import refimpl
         docs, mts, nbytes = cpu_sample(b, mt, 100000, args.cpu_sample_mb * 1e6)
+        is_ref = refimpl.available()
+        if is_ref:
+            refimpl.load()
+            refimpl.run_docs(docs[:2], mts[:2])
         t0 = time.perf_counter()
-        tok = oracle_docs((docs, mts))
+        tok = reference_docs((docs, mts)) if is_ref else oracle_docs((docs, mts))
         dtc = time.perf_counter() - t0
-        cpu = {"value": tok / dtc, "unit": UNIT, "cores": 1, "kind": "port",
-               "sample": "first %d documents (%.1f MB raw text) of the workload, %.1f s, oracle port (Python + tiktoken CoreBPE)"
-                         % (len(docs), nbytes / 1e6, dtc)}
+        cpu = {"value": tok / dtc, "unit": UNIT, "cores": 1, "kind": "reference" if is_ref else "port",
+               "sample": "first %d documents (%.1f MB raw text) of the workload, %.1f s, %s"
+                         % (len(docs), nbytes / 1e6, dtc, "unmodified reference preprocessor.py + big_chunkeroosky.py "
+                            "(tiktoken CoreBPE, nltk shim)" if is_ref else "oracle port (Python + tiktoken CoreBPE)")}
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "u8", "data": "synthetic",
-                "config": {"workload": "config %d: %s" % (args.config, desc), "scale": args.scale,
-                           "docs_per_gpu": b.n_doc, "segments_per_gpu": b.n_seg, "raw_text_bytes_per_gpu": int(counts["b_raw"]),
-                           "tokens_per_gpu_per_step": int(tokens_local), "chunks_per_gpu": counts["n_chunks"],
-                           "rank_table": eng.vocab_name, "l2": "inputs larger than L2 (text + segment arrays > 126 MB)"
-                           if h2d > 126e6 else "inputs smaller than L2: numbers are L2-warm",
-                           "parallelism": "documents sharded by rank, no collective"},
+                "config": workload_config(args, b, mt, desc, eng.vocab_name),
+                "counts": {"tokens_per_gpu_per_step": int(tokens_local), "chunks_per_gpu": counts["n_chunks"],
+                           "merged_segments_per_gpu": counts["n_groups"], "algorithmic_bytes_per_step": int(A)},
                 "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline}
         if cpu:
             line["cpu_baseline"] = cpu

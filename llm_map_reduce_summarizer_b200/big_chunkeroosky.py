@@ -19,16 +19,16 @@ class BigChunkeroosky:
         self.effective_max_tokens = max_tokens_per_chunk - context_tokens
         self.tokenizer_name = tokenizer_name
         self._engine = _eng.default_engine(tokenizer_name)
+        self.rank_table = self._engine.vocab_name     # "cl100k_base", or "trbpe_v1" when the official file is absent
 
     def chunk_transcript(self, processed_segments: List[Dict[Any, Any]], add_context: bool = True) -> List[Dict[Any, Any]]:
         """big_chunkeroosky.py:46-145."""
         if not processed_segments:
             return []
         print(f"Chunkeroosky: Processing {len(processed_segments)} segments")                 # :67
-        h = getattr(processed_segments, "_trc", None)
-        ok = (h is not None and len(processed_segments) == len(h["ids"])
-              and all(id(d) == i for d, i in zip(processed_segments, h["ids"])))
-        if not ok:
+        h = _pre.resident_handle(processed_segments)
+        # the resident batch is only reused when the dicts are untouched and were counted with THIS chunker's table
+        if h is None or h["engine"].vocab_name != self._engine.vocab_name:
             return self._chunk_foreign(processed_segments, add_context)
         eng = h["engine"]
         if eng.batch_serial != h["serial"]:              # another batch replaced it: run stage P again

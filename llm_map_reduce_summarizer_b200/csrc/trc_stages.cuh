@@ -95,6 +95,15 @@ TRC_HD void trc_merge_next(const TrcDev& D, int64_t j) {
   D.mnxt[j] = (int32_t)k;
 }
 
+// Without a duration cap (max_segment_duration=None, preprocessor.py:140-141) or without merging, a group starts
+// exactly where the speaker changes (or at every segment): no forward scan and no orbit, one flag per piece.  A
+// forward scan per piece would be quadratic in the length of a single-speaker run.
+TRC_HD void trc_group_flag_nocap(const TrcDev& D, int64_t j) {
+  const int32_t x = D.sdoc[j];
+  const bool first = j == D.kdoc_off[x];
+  D.gflag[j] = (!D.merge || first || D.spk[D.k2r[j]] != D.spk[D.k2r[j - 1]]) ? 1 : 0;
+}
+
 // Orbit marking (v1): one thread walks one document.  flag[] must be zeroed.
 TRC_HD void trc_orbit_walk(const int64_t* range_off, const int32_t* nxt, int32_t* flag, int64_t x) {
   int64_t a = range_off[x], b = range_off[x + 1];

@@ -554,6 +554,7 @@ __global__ void k_verify_groups(TrcDev D, TrcTables T, const double* __restrict_
 
 __global__ void k_clen32(const int64_t* __restrict__ coff, int64_t nk, int32_t* out) { GSTRIDE(j, nk) out[j] = (int32_t)(coff[j + 1] - coff[j]); }
 __global__ void k_merge_next(TrcDev D) { GSTRIDE(j, D.n_kept) trc_merge_next(D, j); }
+__global__ void k_group_flag_nocap(TrcDev D) { GSTRIDE(j, D.n_kept) trc_group_flag_nocap(D, j); }
 __global__ void k_orbit(const int64_t* __restrict__ range_off, const int32_t* __restrict__ nxt, int32_t* flag, int64_t n_doc) {
   GSTRIDE(x, n_doc) trc_orbit_walk(range_off, nxt, flag, x);
 }
@@ -819,7 +820,8 @@ static int to_device(trc_ctx* ctx, cudaStream_t st, const Tp* src, int64_t count
 static int count_units(trc_ctx* ctx, cudaStream_t st, const uint8_t* bytes, const int64_t* ustart, const int64_t* uend,
                        int64_t n, int64_t total_bytes, int vs, uint32_t* counts, int32_t* special, bool allow_sync_free) {
   if (n <= 0) return TRC_OK;
-  int64_t cap = total_bytes / (TRC_SHORT_SPAN + 1) + 1;
+  // a long span has more than TRC_SHORT_SPAN LOGICAL bytes, and with vs every unit is one byte longer than it is stored
+  const int64_t cap = (total_bytes + (vs ? n : 0)) / (TRC_SHORT_SPAN + 1) + 1;
   LongEntry* wl; unsigned long long* wl_cnt;
   ALLOC(wl, LongEntry, cap);
   ALLOC(wl_cnt, unsigned long long, 2);
@@ -833,6 +835,7 @@ static int count_units(trc_ctx* ctx, cudaStream_t st, const uint8_t* bytes, cons
   ctx->counts[TRC_N_LONG_SPANS] += (int64_t)h[0];
   h[0] = 0;
 #endif
+  if ((int64_t)h[0] > cap) { ctx->err = "long-span work list overflow"; return TRC_EINVAL; }   // cannot happen: cap is the bound
   if (h[0] > 0) {
 #ifndef TRC_HOSTSIM
     uint32_t* scratch;
@@ -1141,8 +1144,8 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
 
   int64_t nk = 0, bclean = 0;
   bool slow_pending = false;                 // k_count_slow_words in flight on the side stream
-  unsigned long long j_h0 = 0, j_h1 = 0; unsigned long long* j_fz = nullptr; LongEntry* j_wl = nullptr;
-  (void)slow_pending; (void)j_h0; (void)j_h1; (void)j_fz; (void)j_wl;
+  unsigned long long j_h0 = 0, j_h1 = 0; unsigned long long* j_fz = nullptr; LongEntry* j_wl = nullptr; int64_t j_wl_cap = 0;
+  (void)slow_pending; (void)j_h0; (void)j_h1; (void)j_fz; (void)j_wl; (void)j_wl_cap;
   int32_t* seg_special = nullptr;
   ALLOC(D.doc_err, int32_t, nd); ALLOC(D.doc_err_seg, int64_t, nd);
   CK(cudaMemsetAsync(D.doc_err, 0, 4 * (size_t)(nd > 0 ? nd : 1), st));
@@ -1178,7 +1181,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       static const bool want_phases = getenv("TRCHUNK_PHASES") != nullptr;
       A.phase = want_phases ? fz + 8 : nullptr;
       A.text_bytes = braw; A.seg_special = seg_special;
-      A.wl_cap = ccap / (TRC_SHORT_SPAN + 1) + 1;
+      A.wl_cap = (ccap + n) / (TRC_SHORT_SPAN + 1) + 1;          // logical bytes: every kept segment carries a virtual leading space
       ALLOC(A.wl, LongEntry, A.wl_cap);
       A.sl_cap = 2 * n + 1024; A.sl_cnt = fz + 7;
       ALLOC(A.sl, SlowWord, A.sl_cap);
@@ -1234,7 +1237,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
                 100.0 * ph[0] / tot, 100.0 * ph[1] / tot, 100.0 * ph[2] / tot, 100.0 * ph[3] / tot, 100.0 * ph[4] / tot, 100.0 * ph[5] / tot,
                 100.0 * ph[6] / tot, 100.0 * ph[11] / tot, 100.0 * ph[9] / tot, 100.0 * ph[10] / tot, 100.0 * ph[7] / tot, 100.0 * ph[8] / tot);
       }
-      j_h0 = h[0]; j_h1 = h[1]; j_fz = fz; j_wl = A.wl;       // long spans: launched at the join below
+      j_h0 = h[0]; j_h1 = h[1]; j_fz = fz; j_wl = A.wl; j_wl_cap = A.wl_cap;      // long spans: launched at the join below
       LAUNCH(k_doc_ranges, nd + 1, 128, D.sdoc, nk, D.kdoc_off, nd);
     }
     ctx->counts[TRC_N_KEPT] = nk; ctx->counts[TRC_B_CLEAN] = bclean;
@@ -1291,6 +1294,8 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   if (modeB && B->group_off) {
     if ((rc = to_device(ctx, st, B->group_off, B->n_groups + 1, B->memory, &d_group_off))) return rc;
     LAUNCH(k_flag_groups, B->n_groups, 256, d_group_off, B->n_groups, D.gflag);
+  } else if (!D.merge || !D.has_cap) {
+    LAUNCH(k_group_flag_nocap, nk, 256, D);
   } else {
     LAUNCH(k_merge_next, nk, 256, D);
     LAUNCH(k_orbit, nd, 64, D.kdoc_off, D.mnxt, D.gflag, nd);
@@ -1328,6 +1333,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
     CK(cudaEventRecord(ctx->ev_aux[1], ctx->aux_stream));
     CK(cudaStreamWaitEvent(st, ctx->ev_aux[1], 0));
   }
+  if ((int64_t)j_h0 > j_wl_cap) { ctx->err = "long-span work list overflow"; return TRC_EINVAL; }   // cannot happen: the cap is the bound
   if (j_h0 > 0) {
     uint32_t* scratch;
     ALLOC(scratch, uint32_t, 4 * (int64_t)j_h1);

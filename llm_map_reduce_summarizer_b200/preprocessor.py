@@ -12,6 +12,23 @@ from typing import Any, Dict, List, Optional, Tuple
 from . import engine as _eng
 
 
+def _fingerprint(d):
+    """Cheap content fingerprint of a processed dict: an in-place edit between preprocess_transcript and
+    chunk_transcript must be honoured (the reference would), so the resident batch is only reused for untouched dicts."""
+    return hash((d.get("text"), d.get("speaker"), repr(d.get("start")), repr(d.get("end")), len(d)))
+
+
+def resident_handle(segments):
+    """The _trc handle of `segments` when it is this package's own, unedited output; else None."""
+    h = getattr(segments, "_trc", None)
+    if h is None or len(segments) != len(h["ids"]):
+        return None
+    for d, i, f in zip(segments, h["ids"], h["fp"]):
+        if id(d) != i or _fingerprint(d) != f:
+            return None
+    return h
+
+
 class ProcessedSegments(list):
     """The list preprocess_transcript returns.  A plain list of dicts for every consumer; it also
     remembers the packed input so that BigChunkeroosky.chunk_transcript can chunk on the device without
@@ -37,7 +54,7 @@ def preprocess_transcript(segments: List[Dict[Any, Any]], merge_same_speaker: bo
         print(f"Preprocessing: Combined {n_kept} segments into {len(out)} segments")           # :161
         print(f"Preprocessing: Compression ratio: {len(out) / n_kept:.2f}")                    # :163
     out._trc = {"engine": eng, "serial": serial, "batch": batch, "params": params, "P": P,
-                "ids": [id(d) for d in out]}
+                "ids": [id(d) for d in out], "fp": [_fingerprint(d) for d in out]}
     if time_interval_seconds and out:
         return aggregate_by_time_interval(out, time_interval_seconds)
     return out
@@ -103,8 +120,8 @@ def aggregate_by_time_interval(segments: List[Dict[Any, Any]], interval_seconds:
         return []
     start_time, end_time = segments[0]["start"], segments[-1]["end"]
     num_intervals = math.ceil((end_time - start_time) / interval_seconds)                        # :236
-    h = getattr(segments, "_trc", None)
-    if h is not None and len(segments) == len(h["ids"]) and all(id(d) == i for d, i in zip(segments, h["ids"])):
+    h = resident_handle(segments)
+    if h is not None:
         eng, batch = h["engine"], h["batch"]
         if eng.batch_serial != h["serial"]:
             h["serial"] = eng.preprocess(batch, want_merged_text=True, **h["params"])

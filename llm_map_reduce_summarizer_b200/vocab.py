@@ -24,16 +24,47 @@ def _parse(raw):
     return toks, ranks
 
 
-def load_rank_table(name="cl100k_base"):
-    """Returns (table_name, tokens: list[bytes], ranks: list[int])."""
+def _cl100k_file():
     cache = os.environ.get("TIKTOKEN_CACHE_DIR") or os.environ.get("DATA_GYM_CACHE_DIR")
-    if cache and name == "cl100k_base":
+    if cache:
         p = os.path.join(cache, CL100K_CACHE_KEY)
         if os.path.exists(p):
             raw = open(p, "rb").read()
             if hashlib.sha256(raw).hexdigest() == CL100K_SHA256:
-                t, r = _parse(raw)
-                return "cl100k_base", t, r
+                return raw
+    return None
+
+
+def resolve_table_name(name="cl100k_base"):
+    """Name of the table `load_rank_table(name)` would return, without parsing it."""
+    if name != "cl100k_base":
+        raise ValueError(
+            f"Unknown encoding {name!r}: this build carries the cl100k pattern and special tokens only "
+            "(the reference never passes anything else, big_chunkeroosky.py:27,43); pass rank_table= to use another table")
+    return "cl100k_base" if _cl100k_file() is not None else "trbpe_v1"
+
+
+_warned = False
+
+
+def load_rank_table(name="cl100k_base"):
+    """Returns (table_name, tokens: list[bytes], ranks: list[int]).
+
+    Any name but "cl100k_base" raises ValueError, as tiktoken.get_encoding does for a name it does not know
+    (the pre-tokenisation pattern and the special tokens here are cl100k's).  Without the official file the
+    repo's own table `trbpe_v1` is used and a warning says so ONCE per process: token counts, and with them
+    every chunk boundary, then differ from a reference run on the real cl100k_base."""
+    global _warned
+    if resolve_table_name(name) == "cl100k_base":
+        t, r = _parse(_cl100k_file())
+        return "cl100k_base", t, r
+    if not _warned and os.environ.get("TRCHUNK_ALLOW_FALLBACK_VOCAB") != "1":
+        import warnings
+        warnings.warn("cl100k_base is not available offline ($TIKTOKEN_CACHE_DIR/%s missing or sha256 mismatch): using the "
+                      "repo's rank table trbpe_v1; token counts and chunk boundaries are those of trbpe_v1, not of a "
+                      "reference run on cl100k_base (set TRCHUNK_ALLOW_FALLBACK_VOCAB=1 to silence)" % CL100K_CACHE_KEY,
+                      RuntimeWarning, stacklevel=2)
+    _warned = True
     with gzip.open(os.path.join(_DATA, "trbpe_v1.tiktoken.gz"), "rb") as f:
         t, r = _parse(f.read())
     return "trbpe_v1", t, r

@@ -1,6 +1,7 @@
 """bench.py's reference arm (the one leg that runs without a GPU) prints one JSON line with the contract's keys."""
 import json, os, subprocess, sys
 
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
 ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..")
 
 
@@ -12,7 +13,13 @@ def test_reference_arm_line():
     for k in ("value", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline", "dtype", "data", "config",
               "cpu_baseline", "e2e"):
         assert k in line, k
-    assert line["value"] > 0 and line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] >= 1
+    from oracle import refimpl
+    kind = "reference" if refimpl.available() else "port"
+    assert line["value"] > 0 and line["cpu_baseline"]["kind"] == kind and line["cpu_baseline"]["cores"] >= 1
+    if kind == "reference":
+        assert line["cpu_baseline"]["oracle_port"]["value"] > 0 and line["cpu_baseline"]["single_process"]["cores"] == 1
+    for k in ("workload", "scale", "docs_per_gpu", "segments_per_gpu", "raw_text_bytes_per_gpu", "rank_table", "l2", "merged_text"):
+        assert k in line["config"], k
     assert line["e2e"]["value"] == line["value"] and line["e2e"]["h2d_bytes_per_step"] == 0 and line["e2e"]["d2h_bytes_per_step"] == 0
     assert line["config"]["workload"].startswith("config 3")
 
@@ -35,4 +42,9 @@ def test_device_arm_line():
     e = line["e2e"]
     assert e["value"] > 0 and e["h2d_bytes_per_step"] > 0 and e["d2h_bytes_per_step"] > 0 and e["value"] < line["value"]
     c = line["cpu_baseline"]
-    assert c["kind"] == "port" and c["cores"] == 1 and c["value"] > 0
+    assert c["kind"] in ("reference", "port") and c["cores"] == 1 and c["value"] > 0
+    # the reference arm prints the very same config object (the driver compares them)
+    ref = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0",
+                          "--scale", "0.05", "--cpu-sample-mb", "0.3", "--no-cpu-baseline"], check=True, capture_output=True, text=True,
+                         timeout=300).stdout
+    assert json.loads(ref.strip().splitlines()[-1])["config"] == line["config"]
