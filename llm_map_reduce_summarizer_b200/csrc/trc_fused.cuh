@@ -65,6 +65,8 @@ struct FuseArgs {
   // word memo of the launch (k_clean_tok_fused3): packed word of <= 15 bytes -> token count, write-once entries of
   // two 64-bit words {bytes 0..7, bytes 8..14 | (count+1) << 56}, claimed through memo_lock; cleared before every launch
   unsigned long long* memo; uint32_t* memo_lock; uint32_t memo_mask;
+  // second level of the look-back of k_clean_tok_w32: per group of 32 tiles an arrival counter and (status, value) words
+  unsigned long long* grp_cnt; unsigned long long* grp_bytes; unsigned long long* grp_kept;
 };
 #define FUSE_PH(i) do { if (A.phase && tid == 0) { long long now_ = clock64(); atomicAdd(&A.phase[i], (unsigned long long)(now_ - ph_t)); ph_t = now_; } } while (0)
 

@@ -16,6 +16,7 @@
 #include "trc_clean.cuh"
 #include "trc_clean_par.cuh"
 #include "trc_swar.cuh"
+#include "trc_w32.cuh"
 #include "trc_tok.cuh"
 #include "trc_stages.cuh"
 #include "trc_sent.cuh"
@@ -86,7 +87,7 @@ struct trc_ctx {
   TrcDev D{};
   bool have_pre = false, have_chunk = false;
   bool use_fused = true;          // single-pass clean+tokenise kernel (TRCHUNK_NO_FUSED=1 selects the v1 kernels)
-  int fused_gen = 3;              // TRCHUNK_FUSED=2 selects the byte-per-lane kernel, 3 the 8-byte-cell kernel
+  int fused_gen = 3;              // TRCHUNK_FUSED=2 selects the byte-per-lane kernel, 3 (default) the 8-byte-cell kernel, 4 warp-private tiles
   int64_t counts[TRC_N_COUNTERS] = {0};
   int64_t* h_pin = nullptr;        // mapped pinned scratch for small counter reads (64 int64)
   void* d_pin = nullptr;           // its device address
@@ -357,6 +358,65 @@ static void hostsim_clean_swar(TrcDev D, TrcTables T, int32_t* keep, uint8_t* co
   }
 }
 
+// The 32-byte-chunk formulation (trc_w32.cuh), tiled exactly like k_clean_tok_w32 (trc_fused4.cuh): tiles of
+// `tile_segs` segments that start at a 16-byte aligned base, the neighbouring tiles' bytes visible past the span,
+// class masks cut to the tile's own bytes, the classification through the same 256-entry table.
+static void hostsim_clean_w32(TrcDev D, TrcTables T, int32_t* keep, uint8_t* code, int64_t braw, int64_t tile_segs) {
+  if (tile_segs <= 0) tile_segs = D.n > 0 ? D.n : 1;
+  std::vector<uint64_t> lut(256);
+  for (uint32_t b = 0; b < 256; ++b) lut[b] = w32_lut_entry(T, b);
+  std::vector<uint8_t> buf;
+  std::vector<uint32_t> arr;
+  for (int64_t s0 = 0; s0 < D.n; s0 += tile_segs) {
+    const int64_t ns = (D.n - s0) < tile_segs ? (D.n - s0) : tile_segs;
+    const int64_t raw0 = D.seg_off[s0], raw1 = D.seg_off[s0 + ns];
+    const int32_t al = (int32_t)(raw0 & 15);
+    const int64_t base = raw0 - al;
+    const int32_t span = (int32_t)(raw1 - base);
+    const int32_t nch = (span + 31) >> 5, nstep = (span + 1023) >> 10, nall = nstep * 32;
+    buf.assign((size_t)nall * 32 + 64, 0);
+    for (int32_t k = 0; k < nall * 32; ++k) buf[k] = base + k < braw ? D.text[base + k] : 0;
+    const size_t stride = (size_t)nall + 2;
+    arr.assign(stride * 8, 0u);
+    W32 M; M.nch = nch;
+    M.sp = arr.data() + 1; M.w = M.sp + stride; M.ct = M.w + stride; M.bd = M.ct + stride; M.ep = M.bd + stride;
+    M.lt = M.ep + stride; M.drop = M.lt + stride; M.ds = M.drop + stride;
+    for (int64_t i = s0; i < s0 + ns; ++i) if (D.seg_off[i + 1] > D.seg_off[i]) w32_or_bit(M.bd, (int32_t)(D.seg_off[i] - base));
+    std::vector<uint32_t> leadv((size_t)nall, 0u);
+    for (int32_t c = 0; c < nall; ++c) {
+      uint32_t x[8];
+      memcpy(x, buf.data() + 32 * (size_t)c, 32);
+      const W32Cls cl = w32_classify(lut.data(), x);
+      const uint32_t v = w32_valid(c, al, span);
+      M.sp[c] = cl.sp & v; M.w[c] = cl.w & v; M.ct[c] = cl.ct & v; M.ep[c] = cl.ep & v; M.lt[c] = cl.lt & v;
+      leadv[c] = cl.na & ~cl.ct & v;
+    }
+    for (int32_t c = 0; c < nall; ++c) if (leadv[c]) w32_fix_multibyte(T, buf.data(), M, c, leadv[c], span);
+    std::vector<int32_t> relv((size_t)ns + 1);
+    for (int64_t i = 0; i <= ns; ++i) relv[(size_t)i] = (int32_t)(D.seg_off[s0 + i] - base);
+    auto seg_of = [&](int32_t k) { int lo = 0, hi = (int)ns; while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (relv[mid] <= k) lo = mid; else hi = mid; } return lo; };
+    for (int32_t c = 0; c < nch; ++c) w32_dup_chunk(buf.data(), M, c, w32_valid(c, al, span), span, relv.data(), seg_of);
+    for (int32_t c = 0; c < nch; ++c) {
+      const W32Codes r = w32_chunk_codes(buf.data(), M, c, al, span);
+      for (int bit = 0; bit < 32; ++bit) {
+        const int32_t k = c * 32 + bit;
+        if (k < al) continue;
+        if (k >= span) break;
+        code[base + k] = ((r.ins >> bit) & 1u) ? 3 : (((r.space >> bit) & 1u) ? 2 : (((r.copy >> bit) & 1u) ? 1 : 0));
+      }
+    }
+  }
+  for (int64_t i = 0; i < D.n; ++i) {
+    int64_t len = 0; int32_t chars = 0;
+    for (int64_t k = D.seg_off[i]; k < D.seg_off[i + 1]; ++k) {
+      uint8_t r = code[k];
+      len += cp_outlen(r);
+      chars += (r == 3) ? 2 : ((r == 2 || (r == 1 && (D.text[k] & 0xC0) != 0x80)) ? 1 : 0);
+    }
+    D.clen[i] = len; D.cchars[i] = chars; keep[i] = len > 0;
+  }
+}
+
 static void hostsim_clean_par_write(TrcDev D, const uint8_t* code) {
   for (int64_t j = 0; j < D.n_kept; ++j) {
     int32_t r = D.k2r[j];
@@ -495,6 +555,7 @@ __global__ void __launch_bounds__(LONG_T) k_bpe_long(TrcTables T, const uint32_t
 #include "trc_giant.cuh"
 #include "trc_fused.cuh"
 #include "trc_fused3.cuh"
+#include "trc_fused4.cuh"
 #endif
 
 __global__ void k_special_docs(TrcDev D, const int32_t* __restrict__ seg_special, const int32_t* __restrict__ spk_special) {
@@ -940,7 +1001,7 @@ extern "C" int trc_create(int device, trc_ctx** out) {
       cudaHostGetDevicePointer(&ctx->d_pin, ctx->h_pin, 0) != cudaSuccess) { delete ctx; return TRC_ECUDA; }
   for (int k = 0; k < 4; ++k) cudaEventCreate(&ctx->ev[k]);
   { const char* e = getenv("TRCHUNK_NO_FUSED"); ctx->use_fused = !(e && e[0] == '1'); }
-  { const char* e = getenv("TRCHUNK_FUSED"); if (e && e[0] == '2') ctx->fused_gen = 2; }
+  { const char* e = getenv("TRCHUNK_FUSED"); if (e && e[0] >= '2' && e[0] <= '4') ctx->fused_gen = e[0] - '0'; }
   { const char* e = getenv("TRCHUNK_NO_MEMO"); ctx->use_memo = !(e && e[0] == '1'); }
   *out = ctx;
   return TRC_OK;
@@ -1171,13 +1232,25 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
     ALLOC(D.C, uint8_t, ccap);
     if (n == 0) { CK(cudaMemsetAsync(D.coff, 0, 8, st)); CK(cudaMemsetAsync(D.kdoc_off, 0, 8 * (size_t)(nd + 1), st)); }
     else {
-      const int64_t tile_segs = ctx->fused_gen >= 3 ? F3_SEGS : FUSE_SEGS;
+      // generation 4 needs a 16-byte aligned text buffer (bulk copies); its tiles hold as many segments as fit a
+      // warp's buffers at this batch's mean segment length (at most 32, one per lane)
+      int gen = ctx->fused_gen;
+      if (gen >= 4 && ((uintptr_t)D.text & 15)) gen = 3;
+      int tsegs4 = F4_SEGS;
+      if (gen >= 4) {
+        const double avg = (double)braw / (double)n;
+        const double fit = (double)(F4_IN_CAP - 16) / (avg * 1.12 + 1.0);
+        tsegs4 = fit >= F4_SEGS ? F4_SEGS : (fit < 1.0 ? 1 : (int)fit);
+      }
+      const int64_t tile_segs = gen >= 4 ? tsegs4 : (gen >= 3 ? F3_SEGS : FUSE_SEGS);
       const int64_t ntiles = (n + tile_segs - 1) / tile_segs;
       FuseArgs A;
       unsigned long long* fz;
-      ALLOC(fz, unsigned long long, 2 * ntiles + 32);
-      CK(cudaMemsetAsync(fz, 0, 8 * (size_t)(2 * ntiles + 32), st));
+      const int64_t ngroups = (ntiles + 31) / 32;
+      ALLOC(fz, unsigned long long, 2 * ntiles + 3 * ngroups + 32);
+      CK(cudaMemsetAsync(fz, 0, 8 * (size_t)(2 * ntiles + 3 * ngroups + 32), st));
       A.tile_counter = fz; A.wl_cnt = fz + 2; A.totals = (int64_t*)(fz + 4); A.desc_bytes = fz + 32; A.desc_kept = fz + 32 + ntiles;
+      A.grp_cnt = fz + 32 + 2 * ntiles; A.grp_bytes = A.grp_cnt + ngroups; A.grp_kept = A.grp_bytes + ngroups;
       static const bool want_phases = getenv("TRCHUNK_PHASES") != nullptr;
       A.phase = want_phases ? fz + 8 : nullptr;
       A.text_bytes = braw; A.seg_special = seg_special;
@@ -1186,22 +1259,28 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       A.sl_cap = 2 * n + 1024; A.sl_cnt = fz + 7;
       ALLOC(A.sl, SlowWord, A.sl_cap);
       A.memo = nullptr; A.memo_lock = nullptr; A.memo_mask = 0;
-      if (ctx->use_memo && ctx->fused_gen >= 3) {
+      if (ctx->use_memo && gen >= 3) {
         const size_t ents = (size_t)1 << TRC_MEMO_LOG2, bytes = ents * 16 + ents * 4;
         if (!ctx->d_memo) CK(cudaMalloc(&ctx->d_memo, bytes));
         CK(cudaMemsetAsync(ctx->d_memo, 0, bytes, st));
         A.memo = ctx->d_memo; A.memo_lock = (uint32_t*)(ctx->d_memo + 2 * ents); A.memo_mask = (uint32_t)(ents - 1);
       }
       A.G = GiantView{};
-      if (ctx->fused_gen >= 3) { if ((rc = giant_stage(ctx, st, braw, &A.G))) return rc; }
+      if (gen >= 3) { if ((rc = giant_stage(ctx, st, braw, &A.G))) return rc; }
       static bool attr_done[64] = {false};
       if (!attr_done[ctx->device & 63]) {
         CK(cudaFuncSetAttribute(k_clean_tok_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FuseSmem)));
         CK(cudaFuncSetAttribute(k_clean_tok_fused3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(F3Smem)));
+        CK(cudaFuncSetAttribute(k_clean_tok_w32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(F4Smem)));
         attr_done[ctx->device & 63] = true;
       }
       int blocks = (int)(ntiles < 148 * 2 ? ntiles : 148 * 2);
-      if (ctx->fused_gen >= 3) {
+      if (gen >= 4) {
+        const int64_t want = (ntiles + F4_WARPS - 1) / F4_WARPS;
+        blocks = (int)(want < 148 ? want : 148);
+        prof_begin(ctx, st, "k_clean_tok_w32");
+        k_clean_tok_w32<<<blocks, F4_T, sizeof(F4Smem), st>>>(D, ctx->T, ctx->d_byte_id, A, ntiles, tsegs4);
+      } else if (gen >= 3) {
         prof_begin(ctx, st, "k_clean_tok_fused3");
         k_clean_tok_fused3<<<blocks, F3_T, sizeof(F3Smem), st>>>(D, ctx->T, ctx->d_byte_id, A, ntiles);
       } else {
@@ -1228,7 +1307,16 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
           slow_pending = true;
         }
       }
-      if (want_phases) {
+      if (want_phases && gen >= 4) {
+        unsigned long long ph[16];
+        if ((rc = read_back(ctx, st, fz + 8, 16 * 8, ph))) return rc;
+        unsigned long long tot = 0; for (int k = 0; k < 13; ++k) tot += ph[k];
+        static const char* nm[13] = {"wait+load", "classify", "dup", "codes+scan", "segments", "scatter+wordstarts", "special", "tok-cache", "tok-match",
+                                     "resolve", "copy-out", "slow-handoff+sums", "outputs"};
+        fprintf(stderr, "[trchunk w32 phases %%]");
+        for (int k = 0; k < 13; ++k) fprintf(stderr, " %s %.1f", nm[k], 100.0 * ph[k] / (tot ? tot : 1));
+        fprintf(stderr, "\n");
+      } else if (want_phases) {
         unsigned long long ph[16];
         if ((rc = read_back(ctx, st, fz + 8, 16 * 8, ph))) return rc;
         fprintf(stderr, "[trchunk words] %llu in word lists, %llu past the word cache, %llu to the slow list, %llu matcher words longer than 15 bytes\n", ph[12], ph[13], ph[14], ph[15]);
@@ -1256,6 +1344,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   if (hs_par) {
     ALLOC(hs_cls, uint8_t, braw); ALLOC(hs_code, uint8_t, braw);
     if (hs_mode && hs_mode[0] == 'p') hostsim_clean_par_count(D, ctx->T, keep, hs_cls, hs_code);
+    else if (hs_mode && hs_mode[0] == 'w') { const char* ts = getenv("TRCHUNK_HOSTSIM_TILE"); hostsim_clean_w32(D, ctx->T, keep, hs_code, braw, ts ? atoll(ts) : 32); }
     else { const char* ts = getenv("TRCHUNK_HOSTSIM_TILE"); hostsim_clean_swar(D, ctx->T, keep, hs_code, braw, ts ? atoll(ts) : 256); }   // 256 = F3_SEGS
   } else
 #endif

@@ -53,6 +53,26 @@ def test_fuzz_cases_tile_edges(hostsim_engine, monkeypatch, tile):
         assert json.dumps(E.build_processed(b, P, x)) == json.dumps(OP.preprocess(synth.doc_to_segments(b, x))), x
 
 
+@pytest.mark.parametrize("tile", ["1", "3", "32", "0"])
+def test_chunk32_cleaner_tile_edges(hostsim_engine, monkeypatch, tile):
+    """The 32-byte-chunk formulation of clean_text that k_clean_tok_w32 runs (trc_w32.cuh), tiled as in the kernel:
+    KATs, the reference's fuzz cases, synthetic documents and the dense tiles, with tile edges on every segment
+    boundary (1), every third (3), the kernel's own 32, and one tile per batch (0)."""
+    monkeypatch.setenv("TRCHUNK_HOSTSIM_CLEAN", "w32")
+    monkeypatch.setenv("TRCHUNK_HOSTSIM_TILE", tile)
+    E.set_default_engine(hostsim_engine)
+    for s, want in load_golden("kat.json")["clean_text"]:
+        assert PP.clean_text(s) == want, repr(s)
+    cases = load_golden("fuzz_cases.json.gz")
+    assert pc.check_fuzz_cases(hostsim_engine, cases[1::2], require_all=True) == 80
+    b, mt, _ = synth.config(5, 0.004)
+    hostsim_engine.preprocess(b)
+    P = hostsim_engine.fetch_processed()
+    for x in range(b.n_doc):
+        assert json.dumps(E.build_processed(b, P, x)) == json.dumps(OP.preprocess(synth.doc_to_segments(b, x))), x
+    assert pc.check_dense_tiles(hostsim_engine) == 6
+
+
 def test_token_counts_vs_corebpe(hostsim_engine):
     import random
     enc = TK.encoding()
