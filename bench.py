@@ -57,6 +57,8 @@ KERNEL_BYTES = {  # algorithmic bytes of one launch of the named kernel (DESIGN.
     "k_emit_merged": lambda c: c["b_clean"] + c["b_merged"] + 24 * c["n_kept"],
     "k_clean_tok_fused": lambda c: c["b_raw"] + c["b_clean"] + 28 * c["n_seg"],
     "k_clean_tok_fused3": lambda c: c["b_raw"] + c["b_clean"] + 28 * c["n_seg"],
+    "k_clean_tok_w32": lambda c: c["b_raw"] + c["b_clean"] + 28 * c["n_seg"],
+    "k_clean_tok_c32": lambda c: c["b_raw"] + c["b_clean"] + 28 * c["n_seg"],
 }
 
 

@@ -87,7 +87,7 @@ struct trc_ctx {
   TrcDev D{};
   bool have_pre = false, have_chunk = false;
   bool use_fused = true;          // single-pass clean+tokenise kernel (TRCHUNK_NO_FUSED=1 selects the v1 kernels)
-  int fused_gen = 3;              // TRCHUNK_FUSED=2 selects the byte-per-lane kernel, 3 (default) the 8-byte-cell kernel, 4 warp-private tiles
+  int fused_gen = 5;              // TRCHUNK_FUSED=2 byte-per-lane kernel, 3 8-byte cells, 4 warp-private tiles, 5 (default) CTA tile with 32-byte chunks
   int64_t counts[TRC_N_COUNTERS] = {0};
   int64_t* h_pin = nullptr;        // mapped pinned scratch for small counter reads (64 int64)
   void* d_pin = nullptr;           // its device address
@@ -556,6 +556,7 @@ __global__ void __launch_bounds__(LONG_T) k_bpe_long(TrcTables T, const uint32_t
 #include "trc_fused.cuh"
 #include "trc_fused3.cuh"
 #include "trc_fused4.cuh"
+#include "trc_fused5.cuh"
 #endif
 
 __global__ void k_special_docs(TrcDev D, const int32_t* __restrict__ seg_special, const int32_t* __restrict__ spk_special) {
@@ -1001,7 +1002,7 @@ extern "C" int trc_create(int device, trc_ctx** out) {
       cudaHostGetDevicePointer(&ctx->d_pin, ctx->h_pin, 0) != cudaSuccess) { delete ctx; return TRC_ECUDA; }
   for (int k = 0; k < 4; ++k) cudaEventCreate(&ctx->ev[k]);
   { const char* e = getenv("TRCHUNK_NO_FUSED"); ctx->use_fused = !(e && e[0] == '1'); }
-  { const char* e = getenv("TRCHUNK_FUSED"); if (e && e[0] >= '2' && e[0] <= '4') ctx->fused_gen = e[0] - '0'; }
+  { const char* e = getenv("TRCHUNK_FUSED"); if (e && e[0] >= '2' && e[0] <= '5') ctx->fused_gen = e[0] - '0'; }
   { const char* e = getenv("TRCHUNK_NO_MEMO"); ctx->use_memo = !(e && e[0] == '1'); }
   *out = ctx;
   return TRC_OK;
@@ -1237,10 +1238,14 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       int gen = ctx->fused_gen;
       if (gen >= 4 && ((uintptr_t)D.text & 15)) gen = 3;
       int tsegs4 = F4_SEGS;
-      if (gen >= 4) {
+      if (gen == 4) {
         const double avg = (double)braw / (double)n;
         const double fit = (double)(F4_IN_CAP - 16) / (avg * 1.12 + 1.0);
         tsegs4 = fit >= F4_SEGS ? F4_SEGS : (fit < 1.0 ? 1 : (int)fit);
+      } else if (gen >= 5) {
+        const double avg = (double)braw / (double)n;
+        const double fit = (double)(F5_IN_CAP - 16) / (avg * 1.06 + 1.0);
+        tsegs4 = fit >= F5_SEGS ? F5_SEGS : (fit < 1.0 ? 1 : (int)fit);
       }
       const int64_t tile_segs = gen >= 4 ? tsegs4 : (gen >= 3 ? F3_SEGS : FUSE_SEGS);
       const int64_t ntiles = (n + tile_segs - 1) / tile_segs;
@@ -1272,10 +1277,14 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
         CK(cudaFuncSetAttribute(k_clean_tok_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FuseSmem)));
         CK(cudaFuncSetAttribute(k_clean_tok_fused3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(F3Smem)));
         CK(cudaFuncSetAttribute(k_clean_tok_w32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(F4Smem)));
+        CK(cudaFuncSetAttribute(k_clean_tok_c32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(F5Smem)));
         attr_done[ctx->device & 63] = true;
       }
       int blocks = (int)(ntiles < 148 * 2 ? ntiles : 148 * 2);
-      if (gen >= 4) {
+      if (gen >= 5) {
+        prof_begin(ctx, st, "k_clean_tok_c32");
+        k_clean_tok_c32<<<blocks, F5_T, sizeof(F5Smem), st>>>(D, ctx->T, ctx->d_byte_id, A, ntiles, tsegs4);
+      } else if (gen >= 4) {
         const int64_t want = (ntiles + F4_WARPS - 1) / F4_WARPS;
         blocks = (int)(want < 148 ? want : 148);
         prof_begin(ctx, st, "k_clean_tok_w32");
@@ -1307,7 +1316,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
           slow_pending = true;
         }
       }
-      if (want_phases && gen >= 4) {
+      if (want_phases && gen == 4) {
         unsigned long long ph[16];
         if ((rc = read_back(ctx, st, fz + 8, 16 * 8, ph))) return rc;
         unsigned long long tot = 0; for (int k = 0; k < 13; ++k) tot += ph[k];
