@@ -18,16 +18,20 @@
 //    than 4 KB arrive pre-cleaned from trc_giant.cuh).
 #pragma once
 
-#define F5_T 512
+#ifndef F5_T
+#define F5_T 256                                // threads per CTA = chunks per tile
+#endif
+#define F5_CTAS (1024 / F5_T)                   // CTAs per SM
 #define F5_NW (F5_T / 32)
-#define F5_SEGS 256
-#define F5_IN_CAP 16384
+#define F5_SEGS (F5_T / 2)
+#define F5_IN_CAP (F5_T * 32)
 #define F5_NCH (F5_IN_CAP / 32)                 // one chunk per thread
 #define F5_OUT_CAP (F5_IN_CAP + F5_IN_CAP / 2)
-#define F5_WORD_CAP 5632
-#define F5_SLOW_CAP 1024
+#define F5_WORD_CAP (F5_T * 11)
+#define F5_SLOW_CAP (F5_T * 2)
 #define F5_NM 14
-#define F5_MATCH_T 128                          // threads that run the packed-word matcher when only a few words are queued
+#define F5_MATCH_T (F5_T / 4)                   // threads that run the packed-word matcher when only a few words are queued
+#define F5_HOT (F5_T * 4)                       // entries of the CTA's word cache
 
 struct F5Smem {
   union alignas(16) {                           // raw tile; after the scatter: word starts (position | first word of its segment << 15)
@@ -40,7 +44,8 @@ struct F5Smem {
     struct { uint8_t cnt[F5_WORD_CAP + 8]; uint16_t miss[F5_WORD_CAP + 8]; uint16_t slow[F5_SLOW_CAP]; } t;   // after the word starts
   } u;
   uint64_t lut[256];
-  uint64_t hot8[TRC_HOT8];
+  uint64_t hot8[F5_HOT];
+  alignas(16) uint4 kmask[17];                  // byte masks of the first 0..16 bytes of a packed word
   int32_t rel[F5_SEGS + 1];
   int32_t xtok[F5_SEGS];
   int32_t spmin[F5_SEGS];
@@ -59,7 +64,7 @@ struct F5Smem {
   alignas(8) unsigned long long mbar;
 };
 static_assert(sizeof(((F5Smem*)0)->u.t) <= sizeof(((F5Smem*)0)->u.m), "token lists fit the mask rows");
-static_assert(sizeof(F5Smem) <= 115200, "two CTAs per SM");
+static_assert(sizeof(F5Smem) * F5_CTAS <= 227 * 1024 - F5_CTAS * 1024, "CTAs per SM");
 
 __device__ __forceinline__ void f5_scan3(F5Smem& S, int lane, int wid, int32_t v0, int32_t v1, int32_t v2, int32_t* e0, int32_t* e1, int32_t* e2) {
   int32_t x0 = v0, x1 = v1, x2 = v2;
@@ -100,13 +105,23 @@ __device__ __forceinline__ void f5_word_key(const F5Smem& S, int32_t w, uint64_t
   const uint32_t w0 = p32[0], w1 = p32[1], w2 = p32[2], w3 = p32[3], w4 = p32[4];
   uint32_t k0 = __funnelshift_r(w0, w1, sh), k1 = __funnelshift_r(w1, w2, sh), k2 = __funnelshift_r(w2, w3, sh), k3 = __funnelshift_r(w3, w4, sh);
   if (vs) { k3 = (k3 << 8) | (k2 >> 24); k2 = (k2 << 8) | (k1 >> 24); k1 = (k1 << 8) | (k0 >> 24); k0 = (k0 << 8) | (uint32_t)' '; }
-  const int r0 = Lw, r1 = Lw - 4, r2 = Lw - 8, r3 = Lw - 12;
-  k0 &= r0 >= 4 ? 0xffffffffu : (r0 <= 0 ? 0u : ((1u << (8 * r0)) - 1u));
-  k1 &= r1 >= 4 ? 0xffffffffu : (r1 <= 0 ? 0u : ((1u << (8 * r1)) - 1u));
-  k2 &= r2 >= 4 ? 0xffffffffu : (r2 <= 0 ? 0u : ((1u << (8 * r2)) - 1u));
-  k3 &= r3 >= 4 ? 0xffffffffu : (r3 <= 0 ? 0u : ((1u << (8 * r3)) - 1u));
+  const uint4 km = S.kmask[Lw];                 // the first Lw bytes
+  k0 &= km.x; k1 &= km.y; k2 &= km.z; k3 &= km.w;
   lo = (uint64_t)k0 | ((uint64_t)k1 << 32);
   hi = (uint64_t)k2 | ((uint64_t)k3 << 32);
+}
+
+// Launch memo, two ways: a word may sit in slot s or s ^ 1 (one 32-byte sector, both loads in flight together).  Entries
+// are write-once as in f3_memo_put (claimed through memo_lock, two aligned 64-bit stores, count + 1 in the top byte).
+__device__ __forceinline__ void f5_memo_put(const FuseArgs& A, uint64_t lo, uint64_t hi, uint32_t c) {
+  if (!A.memo || lo == 0 || c > (uint32_t)F3_MEMO_SLOW) return;
+  uint32_t slot = f3_memo_slot(lo, hi, A.memo_mask);
+  if (atomicCAS(&A.memo_lock[slot], 0u, 1u) != 0u) { slot ^= 1u; if (atomicCAS(&A.memo_lock[slot], 0u, 1u) != 0u) return; }
+  st_relaxed(&A.memo[2 * (size_t)slot], lo);
+  st_relaxed(&A.memo[2 * (size_t)slot + 1], hi | ((uint64_t)(c + 1u) << 56));
+}
+__device__ __forceinline__ int f5_memo_hit(const ulonglong2& e, uint64_t lo, uint64_t hi) {
+  return (e.x == lo && (e.y & 0x00ffffffffffffffULL) == hi && (e.y >> 56)) ? (int)(e.y >> 56) - 1 : -1;
 }
 
 __device__ __forceinline__ int f5_seg_of_word(const F5Smem& S, int ns, int32_t w) {
@@ -115,13 +130,18 @@ __device__ __forceinline__ int f5_seg_of_word(const F5Smem& S, int ns, int32_t w
   return lo;
 }
 
-__global__ void __launch_bounds__(F5_T, 2) k_clean_tok_c32(TrcDev D, TrcTables T, const uint32_t* __restrict__ byte_id, FuseArgs A,
+__global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTables T, const uint32_t* __restrict__ byte_id, FuseArgs A,
                                                            int64_t ntiles, int tsegs) {
   extern __shared__ __align__(16) unsigned char fuse_raw[];
   F5Smem& S = *reinterpret_cast<F5Smem*>(fuse_raw);
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   for (int k = tid; k < 256; k += F5_T) S.lut[k] = w32_lut_entry(T, (uint32_t)k);
-  for (int k = tid; k < TRC_HOT8; k += F5_T) S.hot8[k] = 0ULL;
+  for (int k = tid; k < F5_HOT; k += F5_T) S.hot8[k] = 0ULL;
+  if (tid < 17) {
+    uint32_t q[4];
+    for (int j = 0; j < 4; ++j) { const int r = tid - 4 * j; q[j] = r >= 4 ? 0xffffffffu : (r <= 0 ? 0u : ((1u << (8 * r)) - 1u)); }
+    S.kmask[tid] = make_uint4(q[0], q[1], q[2], q[3]);
+  }
   if (tid == 0) { f4_mbar_init(f4_saddr(&S.mbar), 1u); f4_fence_async(); }
   TrcFast F; F.acls = T.acls; F.hot8 = nullptr; F.hot8_mask = 0;
   W32 M;
@@ -299,14 +319,20 @@ __global__ void __launch_bounds__(F5_T, 2) k_clean_tok_c32(TrcDev D, TrcTables T
         int32_t pos = (int32_t)(p_os[c] & 0xffffu);
         const uint4 q0 = *reinterpret_cast<const uint4*>(S.y.in + 32 * c), q1 = *reinterpret_cast<const uint4*>(S.y.in + 32 * c + 16);
         const uint32_t x[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
-        if (in == 0u && (cp | se) == 0xffffffffu && !(se & m_ns[c])) f4_store32(S.out + pos, x);
+        const uint32_t odd = se & m_ns[c];            // emitted spaces whose source byte is not U+0020
+        if (in == 0u && (cp | se) == 0xffffffffu && !odd) f4_store32(S.out + pos, x);
         else {
           uint8_t* dst = S.out;
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {             // a word of four bytes at a time
+          for (int j = 0; j < 8; ++j) {             // four bytes at a time: dropped, copied as they are, or byte by byte
             const uint32_t c4 = (cp >> (4 * j)) & 15u, s4 = (se >> (4 * j)) & 15u, i4 = (in >> (4 * j)) & 15u;
             if (!(c4 | s4)) continue;
             const uint32_t xv = x[j];
+            if ((c4 | s4) == 15u && !i4 && !((odd >> (4 * j)) & 15u)) {
+              dst[pos] = (uint8_t)xv; dst[pos + 1] = (uint8_t)(xv >> 8); dst[pos + 2] = (uint8_t)(xv >> 16); dst[pos + 3] = (uint8_t)(xv >> 24);
+              pos += 4;
+              continue;
+            }
 #pragma unroll
             for (int b = 0; b < 4; ++b) {
               if ((i4 >> b) & 1u) dst[pos++] = ' ';
@@ -371,16 +397,17 @@ __global__ void __launch_bounds__(F5_T, 2) k_clean_tok_c32(TrcDev D, TrcTables T
             if (Lw <= 15) {
               uint32_t slot8 = 0xffffffffu;
               if (Lw <= 7) {
-                slot8 = trc_key8_slot(lo, TRC_HOT8 - 1);
+                slot8 = trc_key8_slot(lo, F5_HOT - 1);
                 const uint64_t ce = S.hot8[slot8];
                 if ((ce & 0x00ffffffffffffffULL) == lo) mc = (int)(ce >> 56);
               }
               if (mc < 0 && A.memo != nullptr && lo != 0) {
-                const ulonglong2 e = __ldcg(reinterpret_cast<const ulonglong2*>(A.memo) + f3_memo_slot(lo, hi, A.memo_mask));
-                if (e.x == lo && (e.y & 0x00ffffffffffffffULL) == hi && (e.y >> 56)) {
-                  mc = (int)(e.y >> 56) - 1;
-                  if (slot8 != 0xffffffffu) S.hot8[slot8] = lo | ((uint64_t)mc << 56);
-                }
+                const uint32_t ms = f3_memo_slot(lo, hi, A.memo_mask);
+                const ulonglong2 ea = __ldcg(reinterpret_cast<const ulonglong2*>(A.memo) + ms);
+                const ulonglong2 eb = __ldcg(reinterpret_cast<const ulonglong2*>(A.memo) + (ms ^ 1u));
+                int h = f5_memo_hit(ea, lo, hi);
+                if (h < 0) h = f5_memo_hit(eb, lo, hi);
+                if (h >= 0) { mc = h; if (slot8 != 0xffffffffu) S.hot8[slot8] = lo | ((uint64_t)h << 56); }
               }
             }
             cnt[w] = (uint8_t)((mc >= 0 && mc != F3_MEMO_SLOW) ? mc : 0);
@@ -405,8 +432,8 @@ __global__ void __launch_bounds__(F5_T, 2) k_clean_tok_c32(TrcDev D, TrcTables T
             bool done;
             if (Lw <= 16) {
               done = trc_count_word16(T, F, lo, hi, Lw, &cc);
-              if (Lw <= 7) S.hot8[trc_key8_slot(lo, TRC_HOT8 - 1)] = lo | ((uint64_t)(done ? cc : (uint32_t)F3_MEMO_SLOW) << 56);
-              if (Lw <= 15) f3_memo_put(A, lo, hi, done ? cc : (uint32_t)F3_MEMO_SLOW);
+              if (Lw <= 7) S.hot8[trc_key8_slot(lo, F5_HOT - 1)] = lo | ((uint64_t)(done ? cc : (uint32_t)F3_MEMO_SLOW) << 56);
+              if (Lw <= 15) f5_memo_put(A, lo, hi, done ? cc : (uint32_t)F3_MEMO_SLOW);
             } else done = trc_count_word_fast(T, F, S.out + st, n, vs, &cc) && cc < 250u;
             if (done) cnt[w] = (uint8_t)cc;
             else { const int qq = atomicAdd(&S.nslow, 1); if (qq < F5_SLOW_CAP) slow[qq] = (uint16_t)w; else cnt[w] = 255; }

@@ -177,43 +177,65 @@ TRC_HD uint32_t w32_clz64(uint64_t x) {
   return x ? (uint32_t)__builtin_clzll(x) : 64u;
 #endif
 }
-// Returns the candidates that need the generic path.
+// 32 bits of the 64-bit value hi:lo starting at bit s (0 <= s < 32)
+TRC_HD uint32_t w32_fsr(uint32_t lo, uint32_t hi, int s) {
+#if defined(__CUDA_ARCH__)
+  return __funnelshift_r(lo, hi, (unsigned)s);
+#else
+  return s ? ((lo >> s) | (hi << (32 - s))) : lo;
+#endif
+}
+TRC_HD int w32_clz32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+  return __clz((int)x);
+#else
+  return x ? __builtin_clz(x) : 32;
+#endif
+}
+// Returns the candidates that need the generic path (runs of 24 bytes or more, separators of 8 bytes or more, a
+// segment boundary inside the candidate run, a run that reaches the end of the tile).  Per candidate byte k two kinds
+// of 32-bit windows are cut from the chunk's mask words and its neighbours': "down" windows, bit 31 <-> byte k-1 and
+// bit j <-> byte k-32+j, and "up" windows, bit 0 <-> byte k.
 TRC_HD uint32_t w32_dup_chunk_simple(const uint8_t* in, const W32& M, int32_t c, uint32_t valid, int32_t lim) {
-  const uint32_t w = M.w[c], sp = M.sp[c], bd = M.bd[c], ct = M.ct[c];
-  const uint32_t wp = M.w[c - 1], spp = M.sp[c - 1], bdp = M.bd[c - 1], ctp = M.ct[c - 1];
+  const uint32_t w = M.w[c], sp = M.sp[c], bd = M.bd[c];
+  const uint32_t wp = M.w[c - 1], spp = M.sp[c - 1];
   const uint32_t wstart = w & ~((w << 1) | (wp >> 31));
   uint32_t cand = wstart & ((sp << 1) | (spp >> 31)) & ~bd & valid;
   if (!cand) return 0u;
-  const uint32_t wn = M.w[c + 1], bdn = M.bd[c + 1];
-  // per candidate byte k: the separator is one single-byte whitespace character that follows a \w byte
-  const uint32_t sp2 = (sp << 2) | (spp >> 30), ct1 = (ct << 1) | (ctp >> 31), w2 = (w << 2) | (wp >> 30), bd1 = (bd << 1) | (bdp >> 31);
-  const uint32_t plain = cand & ~sp2 & ~ct1 & ~bd1;        // (a segment that starts with the separator has no previous word)
-  uint32_t generic = cand & ~plain;
-  uint32_t simple = plain & w2;                             // plain separators after a non-\w byte: no previous word, no duplicate
-  const uint64_t WW = ((uint64_t)w << 32) | wp, BB = ((uint64_t)bd << 32) | bdp;
-  while (simple) {
-    const int bit = (int)trc_ctz32(simple);
-    simple &= simple - 1;
+  const uint32_t wn = M.w[c + 1], bdn = M.bd[c + 1], bdp = M.bd[c - 1], ct = M.ct[c], ctp = M.ct[c - 1];
+  uint32_t generic = 0;
+  while (cand) {
+    const int bit = (int)trc_ctz32(cand);
+    cand &= cand - 1;
     const int32_t k = (c << 5) + bit;
-    const uint32_t wwin = bit ? ((w >> bit) | (wn << (32 - bit))) : w;
-    if ((wwin & 0xffffffu) == 0xffffffu) { generic |= 1u << bit; continue; }
-    const int32_t L = (int32_t)trc_ctz32(~wwin);
-    const uint32_t bwin = bit ? ((bd >> bit) | (bdn << (32 - bit))) : bd;
-    if (bwin & ((1u << L) - 1u) & ~1u) { generic |= 1u << bit; continue; }          // a segment starts inside the run
-    if (k + L > lim) { generic |= 1u << bit; continue; }
-    if (in[k + L - 1] != in[k - 2]) continue;                                        // equal words end with the same byte
-    const uint32_t L1 = w32_clz64(~(WW << (33 - bit)));                              // \w bytes from k-2 downwards
-    if (L1 < (uint32_t)L) continue;                                                  // the previous run is shorter
-    const int pb = 31 + bit - L;                                                     // position of P = k-1-L in WW / BB
-    if ((BB >> (pb + 1)) & ((1ULL << L) - 1ULL)) continue;                           // a segment starts inside (P, k-1]
-    if (((WW >> (pb - 1)) & 1ULL) && !((BB >> pb) & 1ULL)) continue;                 // the previous run is longer
+    // the candidate run [k, k + L)
+    const uint32_t wup = w32_fsr(w, wn, bit);
+    if ((wup & 0xffffffu) == 0xffffffu) { generic |= 1u << bit; continue; }
+    const int32_t L = (int32_t)trc_ctz32(~wup);
+    if ((w32_fsr(bd, bdn, bit) & ((1u << L) - 1u) & ~1u) || k + L > lim) { generic |= 1u << bit; continue; }   // a segment starts inside the run
+    // the whitespace run [p, k) in front of it
+    const uint32_t ds = w32_fsr(spp, sp, bit);
+    const int lws = w32_clz32(~ds);                                                  // whitespace bytes from k-1 downwards (>= 1)
+    if (lws > 7) { generic |= 1u << bit; continue; }
+    const uint32_t db = w32_fsr(bdp, bd, bit);
+    if (db >> (32 - lws)) continue;                                                  // the run starts its segment (or spans a boundary): no previous word
+    if (in[k + L - 1] != in[k - lws - 1]) continue;                                  // equal words end with the same byte: rejects most
+    const uint32_t dw = w32_fsr(wp, w, bit);
+    // the previous run ends at p - 1: it must be exactly L bytes long inside the same segment
+    if (w32_clz32(~(dw << lws)) < L) continue;                                       // (a run of zero bytes when p-1 is not \w)
+    const int pb = 32 - lws - L;                                                     // window position of P = p - L  (>= 32 - 7 - 23 = 2)
+    if ((db >> (pb + 1)) & ((1u << (L - 1)) - 1u)) continue;                         // a segment starts inside (P, p-1]
+    if (((dw >> (pb - 1)) & 1u) && !((db >> pb) & 1u)) continue;                     // the previous run is longer
     bool eq = true;
-    for (int32_t i = 0; i + 1 < L; ++i) if (in[k - 1 - L + i] != in[k + i]) { eq = false; break; }
+    for (int32_t i = 0; i + 1 < L; ++i) if (in[k - lws - L + i] != in[k + i]) { eq = false; break; }
     if (!eq) continue;
-    const uint32_t run = (L == 32 ? 0xffffffffu : ((1u << L) - 1u));
+    const uint32_t run = (1u << L) - 1u;                                             // L < 24
     w32_or(M.drop, c, run << bit);
     if (bit + L > 32) w32_or(M.drop, c + 1, run >> (32 - bit));
-    if (bit) w32_or(M.ds, c, 1u << (bit - 1)); else w32_or(M.ds, c - 1, 0x80000000u);
+    // the emitted space would come from the last whitespace character of the run: its lead byte
+    const int nct = w32_clz32(~w32_fsr(ctp, ct, bit));                               // continuation bytes from k-1 downwards (< lws)
+    const int qb = bit - 1 - nct;                                                    // relative to this chunk
+    if (qb >= 0) w32_or(M.ds, c, 1u << qb); else w32_or(M.ds, c - 1, 1u << (32 + qb));
   }
   return generic;
 }

@@ -1282,6 +1282,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       }
       int blocks = (int)(ntiles < 148 * 2 ? ntiles : 148 * 2);
       if (gen >= 5) {
+        blocks = (int)(ntiles < 148 * F5_CTAS ? ntiles : 148 * F5_CTAS);
         prof_begin(ctx, st, "k_clean_tok_c32");
         k_clean_tok_c32<<<blocks, F5_T, sizeof(F5Smem), st>>>(D, ctx->T, ctx->d_byte_id, A, ntiles, tsegs4);
       } else if (gen >= 4) {
