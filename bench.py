@@ -32,16 +32,151 @@ OUT_ARRAYS = [("K2R", "<i4"), ("CLEN32", "<i4"), ("PDST", "<i8"), ("GSTART", "<i
 
 def workload(args, rank):
     from llm_map_reduce_summarizer_b200 import synth
-    b, mt, desc = synth.config(args.config, args.scale)
+    lex = getattr(args, "lexicon", 0) or None
+    b, mt, desc = synth.config(args.config, args.scale, lexicon=lex)
     if rank:
         # weak scaling: every rank gets its own shard of the same shape (different seed)
         saved = synth.BASE_SEED
         synth.BASE_SEED = saved + 1000 * rank
         try:
-            b, mt, desc = synth.config(args.config, args.scale)
+            b, mt, desc = synth.config(args.config, args.scale, lexicon=lex)
         finally:
             synth.BASE_SEED = saved
     return b, mt, desc
+
+
+class _DevBatch:
+    """What Engine.preprocess needs besides the device pointers."""
+
+    def __init__(self, n_seg, n_doc, speakers):
+        self.n_seg, self.n_doc, self.speakers = int(n_seg), int(n_doc), speakers
+
+
+def resident_ms(torch, eng, hb, mt, dev, steps, warm=3, tensors=None):
+    """ms per step of preprocess + chunk with the batch resident on the device (CUDA events on the current stream)."""
+    if tensors is None:
+        tensors = {k: torch.from_numpy(getattr(hb, k)).to(dev) for k in ("text", "seg_off", "start", "end", "speaker", "doc_off", "spk_bytes", "spk_off")}
+    ptrs = {k: v.data_ptr() for k, v in tensors.items()}
+    st = torch.cuda.current_stream()
+
+    def step():
+        eng.preprocess(hb, want_merged_text=False, stream=st.cuda_stream, device_ptrs=ptrs)
+        eng.chunk(mt, stream=st.cuda_stream)
+
+    for _ in range(warm):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(st)
+    for _ in range(steps):
+        step()
+    e1.record(st)
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps, eng.counts()
+
+
+def config5_shard(torch, dev, rank, world, corpus_bytes=10e9):
+    """This rank's shard of the 10 GB corpus of config 5 (the 100 MB base tiled to 10 GB at distinct
+    addresses): the virtual corpus is the base repeated, shard.shard_ranges cuts it by bytes, and the rank's document
+    range is assembled on the device from contiguous slices of the base.  Limits 2k / 8k / 32k by (corpus doc id) % 3."""
+    from llm_map_reduce_summarizer_b200 import shard as SH, synth
+    base, _, _ = synth.config(5, 1.0)
+    nb = base.n_doc
+    reps = max(1, int(round(corpus_bytes / base.text.nbytes)))
+    doc_bytes = np.diff(base.seg_off[base.doc_off])
+    voff = np.concatenate([[0], np.cumsum(np.tile(doc_bytes, reps))])
+    x0, x1 = SH.shard_ranges_from_offsets(voff, world)[rank]
+    T = {k: torch.from_numpy(getattr(base, k)).to(dev) for k in ("text", "seg_off", "start", "end", "speaker", "doc_off")}
+    seg_len = T["seg_off"][1:] - T["seg_off"][:-1]
+    doc_segs = T["doc_off"][1:] - T["doc_off"][:-1]
+    parts = {k: [] for k in ("text", "seg_len", "start", "end", "speaker", "doc_segs")}
+    x = x0
+    while x < x1:
+        d0 = x % nb
+        d1 = min(nb, d0 + (x1 - x))
+        s0, s1 = int(base.doc_off[d0]), int(base.doc_off[d1])
+        t0, t1 = int(base.seg_off[s0]), int(base.seg_off[s1])
+        parts["text"].append(T["text"][t0:t1]); parts["seg_len"].append(seg_len[s0:s1]); parts["start"].append(T["start"][s0:s1])
+        parts["end"].append(T["end"][s0:s1]); parts["speaker"].append(T["speaker"][s0:s1]); parts["doc_segs"].append(doc_segs[d0:d1])
+        x += d1 - d0
+    z = torch.zeros(1, dtype=torch.int64, device=dev)
+    out = {"text": torch.cat(parts["text"]), "start": torch.cat(parts["start"]), "end": torch.cat(parts["end"]),
+           "speaker": torch.cat(parts["speaker"]),
+           "seg_off": torch.cat([z, torch.cumsum(torch.cat(parts["seg_len"]), 0)]),
+           "doc_off": torch.cat([z, torch.cumsum(torch.cat(parts["doc_segs"]), 0)]),
+           "spk_bytes": torch.from_numpy(base.spk_bytes).to(dev), "spk_off": torch.from_numpy(base.spk_off).to(dev)}
+    del T, parts
+    mt = np.array([2000, 8000, 32000], dtype=np.int32)[np.arange(x0, x1) % 3]
+    hb = _DevBatch(out["start"].numel(), x1 - x0, base.speakers)
+    return hb, mt, out, {"corpus_docs": int(nb * reps), "corpus_bytes": int(voff[-1]), "docs": [int(x0), int(x1)]}
+
+
+def extra_configs(args, torch, dist, eng, dev, rank, world):
+    """Driver-visible numbers for the other BASELINE.json configs, measured in the same run (device-resident, CUDA
+    events): N = 1: config 2 (one meeting: a latency case), config 4 (one 1 M-segment transcript: does not shard) and an
+    open-vocabulary variant of config 3; N > 1: config 5, the 10 GB corpus cut by shard.shard_ranges, max over ranks."""
+    from llm_map_reduce_summarizer_b200 import synth
+    rec = {}
+    if world == 1:
+        for num, key in ((2, "config2_one_meeting"), (4, "config4_one_long_transcript")):
+            b, mt, desc = synth.config(num, 1.0)
+            ms, c = resident_ms(torch, eng, b, mt, dev, steps=5)
+            rec[key] = {"workload": desc, "ms_per_step": ms, "tokens_per_s": c["tokens"] / (ms / 1e3), "tokens": c["tokens"],
+                        "segments": c["n_seg"], "raw_text_bytes": c["b_raw"], "chunks": c["n_chunks"], "sentences": c["n_sent"],
+                        "sub_chunks": c["n_subs"]}
+        b, mt, desc = synth.config(3, 0.25, lexicon=500000)
+        ms, c = resident_ms(torch, eng, b, mt, dev, steps=5)
+        rec["open_vocabulary"] = {"workload": desc + " (scale 0.25)", "ms_per_step": ms, "tokens_per_s": c["tokens"] / (ms / 1e3),
+                                  "tokens": c["tokens"], "raw_text_bytes": c["b_raw"], "words": c["n_words"],
+                                  "words_first_sighting": c["n_word_first"], "words_generic_matcher": c["n_word_slow"],
+                                  "long_spans": c["n_long_spans"]}
+        b, mt, desc = synth.config(3, 0.25)
+        ms, c = resident_ms(torch, eng, b, mt, dev, steps=5)
+        rec["open_vocabulary"]["closed_vocabulary_same_size"] = {"ms_per_step": ms, "tokens_per_s": c["tokens"] / (ms / 1e3), "words": c["n_words"],
+                                                                 "words_first_sighting": c["n_word_first"], "words_generic_matcher": c["n_word_slow"]}
+    else:
+        hb, mt, tensors, info = config5_shard(torch, dev, rank, world)
+        ms, c = resident_ms(torch, eng, hb, mt, dev, steps=3, warm=2, tensors=tensors)
+        t = torch.tensor([ms, float(c["tokens"]), float(c["b_raw"])], device=dev, dtype=torch.float64)
+        tmax = t.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        rec["config5_corpus"] = dict(info, workload="10 GB corpus sharded by document over %d GPUs, limits 2k/8k/32k by doc id %% 3" % world,
+                                     ms_per_step=float(tmax[0].item()), tokens=float(t[1].item()), raw_text_bytes=float(t[2].item()),
+                                     tokens_per_s=float(t[1].item()) / (float(tmax[0].item()) / 1e3), scaling="strong (the corpus is fixed)")
+        del tensors
+        torch.cuda.empty_cache()
+    return rec
+
+
+def dropin_config1(eng):
+    """config 1 end to end through the drop-in modules - the example transcript as Python dicts in,
+    the reference's dict formats out, wall clock, median of 10 (packing, H2D, kernels, D2H, dict building)."""
+    import contextlib, gzip, io
+    from llm_map_reduce_summarizer_b200 import big_chunkeroosky as BC, engine as E, preprocessor as PP
+    p = os.path.join(ROOT, "tests", "golden", "example_segments.json.gz")
+    if not os.path.exists(p):
+        return None
+    segs = json.load(gzip.open(p))
+    E.set_default_engine(eng)
+
+    def once():
+        with contextlib.redirect_stdout(io.StringIO()):
+            proc = PP.preprocess_transcript(segs)
+            c = BC.BigChunkeroosky()
+            return c.postprocess_chunks(c.chunk_transcript(proc))
+
+    once(); once()
+    ts = []
+    for _ in range(10):
+        t0 = time.perf_counter()
+        r = once()
+        ts.append(time.perf_counter() - t0)
+    ms = 1e3 * sorted(ts)[5]
+    tok = sum(c["token_count"] for c in r)
+    return {"workload": "config 1: transcript-example.json (4778 segments) through preprocess_transcript + chunk_transcript + "
+                        "postprocess_chunks of the drop-in modules, dicts in and out", "ms": ms, "chunks": len(r), "tokens": tok,
+            "tokens_per_s": tok / (ms / 1e3)}
 
 
 def algorithmic_bytes(c):
@@ -247,6 +382,8 @@ def main():
     ap.add_argument("--config", type=int, default=3)
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--cpu-sample-mb", type=float, default=12.0)
+    ap.add_argument("--lexicon", type=int, default=0, help="draw words from an open vocabulary of this many forms (sensitivity run)")
+    ap.add_argument("--no-extra-configs", action="store_true", help="skip the sub-records of configs 2, 4, 5 and the open-vocabulary run")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-offsets64", action="store_true", help="upload the int64 segment offsets instead of int32 lengths")
     ap.add_argument("--e2e-repeats", type=int, default=3, help="repetitions of the K-step end-to-end leg (median reported)")
@@ -468,6 +605,15 @@ def main():
                          % (len(docs), nbytes / 1e6, dtc, "unmodified reference preprocessor.py + big_chunkeroosky.py "
                             "(tiktoken CoreBPE, nltk shim)" if is_ref else "oracle port (Python + tiktoken CoreBPE)")}
 
+    extra = None
+    if not args.no_extra_configs and args.config == 3 and not args.lexicon:
+        for w_eng, _ in workers[1:]:
+            w_eng.close()
+        torch.cuda.empty_cache()
+        extra = extra_configs(args, torch, dist if world > 1 else None, eng, dev, rank, world)
+        if rank == 0 and world == 1:
+            extra["config1_dropin"] = dropin_config1(eng)
+
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -478,6 +624,10 @@ def main():
                 "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline}
         if cpu:
             line["cpu_baseline"] = cpu
+        if extra:
+            line["configs"] = extra
+        line["counts"].update({"words": counts["n_words"], "words_first_sighting": counts["n_word_first"],
+                               "words_generic_matcher": counts["n_word_slow"]})
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

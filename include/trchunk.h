@@ -105,7 +105,11 @@ int trc_chunk(trc_ctx* ctx, const int32_t* doc_max_tokens, int32_t context_token
 enum {
   TRC_N_SEG = 0, TRC_N_KEPT, TRC_N_GROUPS, TRC_N_ITEMS, TRC_N_SUBS, TRC_N_CHUNKS, TRC_B_RAW, TRC_B_CLEAN,
   TRC_B_MERGED, TRC_B_TWC, TRC_TOKENS, TRC_N_DOC, TRC_N_LONG_SPANS, TRC_N_ERR_DOCS, TRC_N_SENT, TRC_N_GIANTS,
-  TRC_N_AGG, TRC_N_AGG_MEM, TRC_B_AGG, TRC_N_COUNTERS = 24
+  TRC_N_AGG, TRC_N_AGG_MEM, TRC_B_AGG,
+  TRC_N_WORDS,        /* whitespace-delimited words of the cleaned text that went through the word-level token counter */
+  TRC_N_WORD_FIRST,   /* of those: not found in the word cache / launch memo (first sightings -> packed-word matcher)  */
+  TRC_N_WORD_SLOW,    /* of those: left to the generic matcher + byte-pair merge (k_count_slow_words)                 */
+  TRC_N_COUNTERS = 24
 };
 int trc_get_counts(trc_ctx* ctx, int64_t* counts /* TRC_N_COUNTERS */);
 

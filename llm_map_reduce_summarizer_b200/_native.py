@@ -7,7 +7,8 @@ DEFAULT_LIB = os.environ.get("TRCHUNK_LIB") or os.path.join(_HERE, "libtrchunk.s
 
 TRC_MEM_HOST, TRC_MEM_DEVICE = 0, 1
 COUNTERS = ["n_seg", "n_kept", "n_groups", "n_items", "n_subs", "n_chunks", "b_raw", "b_clean", "b_merged", "b_twc",
-            "tokens", "n_doc", "n_long_spans", "n_err_docs", "n_sent", "n_giants", "n_agg", "n_agg_mem", "b_agg"]
+            "tokens", "n_doc", "n_long_spans", "n_err_docs", "n_sent", "n_giants", "n_agg", "n_agg_mem", "b_agg",
+            "n_words", "n_word_first", "n_word_slow"]
 N_COUNTERS = 24
 ARRAYS = ["K2R", "COFF", "CLEAN", "CTOK", "GSTART", "POFF", "MERGED", "GTS", "GTOK", "ITEM_GROUP", "ITEM_SUB", "ITEM_TOK",
           "ITEM_LEN", "ITEM_DST", "SUBS", "CHUNKS", "SPK_LIST", "TWC", "DOC_ERR", "GDOC_OFF", "CDOC_OFF", "CCHARS", "SENT", "PDST",

@@ -67,6 +67,7 @@ struct FuseArgs {
   unsigned long long* memo; uint32_t* memo_lock; uint32_t memo_mask;
   // second level of the look-back of k_clean_tok_w32: per group of 32 tiles an arrival counter and (status, value) words
   unsigned long long* grp_cnt; unsigned long long* grp_bytes; unsigned long long* grp_kept;
+  unsigned long long* wstat;        // [0] words through the word-level counter, [1] first sightings, [2] words left to the generic matcher
 };
 #define FUSE_PH(i) do { if (A.phase && tid == 0) { long long now_ = clock64(); atomicAdd(&A.phase[i], (unsigned long long)(now_ - ph_t)); ph_t = now_; } } while (0)
 
@@ -478,7 +479,17 @@ __global__ void __launch_bounds__(FUSE_T, 2) k_clean_tok_fused(TrcDev D, TrcTabl
   }
 }
 
-// kdoc_off[x] = first kept segment whose document is >= x   (sdoc is non-decreasing)
+// kdoc_off[x] = first kept segment whose document is >= x   (sdoc is non-decreasing).  One thread per kept segment:
+// where the document changes between j-1 and j, every document in (sdoc[j-1], sdoc[j]] starts at j.  Streams sdoc once
+// instead of a 21-step binary search per document.
+__global__ void k_doc_ranges_stream(const int32_t* __restrict__ sdoc, int64_t n_kept, int64_t* kdoc_off, int64_t n_doc) {
+  GSTRIDE(j, n_kept + 1) {
+    const int64_t a = j == 0 ? -1 : (int64_t)sdoc[j - 1];
+    const int64_t b = j == n_kept ? n_doc : (int64_t)sdoc[j];
+    for (int64_t x = a + 1; x <= b; ++x) kdoc_off[x] = j;
+  }
+}
+// (binary-search form, kept for the older fused kernels)
 __global__ void k_doc_ranges(const int32_t* __restrict__ sdoc, int64_t n_kept, int64_t* kdoc_off, int64_t n_doc) {
   GSTRIDE(x, n_doc + 1) {
     int64_t lo = 0, hi = n_kept;

@@ -467,7 +467,7 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
         }
         gbase = S.gbase; kbase = S.kbase;
         FUSE_PH(9);
-        if (A.phase && tid == 0) { atomicAdd(&A.phase[12], (unsigned long long)tot_words); atomicAdd(&A.phase[13], (unsigned long long)nmiss); atomicAdd(&A.phase[14], (unsigned long long)S.nslow); }
+        if (tid == 0) { atomicAdd(&A.wstat[0], (unsigned long long)tot_words); atomicAdd(&A.wstat[1], (unsigned long long)nmiss); atomicAdd(&A.wstat[2], (unsigned long long)S.nslow); }
         // words for the generic matcher: handed to k_count_slow_words (full occupancy) unless its list is full
         const int32_t nslow = S.nslow, nl = nslow < F5_SLOW_CAP ? nslow : F5_SLOW_CAP;
         if (tid == 0) {

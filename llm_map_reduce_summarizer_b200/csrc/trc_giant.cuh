@@ -24,6 +24,11 @@ struct GiantState {
   const int32_t* of_seg;            // per raw segment: giant index or -1 (n entries)
 };
 
+__global__ void k_giant_any(TrcDev D, unsigned long long* cnt) {
+  int found = 0;
+  GSTRIDE(i, D.n) found |= (D.seg_off[i + 1] - D.seg_off[i]) > TRC_GIANT_MIN;
+  if (__any_sync(0xffffffffu, found) && (threadIdx.x & 31) == 0) atomicAdd(cnt, 1ULL);
+}
 __global__ void k_giant_flag(TrcDev D, int32_t* flag) { GSTRIDE(i, D.n) flag[i] = (D.seg_off[i + 1] - D.seg_off[i]) > TRC_GIANT_MIN; }
 __global__ void k_giant_list(TrcDev D, const int32_t* __restrict__ flag, const int64_t* __restrict__ scan, int32_t* list, int64_t* len,
                              int32_t* of_seg) {

@@ -731,13 +731,15 @@ __global__ void k_emit_pieces_flat(TrcDev D) {
   for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; (q >> 3) < D.n_kept; q += (int64_t)gridDim.x * blockDim.x) {
     const int64_t j = q >> 3;
     const int lane = (int)(q & 7);
+    // everything that only depends on j is requested at once (the kernel is bound by dependent-load latency)
     const int64_t d = D.pdst[j];
-    if (d < 0) continue;
     const uint8_t f = D.pflag[j];
+    const int64_t c0 = D.coff[j], c1 = D.coff[j + 1];
+    const double st = D.start[D.k2r[j]];
+    if (d < 0) continue;
     uint8_t* dst = D.twc + d;
     int64_t o = 0;
     if (f & 1) {
-      const double st = D.start[D.k2r[j]];
       int64_t h; int m, sec;
       trc_ts_split(st, &h, &m, &sec);
       if (h <= 0) {                          // "[MM:SS] " is exactly eight bytes: every lane of the group writes one of them
@@ -756,8 +758,7 @@ __global__ void k_emit_pieces_flat(TrcDev D) {
         }
       }
     }
-    const int64_t c0 = D.coff[j];
-    const int64_t len = D.coff[j + 1] - c0;
+    const int64_t len = c1 - c0;
     const uint8_t* src = D.C + c0;
     uint8_t* db = dst + o;
     if ((f & 2) && lane == 7) db[len] = ' ';
@@ -922,6 +923,15 @@ static int giant_stage(trc_ctx* ctx, cudaStream_t st, int64_t braw, GiantView* V
   TrcDev& D = ctx->D;
   const int64_t n = D.n;
   int rc;
+  {                                            // most batches have none: one counting pass decides
+    unsigned long long* gcnt;
+    ALLOC(gcnt, unsigned long long, 1);
+    CK(cudaMemsetAsync(gcnt, 0, 8, st));
+    LAUNCH(k_giant_any, n, 256, D, gcnt);
+    int64_t any = 0;
+    if ((rc = read_back(ctx, st, gcnt, 8, &any))) return rc;
+    if (any == 0) return TRC_OK;
+  }
   int32_t* gflag; int64_t* gscan;
   ALLOC(gflag, int32_t, n); ALLOC(gscan, int64_t, n + 1);
   LAUNCH(k_giant_flag, n, 256, D, gflag);
@@ -1255,6 +1265,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       ALLOC(fz, unsigned long long, 2 * ntiles + 3 * ngroups + 32);
       CK(cudaMemsetAsync(fz, 0, 8 * (size_t)(2 * ntiles + 3 * ngroups + 32), st));
       A.tile_counter = fz; A.wl_cnt = fz + 2; A.totals = (int64_t*)(fz + 4); A.desc_bytes = fz + 32; A.desc_kept = fz + 32 + ntiles;
+      A.wstat = fz + 24;
       A.grp_cnt = fz + 32 + 2 * ntiles; A.grp_bytes = A.grp_cnt + ngroups; A.grp_kept = A.grp_bytes + ngroups;
       static const bool want_phases = getenv("TRCHUNK_PHASES") != nullptr;
       A.phase = want_phases ? fz + 8 : nullptr;
@@ -1300,8 +1311,9 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       prof_end(ctx, st);
       ctx->launches++;
       CK(cudaGetLastError());
-      unsigned long long h[6];
-      if ((rc = read_back(ctx, st, fz + 2, 48, h))) return rc;      // wl count, wl scratch, n_kept, bclean, -, slow words
+      unsigned long long h[25];
+      if ((rc = read_back(ctx, st, fz + 2, 200, h))) return rc;     // wl count, wl scratch, n_kept, bclean, -, slow words, ..., word statistics
+      ctx->counts[TRC_N_WORDS] = (int64_t)h[22]; ctx->counts[TRC_N_WORD_FIRST] = (int64_t)h[23]; ctx->counts[TRC_N_WORD_SLOW] = (int64_t)h[24];
       nk = (int64_t)h[2]; bclean = (int64_t)h[3];
       D.n_kept = nk;
       {
@@ -1336,7 +1348,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
                 100.0 * ph[6] / tot, 100.0 * ph[11] / tot, 100.0 * ph[9] / tot, 100.0 * ph[10] / tot, 100.0 * ph[7] / tot, 100.0 * ph[8] / tot);
       }
       j_h0 = h[0]; j_h1 = h[1]; j_fz = fz; j_wl = A.wl; j_wl_cap = A.wl_cap;      // long spans: launched at the join below
-      LAUNCH(k_doc_ranges, nd + 1, 128, D.sdoc, nk, D.kdoc_off, nd);
+      LAUNCH(k_doc_ranges_stream, nk + 1, 256, D.sdoc, nk, D.kdoc_off, nd);
     }
     ctx->counts[TRC_N_KEPT] = nk; ctx->counts[TRC_B_CLEAN] = bclean;
   } else

@@ -21,10 +21,12 @@ BASE_SEED = 20261106
 
 
 class _Atoms:
-    def __init__(self):
-        lex = json.load(open(os.path.join(_DATA, "lexicon.json")))
-        self.words = lex["words"]
-        p = np.array(lex["counts"], dtype=np.float64)
+    def __init__(self, words=None, p=None):
+        if words is None:
+            lex = json.load(open(os.path.join(_DATA, "lexicon.json")))
+            words = lex["words"]
+            p = np.array(lex["counts"], dtype=np.float64)
+        self.words = words
         self.p = p / p.sum()
         atoms = [w.encode() for w in self.words]
         self.na0 = len(atoms)
@@ -52,6 +54,55 @@ def _atoms():
     return _ATOMS
 
 
+_OPEN = {}
+
+
+def open_lexicon(n_forms, seed=BASE_SEED):
+    """An OPEN vocabulary of n_forms distinct word forms for the sensitivity bench (bench.py --lexicon N): the example's
+    5 390 words plus derived forms - capitalised / upper-cased, inflected, compounded, with digits (years, amounts,
+    identifiers), and 5 % non-ASCII (accents, CJK) - under a Zipf law, so that most running words are still common ones
+    but the tail never ends: many words miss the word cache and a good share needs byte-pair merging."""
+    key = (n_forms, seed)
+    if key in _OPEN:
+        return _OPEN[key]
+    base = _atoms().words
+    rng = np.random.Generator(np.random.PCG64(seed + 7))
+    forms, seen = list(base), set(base)
+    suffixes = ["s", "ed", "ing", "ly", "er", "ness", "able", "ism", "ize", "tion"]
+    accents = {"a": "á", "e": "é", "i": "ï", "o": "ö", "u": "ü", "n": "ñ", "c": "ç"}
+    cjk = "的一是不了人我在有他这为之大来以个中上们到说国和地也子时道出而要于就下得可你年生自会那后能对着事其里所去行过家十用发天如然作方成者多日都三小军二无同么经法当起与好看学进种将还分此心前面又定见只主没公从"
+    while len(forms) < n_forms:
+        k = int(rng.integers(0, 8))
+        w = base[int(rng.integers(0, len(base)))].strip(",.;:?!'\"") or "uh"
+        if k == 0:
+            f = w.capitalize()
+        elif k == 1:
+            f = w.upper()
+        elif k == 2:
+            f = w + suffixes[int(rng.integers(0, len(suffixes)))]
+        elif k == 3:
+            f = w + base[int(rng.integers(0, len(base)))].strip(",.;:?!'\"")
+        elif k == 4:
+            f = str(int(rng.integers(0, 10 ** int(rng.integers(1, 8)))))
+        elif k == 5:
+            f = w + str(int(rng.integers(0, 1000)))
+        elif k == 6:
+            f = "".join(accents.get(ch, ch) if rng.random() < 0.5 else ch for ch in w)
+            if f == w:
+                f = w + "é"
+        else:
+            f = "".join(cjk[int(rng.integers(0, len(cjk)))] for _ in range(int(rng.integers(1, 4))))
+        if rng.random() < 0.15:
+            f += [",", ".", "?", "!", ";", ":"][int(rng.integers(0, 6))]
+        if f not in seen:
+            seen.add(f); forms.append(f)
+    p = 1.0 / (np.arange(len(forms), dtype=np.float64) + 10.0)
+    order = np.concatenate([np.arange(len(base)), len(base) + rng.permutation(len(forms) - len(base))])
+    forms = [forms[i] for i in order]
+    _OPEN[key] = _Atoms(forms, p)
+    return _OPEN[key]
+
+
 def _gather(atom_ids, A):
     lens = A.len[atom_ids]
     dst = np.concatenate([[0], np.cumsum(lens)])
@@ -61,9 +112,9 @@ def _gather(atom_ids, A):
 
 
 def make_corpus(n_docs, seed, segs_per_doc=None, segs_mu=180.0, segs_sigma=0.6, words_lambda=9.8, n_speakers=2,
-                turn_mean=8.0, sec_per_word=0.36, artefacts=True):
+                turn_mean=8.0, sec_per_word=0.36, artefacts=True, atoms=None):
     """n_docs transcripts -> PackedBatch (originals=None: times are the float64 arrays themselves)."""
-    A = _atoms()
+    A = atoms if atoms is not None else _atoms()
     rng = np.random.Generator(np.random.PCG64(seed))
     if segs_per_doc is None:
         nseg = np.maximum(1, np.round(rng.lognormal(np.log(segs_mu), segs_sigma, n_docs))).astype(np.int64)
@@ -186,10 +237,14 @@ def add_monologues(batch, seed, n_mono, min_bytes=20000, max_bytes=80000, clause
     return PackedBatch(out, new_seg_off, start, end, batch.speaker, batch.doc_off, batch.speakers, None)
 
 
-def config(num, scale=1.0):
+def config(num, scale=1.0, lexicon=None):
     """The BASELINE.json configs 2-5 (config 1 is the example transcript fixture).
-    Returns (PackedBatch, per-document max_tokens array, description)."""
+    Returns (PackedBatch, per-document max_tokens array, description).  lexicon=N: config 3's shape with words drawn
+    from an open vocabulary of N forms (open_lexicon) instead of the example's 5 390."""
     seed = BASE_SEED + num
+    if lexicon:
+        b = make_corpus(int(10000 * scale), seed, n_speakers=2, atoms=open_lexicon(int(lexicon)))
+        return b, np.full(b.n_doc, 8000, dtype=np.int32), "10k podcast transcripts, open vocabulary of %d word forms, 8k-token chunks" % int(lexicon)
     if num == 2:
         b = make_corpus(1, seed, segs_per_doc=int(10000 * scale), words_lambda=3.0, n_speakers=4, turn_mean=8.0, sec_per_word=0.09)
         return b, np.full(1, 4000, dtype=np.int32), "1-hour 4-speaker meeting, 10k segments, 4k-token chunks"

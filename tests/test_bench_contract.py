@@ -30,7 +30,7 @@ import pytest
 @pytest.mark.gpu
 def test_device_arm_line():
     out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "3", "--warmup", "3", "--scale", "0.05",
-                          "--cpu-sample-mb", "0.3", "--e2e-repeats", "1"], check=True, capture_output=True, text=True, timeout=600).stdout
+                          "--cpu-sample-mb", "0.3", "--e2e-repeats", "1", "--no-extra-configs"], check=True, capture_output=True, text=True, timeout=600).stdout
     line = json.loads(out.strip().splitlines()[-1])
     for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline", "dtype",
               "data", "config", "clocks", "e2e", "gpu_launches", "roofline", "cpu_baseline"):
