@@ -536,17 +536,14 @@ def main():
             hb_, mt_, pin_ = parts[item % nparts]
             en.preprocess(hb_, want_merged_text=False, stream=stream.cuda_stream, seg_len32=None if args.e2e_offsets64 else pin_["seg_len32"].numpy())
             en.chunk(mt_, stream=stream.cuda_stream)
-            total = 0
             cn = en.counts()
-            for name, _ in OUT_ARRAYS:
-                if name == "K2R" and cn["n_kept"] == cn["n_seg"]:
-                    continue
-                nb = en.array_into(name, None, 0)
-                if name not in po or po[name].numel() < nb:
-                    po[name] = torch.empty(max(nb, 1) + max(nb, 1) // 8, dtype=torch.uint8).pin_memory()
-                if nb:
-                    en.array_into(name, po[name].data_ptr(), po[name].numel(), N.TRC_MEM_HOST, stream.cuda_stream)
-                total += nb
+            names = [name for name, _ in OUT_ARRAYS if not (name == "K2R" and cn["n_kept"] == cn["n_seg"])]
+            _, nb, slab = en.arrays_into(names, None, 0)            # layout only
+            if "slab" not in po or po["slab"].numel() < slab:
+                po["slab"] = torch.empty(slab + slab // 8 + 4096, dtype=torch.uint8).pin_memory()
+            # every result array of the step with ONE call: a copy per array into the pinned slab, one synchronisation
+            en.arrays_into(names, po["slab"].data_ptr(), po["slab"].numel(), N.TRC_MEM_HOST, stream.cuda_stream)
+            total = int(nb.sum())
             with qlock:
                 res[item % nparts] = total
 
@@ -584,7 +581,7 @@ def main():
     e2e = {"value": tokens_all * args.steps / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps,
            "ms_per_step_runs": [r / args.steps for r in runs],
-           "api": "trc_preprocess + trc_chunk + trc_get_array (C ABI, pinned host buffers); every step's documents go "
+           "api": "trc_preprocess + trc_chunk + trc_get_arrays (C ABI, pinned host buffers, one download call per step); every step's documents go "
                   "through as %d sub-batches taken in turn by %d contexts on %d host threads; timed with the host "
                   "clock around K steps" % (nparts, nctx, nctx)}
 

@@ -157,6 +157,17 @@ enum {
 int trc_get_array(trc_ctx* ctx, int which, void* dst, int64_t dst_bytes, int32_t memory, int64_t* nbytes,
                   void* stream);
 
+/* Several result arrays in one call, e.g. everything main.py:148-149 needs for its chunk dicts: array which[k] is
+ * copied to dst + offsets[k] (offsets chosen by the library, 256-byte aligned, returned together with the sizes);
+ * one copy per array and ONE stream synchronisation when dst is host memory.  dst == NULL: sizes only. */
+int trc_get_arrays(trc_ctx* ctx, const int32_t* which, int32_t n_which, void* dst, int64_t dst_bytes, int32_t memory,
+                   int64_t* offsets /* n_which */, int64_t* nbytes /* n_which */, int64_t* total_bytes, void* stream);
+
+/* preprocessor.py:91-107 format_timestamp == big_chunkeroosky.py:234-242 _format_time for n values with one small
+ * kernel: out24 receives n slots of 24 bytes, [length][characters].  The resident batch is not touched (the other
+ * scripts of the reference call _format_time per chunk: llm_executor.py:503, result_aggregator.py:569). */
+int trc_format_timestamps(trc_ctx* ctx, const double* seconds, int64_t n, uint8_t* out24, int32_t memory, void* stream);
+
 /* Record layouts of TRC_A_SUBS / TRC_A_CHUNKS / TRC_A_SENT (mirrored by ctypes.Structure in _native.py). */
 typedef struct {
   int32_t group, kind, r0, r1, start_src, end_src, tok, pad;

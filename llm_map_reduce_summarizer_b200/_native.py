@@ -44,7 +44,7 @@ AGG_MEM_DTYPE = [("group", "<i4"), ("n_pieces", "<i4"), ("piece0", "<i8"), ("tex
 
 EXPORTS = ["trc_create", "trc_destroy", "trc_last_error", "trc_load_tables", "trc_load_vocab", "trc_preprocess",
            "trc_chunk", "trc_aggregate", "trc_get_counts", "trc_get_array", "trc_count_tokens", "trc_last_stage_ms", "trc_kernel_launches", "trc_set_profiling",
-           "trc_get_profile", "trc_bpe_span_count_static", "trc_ingest_json", "trc_ingest_view", "trc_ingest_free", "trc_assemble_prompts"]
+           "trc_get_profile", "trc_get_arrays", "trc_format_timestamps", "trc_bpe_span_count_static", "trc_ingest_json", "trc_ingest_view", "trc_ingest_free", "trc_assemble_prompts"]
 
 
 def load_library(path=None):
@@ -68,6 +68,9 @@ def load_library(path=None):
         lib.trc_aggregate.argtypes = [vp, C.c_double, vp]
     lib.trc_get_counts.argtypes = [vp, vp]
     lib.trc_get_array.argtypes = [vp, C.c_int, vp, i64, i32, C.POINTER(i64), vp]
+    if hasattr(lib, "trc_get_arrays"):
+        lib.trc_get_arrays.argtypes = [vp, vp, i32, vp, i64, i32, vp, vp, C.POINTER(i64), vp]
+        lib.trc_format_timestamps.argtypes = [vp, vp, i64, vp, i32, vp]
     lib.trc_count_tokens.argtypes = [vp, vp, vp, i64, i32, i32, vp, vp, vp]
     lib.trc_last_stage_ms.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     lib.trc_kernel_launches.argtypes = [vp, C.POINTER(i64)]

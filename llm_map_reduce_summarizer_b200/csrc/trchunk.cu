@@ -1272,7 +1272,10 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       A.text_bytes = braw; A.seg_special = seg_special;
       A.wl_cap = (ccap + n) / (TRC_SHORT_SPAN + 1) + 1;          // logical bytes: every kept segment carries a virtual leading space
       ALLOC(A.wl, LongEntry, A.wl_cap);
-      A.sl_cap = 2 * n + 1024; A.sl_cnt = fz + 7;
+      // words that need the generic matcher: open-vocabulary text sends a quarter of its words there, so the list is sized
+      // by the most words the text can hold (a word and its separator take at least three bytes on average); past it,
+      // tiles count their words in place
+      A.sl_cap = braw / 3 + 2 * n + 1024; A.sl_cnt = fz + 7;
       ALLOC(A.sl, SlowWord, A.sl_cap);
       A.memo = nullptr; A.memo_lock = nullptr; A.memo_mask = 0;
       if (ctx->use_memo && gen >= 3) {
@@ -1707,6 +1710,66 @@ extern "C" int trc_get_array(trc_ctx* ctx, int which, void* dst, int64_t dst_byt
   CK(cudaMemcpyAsync(dst, a.p, (size_t)a.bytes, memory == TRC_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, st));
   if (memory == TRC_MEM_HOST) CK(cudaStreamSynchronize(st));
   return TRC_OK;
+}
+
+// Several result arrays in ONE call: array which[k] lands at dst + offsets[k] (offsets are chosen here, 256-byte
+// aligned, and returned); one cudaMemcpyAsync per array and a single stream synchronisation at the end when the
+// destination is host memory.  With dst == NULL only the offsets and the total size are computed.
+extern "C" int trc_get_arrays(trc_ctx* ctx, const int32_t* which, int32_t n_which, void* dst, int64_t dst_bytes, int32_t memory,
+                              int64_t* offsets, int64_t* nbytes, int64_t* total_bytes, void* stream) {
+  if (!ctx || !which || n_which < 0 || !offsets || !nbytes) return TRC_EINVAL;
+  if (!ctx->have_pre) { ctx->err = "no batch resident"; return TRC_EINVAL; }
+  int64_t off = 0;
+  for (int32_t k = 0; k < n_which; ++k) {
+    if (which[k] < 0 || which[k] >= TRC_A__COUNT) { ctx->err = "unknown array"; return TRC_EINVAL; }
+    const trc_ctx::Arr& a = ctx->arr[which[k]];
+    if (!a.p && a.bytes > 0) { ctx->err = "array not produced by the stages run so far"; return TRC_EINVAL; }
+    offsets[k] = off; nbytes[k] = a.bytes;
+    off += (a.bytes + 255) & ~(int64_t)255;
+  }
+  if (total_bytes) *total_bytes = off;
+  if (!dst) return TRC_OK;
+  if (dst_bytes < off) { ctx->err = "destination too small"; return TRC_EINVAL; }
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : ctx->own_stream;
+  const cudaMemcpyKind kind = memory == TRC_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
+  for (int32_t k = 0; k < n_which; ++k)
+    if (nbytes[k] > 0) CK(cudaMemcpyAsync((char*)dst + offsets[k], ctx->arr[which[k]].p, (size_t)nbytes[k], kind, st));
+  if (memory == TRC_MEM_HOST) CK(cudaStreamSynchronize(st));
+  return TRC_OK;
+}
+
+// format_timestamp / _format_time for n values with one small kernel (preprocessor.py:91-107 ==
+// big_chunkeroosky.py:234-242).  out: n slots of 24 bytes, [length][characters].  Does not touch the resident batch.
+__global__ void k_format_ts(const double* __restrict__ sec, int64_t n, uint8_t* __restrict__ out) {
+  GSTRIDE(i, n) { uint8_t* o = out + 24 * i; o[0] = (uint8_t)trc_fmt_ts(sec[i], o + 1); }
+}
+extern "C" int trc_format_timestamps(trc_ctx* ctx, const double* seconds, int64_t n, uint8_t* out24, int32_t memory, void* stream) {
+  if (!ctx || n < 0 || (n > 0 && (!seconds || !out24))) return TRC_EINVAL;
+  if (n == 0) return TRC_OK;
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : ctx->own_stream;
+  const double* d_sec = seconds; uint8_t* d_out = out24;
+  void* tmp = nullptr;
+  if (memory == TRC_MEM_HOST) {                       // a short-lived allocation of its own: the arena keeps the resident batch
+    CK(cudaMalloc(&tmp, (size_t)n * 32));
+    d_sec = (const double*)tmp; d_out = (uint8_t*)tmp + 8 * (size_t)n;
+    if (cudaMemcpyAsync(tmp, seconds, 8 * (size_t)n, cudaMemcpyHostToDevice, st) != cudaSuccess) { cudaFree(tmp); ctx->err = "copy of the timestamps failed"; return TRC_ECUDA; }
+  }
+#ifdef TRC_HOSTSIM
+  k_format_ts(d_sec, n, d_out);
+#else
+  k_format_ts<<<grid_for(n, 128), 128, 0, st>>>(d_sec, n, d_out);
+#endif
+  ctx->launches++;
+  int rc = TRC_OK;
+  if (memory == TRC_MEM_HOST) {
+    if (cudaMemcpyAsync(out24, d_out, 24 * (size_t)n, cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) {
+      ctx->err = "copy of the formatted timestamps failed"; rc = TRC_ECUDA;
+    }
+    cudaFree(tmp);
+  } else if (cudaGetLastError() != cudaSuccess) { ctx->err = "k_format_ts launch failed"; rc = TRC_ECUDA; }
+  return rc;
 }
 
 extern "C" int trc_last_stage_ms(trc_ctx* ctx, float* pre, float* chk) {

@@ -332,6 +332,25 @@ class Engine:
         self._check(self.lib.trc_get_array(self.h, N.A[name], dst_ptr, dst_bytes, memory, C.byref(nb), stream))
         return nb.value
 
+    def arrays_into(self, names, dst_ptr, dst_bytes, memory=N.TRC_MEM_HOST, stream=None):
+        """Several result arrays with ONE call and one synchronisation (trc_get_arrays).  Returns (offsets, sizes,
+        total); with dst_ptr None only the layout is computed."""
+        which = np.array([N.A[n] for n in names], dtype=np.int32)
+        off = np.zeros(len(names), dtype=np.int64)
+        nb = np.zeros(len(names), dtype=np.int64)
+        tot = C.c_int64()
+        self._check(self.lib.trc_get_arrays(self.h, which.ctypes.data, len(names), dst_ptr, dst_bytes, memory, off.ctypes.data,
+                                            nb.ctypes.data, C.byref(tot), stream))
+        return off, nb, tot.value
+
+    def format_timestamps(self, seconds):
+        """format_timestamp / _format_time of many values with one kernel launch; the resident batch stays resident."""
+        x = np.ascontiguousarray(np.array(list(seconds), dtype=np.float64))
+        out = np.zeros(24 * max(len(x), 1), dtype=np.uint8)
+        self._check(self.lib.trc_format_timestamps(self.h, x.ctypes.data, len(x), out.ctypes.data, N.TRC_MEM_HOST, None))
+        raw = out.tobytes()
+        return [raw[24 * i + 1:24 * i + 1 + raw[24 * i]].decode("ascii") for i in range(len(x))]
+
     def stage_ms(self):
         a, b = C.c_float(), C.c_float()
         self._check(self.lib.trc_last_stage_ms(self.h, C.byref(a), C.byref(b)))

@@ -70,12 +70,9 @@ def clean_text(text: str) -> str:
 
 
 def format_timestamp(seconds: float) -> str:
-    """preprocessor.py:91-107 (formatted on the device; see trc_format.cuh)."""
-    eng = _eng.default_engine()
-    batch = _eng.pack_documents([[{"start": seconds, "end": seconds, "text": "x", "speaker": ""}]])
-    eng.preprocess(batch, merge_same_speaker=False, want_merged_text=False)
-    g = eng.array("GTS", "u1").tobytes()
-    return g[1:1 + g[0]].decode("ascii")
+    """preprocessor.py:91-107: one small kernel (trc_format_timestamps, trc_format.cuh); the resident batch is not
+    disturbed.  int() of the reference: truncation toward zero, bool is an int, NaN / infinity raise as in Python."""
+    return _eng.default_engine().format_timestamps(_eng._finite_f64([seconds]))[0]
 
 
 def combine_same_speaker_segments(segments: List[Dict[Any, Any]], max_duration: Optional[int] = 120,

@@ -68,3 +68,69 @@ def test_single_speaker_uncapped_is_linear(gpu_engine):
     dt = time.perf_counter() - t0
     assert c["n_groups"] == 1 and c["n_kept"] == n
     assert dt < 0.5, dt
+
+
+def test_save_chunks_records_and_timestamps_cuda(gpu_engine, tmp_path):
+    """--save-chunks records (main.py:178-201) from the CUDA engine's chunks equal those from the oracle's chunks;
+    format_timestamp / _format_time run as one small kernel and leave the resident batch resident."""
+    import json
+    from conftest import load_golden, quiet
+    from llm_map_reduce_summarizer_b200 import big_chunkeroosky as BC, egress, preprocessor as PP
+    from oracle import chunker as OC, preprocess as OP
+    E.set_default_engine(gpu_engine)
+    segs = load_golden("example_segments.json.gz")
+    with quiet():
+        proc = PP.preprocess_transcript(segs)
+        serial = gpu_engine.batch_serial
+        c = BC.BigChunkeroosky(max_tokens_per_chunk=2000)
+        assert [c._format_time(x) for x in (0, 59.999, 3600, -1, 360000)] == ["00:00", "00:59", "01:00:00", "59:59", "100:00:00"]
+        assert gpu_engine.batch_serial == serial                      # the helper did not evict the batch
+        chunks = c.postprocess_chunks(c.chunk_transcript(proc))
+    want = OC.ChunkerOracle(2000).chunk(OP.preprocess(segs))
+    a, b = tmp_path / "a.json", tmp_path / "b.json"
+    egress.save_chunk_records(chunks, str(a), timestamp="t")
+    egress.save_chunk_records(want, str(b), timestamp="t")
+    assert open(a).read() == open(b).read()
+    assert len(json.load(open(a))["chunks"]) == len(want) > 10
+    assert gpu_engine.format_timestamps([1e6, 26561.26, True]) == ["277:46:40", "07:22:41", "00:01"]
+
+
+def test_multi_gpu_single_process(gpu_engine):
+    """shard.MultiGpu: one process, every visible GPU, documents cut by bytes; the shards' results are the single-GPU
+    results of the same documents."""
+    import torch
+    from llm_map_reduce_summarizer_b200 import shard as SH, synth
+    b, mt, _ = synth.config(5, 0.01)
+    ndev = torch.cuda.device_count()
+    mg = SH.MultiGpu(devices=list(range(ndev)) if ndev > 1 else [0, 0])      # two contexts on one GPU when there is only one
+    try:
+        res = mg.run(b, mt, fetch=True)
+        assert [r["docs"] for r in res] == SH.shard_ranges(b, len(res)) and res[0]["docs"][0] == 0 and res[-1]["docs"][1] == b.n_doc
+        gpu_engine.preprocess(b)
+        gpu_engine.chunk(mt)
+        whole = gpu_engine.fetch_chunks()["chunks"]
+        got = np.concatenate([r["chunks"]["chunks"]["token_count"] for r in res if "chunks" in r])
+        assert (got == whole["token_count"]).all()
+        assert sum(r["counts"]["tokens"] for r in res if "counts" in r) == gpu_engine.counts()["tokens"]
+    finally:
+        mg.close()
+
+
+def test_published_punkt_examples_through_the_sentence_kernels(gpu_engine):
+    """The nltk examples of tests/test_oracle_golden.py as over-budget segments: the CUDA sentence path
+    (k_punkt_breaks and the sentence greedy) must cut them where the restated Punkt does."""
+    import parity_common as pc
+    from oracle import chunker as OC, preprocess as OP
+    texts = ['(How does it deal with this parenthesis?)  "It should be part of the\nprevious sentence." "(And the same with this one.)" '
+             '(\'And this one!\')\n"(\'(And (this)) \'?)" [(and this. )]',
+             "this is a test. . new sentence.", "This. . . That", "This..... That", "This... That", "This.. . That", "This. .. That",
+             "This. ,. That", "This!!! That", "This! That", "1. This is R .\n2. This is A .\n3. That's all",
+             "1. This is R .\t2. This is A .\t3. That's all", "Hello.\tThere", "Very bad acting!!! I promise.",
+             "Punkt knows that the periods in Mr. Smith and Johann S. Bach\ndo not mark sentence boundaries.  And sometimes sentences\n"
+             "can start with non-capitalized words.  i is a good variable\nname."]
+    for t in texts:
+        segs = [{"start": 0.0, "end": 60.0, "text": t, "speaker": "A"}]
+        for mx in (153, 156, 170):
+            proc, chunks = pc.run_dropin(gpu_engine, segs, mx)
+            want = OC.ChunkerOracle(mx).chunk(OP.preprocess(segs))
+            assert pc.same(chunks, want), (t, mx)

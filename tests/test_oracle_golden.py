@@ -90,3 +90,39 @@ def test_punkt_documented_examples():
     assert p.tokenize("J. Bach wrote it. He left.") == ["J. Bach wrote it.", "He left."]
     assert p.tokenize('He said "No." Then left') == ['He said "No."', "Then left"]
     assert p.tokenize("Ok... fine. 3.5 is. 3. then x") == ["Ok... fine.", "3.5 is.", "3. then x"]
+
+
+def test_punkt_examples_published_with_nltk():
+    """Examples that ship with nltk 3.8.1 and do not depend on trained parameters (no abbreviation, collocation or
+    sentence-starter decision is involved, so the pre-trained English model and the untrained tokenizer the reference
+    constructs agree on them): the realignment example of the nltk/tokenize/punkt.py module docstring, with and
+    without realign_boundaries, and the cases of nltk/test/unit/test_tokenize.py::test_sent_tokenize.  Restated from
+    the published sources (nltk is not installable here), so the Punkt row stays "parity unpinned" - these widen
+    the external evidence from one example to fifteen."""
+    p = punkt.PunktSentenceTokenizer()
+    text = ('(How does it deal with this parenthesis?)  "It should be part of the\nprevious sentence." '
+            '"(And the same with this one.)" (\'And this one!\')\n"(\'(And (this)) \'?)" [(and this. )]')
+    assert p.tokenize(text) == ['(How does it deal with this parenthesis?)', '"It should be part of the\nprevious sentence."',
+                                '"(And the same with this one.)"', "('And this one!')", '"(\'(And (this)) \'?)"', '[(and this. )]']
+    assert p.tokenize(text, realign_boundaries=False) == [
+        '(How does it deal with this parenthesis?', ')  "It should be part of the\nprevious sentence.', '" "(And the same with this one.',
+        ')" (\'And this one!', '\')\n"(\'(And (this)) \'?', ')" [(and this.', ')]']
+    for t, want in [("this is a test. . new sentence.", ["this is a test.", ".", "new sentence."]),
+                    ("This. . . That", ["This.", ".", ".", "That"]),
+                    ("This..... That", ["This..... That"]),
+                    ("This... That", ["This... That"]),
+                    ("This.. . That", ["This.. .", "That"]),
+                    ("This. .. That", ["This.", ".. That"]),
+                    ("This. ,. That", ["This.", ",.", "That"]),
+                    ("This!!! That", ["This!!!", "That"]),
+                    ("This! That", ["This!", "That"]),
+                    ("1. This is R .\n2. This is A .\n3. That's all", ["1.", "This is R .", "2.", "This is A .", "3.", "That's all"]),
+                    ("1. This is R .\t2. This is A .\t3. That's all", ["1.", "This is R .", "2.", "This is A .", "3.", "That's all"]),
+                    ("Hello.\tThere", ["Hello.", "There"])]:
+        assert p.tokenize(t) == want, t
+    # the module docstring's first example needs the trained abbreviation "Mr."; untrained, the same rules split after it
+    # and keep the initial "S." with "Bach" (A.8: is_initial + upper-case next token)
+    t2 = ("Punkt knows that the periods in Mr. Smith and Johann S. Bach\ndo not mark sentence boundaries.  And sometimes sentences\n"
+          "can start with non-capitalized words.  i is a good variable\nname.")
+    assert p.tokenize(t2) == ["Punkt knows that the periods in Mr.", "Smith and Johann S. Bach\ndo not mark sentence boundaries.",
+                              "And sometimes sentences\ncan start with non-capitalized words.", "i is a good variable\nname."]
