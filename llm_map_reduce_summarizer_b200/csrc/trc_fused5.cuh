@@ -124,6 +124,40 @@ __device__ __forceinline__ int f5_memo_hit(const ulonglong2& e, uint64_t lo, uin
   return (e.x == lo && (e.y & 0x00ffffffffffffffULL) == hi && (e.y >> 56)) ? (int)(e.y >> 56) - 1 : -1;
 }
 
+// Decoupled look-back over BOTH descriptor rows at once (cleaned bytes, kept segments): the two loads of a round are in
+// flight together, so the resolve costs the round trips of one row.  Each row keeps its own "inclusive prefix found" state.
+__device__ __forceinline__ void f5_resolve2(unsigned long long* db, unsigned long long* dk, unsigned tile, long long agg_b, long long agg_k,
+                                            int lane, long long* out_b, long long* out_k) {
+  long long eb = 0, ek = 0;
+  if (tile > 0) {
+    bool done_b = false, done_k = false;
+    long long idx = (long long)tile - 1;
+    while (!(done_b && done_k)) {
+      const long long my = idx - lane;
+      unsigned long long vb = (2ULL << 62), vk = (2ULL << 62);
+      if (my >= 0) {
+        vb = ld_relaxed(&db[my]); vk = ld_relaxed(&dk[my]);
+        while ((vb >> 62) == 0) vb = ld_relaxed(&db[my]);
+        while ((vk >> 62) == 0) vk = ld_relaxed(&dk[my]);
+      }
+      const unsigned b2 = __ballot_sync(0xffffffffu, (vb >> 62) == 2), k2 = __ballot_sync(0xffffffffu, (vk >> 62) == 2);
+      const int fb = b2 ? __ffs(b2) - 1 : 31, fk = k2 ? __ffs(k2) - 1 : 31;
+      long long cb = (!done_b && lane <= fb) ? (long long)(vb & ((1ULL << 62) - 1)) : 0;
+      long long ck = (!done_k && lane <= fk) ? (long long)(vk & ((1ULL << 62) - 1)) : 0;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) { cb += __shfl_xor_sync(0xffffffffu, cb, o); ck += __shfl_xor_sync(0xffffffffu, ck, o); }
+      eb += cb; ek += ck;
+      done_b = done_b || b2 != 0; done_k = done_k || k2 != 0;
+      idx -= 32;
+    }
+    if (lane == 0) {
+      st_relaxed(&db[tile], (2ULL << 62) | (unsigned long long)(eb + agg_b));
+      st_relaxed(&dk[tile], (2ULL << 62) | (unsigned long long)(ek + agg_k));
+    }
+  }
+  *out_b = eb; *out_k = ek;
+}
+
 __device__ __forceinline__ int f5_seg_of_word(const F5Smem& S, int ns, int32_t w) {
   int lo = 0, hi = ns;
   while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if ((int32_t)S.wfirst[mid] <= w) lo = mid; else hi = mid; }
@@ -387,6 +421,9 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
         FUSE_PH(6);
         // ---- P7: tokens, word by word
         uint8_t* const cnt = S.u.t.cnt; uint16_t* const miss = S.u.t.miss; uint16_t* const slow = S.u.t.slow;
+        // one pass: the CTA's word cache (shared memory), then the launch memo (L2, two ways in one 32-byte sector).  (Queueing
+        // the memo probes so that they go out in one round was slower: the second key build costs more than the latency,
+        // which 32 resident warps already hide.)
         for (int32_t wb = 0; wb < tot_words; wb += F5_T) {
           const int32_t w = wb + tid;
           int mc = -2;                                 // -2 no word, -1 unknown, >= 0 count, F3_MEMO_SLOW: generic matcher
@@ -446,8 +483,8 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
           if (wid < F5_MATCH_T / 32) match_words(tid, F5_MATCH_T);
           else {
             if (wid == F5_MATCH_T / 32) {
-              long long gb = fuse_resolve(A.desc_bytes, tile, tot_out, lane);
-              long long kb = fuse_resolve(A.desc_kept, tile, tot_kept, lane);
+              long long gb, kb;
+              f5_resolve2(A.desc_bytes, A.desc_kept, tile, tot_out, tot_kept, lane, &gb, &kb);
               if (lane == 0) { S.gbase = gb; S.kbase = kb; }
             }
             asm volatile("bar.sync 1, %0;" ::"n"(F5_T - F5_MATCH_T) : "memory");
@@ -458,8 +495,8 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
           match_words(tid, F5_T);
           __syncthreads();
           if (wid == 0) {
-            long long gb = fuse_resolve(A.desc_bytes, tile, tot_out, lane);
-            long long kb = fuse_resolve(A.desc_kept, tile, tot_kept, lane);
+            long long gb, kb;
+            f5_resolve2(A.desc_bytes, A.desc_kept, tile, tot_out, tot_kept, lane, &gb, &kb);
             if (lane == 0) { S.gbase = gb; S.kbase = kb; }
           }
           __syncthreads();
@@ -525,8 +562,8 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
       } else {
         // too many words for the list: write the tile out and count per segment
         if (wid == 0) {
-          long long gb = fuse_resolve(A.desc_bytes, tile, tot_out, lane);
-          long long kb = fuse_resolve(A.desc_kept, tile, tot_kept, lane);
+          long long gb, kb;
+          f5_resolve2(A.desc_bytes, A.desc_kept, tile, tot_out, tot_kept, lane, &gb, &kb);
           if (lane == 0) { S.gbase = gb; S.kbase = kb; }
         }
         __syncthreads();

@@ -620,6 +620,25 @@ __global__ void k_group_flag_nocap(TrcDev D) { GSTRIDE(j, D.n_kept) trc_group_fl
 __global__ void k_orbit(const int64_t* __restrict__ range_off, const int32_t* __restrict__ nxt, int32_t* flag, int64_t n_doc) {
   GSTRIDE(x, n_doc) trc_orbit_walk(range_off, nxt, flag, x);
 }
+#ifndef TRC_HOSTSIM
+// Orbit of ONE long chain (a single huge document: config 4 walks 10 k chunk starts one after the other).  The hops are a
+// dependent chain whatever is done, so the link array is staged in shared memory first (coalesced, by the whole block)
+// and one thread walks it there: ~30 cycles per hop instead of an L2 round trip.  Ranges of up to ORBIT_SMEM links.
+#define ORBIT_SMEM 49152
+__global__ void __launch_bounds__(1024) k_orbit_staged(const int64_t* __restrict__ range_off, const int32_t* __restrict__ nxt, int32_t* flag, int64_t n_doc) {
+  extern __shared__ int32_t s_nxt[];
+  for (int64_t x = blockIdx.x; x < n_doc; x += gridDim.x) {
+    const int64_t a = range_off[x], b = range_off[x + 1];
+    const int64_t n = b - a;
+    if (n <= 0) continue;
+    if (n > ORBIT_SMEM) { if (threadIdx.x == 0) trc_orbit_walk(range_off, nxt, flag, x); continue; }
+    for (int64_t k = threadIdx.x; k < n; k += blockDim.x) s_nxt[k] = (int32_t)(nxt[a + k] - a);
+    __syncthreads();
+    if (threadIdx.x == 0) { int32_t p = 0; while (p < n) { flag[a + p] = 1; p = s_nxt[p]; } }
+    __syncthreads();
+  }
+}
+#endif
 __global__ void k_scatter_starts(const int32_t* __restrict__ flag, const int64_t* __restrict__ scan, int32_t* starts, int64_t n) {
   GSTRIDE(j, n) {
     if (flag[j]) starts[scan[j]] = (int32_t)j;
@@ -826,6 +845,29 @@ static void prof_collect(trc_ctx* ctx) {
   } while (0)
 #endif
 #define LAUNCH_W(kern, nwarps, ...) LAUNCH(kern, (nwarps) * 32, 256, __VA_ARGS__)
+
+// Orbit marking: a thread per document, or - few documents with long chains - a block per document that stages the
+// links in shared memory (k_orbit_staged).
+static int orbit_marks(trc_ctx* ctx, cudaStream_t st, const int64_t* range_off, const int32_t* nxt, int32_t* flag, int64_t n_doc, int64_t n_links) {
+#ifndef TRC_HOSTSIM
+  if (n_doc > 0 && n_doc <= 64 && n_links >= 2048 * n_doc) {
+    static bool attr_done[64] = {false};
+    if (!attr_done[ctx->device & 63]) {
+      CK(cudaFuncSetAttribute(k_orbit_staged, cudaFuncAttributeMaxDynamicSharedMemorySize, ORBIT_SMEM * 4));
+      attr_done[ctx->device & 63] = true;
+    }
+    prof_begin(ctx, st, "k_orbit_staged");
+    k_orbit_staged<<<(unsigned)n_doc, 1024, ORBIT_SMEM * 4, st>>>(range_off, nxt, flag, n_doc);
+    prof_end(ctx, st);
+    ctx->launches++;
+    CK(cudaGetLastError());
+    return TRC_OK;
+  }
+#endif
+  (void)n_links;
+  LAUNCH(k_orbit, n_doc, 64, range_off, nxt, flag, n_doc);
+  return TRC_OK;
+}
 
 // Small counter reads.  A tiny kernel stores the words into mapped pinned memory instead of a D2H copy: a copy
 // would queue on the copy engine behind the bulk result transfers of other contexts working on the same GPU
@@ -1412,7 +1454,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
     LAUNCH(k_group_flag_nocap, nk, 256, D);
   } else {
     LAUNCH(k_merge_next, nk, 256, D);
-    LAUNCH(k_orbit, nd, 64, D.kdoc_off, D.mnxt, D.gflag, nd);
+    if ((rc = orbit_marks(ctx, st, D.kdoc_off, D.mnxt, D.gflag, nd, nk))) return rc;
   }
   if ((rc = scan_excl(ctx, st, D.gflag, D.gscan, nk))) return rc;
   // (the number of merged segments is only needed on the host after the piece layout: gstart is sized by its
@@ -1622,7 +1664,7 @@ extern "C" int trc_chunk(trc_ctx* ctx, const int32_t* doc_max_tokens, int32_t co
   ALLOC(D.pnxt, int32_t, ni); ALLOC(D.cflag, int32_t, ni); ALLOC(D.cscanf, int64_t, ni + 1);
   LAUNCH(k_pack_next, ni, 256, D, forced_pos, nforced);
   CK(cudaMemsetAsync(D.cflag, 0, 4 * (size_t)(ni > 0 ? ni : 1), st));
-  LAUNCH(k_orbit, nd, 64, D.idoc_off, D.pnxt, D.cflag, nd);
+  if ((rc = orbit_marks(ctx, st, D.idoc_off, D.pnxt, D.cflag, nd, ni))) return rc;
   if ((rc = scan_excl(ctx, st, D.cflag, D.cscanf, ni))) return rc;
   int64_t nc = 0;
   if (ni) { if ((rc = read_back(ctx, st, D.cscanf + ni, 8, &nc))) return rc; }
