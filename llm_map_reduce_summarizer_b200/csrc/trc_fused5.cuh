@@ -59,6 +59,7 @@ struct F5Smem {
   uint32_t tot_os, tot_tb;
   int32_t nmiss, nslow, flag, sfflag;
   unsigned int tile;
+  long long next_raw[2];                        // the tile's seg_off[s0], seg_off[s0 + ns], loaded once by thread 0
   int32_t doc0;
   long long gbase, kbase, slbase;
   alignas(8) unsigned long long mbar;
@@ -188,13 +189,24 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
   __syncthreads();
   long long ph_t = clock64();
   for (;;) {
-    if (tid == 0) S.tile = (unsigned int)atomicAdd(A.tile_counter, 1ULL);
+    // (Claiming the next tile ahead - during the matcher phase, with its byte range - was measured twice: no gain on uniform
+    // tiles, the other CTAs of the SM already cover the claim's round trips, and 1.3 -> 4.2 ms on config 4, where a tile id
+    // held back behind slow-lane tiles stalls the look-back of every later tile.  Tiles are claimed when they are started.)
+    if (tid == 0) {
+      const unsigned t = (unsigned int)atomicAdd(A.tile_counter, 1ULL);
+      S.tile = t;
+      if ((int64_t)t < ntiles) {
+        const int64_t q0 = (int64_t)t * tsegs;
+        const int64_t qn = (D.n - q0) < tsegs ? (D.n - q0) : tsegs;
+        S.next_raw[0] = D.seg_off[q0]; S.next_raw[1] = D.seg_off[q0 + qn];
+      }
+    }
     __syncthreads();
     const unsigned tile = S.tile;
     if ((int64_t)tile >= ntiles) break;
     const int64_t s0 = (int64_t)tile * tsegs;
     const int ns = (int)((D.n - s0) < tsegs ? (D.n - s0) : tsegs);
-    const int64_t raw0 = D.seg_off[s0], raw1 = D.seg_off[s0 + ns];
+    const int64_t raw0 = S.next_raw[0], raw1 = S.next_raw[1];
     const int al = (int)(raw0 & 15);
     const int64_t base = raw0 - al;
     const bool fast_in = (raw1 - base) <= F5_IN_CAP;
