@@ -256,7 +256,8 @@ TRC_HD void trc_build_items(const TrcDev& D, int64_t g) {
 // ---- C3: greedy packing, big_chunkeroosky.py:86-137 ------------------------------------
 // pnxt[a] = first item t > a with W[t+1] - W[a] > E (binary search over the integer prefix sums), cut at
 // the next forced break (first sub-item of an over-budget segment) and at the document end.
-TRC_HD void trc_pack_next(const TrcDev& D, const int64_t* forced_pos, int64_t n_forced, int64_t a) {
+TRC_HD void trc_pack_next(const TrcDev& D, const int64_t* forced_pos, const int64_t* n_forced_ptr, int64_t a) {
+  const int64_t n_forced = *n_forced_ptr;            // counted on the device: no host round trip for it
   int32_t x = D.sdoc[D.gstart[D.it_group[a]]];
   int64_t hi = D.idoc_off[x + 1];
   int64_t E = D.doc_E[x];

@@ -496,12 +496,20 @@ __global__ void k_count_units(TrcTables T, const uint32_t* __restrict__ byte_id,
 #ifndef TRC_HOSTSIM
 // Byte-pair merge of one long span per block; the four work arrays live in global scratch.
 #define LONG_T 256
-__global__ void __launch_bounds__(LONG_T) k_bpe_long(TrcTables T, const uint32_t* __restrict__ byte_id, const uint8_t* __restrict__ bytes,
-                                                     const int64_t* __restrict__ ustart, const int64_t* __restrict__ uend, int vs,
-                                                     uint32_t* counts, const LongEntry* __restrict__ wl, int64_t n_entries,
-                                                     uint32_t* __restrict__ scratch /* 4 words per span byte */, int64_t scratch_total) {
-  __shared__ unsigned long long s_red[LONG_T / 32];
+#define LONGB_T 1024                     // threads of the long-span block = most chunks a span is cut into
+#define LONGB_CAND 2048                  // rank-r pairs one round can take through the short list
+__global__ void __launch_bounds__(LONGB_T) k_bpe_long(TrcTables T, const uint32_t* __restrict__ byte_id, const uint8_t* __restrict__ bytes,
+                                                      const int64_t* __restrict__ ustart, const int64_t* __restrict__ uend, int vs,
+                                                      uint32_t* counts, const LongEntry* __restrict__ wl, int64_t n_entries,
+                                                      uint32_t* __restrict__ scratch /* 4 words per span byte */, int64_t scratch_total) {
+  __shared__ unsigned long long s_red[LONGB_T / 32];
   __shared__ unsigned long long s_best;
+  __shared__ unsigned long long s_cm[LONGB_T];          // per chunk: smallest (rank << 32 | position)
+  __shared__ int32_t s_cand[LONGB_CAND];
+  __shared__ uint8_t s_dirty[LONGB_T];
+  __shared__ int s_ncand, s_cnt, s_bad;
+  const uint32_t SEL = 0x80000000u, IDM = 0x7fffffffu;  // token ids stay below 2^21: the top bit marks a pair taken this round
+  const int tid = threadIdx.x;
   for (int64_t w = blockIdx.x; w < n_entries; w += gridDim.x) {
     const LongEntry e = wl[w];
     TrcStr S; S.p = bytes + ustart[e.unit]; S.vs = vs; S.n = uend[e.unit] - ustart[e.unit] + vs;
@@ -510,41 +518,125 @@ __global__ void __launch_bounds__(LONG_T) k_bpe_long(TrcTables T, const uint32_t
     uint32_t* rk = scratch + scratch_total + e.scratch_off;
     int32_t* nx = (int32_t*)(scratch + 2 * scratch_total + e.scratch_off);
     int32_t* pv = (int32_t*)(scratch + 3 * scratch_total + e.scratch_off);
-    for (int64_t i = threadIdx.x; i < len; i += LONG_T) { id[i] = byte_id[S.at(e.lstart + i)]; nx[i] = (int32_t)(i + 1); pv[i] = (int32_t)(i - 1); }
-    __syncthreads();
-    for (int64_t i = threadIdx.x; i < len; i += LONG_T) rk[i] = i + 1 < len ? trc_pair_rank(T, id[i], id[i + 1]) : TRC_NO_RANK;
-    __syncthreads();
+    // One ROUND per distinct rank instead of one per merge: with r the smallest rank present, tiktoken's order merges
+    // every pair of rank r, left to right, before anything else - PROVIDED no merge creates a pair of rank below r.  That
+    // holds for rank tables that are merge lists (a token is ranked after its parts) and is checked after every round: a
+    // table that violates it sends the span back to the start with one merge per round.  Overlapping occurrences ("aaa":
+    // two pairs that share the middle token) go leftmost first: a pair is taken iff an even number of rank-r pairs chain up
+    // to it from the left.  The span is cut into at most 1 024 chunks whose minima live in shared memory, so a round
+    // reduces the chunk minima, lists the rank-r pairs of the chunks that hold one, merges them and rescans only the
+    // chunks it touched: a few thousand cheap rounds for a 64 KB span instead of ~60 000 reductions over the whole span.
+    const int64_t csz = ((len + LONGB_T - 1) / LONGB_T + 31) & ~(int64_t)31;     // chunk size (multiple of 32)
+    const int nchunk = (int)((len + csz - 1) / csz);
+    auto chunk_min = [&](int c) {
+      unsigned long long best = ~0ULL;
+      const int64_t a0 = (int64_t)c * csz, a1 = a0 + csz < len ? a0 + csz : len;
+      for (int64_t i = a0; i < a1; ++i) { const unsigned long long k = ((unsigned long long)rk[i] << 32) | (unsigned long long)i; best = k < best ? k : best; }
+      return best;
+    };
+    bool batched = true;
     int64_t m = len;
     for (;;) {
-      unsigned long long best = ~0ULL;
-      for (int64_t i = threadIdx.x; i < len; i += LONG_T) {
-        unsigned long long k = ((unsigned long long)rk[i] << 32) | (unsigned long long)i;
-        best = k < best ? k : best;
-      }
+      for (int64_t i = tid; i < len; i += LONGB_T) { id[i] = byte_id[S.at(e.lstart + i)]; nx[i] = (int32_t)(i + 1); pv[i] = (int32_t)(i - 1); }
+      __syncthreads();
+      for (int64_t i = tid; i < len; i += LONGB_T) rk[i] = i + 1 < len ? trc_pair_rank(T, id[i], id[i + 1]) : TRC_NO_RANK;
+      __syncthreads();
+      s_cm[tid] = tid < nchunk ? chunk_min(tid) : ~0ULL;
+      s_dirty[tid] = 0;
+      m = len;
+      bool bad = false;
+      __syncthreads();
+      for (;;) {
+        unsigned long long best = s_cm[tid];
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) { unsigned long long y = __shfl_xor_sync(0xffffffffu, best, o); best = y < best ? y : best; }
-      if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = best;
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        unsigned long long b = s_red[0];
-        for (int k = 1; k < LONG_T / 32; ++k) b = s_red[k] < b ? s_red[k] : b;
-        s_best = b;
-        uint32_t r = (uint32_t)(b >> 32);
-        if (r != TRC_NO_RANK) {
-          int32_t i = (int32_t)(b & 0xffffffffu);
-          int32_t j = nx[i], nj = nx[j];
-          id[i] = r; nx[i] = nj; rk[j] = TRC_NO_RANK;
-          if (nj < len) { pv[nj] = i; rk[i] = trc_pair_rank(T, r, id[nj]); } else rk[i] = TRC_NO_RANK;
-          int32_t p = pv[i];
-          if (p >= 0) rk[p] = trc_pair_rank(T, id[p], r);
+        for (int o = 16; o > 0; o >>= 1) { unsigned long long y = __shfl_xor_sync(0xffffffffu, best, o); best = y < best ? y : best; }
+        if ((tid & 31) == 0) s_red[tid >> 5] = best;
+        __syncthreads();
+        if (tid < 32) {
+          unsigned long long bb = s_red[tid];
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) { unsigned long long y = __shfl_xor_sync(0xffffffffu, bb, o); bb = y < bb ? y : bb; }
+          if (tid == 0) { s_best = bb; s_ncand = 0; s_cnt = 0; s_bad = 0; }
         }
+        __syncthreads();
+        const uint32_t r = (uint32_t)(s_best >> 32);
+        if (r == TRC_NO_RANK) break;
+        if (!batched) {                                 // one merge per round
+          if (tid == 0) {
+            const int32_t i = (int32_t)(s_best & 0xffffffffu);
+            const int32_t j = nx[i], nj = nx[j];
+            id[i] = r; nx[i] = nj; rk[j] = TRC_NO_RANK;
+            if (nj < len) { pv[nj] = i; rk[i] = trc_pair_rank(T, r, id[nj]); } else rk[i] = TRC_NO_RANK;
+            const int32_t p = pv[i];
+            if (p >= 0) rk[p] = trc_pair_rank(T, id[p], r);
+            s_dirty[i / csz] = 1; s_dirty[j / csz] = 1; if (p >= 0) s_dirty[p / csz] = 1;
+          }
+          --m;
+          __syncthreads();
+          if (tid < nchunk && s_dirty[tid]) { s_cm[tid] = chunk_min(tid); s_dirty[tid] = 0; }
+          __syncthreads();
+          continue;
+        }
+        // list the pairs of rank r (only chunks whose minimum is r can hold one)
+        if (tid < nchunk && (uint32_t)(s_cm[tid] >> 32) == r) {
+          const int64_t a0 = (int64_t)tid * csz, a1 = a0 + csz < len ? a0 + csz : len;
+          for (int64_t i = a0; i < a1; ++i) if (rk[i] == r) { const int q = atomicAdd(&s_ncand, 1); if (q < LONGB_CAND) s_cand[q] = (int32_t)i; }
+        }
+        __syncthreads();
+        const int ncand = s_ncand;
+        const bool listed = ncand <= LONGB_CAND;        // otherwise every thread walks its share of the span
+        // A: choose (reads rk / pv only, marks in the id word)
+        int taken = 0;
+        auto choose = [&](int64_t i) {
+          int back = 0;
+          for (int32_t p = pv[i]; p >= 0 && rk[p] == r; p = pv[p]) ++back;
+          if (!(back & 1)) { id[i] |= SEL; ++taken; }
+        };
+        if (listed) { for (int q = tid; q < ncand; q += LONGB_T) choose(s_cand[q]); }
+        else { for (int64_t i = tid; i < len; i += LONGB_T) if (rk[i] == r) choose(i); }
+        if (taken) atomicAdd(&s_cnt, taken);
+        __syncthreads();
+        // B: merge: the right token of every taken pair dies, links skip it
+        auto merge = [&](int64_t i) {
+          if (!(id[i] & SEL)) return;
+          const int32_t j = nx[i], nj = nx[j];
+          rk[j] = TRC_NO_RANK;
+          nx[i] = nj;
+          if (nj < len) pv[nj] = (int32_t)i;
+          id[i] = r | SEL;
+          s_dirty[i / csz] = 1; s_dirty[j / csz] = 1;
+        };
+        if (listed) { for (int q = tid; q < ncand; q += LONGB_T) merge(s_cand[q]); }
+        else { for (int64_t i = tid; i < len; i += LONGB_T) merge(i); }
+        __syncthreads();
+        // C: ranks of the pairs that changed; none may fall below r
+        int worse = 0;
+        auto rerank = [&](int64_t i) {
+          if (!(id[i] & SEL)) return;
+          const int32_t right = nx[i], left = pv[i];
+          const uint32_t a = right < len ? trc_pair_rank(T, r, id[right] & IDM) : TRC_NO_RANK;
+          rk[i] = a;
+          worse |= a < r;
+          if (left >= 0) { const uint32_t b2 = trc_pair_rank(T, id[left] & IDM, r); rk[left] = b2; worse |= b2 < r; s_dirty[left / csz] = 1; }
+        };
+        if (listed) { for (int q = tid; q < ncand; q += LONGB_T) rerank(s_cand[q]); }
+        else { for (int64_t i = tid; i < len; i += LONGB_T) rerank(i); }
+        if (worse) s_bad = 1;
+        __syncthreads();
+        // D: clear the marks, refresh the minima of the chunks that changed
+        if (listed) { for (int q = tid; q < ncand; q += LONGB_T) { const int32_t i = s_cand[q]; if (id[i] & SEL) id[i] = r; } }
+        else { for (int64_t i = tid; i < len; i += LONGB_T) if (id[i] & SEL) id[i] = r; }
+        m -= s_cnt;
+        bad = s_bad != 0;
+        __syncthreads();
+        if (tid < nchunk && s_dirty[tid]) { s_cm[tid] = chunk_min(tid); s_dirty[tid] = 0; }
+        __syncthreads();
+        if (bad) break;
       }
-      __syncthreads();
-      if ((uint32_t)(s_best >> 32) == TRC_NO_RANK) break;
-      --m;
-      __syncthreads();
+      if (!bad) break;
+      batched = false;                                  // not a merge list: start over, one merge per round
     }
-    if (threadIdx.x == 0) atomicAdd(&counts[e.unit], (uint32_t)m);
+    if (tid == 0) atomicAdd(&counts[e.unit], (uint32_t)m);
     __syncthreads();
   }
 }
@@ -734,7 +826,7 @@ __global__ void k_forced_list(TrcDev D, const int32_t* __restrict__ large_flag, 
 __global__ void k_large_flag(TrcDev D, int32_t* large_flag) {
   GSTRIDE(g, D.m) large_flag[g] = D.gtok[g] > (int64_t)D.doc_E[D.sdoc[D.gstart[g]]];
 }
-__global__ void k_pack_next(TrcDev D, const int64_t* __restrict__ forced_pos, int64_t n_forced) {
+__global__ void k_pack_next(TrcDev D, const int64_t* __restrict__ forced_pos, const int64_t* __restrict__ n_forced) {
   GSTRIDE(a, D.n_items) trc_pack_next(D, forced_pos, n_forced, a);
 }
 __global__ void k_chunk_record(TrcDev D) { GSTRIDE(c, D.n_chunks) trc_chunk_record(D, c); }
@@ -911,6 +1003,27 @@ static int read_back2(trc_ctx* ctx, cudaStream_t st, const void* a, const void* 
   return TRC_OK;
 }
 
+// Three counters in one round trip: a 4-byte and two 8-byte values (any pointer may be null: 0).
+#ifndef TRC_HOSTSIM
+__global__ void k_read_back3(const int32_t* a, const unsigned long long* b, const unsigned long long* c, unsigned long long* dst) {
+  if (threadIdx.x == 0) dst[0] = a ? (unsigned long long)(long long)*a : 0ULL;
+  if (threadIdx.x == 1) dst[1] = b ? *b : 0ULL;
+  if (threadIdx.x == 2) dst[2] = c ? *c : 0ULL;
+}
+#endif
+static int read_back3(trc_ctx* ctx, cudaStream_t st, const int32_t* a, const void* b, const void* c, int64_t out[3]) {
+#ifdef TRC_HOSTSIM
+  out[0] = a ? *a : 0; out[1] = b ? *(const int64_t*)b : 0; out[2] = c ? *(const int64_t*)c : 0;
+#else
+  k_read_back3<<<1, 32, 0, st>>>(a, (const unsigned long long*)b, (const unsigned long long*)c, (unsigned long long*)ctx->d_pin);
+  ctx->launches++;
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(st));
+  out[0] = ctx->h_pin[0]; out[1] = ctx->h_pin[1]; out[2] = ctx->h_pin[2];
+#endif
+  return TRC_OK;
+}
+
 template <class Tp>
 static int to_device(trc_ctx* ctx, cudaStream_t st, const Tp* src, int64_t count, int memory, const Tp** out) {
   if (memory == TRC_MEM_DEVICE) { *out = src; return TRC_OK; }
@@ -947,7 +1060,7 @@ static int count_units(trc_ctx* ctx, cudaStream_t st, const uint8_t* bytes, cons
     ALLOC(scratch, uint32_t, 4 * (int64_t)h[1]);
     int blocks = (int)(h[0] < 148 * 8 ? h[0] : 148 * 8);
     prof_begin(ctx, st, "k_bpe_long");
-    k_bpe_long<<<blocks, LONG_T, 0, st>>>(ctx->T, ctx->d_byte_id, bytes, ustart, uend, vs, counts, wl, (int64_t)h[0], scratch, (int64_t)h[1]);
+    k_bpe_long<<<blocks, LONGB_T, 0, st>>>(ctx->T, ctx->d_byte_id, bytes, ustart, uend, vs, counts, wl, (int64_t)h[0], scratch, (int64_t)h[1]);
     prof_end(ctx, st);
     ctx->launches++;
     CK(cudaGetLastError());
@@ -1495,7 +1608,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
     ALLOC(scratch, uint32_t, 4 * (int64_t)j_h1);
     int lblocks = (int)(j_h0 < 148 * 8 ? j_h0 : 148 * 8);
     prof_begin(ctx, st, "k_bpe_long");
-    k_bpe_long<<<lblocks, LONG_T, 0, st>>>(ctx->T, ctx->d_byte_id, D.C, D.coff, D.coff + 1, 1, D.ctok, j_wl, (int64_t)j_h0, scratch, (int64_t)j_h1);
+    k_bpe_long<<<lblocks, LONGB_T, 0, st>>>(ctx->T, ctx->d_byte_id, D.C, D.coff, D.coff + 1, 1, D.ctok, j_wl, (int64_t)j_h0, scratch, (int64_t)j_h1);
     prof_end(ctx, st);
     ctx->launches++;
     CK(cudaGetLastError());
@@ -1615,8 +1728,8 @@ extern "C" int trc_chunk(trc_ctx* ctx, const int32_t* doc_max_tokens, int32_t co
     for (int64_t x = 0; x < nd; ++x) E[x] = doc_max_tokens[x] - context_tokens;   // big_chunkeroosky.py:42
     int32_t* dE;
     ALLOC(dE, int32_t, nd);
+    // (pageable source: the call returns once the bytes are staged, so E may go out of scope without a synchronisation)
     CK(cudaMemcpyAsync(dE, E.data(), 4 * (size_t)(nd > 0 ? nd : 1), cudaMemcpyHostToDevice, st));
-    CK(cudaStreamSynchronize(st));
     D.doc_E = dE;
   }
   // C1: over-budget segments -> sub-chunks
@@ -1625,15 +1738,24 @@ extern "C" int trc_chunk(trc_ctx* ctx, const int32_t* doc_max_tokens, int32_t co
   ALLOC(D.nitems_g, int32_t, m); ALLOC(D.item_off, int64_t, m + 1);
   CK(cudaMemsetAsync(d_nraw, 0, 4, st));
   if (nk >= 64 * m) LAUNCH_W(k_large_count, m, D, ctx->T, nsub_g, d_nraw); else LAUNCH(k_large_count_t, m, 128, D, ctx->T, nsub_g, d_nraw);
+  // Optimistic: most batches have no over-budget raw segment, so the sub-chunk and item scans run right away and ONE round
+  // trip returns (raw large segments, sub-chunks, items); only when the sentence path is needed are the scans redone.
   int32_t nraw = 0;
-  if (m) { if ((rc = read_back(ctx, st, d_nraw, 4, &nraw))) return rc; }
+  int64_t h2[2] = {0, 0};
   ctx->SS = TrcSentState{};
-  if (nraw > 0) { if ((rc = sentence_stage_count(ctx, st, nsub_g, nraw))) return rc; }
   if ((rc = scan_excl(ctx, st, nsub_g, D.sub_off, m))) return rc;
   LAUNCH(k_nitems, m, 256, D, nsub_g);
   if ((rc = scan_excl(ctx, st, D.nitems_g, D.item_off, m))) return rc;
-  int64_t h2[2] = {0, 0};
   if (m) {
+    int64_t h3[3];
+    if ((rc = read_back3(ctx, st, d_nraw, D.sub_off + m, D.item_off + m, h3))) return rc;
+    nraw = (int32_t)h3[0]; h2[0] = h3[1]; h2[1] = h3[2];
+  }
+  if (nraw > 0) {
+    if ((rc = sentence_stage_count(ctx, st, nsub_g, nraw))) return rc;
+    if ((rc = scan_excl(ctx, st, nsub_g, D.sub_off, m))) return rc;
+    LAUNCH(k_nitems, m, 256, D, nsub_g);
+    if ((rc = scan_excl(ctx, st, D.nitems_g, D.item_off, m))) return rc;
     if ((rc = read_back2(ctx, st, D.sub_off + m, D.item_off + m, h2))) return rc;
   }
   const int64_t nsub = h2[0], ni = h2[1];
@@ -1656,13 +1778,11 @@ extern "C" int trc_chunk(trc_ctx* ctx, const int32_t* doc_max_tokens, int32_t co
   ALLOC(large_flag, int32_t, m); ALLOC(large_scan, int64_t, m + 1);
   LAUNCH(k_large_flag, m, 256, D, large_flag);
   if ((rc = scan_excl(ctx, st, large_flag, large_scan, m))) return rc;
-  int64_t nforced = 0;
-  if (m) { if ((rc = read_back(ctx, st, large_scan + m, 8, &nforced))) return rc; }
-  ALLOC(forced_pos, int64_t, nforced);
+  ALLOC(forced_pos, int64_t, m);                 // at most one forced break per merged segment; the count stays on the device
   LAUNCH(k_forced_list, m, 256, D, large_flag, large_scan, forced_pos);
   // C3: greedy packing as orbit of pnxt
   ALLOC(D.pnxt, int32_t, ni); ALLOC(D.cflag, int32_t, ni); ALLOC(D.cscanf, int64_t, ni + 1);
-  LAUNCH(k_pack_next, ni, 256, D, forced_pos, nforced);
+  LAUNCH(k_pack_next, ni, 256, D, forced_pos, large_scan + m);
   CK(cudaMemsetAsync(D.cflag, 0, 4 * (size_t)(ni > 0 ? ni : 1), st));
   if ((rc = orbit_marks(ctx, st, D.idoc_off, D.pnxt, D.cflag, nd, ni))) return rc;
   if ((rc = scan_excl(ctx, st, D.cflag, D.cscanf, ni))) return rc;

@@ -134,3 +134,26 @@ def test_published_punkt_examples_through_the_sentence_kernels(gpu_engine):
             proc, chunks = pc.run_dropin(gpu_engine, segs, mx)
             want = OC.ChunkerOracle(mx).chunk(OP.preprocess(segs))
             assert pc.same(chunks, want), (t, mx)
+
+
+def test_long_spans_batched_merge(gpu_engine):
+    """Spans far beyond the thread-local limit (k_bpe_long): one round per distinct rank.  Letters without a separator
+    (one pre-tokeniser span), a base64-like blob, runs of one letter (chains of overlapping equal pairs), against the real
+    CoreBPE; a 64 KB span of random letters takes ~30 ms through trc_count_tokens (22 ms of it the single thread that walks the
+    span for the pre-tokeniser, 8 ms the merges), where one merge per block-wide reduction took 183 ms."""
+    import time
+    enc = TK.encoding()
+    rng = random.Random(9)
+    b64 = "ABCDEFGHIJKLMNOPQRSTUVWXYZabcdefghijklmnopqrstuvwxyz"
+    strs = ["a" * 4097, "ab" * 3000, "aaab" * 1500, "".join(rng.choice("etaoinshr") for _ in range(20000)),
+            "".join(rng.choice(b64) for _ in range(65536)), "the" * 9000, "z" * 65000]
+    cnt, _ = gpu_engine.count_tokens(strs, leading_space=False)
+    want = [len(enc.encode_ordinary(s)) for s in strs]
+    assert [int(c) for c in cnt] == want
+    one = ["".join(rng.choice(b64) for _ in range(65536))]
+    gpu_engine.count_tokens(one)
+    t0 = time.perf_counter()
+    c1, _ = gpu_engine.count_tokens(one)
+    dt = time.perf_counter() - t0
+    assert int(c1[0]) == len(enc.encode_ordinary(one[0]))
+    assert dt < 0.1, dt
