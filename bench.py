@@ -388,7 +388,7 @@ def main():
     ap.add_argument("--e2e-offsets64", action="store_true", help="upload the int64 segment offsets instead of int32 lengths")
     ap.add_argument("--e2e-repeats", type=int, default=3, help="repetitions of the K-step end-to-end leg (median reported)")
     ap.add_argument("--e2e-parts", type=int, default=1, help="sub-batches a step's documents are cut into in the end-to-end leg")
-    ap.add_argument("--e2e-contexts", type=int, default=4, help="contexts (host threads) that take batches in turn in the end-to-end leg")
+    ap.add_argument("--e2e-contexts", type=int, default=6, help="contexts (host threads) that take batches in turn in the end-to-end leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
     if args.impl == "reference":
