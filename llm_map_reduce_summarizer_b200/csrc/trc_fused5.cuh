@@ -673,3 +673,96 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
     FUSE_PH(8);
   }
 }
+
+
+// ---- the generic matcher once per DISTINCT word ------------------------------------------------------------------------
+// The fused kernel hands over every OCCURRENCE of a word its fast paths cannot count; the launch memo knows these words
+// (entries with the "generic matcher" mark).  Pass A: the first occurrence to claim a word's memo entry counts it with the
+// generic matcher + byte-pair merges and writes the count into the entry; the other occurrences queue (occurrence, entry).
+// Pass B: the queued occurrences read the finished counts.  On the bench lexicon ~400 k occurrences are ~2 k distinct
+// words; on an open vocabulary of 500 k forms 1.47 M occurrences are ~0.35 M.  Words that are not in the memo (longer
+// than 15 bytes, or crowded out of their two slots) are counted per occurrence as before.
+__device__ __forceinline__ uint32_t f5_count_slow_word(const TrcDev& D, const TrcTables& T, const TrcFast& F, const uint32_t* byte_id, const SlowWord& w,
+                                                       LongEntry* wl, unsigned long long* wl_cnt, int64_t wl_cap) {
+  const int vs = (int)((uint32_t)w.len_vs >> 31);
+  const int64_t len = w.len_vs & 0x7fffffff;
+  const int64_t j = w.unit;
+  const int64_t rel = w.pos - D.coff[j];
+  return trc_count_unit(T, F, byte_id, D.C + w.pos, len, vs, [&](int64_t ls, int64_t slen) -> uint32_t {
+    unsigned long long slot = atomicAdd(&wl_cnt[0], 1ULL);
+    unsigned long long off = atomicAdd(&wl_cnt[1], (unsigned long long)slen);
+    if ((int64_t)slot < wl_cap) { LongEntry e; e.unit = j; e.lstart = ls + (vs ? 0 : rel + 1); e.len = slen; e.scratch_off = (int64_t)off; wl[slot] = e; }
+    return 0u;
+  });
+}
+// Pass A: claim only.  work[]: occurrences that must run the generic matcher (first occurrence of a memo word: entry in
+// the high bits; or a word that is not in the memo: entry = all ones); deferred[]: the other occurrences of memo words.
+// The lists are dense, so the expensive pass below has a word for every lane.
+#define F5_NOSLOT ((1ULL << 24) - 1)
+__global__ void k_slow_words_claim(TrcDev D, FuseArgs A, const SlowWord* __restrict__ sl, int64_t n, unsigned long long* work,
+                                   unsigned long long* deferred, unsigned long long* counters /* [0] work, [1] deferred */) {
+  GSTRIDE(q, n) {
+    const SlowWord w = sl[q];
+    const int vs = (int)((uint32_t)w.len_vs >> 31);
+    const int64_t len = w.len_vs & 0x7fffffff;
+    const int Lw = (int)(len + vs);
+    long long slot = -1;
+    if (len > 0 && Lw <= 15) {
+      uint64_t lo = 0, hi = 0;
+      const uint8_t* p = D.C + w.pos;
+      for (int i = 0; i < Lw; ++i) {
+        const uint64_t b = (vs && i == 0) ? (uint64_t)' ' : (uint64_t)p[i - vs];
+        if (i < 8) lo |= b << (8 * i); else hi |= b << (8 * (i - 8));
+      }
+      if (lo != 0) {
+        const uint32_t s0 = f3_memo_slot(lo, hi, A.memo_mask);
+        for (int way = 0; way < 2 && slot < 0; ++way) {
+          const uint32_t sw = s0 ^ (uint32_t)way;
+          const unsigned long long ex = ld_relaxed(&A.memo[2 * (size_t)sw]), ey = ld_relaxed(&A.memo[2 * (size_t)sw + 1]);
+          if (ex == lo && (ey & 0x00ffffffffffffffULL) == hi && (ey >> 56)) slot = sw;
+        }
+      }
+    }
+    if (slot >= 0 && atomicCAS(&A.memo_lock[slot], 1u, 2u) != 1u) {
+      deferred[atomicAdd(&counters[1], 1ULL)] = ((unsigned long long)slot << 40) | (unsigned long long)q;
+    } else {
+      work[atomicAdd(&counters[0], 1ULL)] = ((slot >= 0 ? (unsigned long long)slot : F5_NOSLOT) << 40) | (unsigned long long)q;
+    }
+  }
+}
+// Pass A2: the generic matcher + byte-pair merges, a listed occurrence per thread; counts of memo words go into their entry.
+__global__ void k_slow_words_count(TrcDev D, TrcTables T, const uint32_t* __restrict__ byte_id, FuseArgs A, const SlowWord* __restrict__ sl,
+                                   const unsigned long long* __restrict__ work, const unsigned long long* __restrict__ counters) {
+  const TrcFast F = trc_fast_default(T);
+  const int64_t n = (int64_t)counters[0];
+  GSTRIDE(k, n) {
+    const unsigned long long d = work[k];
+    const int64_t q = (int64_t)(d & ((1ULL << 40) - 1));
+    const unsigned long long slot = d >> 40;
+    const SlowWord w = sl[q];
+    const uint32_t c = f5_count_slow_word(D, T, F, byte_id, w, A.wl, A.wl_cnt, A.wl_cap);
+    atomicAdd(&D.ctok[w.unit], c);
+    if (slot != F5_NOSLOT) {
+      const bool whole = c > 0 && c < 250u;             // (words of <= 15 bytes have no span for the long-span kernel)
+      if (whole) {
+        const unsigned long long ey = ld_relaxed(&A.memo[2 * (size_t)slot + 1]);
+        st_relaxed(&A.memo[2 * (size_t)slot + 1], (ey & 0x00ffffffffffffffULL) | ((uint64_t)(c + 1u) << 56));
+      }
+      A.memo_lock[slot] = whole ? 3u : 4u;
+    }
+  }
+}
+// Pass B: the other occurrences read the finished counts.
+__global__ void k_slow_words_follow(TrcDev D, TrcTables T, const uint32_t* __restrict__ byte_id, FuseArgs A, const SlowWord* __restrict__ sl,
+                                    const unsigned long long* __restrict__ deferred, const unsigned long long* __restrict__ counters) {
+  const TrcFast F = trc_fast_default(T);
+  const int64_t n = (int64_t)counters[1];
+  GSTRIDE(k, n) {
+    const unsigned long long d = deferred[k];
+    const int64_t q = (int64_t)(d & ((1ULL << 40) - 1));
+    const size_t slot = (size_t)(d >> 40);
+    const SlowWord w = sl[q];
+    if (A.memo_lock[slot] == 3u) atomicAdd(&D.ctok[w.unit], (uint32_t)(A.memo[2 * slot + 1] >> 56) - 1u);
+    else atomicAdd(&D.ctok[w.unit], f5_count_slow_word(D, T, F, byte_id, w, A.wl, A.wl_cnt, A.wl_cap));
+  }
+}

@@ -643,7 +643,7 @@ __global__ void __launch_bounds__(LONGB_T) k_bpe_long(TrcTables T, const uint32_
 
 #endif
 #ifndef TRC_HOSTSIM
-#define TRC_MEMO_LOG2 18
+#define TRC_MEMO_LOG2 20
 #include "trc_giant.cuh"
 #include "trc_fused.cuh"
 #include "trc_fused3.cuh"
@@ -1479,10 +1479,27 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
         if (nslow > 0) {       // on the side stream: nothing before the per-group token totals needs these counts
           CK(cudaEventRecord(ctx->ev_aux[0], st));
           CK(cudaStreamWaitEvent(ctx->aux_stream, ctx->ev_aux[0], 0));
-          prof_begin(ctx, ctx->aux_stream, "k_count_slow_words");
-          k_count_slow_words<<<grid_for(nslow, 128), 128, 0, ctx->aux_stream>>>(D, ctx->T, ctx->d_byte_id, A.sl, nslow, A.wl, A.wl_cnt, A.wl_cap);
-          prof_end(ctx, ctx->aux_stream);
-          ctx->launches++;
+          if (gen >= 5 && A.memo) {              // the generic matcher once per distinct word (claim), then the other occurrences
+            unsigned long long* work; unsigned long long* deferred; unsigned long long* lcnt;
+            ALLOC(work, unsigned long long, nslow); ALLOC(deferred, unsigned long long, nslow); ALLOC(lcnt, unsigned long long, 2);
+            CK(cudaMemsetAsync(lcnt, 0, 16, ctx->aux_stream));
+            prof_begin(ctx, ctx->aux_stream, "k_slow_words_claim");
+            k_slow_words_claim<<<grid_for(nslow, 256), 256, 0, ctx->aux_stream>>>(D, A, A.sl, nslow, work, deferred, lcnt);
+            prof_end(ctx, ctx->aux_stream);
+            prof_begin(ctx, ctx->aux_stream, "k_slow_words_count");
+            k_slow_words_count<<<grid_for(nslow, 128), 128, 0, ctx->aux_stream>>>(D, ctx->T, ctx->d_byte_id, A, A.sl, work, lcnt);
+            prof_end(ctx, ctx->aux_stream);
+            prof_begin(ctx, ctx->aux_stream, "k_slow_words_follow");
+            k_slow_words_follow<<<grid_for(nslow, 256), 256, 0, ctx->aux_stream>>>(D, ctx->T, ctx->d_byte_id, A, A.sl, deferred, lcnt);
+            prof_end(ctx, ctx->aux_stream);
+            ctx->launches += 3;
+            ctx->launches += 2;
+          } else {
+            prof_begin(ctx, ctx->aux_stream, "k_count_slow_words");
+            k_count_slow_words<<<grid_for(nslow, 128), 128, 0, ctx->aux_stream>>>(D, ctx->T, ctx->d_byte_id, A.sl, nslow, A.wl, A.wl_cnt, A.wl_cap);
+            prof_end(ctx, ctx->aux_stream);
+            ctx->launches++;
+          }
           CK(cudaGetLastError());
           slow_pending = true;
         }
