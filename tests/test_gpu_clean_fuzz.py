@@ -1,0 +1,56 @@
+"""Random segments through stage P on the GPU: cleaned text and token counts per segment against the oracle.
+Shapes that steer the fused kernel through its paths: odd whitespace (tabs, NBSP, U+2003, U+3000, runs of them),
+multi-byte words, duplicate chains, `.X` insertions, special-token fragments, empty and whitespace-only segments, and
+segment lengths from 0 to several KB (the tile size follows the batch's mean segment length; segments beyond a tile take
+the slow lane, beyond 4 KB the pre-pass for oversized segments)."""
+import random
+
+import numpy as np
+import pytest
+
+from llm_map_reduce_summarizer_b200 import engine as E
+from oracle import preprocess as OP, tokenizer as TK
+
+pytestmark = pytest.mark.gpu
+ALPHA = ["a", "b", "the", "the", "is", "Z", "é", "1", " ", " ", " ", "  ", "\t", " ", " ", "　", ".", ",", "!", "?", "-",
+         "你好", "_", "x0", "​", "word", "end.Next", "café", " \t ", "́", "<|", "'s"]
+
+
+def _run(eng, segs):
+    enc = TK.encoding()
+    b = E.pack_documents([segs])
+    eng.preprocess(b, merge_same_speaker=False, want_merged_text=False)
+    P = eng.fetch_processed()
+    clean, coff, k2r, ctok = P["clean"].tobytes(), P["coff"], P["k2r"], P["ctok"]
+    want = [(i, OP.clean_text(s["text"])) for i, s in enumerate(segs)]
+    want = [(i, t) for i, t in want if t]
+    assert [i for i, _ in want] == k2r.tolist()
+    for j, (i, t) in enumerate(want):
+        got = clean[int(coff[j]):int(coff[j + 1])]
+        assert got == t.encode(), (i, segs[i]["text"][:80])
+        assert int(ctok[j]) == len(enc.encode_ordinary(" " + t)), (i, t[:80])
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_random_segments(gpu_engine, seed):
+    rng = random.Random(seed)
+    for trial in range(12):
+        nseg = rng.choice([1, 3, 40, 200, 700])
+        segs = []
+        for i in range(nseg):
+            L = rng.choice([0, 1, 5, 30, 60, 200, 900]) if rng.random() < 0.3 else rng.randint(0, 80)
+            segs.append({"start": float(i), "end": float(i + 1), "text": "".join(rng.choice(ALPHA) for _ in range(L)), "speaker": "A"})
+        _run(gpu_engine, segs)
+
+
+@pytest.mark.parametrize("mean_len", [400, 1500, 6000])
+def test_long_segments(gpu_engine, mean_len):
+    """Batches whose segments are hundreds to thousands of bytes: smaller tiles, the slow lane, oversized segments."""
+    rng = random.Random(mean_len)
+    segs = []
+    for i in range(60):
+        L = max(1, int(rng.gauss(mean_len, mean_len / 3)))
+        segs.append({"start": float(i), "end": float(i + 1), "text": "".join(rng.choice(ALPHA) for _ in range(L // 3)), "speaker": "A"})
+    segs.insert(7, {"start": 0.0, "end": 1.0, "text": " \t ", "speaker": "A"})
+    segs.insert(9, {"start": 0.0, "end": 1.0, "text": "", "speaker": "A"})
+    _run(gpu_engine, segs)

@@ -212,7 +212,7 @@ def test_dense_tiles(gpu_engine):
     assert pc.check_dense_tiles(gpu_engine) == 6
 
 
-@pytest.mark.parametrize("env", ["TRCHUNK_FUSED=2", "TRCHUNK_NO_FUSED=1", "TRCHUNK_NO_MEMO=1"])
+@pytest.mark.parametrize("env", ["TRCHUNK_FUSED=2", "TRCHUNK_FUSED=3", "TRCHUNK_FUSED=4", "TRCHUNK_NO_FUSED=1", "TRCHUNK_NO_MEMO=1"])
 def test_alternate_kernel_paths(monkeypatch, env):
     """The older kernel generations kept for A/B runs and the fused kernel without its word memo:
     the switches are read when a context is created."""
