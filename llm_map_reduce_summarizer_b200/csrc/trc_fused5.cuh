@@ -368,22 +368,35 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
         const uint32_t odd = se & m_ns[c];            // emitted spaces whose source byte is not U+0020
         if (in == 0u && (cp | se) == 0xffffffffu && !odd) f4_store32(S.out + pos, x);
         else {
+          // Four bytes at a time.  Groups that are copied as they are go first, in chunk order (the lanes of a warp agree
+          // on most of them); the others - a dropped byte, an inserted or replaced space - are left for a second loop in
+          // which every lane walks ITS OWN list of such groups, so the lanes run the byte-wise code together instead of
+          // once per group index (profiles/r2s: that code ran with 2.4 of 32 lanes).
           uint8_t* dst = S.out;
+          const uint32_t any = cp | se, bytewise = in | odd;
+          const int32_t pos0 = pos;
+          uint32_t nt = 0;
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {             // four bytes at a time: dropped, copied as they are, or byte by byte
-            const uint32_t c4 = (cp >> (4 * j)) & 15u, s4 = (se >> (4 * j)) & 15u, i4 = (in >> (4 * j)) & 15u;
-            if (!(c4 | s4)) continue;
-            const uint32_t xv = x[j];
-            if ((c4 | s4) == 15u && !i4 && !((odd >> (4 * j)) & 15u)) {
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t a4 = (any >> (4 * j)) & 15u;
+            if (!a4) continue;
+            if (a4 == 15u && !((bytewise >> (4 * j)) & 15u)) {
+              const uint32_t xv = x[j];
               dst[pos] = (uint8_t)xv; dst[pos + 1] = (uint8_t)(xv >> 8); dst[pos + 2] = (uint8_t)(xv >> 16); dst[pos + 3] = (uint8_t)(xv >> 24);
               pos += 4;
-              continue;
-            }
+            } else { nt |= 1u << j; pos += __popc(a4) + __popc((in >> (4 * j)) & 15u); }
+          }
+          while (nt) {
+            const int j = (int)trc_ctz32(nt);
+            nt &= nt - 1u;
+            const uint32_t below = (1u << (4 * j)) - 1u;
+            int32_t p = pos0 + __popc(any & below) + __popc(in & below);
+            const uint32_t xv = *reinterpret_cast<const uint32_t*>(S.y.in + 32 * c + 4 * j);
+            const uint32_t c4 = (cp >> (4 * j)) & 15u, s4 = (se >> (4 * j)) & 15u, i4 = (in >> (4 * j)) & 15u;
 #pragma unroll
             for (int b = 0; b < 4; ++b) {
-              if ((i4 >> b) & 1u) dst[pos++] = ' ';
-              if ((c4 >> b) & 1u) dst[pos++] = (uint8_t)(xv >> (8 * b));
-              else if ((s4 >> b) & 1u) dst[pos++] = ' ';
+              if ((i4 >> b) & 1u) dst[p++] = ' ';
+              if (((c4 | s4) >> b) & 1u) dst[p++] = ((c4 >> b) & 1u) ? (uint8_t)(xv >> (8 * b)) : (uint8_t)' ';
             }
           }
         }

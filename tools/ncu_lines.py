@@ -47,5 +47,6 @@ def src(f, n):
         src_cache[p] = open(p).read().splitlines() if os.path.exists(p) else []
     L = src_cache[p]
     return L[n - 1].strip()[:90] if 0 < n <= len(L) else ""
-for key, v in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
+sk = 1 if os.environ.get("SORT") == "instr" else 0      # SORT=instr: by warp instructions instead of samples
+for key, v in sorted(agg.items(), key=lambda kv: -kv[1][sk])[:top]:
     print("%5.1f%% samples %5.1f%% instr  %4.1f lanes  %s:%d  %s" % (100.0 * v[0] / max(tot[0], 1), 100.0 * v[1] / max(tot[1], 1), v[2] / max(v[1], 1), key[0], key[1], src(*key)))
