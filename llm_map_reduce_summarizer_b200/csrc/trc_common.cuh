@@ -38,6 +38,7 @@ struct TrcTables {
   const uint8_t* tok_bytes;
   const uint32_t* tok_off;  // n_tok+1
   uint32_t n_tok;
+  uint32_t tok_max_len;     // longest vocabulary entry in bytes: longer spans are not tokens (no need to hash 64 KB to find out)
   const uint64_t* tokhash;  // (fingerprint32 << 32 | id), empty = ~0
   uint32_t tokhash_mask;
   const uint64_t* pairhash;  // (idL << 42 | idR << 21 | rank), empty = ~0
@@ -81,6 +82,15 @@ TRC_HD int64_t trc_lanes_sum(int64_t v) {
 #if defined(__CUDA_ARCH__)
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+#endif
+  return v;
+}
+// the same over aligned groups of nl lanes (nl a power of two); `mask` names the lanes that take part
+TRC_HD int64_t trc_lanes_sum_w(int64_t v, int nl, uint32_t mask) {
+#if defined(__CUDA_ARCH__)
+  for (int o = nl >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(mask, v, o);
+#else
+  (void)nl; (void)mask;
 #endif
   return v;
 }

@@ -68,6 +68,7 @@ struct FuseArgs {
   // second level of the look-back of k_clean_tok_w32: per group of 32 tiles an arrival counter and (status, value) words
   unsigned long long* grp_cnt; unsigned long long* grp_bytes; unsigned long long* grp_kept;
   unsigned long long* wstat;        // [0] words through the word-level counter, [1] first sightings, [2] words left to the generic matcher
+  const int32_t* tile_start;        // k_clean_tok_c32: first segment of every tile (+ n at the end), or null: tile t = segments [t * tsegs, ...)
 };
 #define FUSE_PH(i) do { if (A.phase && tid == 0) { long long now_ = clock64(); atomicAdd(&A.phase[i], (unsigned long long)(now_ - ph_t)); ph_t = now_; } } while (0)
 

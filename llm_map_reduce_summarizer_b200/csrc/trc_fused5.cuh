@@ -60,6 +60,7 @@ struct F5Smem {
   int32_t nmiss, nslow, flag, sfflag;
   unsigned int tile;
   long long next_raw[2];                        // the tile's seg_off[s0], seg_off[s0 + ns], loaded once by thread 0
+  long long tile_s0; int32_t tile_ns;           // its first segment and segment count
   int32_t doc0;
   long long gbase, kbase, slbase;
   alignas(8) unsigned long long mbar;
@@ -196,16 +197,18 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
       const unsigned t = (unsigned int)atomicAdd(A.tile_counter, 1ULL);
       S.tile = t;
       if ((int64_t)t < ntiles) {
-        const int64_t q0 = (int64_t)t * tsegs;
-        const int64_t qn = (D.n - q0) < tsegs ? (D.n - q0) : tsegs;
+        int64_t q0, qn;
+        if (A.tile_start) { q0 = A.tile_start[t]; qn = A.tile_start[t + 1] - q0; }
+        else { q0 = (int64_t)t * tsegs; qn = (D.n - q0) < tsegs ? (D.n - q0) : tsegs; }
         S.next_raw[0] = D.seg_off[q0]; S.next_raw[1] = D.seg_off[q0 + qn];
+        S.tile_s0 = q0; S.tile_ns = (int32_t)qn;
       }
     }
     __syncthreads();
     const unsigned tile = S.tile;
     if ((int64_t)tile >= ntiles) break;
-    const int64_t s0 = (int64_t)tile * tsegs;
-    const int ns = (int)((D.n - s0) < tsegs ? (D.n - s0) : tsegs);
+    const int64_t s0 = S.tile_s0;
+    const int ns = S.tile_ns;
     const int64_t raw0 = S.next_raw[0], raw1 = S.next_raw[1];
     const int al = (int)(raw0 & 15);
     const int64_t base = raw0 - al;
@@ -624,9 +627,11 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
       int32_t d1;
       f5_scan3(S, lane, wid, mylen, mykeep, 0, &loff, &koff, &d1);
       tot_out = S.tot[0]; tot_kept = S.tot[1];
-      if (wid == 0) {
-        long long gb = fuse_lookback(A.desc_bytes, tile, tot_out, lane);
-        long long kb = fuse_lookback(A.desc_kept, tile, tot_kept, lane);
+      if (wid == 0) {                           // both aggregates go out before either prefix is looked up
+        if (lane == 0) { fuse_publish(A.desc_bytes, tile, tot_out); fuse_publish(A.desc_kept, tile, tot_kept); }
+        __syncwarp();
+        long long gb, kb;
+        f5_resolve2(A.desc_bytes, A.desc_kept, tile, tot_out, tot_kept, lane, &gb, &kb);
         if (lane == 0) { S.gbase = gb; S.kbase = kb; }
       }
       __syncthreads();

@@ -24,10 +24,37 @@ struct GiantState {
   const int32_t* of_seg;            // per raw segment: giant index or -1 (n entries)
 };
 
-__global__ void k_giant_any(TrcDev D, unsigned long long* cnt) {
+// cnt[0]: warps that saw an oversized segment.  cnt[1 + q]: tiles of cand.v[q] segments whose raw bytes would not fit a
+// tile of the fused kernel (`cap` bytes from the 16-byte aligned start) - the host picks the tile size from these.
+struct TileCand { int v[4]; };
+__global__ void k_giant_any(TrcDev D, unsigned long long* cnt, TileCand cand, int64_t cap) {
   int found = 0;
-  GSTRIDE(i, D.n) found |= (D.seg_off[i + 1] - D.seg_off[i]) > TRC_GIANT_MIN;
+  GSTRIDE(i, D.n) {
+    const int64_t a = D.seg_off[i];
+    found |= (D.seg_off[i + 1] - a) > TRC_GIANT_MIN;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int ts = cand.v[q];
+      if (ts > 0 && (uint32_t)i % (uint32_t)ts == 0u) {            // (segment indices fit 31 bits: k2r is int32)
+        const int64_t e = i + ts < D.n ? i + ts : D.n;
+        if (D.seg_off[e] - (a & ~(int64_t)15) > cap) atomicAdd(cnt + 1 + q, 1ULL);
+      }
+    }
+  }
   if (__any_sync(0xffffffffu, found) && (threadIdx.x & 31) == 0) atomicAdd(cnt, 1ULL);
+}
+// Tiles of varying size for batches whose segments do not fit tiles of a fixed segment count (oversized segments, heavy
+// tails): a tile is a run of segments that start inside the same window of `win` bytes, at most `max_segs` of them, and an
+// oversized segment is a tile of its own.  Its raw bytes then span less than win + TRC_GIANT_MIN + 16.
+__global__ void k_tile_flags(TrcDev D, int32_t* flag, int64_t win, int max_segs) {
+  GSTRIDE(i, D.n) {
+    int f = (uint32_t)i % (uint32_t)max_segs == 0u;
+    if (!f) {
+      const int64_t a = D.seg_off[i], p = D.seg_off[i - 1], b = D.seg_off[i + 1];
+      f = (a / win != p / win) || (b - a > TRC_GIANT_MIN) || (a - p > TRC_GIANT_MIN);
+    }
+    flag[i] = f;
+  }
 }
 __global__ void k_giant_flag(TrcDev D, int32_t* flag) { GSTRIDE(i, D.n) flag[i] = (D.seg_off[i + 1] - D.seg_off[i]) > TRC_GIANT_MIN; }
 __global__ void k_giant_list(TrcDev D, const int32_t* __restrict__ flag, const int64_t* __restrict__ scan, int32_t* list, int64_t* len,

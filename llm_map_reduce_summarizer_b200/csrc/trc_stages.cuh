@@ -52,6 +52,7 @@ struct TrcDev {
   int64_t n_kept;
   int32_t* k2r; int64_t* coff; uint8_t* C; int32_t* sdoc; int64_t* kdoc_off;
   uint32_t* ctok;                          // count(" " + cleaned text)
+  int32_t* kspk; double* kdur;             // per piece: speaker id and end - start (null unless the capped merge runs)
   int32_t* mnxt; int32_t* gflag; int64_t* gscan; int64_t m; int32_t* gstart; int64_t* gdoc_off;
   int32_t* plen; int64_t* poff; uint8_t* M;
   int64_t* poffs;                          // piece layout WITH timestamps (== poff when preserve), for sub-chunk text
@@ -79,7 +80,17 @@ TRC_HD void trc_merge_next(const TrcDev& D, int64_t j) {
   int32_t x = D.sdoc[j];
   int64_t hi = D.kdoc_off[x + 1];
   int64_t k = j + 1;
-  if (D.merge) {
+  if (D.merge && D.kspk) {                   // the same scan on the per-piece copies (contiguous loads, no indirection)
+    const int32_t sp = D.kspk[j];
+    double cur = D.kdur[j];
+    while (k < hi) {
+      if (D.kspk[k] != sp) break;
+      const double d = D.kdur[k];
+      if (D.has_cap && cur + d > D.cap) break;
+      cur += d;
+      ++k;
+    }
+  } else if (D.merge) {
     int32_t r = D.k2r[j];
     int32_t sp = D.spk[r];
     double cur = D.end[r] - D.start[r];
@@ -151,7 +162,7 @@ TRC_HD void trc_emit_merged(const TrcDev& D, int64_t j, int lane, int nl) {
 // formatted = "[" ts(start) "] " speaker ": " text        (big_chunkeroosky.py:244-265)
 // tokens    = count("[ts]") + count(" speaker:") + count(" " + text), exact because the pre-tokeniser
 //             always has match boundaries after "]" and after ":" (DESIGN.md §3).
-TRC_HD void trc_group_stats(const TrcDev& D, const TrcTables& T, int64_t g, int lane, int nl) {   // lanes share the pieces
+TRC_HD void trc_group_stats(const TrcDev& D, const TrcTables& T, int64_t g, int lane, int nl, uint32_t mask = 0xffffffffu) {   // lanes share the pieces
   int32_t a = D.gstart[g], b = D.gstart[g + 1];
   int32_t ra = D.k2r[a], rb = D.k2r[b - 1];
   double st = D.start[ra];
@@ -163,7 +174,7 @@ TRC_HD void trc_group_stats(const TrcDev& D, const TrcTables& T, int64_t g, int 
       if (D.preserve) part += T.cnt_space_lbracket + trc_ts_tokens(T, D.start[D.k2r[j]]) + 1;
     }
   }
-  const int64_t tok = 2 + trc_ts_tokens(T, st) + D.spk_tok[D.spk[ra]] + (nl > 1 ? trc_lanes_sum(part) : part);
+  const int64_t tok = 2 + trc_ts_tokens(T, st) + D.spk_tok[D.spk[ra]] + (nl > 1 ? trc_lanes_sum_w(part, nl, mask) : part);
   if (lane != 0) return;
   D.gtok[g] = tok;
   int64_t mlen = D.poff[b] - D.poff[a];
@@ -338,7 +349,9 @@ TRC_HD int64_t trc_header(const TrcDev& D, const TrcChunk& c, uint8_t* dst) {
   return o;
 }
 
-TRC_HD void trc_chunk_record(const TrcDev& D, int64_t c) {
+// The record of chunk c in three parts, so that the CUDA build can give the middle one (the speaker set) to a whole warp
+// (k_chunk_record_w in trchunk.cu): everything that is one value per chunk / the sorted distinct speakers / the lengths.
+TRC_HD void trc_chunk_record_head(const TrcDev& D, int64_t c) {
   TrcChunk& ch = D.chunks[c];
   int64_t a = D.cstart[c], b = D.cstart[c + 1];
   int32_t x = D.sdoc[D.gstart[D.it_group[a]]];
@@ -362,6 +375,18 @@ TRC_HD void trc_chunk_record(const TrcDev& D, int64_t c) {
     double av = ch.position_percentage < 0 ? -ch.position_percentage : ch.position_percentage;
     if (av >= 576460752303423488.0 && av <= 1.7976931348623157e308) ch.err = 1;
   } else { ch.position_percentage = 0.0; ch.pct_is_int_zero = 1; }
+}
+TRC_HD void trc_chunk_record_tail(const TrcDev& D, int64_t c, int32_t ns) {
+  TrcChunk& ch = D.chunks[c];
+  const int64_t a = ch.item0, b = ch.item1;
+  ch.n_speakers = ns;
+  ch.text_len = (D.L[b] - D.L[a]) - 2;
+  ch.hdr_len = D.add_context ? (int32_t)trc_header<false>(D, ch, nullptr) : 0;
+  D.twc_len[c] = ch.text_len + (D.add_context ? ch.hdr_len + 2 : 0);
+}
+TRC_HD void trc_chunk_record(const TrcDev& D, int64_t c) {
+  trc_chunk_record_head(D, c);
+  const int64_t a = D.chunks[c].item0, b = D.chunks[c].item1;
   // sorted distinct speaker ids (ids are assigned in code-point order of the strings, so sorted(set) == ascending ids)
   int32_t ns = 0;
   int32_t* lst = D.spk_list + a;
@@ -373,10 +398,7 @@ TRC_HD void trc_chunk_record(const TrcDev& D, int64_t c) {
     for (int32_t q = ns; q > k; --q) lst[q] = lst[q - 1];
     lst[k] = v; ++ns;
   }
-  ch.n_speakers = ns;
-  ch.text_len = (D.L[b] - D.L[a]) - 2;
-  ch.hdr_len = D.add_context ? (int32_t)trc_header<false>(D, ch, nullptr) : 0;
-  D.twc_len[c] = ch.text_len + (D.add_context ? ch.hdr_len + 2 : 0);
+  trc_chunk_record_tail(D, c, ns);
 }
 
 TRC_HD void trc_chunk_header_write(const TrcDev& D, int64_t c) {

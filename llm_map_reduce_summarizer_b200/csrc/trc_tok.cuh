@@ -26,6 +26,12 @@ TRC_HD uint32_t trc_sdecode(const TrcStr& S, int64_t i, int* len) {
 // Alternatives in pattern order:
 //  1 (?i:'s|'t|'re|'ve|'m|'ll|'d)   2 [^\r\n\p{L}\p{N}]?\p{L}+   3 \p{N}{1,3}
 //  4  ?[^\s\p{L}\p{N}]+[\r\n]*      5 \s*[\r\n]+   6 \s+(?!\S)   7 \s+
+TRC_HD uint64_t trc_swar_letters(uint64_t x) {          // bit 7 of every byte that is an ASCII letter
+  const uint64_t H = 0x8080808080808080ULL, L = 0x0101010101010101ULL;
+  const uint64_t t = ((x | 0x2020202020202020ULL) & ~H) | H;   // lower-cased, high bit forced
+  const uint64_t ge_a = (t - L * 0x61) & H, ge_z1 = (t - L * 0x7b) & H;
+  return ge_a & ~ge_z1 & ~(x & H);
+}
 TRC_HD int64_t trc_span_end(const TrcTables& T, const TrcFast& F, const TrcStr& S, int64_t p) {
   const int64_t N = S.n;
   int l0, l1 = 0, l2 = 0;
@@ -52,6 +58,10 @@ TRC_HD int64_t trc_span_end(const TrcTables& T, const TrcFast& F, const TrcStr& 
     if (k0 != TRC_RS_L && k0 != TRC_RS_N && c0 != '\r' && c0 != '\n' && has1 && k1 == TRC_RS_L) { q = p + l0; kq = k1; }
     if (kq == TRC_RS_L) {
       while (q < N) {
+        if (q >= S.vs && q + 8 <= N) {         // eight ASCII letters at a time (a 64 KB run of letters paid a load latency per byte)
+          const uint8_t* a8 = S.p + (q - S.vs);
+          if (((uintptr_t)a8 & 7) == 0 && trc_swar_letters(*reinterpret_cast<const uint64_t*>(a8)) == 0x8080808080808080ULL) { q += 8; continue; }
+        }
         int l; uint32_t c = trc_sdecode(S, q, &l);
         if (trc_cls(T, F, c) != TRC_RS_L) break;
         q += l;
@@ -104,6 +114,7 @@ TRC_HD bool trc_is_token_generic(const TrcTables& T, const TrcStr& S, int64_t a,
 // Exact membership test with the <=16-byte key sets; longer spans (and spans holding a NUL byte) use the
 // hashed byte-string table.
 TRC_HD bool trc_is_token(const TrcTables& T, const TrcFast& F, const TrcStr& S, int64_t a, int n) {
+  if ((uint32_t)n > T.tok_max_len) return false;
   if (n <= 16) {
     uint64_t lo = 0, hi = 0;
     bool nul = false;
@@ -199,12 +210,6 @@ TRC_HD int trc_find_special(const TrcTables& T, const uint8_t* p, int64_t n) {
 //   ' ' letters + contraction        -> alt 2 + alt 1 ('s 't 'm 'd 'll 've 're, any case)
 // Letter spans must be vocabulary entries (exact-key sets); anything else returns false and the caller
 // uses the generic matcher.  Exact: every decision is the regex's decision for these shapes.
-TRC_HD uint64_t trc_swar_letters(uint64_t x) {          // bit 7 of every byte that is an ASCII letter
-  const uint64_t H = 0x8080808080808080ULL, L = 0x0101010101010101ULL;
-  const uint64_t t = ((x | 0x2020202020202020ULL) & ~H) | H;   // lower-cased, high bit forced
-  const uint64_t ge_a = (t - L * 0x61) & H, ge_z1 = (t - L * 0x7b) & H;
-  return ge_a & ~ge_z1 & ~(x & H);
-}
 
 TRC_HD bool trc_key_is_token(const TrcTables& T, const TrcFast& F, uint64_t lo, uint64_t hi, int n) {
   if (n <= 8) {

@@ -653,7 +653,10 @@ __global__ void __launch_bounds__(LONGB_T) k_bpe_long(TrcTables T, const uint32_
 
 __global__ void k_special_docs(TrcDev D, const int32_t* __restrict__ seg_special, const int32_t* __restrict__ spk_special) {
   GSTRIDE(j, D.n_kept) {
-    if (seg_special[j] >= 0 || spk_special[D.spk[D.k2r[j]]] >= 0)
+    const int32_t r = D.k2r[j];
+    const int32_t sp = D.spk[r];
+    if (D.kspk) { D.kspk[j] = sp; D.kdur[j] = D.end[r] - D.start[r]; }     // per piece, for the forward scans of trc_merge_next
+    if (seg_special[j] >= 0 || spk_special[sp] >= 0)
       atomicMin((unsigned long long*)&D.doc_err_seg[D.sdoc[j]], (unsigned long long)j);
   }
 }
@@ -731,6 +734,26 @@ __global__ void __launch_bounds__(1024) k_orbit_staged(const int64_t* __restrict
   }
 }
 #endif
+#ifndef TRC_HOSTSIM
+// Many documents of moderate length (config 3: 10 k documents of ~220 pieces, ~16 hops each): a WARP per document stages
+// the document's links in shared memory with coalesced loads and lane 0 walks them there; a thread per document
+// paid an L2 round trip per hop and the longest document set the kernel's time.  Longer ranges are walked in place.
+#define ORBIT_W_LINKS 1024
+__global__ void __launch_bounds__(256) k_orbit_warp(const int64_t* __restrict__ range_off, const int32_t* __restrict__ nxt, int32_t* flag, int64_t n_doc) {
+  __shared__ int32_t s_nxt[8][ORBIT_W_LINKS];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int64_t x = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5; x < n_doc; x += ((int64_t)gridDim.x * blockDim.x) >> 5) {
+    const int64_t a = range_off[x], b = range_off[x + 1];
+    const int64_t n = b - a;
+    if (n <= 0) continue;
+    if (n > ORBIT_W_LINKS) { if (lane == 0) trc_orbit_walk(range_off, nxt, flag, x); continue; }
+    for (int64_t k = lane; k < n; k += 32) s_nxt[w][k] = (int32_t)(nxt[a + k] - a);
+    __syncwarp();
+    if (lane == 0) { int32_t p = 0; while (p < n) { flag[a + p] = 1; p = s_nxt[w][p]; } }
+    __syncwarp();
+  }
+}
+#endif
 __global__ void k_scatter_starts(const int32_t* __restrict__ flag, const int64_t* __restrict__ scan, int32_t* starts, int64_t n) {
   GSTRIDE(j, n) {
     if (flag[j]) starts[scan[j]] = (int32_t)j;
@@ -752,6 +775,17 @@ __global__ void k_piece_len(TrcDev D, int32_t* plen_sub) {
 __global__ void k_emit_merged(TrcDev D) { WSTRIDE(j, D.n_kept) trc_emit_merged(D, j, TRC_LANE, TRC_NL); }
 __global__ void k_group_stats(TrcDev D, TrcTables T) { WSTRIDE(g, D.m) trc_group_stats(D, T, g, TRC_LANE, TRC_NL); }
 __global__ void k_group_stats_t(TrcDev D, TrcTables T) { GSTRIDE(g, D.m) trc_group_stats(D, T, g, 0, 1); }   // short groups: a thread each
+#ifndef TRC_HOSTSIM
+// groups of a dozen pieces (config 3): eight lanes per group, four groups per warp
+__global__ void k_group_stats_8(TrcDev D, TrcTables T) {
+  const int lane = threadIdx.x & 31;
+  for (int64_t base = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) - lane; (base >> 3) < D.m; base += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t g = (base + lane) >> 3;
+    const uint32_t mask = __ballot_sync(0xffffffffu, g < D.m);
+    if (g < D.m) trc_group_stats(D, T, g, lane & 7, 8, mask);
+  }
+}
+#endif
 
 // ---- chunk stage
 // warp per merged segment (the sub-chunk greedy of an over-budget combined segment walks thousands of pieces)
@@ -836,18 +870,120 @@ __global__ void k_item_layout(TrcDev D) { GSTRIDE(t, D.n_items) trc_item_layout(
 #ifdef TRC_HOSTSIM
 __global__ void k_emit_pieces_flat(TrcDev D) { GSTRIDE(j, D.n_kept) trc_emit_piece_flat(D, j, 0, 1); }
 #else
+// ---- chunk records, headers and item prefixes, CUDA build ---------------------------------------------------------------
+// The per-chunk and per-item routines of trc_stages.cuh are chains of dependent loads (item -> group -> piece -> raw segment
+// -> value); a thread per chunk walked its ~15 items one after the other (profiles/r2s: 68 + 43 + 69 us for 11 k chunks and
+// 165 k items).  Here a WARP owns a chunk and its lanes take the items, and the loop over an item's pieces is gone: the
+// item kernel leaves one 16-byte layout record per item and the copy kernel derives a piece's destination from it.
+struct TrcItemLay {
+  int64_t base;        // destination of piece j of the item = base + po[j]   (po = poff, or poffs with TRC_LAY_SUBS)
+  int32_t p1;          // last piece of the item; -1: the item's text is written by the sentence stage
+  uint32_t flags;
+};
+#define TRC_LAY_TS 1u
+#define TRC_LAY_COMB 2u
+#define TRC_LAY_SUBS 4u
+
+__global__ void k_chunk_record_w(TrcDev D) {
+  const int lane = threadIdx.x & 31;
+  for (int64_t c = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5; c < D.n_chunks; c += ((int64_t)gridDim.x * blockDim.x) >> 5) {
+    const int64_t a = D.cstart[c], b = D.cstart[c + 1];
+    if (lane == 0) trc_chunk_record_head(D, c);
+    // sorted distinct speaker ids: every round finds the smallest id above the last one found.  A lane keeps the
+    // speakers of its first four items in registers (chunks of up to 128 items never look an item up twice).
+    int32_t v[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { const int64_t t = a + lane + 32 * q; v[q] = t < b ? trc_item_speaker(D, t) : 0x7fffffff; }
+    int32_t* lst = D.spk_list + a;
+    int32_t ns = 0, cur = -1;
+    for (;;) {
+      uint32_t best = 0x7fffffffu;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) if (v[q] > cur && (uint32_t)v[q] < best) best = (uint32_t)v[q];
+      for (int64_t t = a + lane + 128; t < b; t += 32) { const int32_t w = trc_item_speaker(D, t); if (w > cur && (uint32_t)w < best) best = (uint32_t)w; }
+      best = __reduce_min_sync(0xffffffffu, best);
+      if (best == 0x7fffffffu) break;
+      if (lane == 0) lst[ns] = (int32_t)best;
+      ++ns; cur = (int32_t)best;
+    }
+    __syncwarp();
+    if (lane == 0) trc_chunk_record_tail(D, c, ns);
+  }
+}
+
+// One launch, two roles.  Blocks [0, hb): a warp per chunk writes the chunk's header.  Blocks [hb, ...): a thread per item
+// works out where the item's text goes (it_dst, from the chunk's offset, header length and the item-length prefix sums:
+// nothing the header role writes), writes the "\n\n" in front of it and the "[ts] speaker: " prefix of whole segments,
+// and leaves the layout record for k_emit_pieces_flat.
+__global__ void k_headers_items(TrcDev D, TrcItemLay* __restrict__ lay, int hb) {
+  if ((int)blockIdx.x < hb) {
+    const int lane = threadIdx.x & 31;
+    const int64_t c = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    if (c >= D.n_chunks || lane != 0) return;
+    TrcChunk& ch = D.chunks[c];
+    ch.twc_off = D.twc_scan[c];
+    if (D.add_context) {
+      uint8_t* dst = D.twc + ch.twc_off;
+      const int64_t o = trc_header<true>(D, ch, dst);
+      dst[o] = '\n'; dst[o + 1] = '\n';
+    }
+    return;
+  }
+  const int64_t t = ((int64_t)blockIdx.x - hb) * blockDim.x + threadIdx.x;
+  if (t >= D.n_items) return;
+  const int64_t c = D.cscanf[t + 1] - 1;
+  const TrcChunk& ch = D.chunks[c];
+  const int64_t dst_off = D.twc_scan[c] + (D.add_context ? ch.hdr_len + 2 : 0) + (D.L[t] - D.L[ch.item0]);
+  D.it_dst[t] = dst_off;
+  const int32_t g = D.it_group[t];
+  const int32_t s = D.it_sub[t];
+  TrcItemLay r; r.base = 0; r.p1 = -1; r.flags = 0;
+  if (s >= 0 && D.subs[s].kind != 0) { lay[t] = r; return; }             // sentence / clause items: k_emit_sent_recs
+  const int32_t ga = D.gstart[g], gb = D.gstart[g + 1];
+  const int32_t p0 = s >= 0 ? D.subs[s].r0 : ga;
+  const int32_t p1 = s >= 0 ? D.subs[s].r1 : gb - 1;
+  const bool comb = gb - ga > 1;
+  uint8_t* base = D.twc + dst_off;
+  int64_t pre = 0;
+  if (s < 0) {
+    const int32_t rr = D.k2r[ga];
+    const int32_t sp = D.spk[rr];
+    const int64_t so = D.spk_off[sp], sl = D.spk_off[sp + 1] - so;
+    uint8_t buf[TRC_TS_MAX + 4];
+    const int tl = trc_fmt_ts(D.start[rr], buf + 1);
+    buf[0] = '['; buf[tl + 1] = ']'; buf[tl + 2] = ' ';
+    for (int k = 0; k < tl + 3; ++k) base[k] = buf[k];
+    for (int64_t k = 0; k < sl; ++k) base[tl + 3 + k] = D.spk_bytes[so + k];
+    base[tl + 3 + sl] = ':'; base[tl + 4 + sl] = ' ';
+    pre = tl + 5 + sl;
+  }
+  if (t > ch.item0) { base[-2] = '\n'; base[-1] = '\n'; }
+  const int64_t* po = s >= 0 ? D.poffs : D.poff;
+  r.base = dst_off + pre - po[p0];
+  r.p1 = p1;
+  r.flags = ((comb && (D.preserve || s >= 0)) ? TRC_LAY_TS : 0u) | (comb ? TRC_LAY_COMB : 0u) | (s >= 0 ? TRC_LAY_SUBS : 0u);
+  lay[t] = r;
+}
+
 // 8 lanes per piece.  The body is copied in 4-byte words aligned to the DESTINATION (two aligned source
 // words + a funnel shift per destination word); head, tail and the "[ts] " prefix go byte by byte.
-__global__ void k_emit_pieces_flat(TrcDev D) {
+__global__ void k_emit_pieces_flat(TrcDev D, const TrcItemLay* __restrict__ lay) {
   for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; (q >> 3) < D.n_kept; q += (int64_t)gridDim.x * blockDim.x) {
     const int64_t j = q >> 3;
     const int lane = (int)(q & 7);
     // everything that only depends on j is requested at once (the kernel is bound by dependent-load latency)
-    const int64_t d = D.pdst[j];
-    const uint8_t f = D.pflag[j];
+    const int32_t t = D.pc_item[j];
     const int64_t c0 = D.coff[j], c1 = D.coff[j + 1];
     const double st = D.start[D.k2r[j]];
-    if (d < 0) continue;
+    const int64_t pa = D.poff[j], pb = D.poffs == D.poff ? pa : D.poffs[j];
+    if (t < 0) continue;                                     // (pdst stays -1: the piece belongs to a sentence-path item)
+    const int4 lr = __ldg(reinterpret_cast<const int4*>(lay + t));
+    const int32_t p1 = lr.z;
+    if (p1 < 0) continue;
+    const uint32_t lf = (uint32_t)lr.w;
+    const int64_t d = (((int64_t)(uint32_t)lr.y << 32) | (int64_t)(uint32_t)lr.x) + ((lf & TRC_LAY_SUBS) ? pb : pa);
+    const uint8_t f = (uint8_t)(((lf & TRC_LAY_TS) ? 1 : 0) | (((lf & TRC_LAY_COMB) && j < p1) ? 2 : 0));
+    if (lane == 0) D.pdst[j] = d;
     uint8_t* dst = D.twc + d;
     int64_t o = 0;
     if (f & 1) {
@@ -955,6 +1091,9 @@ static int orbit_marks(trc_ctx* ctx, cudaStream_t st, const int64_t* range_off, 
     CK(cudaGetLastError());
     return TRC_OK;
   }
+#endif
+#ifndef TRC_HOSTSIM
+  if (n_links >= 8 * n_doc) { LAUNCH_W(k_orbit_warp, n_doc, range_off, nxt, flag, n_doc); return TRC_OK; }
 #endif
   (void)n_links;
   LAUNCH(k_orbit, n_doc, 64, range_off, nxt, flag, n_doc);
@@ -1074,18 +1213,17 @@ static int count_units(trc_ctx* ctx, cudaStream_t st, const uint8_t* bytes, cons
 
 #ifndef TRC_HOSTSIM
 // Pre-pass for segments larger than a fused tile (trc_giant.cuh).  Leaves *V empty when there are none.
-static int giant_stage(trc_ctx* ctx, cudaStream_t st, int64_t braw, GiantView* V) {
+static int giant_stage(trc_ctx* ctx, cudaStream_t st, int64_t braw, GiantView* V, TileCand cand, int64_t tile_cap, int64_t* stats) {
   TrcDev& D = ctx->D;
   const int64_t n = D.n;
   int rc;
   {                                            // most batches have none: one counting pass decides
     unsigned long long* gcnt;
-    ALLOC(gcnt, unsigned long long, 1);
-    CK(cudaMemsetAsync(gcnt, 0, 8, st));
-    LAUNCH(k_giant_any, n, 256, D, gcnt);
-    int64_t any = 0;
-    if ((rc = read_back(ctx, st, gcnt, 8, &any))) return rc;
-    if (any == 0) return TRC_OK;
+    ALLOC(gcnt, unsigned long long, 5);
+    CK(cudaMemsetAsync(gcnt, 0, 40, st));
+    LAUNCH(k_giant_any, n, 256, D, gcnt, cand, tile_cap);
+    if ((rc = read_back(ctx, st, gcnt, 40, stats))) return rc;      // [0] oversized segments seen, [1..4] tiles that would not fit, per candidate
+    if (stats[0] == 0) return TRC_OK;
   }
   int32_t* gflag; int64_t* gscan;
   ALLOC(gflag, int32_t, n); ALLOC(gscan, int64_t, n + 1);
@@ -1252,6 +1390,8 @@ extern "C" int trc_load_vocab(trc_ctx* ctx, const uint8_t* token_bytes, const in
   }
   ctx->d_byte_id = (uint32_t*)byte_id;
   ctx->T.n_tok = V.n_tok; ctx->T.n_sp = V.n_sp;
+  ctx->T.tok_max_len = 0;
+  for (uint32_t r = 0; r < V.n_tok; ++r) { const uint32_t l = V.tok_off[r + 1] - V.tok_off[r]; if (l > ctx->T.tok_max_len) ctx->T.tok_max_len = l; }
   ctx->T.tokhash_mask = (uint32_t)V.tokhash.size() - 1;
   ctx->T.pairhash_mask = (uint32_t)V.pairhash.size() - 1;
   ctx->n_special = V.n_sp;
@@ -1412,9 +1552,41 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
         const double fit = (double)(F5_IN_CAP - 16) / (avg * 1.06 + 1.0);
         tsegs4 = fit >= F5_SEGS ? F5_SEGS : (fit < 1.0 ? 1 : (int)fit);
       }
-      const int64_t tile_segs = gen >= 4 ? tsegs4 : (gen >= 3 ? F3_SEGS : FUSE_SEGS);
-      const int64_t ntiles = (n + tile_segs - 1) / tile_segs;
+      // The pre-pass for oversized segments also says how many tiles of a few candidate sizes would not fit the fused
+      // kernel's tile buffer.  Such a tile takes the kernel's slow lane, and while its thread-per-segment cleaning runs
+      // every later tile waits for its byte count in the look-back (measured: 87 such tiles of 5 900 cost 1.7 ms of
+      // 2.2).  So generation 5 takes the largest candidate that fits everywhere, and when none does - oversized
+      // segments, heavy-tailed lengths - tiles of varying size (k_tile_flags).
       FuseArgs A;
+      A.G = GiantView{};
+      A.tile_start = nullptr;
+      int64_t ntiles_var = -1;
+      if (gen >= 3) {
+        TileCand cand{{0, 0, 0, 0}};
+        int64_t stats[5] = {0, 0, 0, 0, 0};
+        const char* forced = gen >= 5 ? getenv("TRCHUNK_TSEGS") : nullptr;          // experiments: a fixed tile size
+        if (forced) { const int v = atoi(forced); if (v >= 1 && v <= F5_SEGS) tsegs4 = v; else forced = nullptr; }
+        if (gen >= 5 && !forced) for (int q = 0; q < 4; ++q) { cand.v[q] = tsegs4 * (8 - q) / 8; if (cand.v[q] < 1) cand.v[q] = 1; }
+        if ((rc = giant_stage(ctx, st, braw, &A.G, cand, F5_IN_CAP, stats))) return rc;
+        if (gen >= 5 && !forced) {
+          int pick = -1;
+          if (stats[0] == 0) for (int q = 0; q < 4 && pick < 0; ++q) if (stats[1 + q] == 0) pick = q;
+          if (pick >= 0) tsegs4 = cand.v[pick];
+          else {
+            static_assert(F5_IN_CAP > TRC_GIANT_MIN + 16, "a window of the varying tiles");
+            int32_t* tflag; int64_t* tscan; int32_t* tstart;
+            ALLOC(tflag, int32_t, n); ALLOC(tscan, int64_t, n + 1);
+            LAUNCH(k_tile_flags, n, 256, D, tflag, (int64_t)(F5_IN_CAP - TRC_GIANT_MIN - 16), (int)F5_SEGS);
+            if ((rc = scan_excl(ctx, st, tflag, tscan, n))) return rc;
+            if ((rc = read_back(ctx, st, tscan + n, 8, &ntiles_var))) return rc;
+            ALLOC(tstart, int32_t, ntiles_var + 1);
+            LAUNCH(k_scatter_starts, n, 256, tflag, tscan, tstart, n);
+            A.tile_start = tstart;
+          }
+        }
+      }
+      const int64_t tile_segs = gen >= 4 ? tsegs4 : (gen >= 3 ? F3_SEGS : FUSE_SEGS);
+      const int64_t ntiles = ntiles_var >= 0 ? ntiles_var : (n + tile_segs - 1) / tile_segs;
       unsigned long long* fz;
       const int64_t ngroups = (ntiles + 31) / 32;
       ALLOC(fz, unsigned long long, 2 * ntiles + 3 * ngroups + 32);
@@ -1439,8 +1611,6 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
         CK(cudaMemsetAsync(ctx->d_memo, 0, bytes, st));
         A.memo = ctx->d_memo; A.memo_lock = (uint32_t*)(ctx->d_memo + 2 * ents); A.memo_mask = (uint32_t)(ents - 1);
       }
-      A.G = GiantView{};
-      if (gen >= 3) { if ((rc = giant_stage(ctx, st, braw, &A.G))) return rc; }
       static bool attr_done[64] = {false};
       if (!attr_done[ctx->device & 63]) {
         CK(cudaFuncSetAttribute(k_clean_tok_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FuseSmem)));
@@ -1570,6 +1740,8 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   ALLOC(D.ctok, uint32_t, nk); ALLOC(seg_special, int32_t, nk);
   if ((rc = count_units(ctx, st, D.C, D.coff, D.coff + 1, nk, bclean, 1, D.ctok, seg_special, true))) return rc;
   }
+  D.kspk = nullptr; D.kdur = nullptr;
+  if (D.merge && D.has_cap && !(modeB && B->group_off)) { ALLOC(D.kspk, int32_t, nk); ALLOC(D.kdur, double, nk); }
   LAUNCH(k_special_docs, nk, 256, D, seg_special, spk_special);
   LAUNCH(k_doc_err, nd, 128, D, seg_special, spk_special);
 
@@ -1634,7 +1806,13 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
 #endif
   // P5: group token totals, formatted lengths, formatted timestamps
   ALLOC(D.gts, uint8_t, m * 48); ALLOC(D.gtok, int64_t, m); ALLOC(D.glen, int64_t, m);
+#ifdef TRC_HOSTSIM
   if (nk >= 64 * m) LAUNCH_W(k_group_stats, m, D, ctx->T); else LAUNCH(k_group_stats_t, m, 128, D, ctx->T);
+#else
+  if (nk >= 64 * m) LAUNCH_W(k_group_stats, m, D, ctx->T);
+  else if (nk >= 4 * m) LAUNCH(k_group_stats_8, m * 8, 256, D, ctx->T);
+  else LAUNCH(k_group_stats_t, m, 128, D, ctx->T);
+#endif
   if (modeB && B->group_off) {
     if (m != B->n_groups) { ctx->err = "group_off does not describe the pieces"; return TRC_EINVAL; }
     const double* d_gs; const double* d_ge; const uint8_t* d_full; const int64_t* d_foff;
@@ -1813,19 +1991,40 @@ extern "C" int trc_chunk(trc_ctx* ctx, const int32_t* doc_max_tokens, int32_t co
   // C4: chunk records, headers
   ALLOC(D.chunks, TrcChunk, nc); ALLOC(D.spk_list, int32_t, ni); ALLOC(D.twc_len, int64_t, nc); ALLOC(D.twc_scan, int64_t, nc + 1);
   ALLOC(D.it_dst, int64_t, ni);
+#ifdef TRC_HOSTSIM
   LAUNCH(k_chunk_record, nc, 64, D);
+#else
+  LAUNCH_W(k_chunk_record_w, nc, D);
+#endif
   if ((rc = scan_excl(ctx, st, D.twc_len, D.twc_scan, nc))) return rc;
   int64_t h3[2] = {0, 0};
   if (nc || ni) { if ((rc = read_back2(ctx, st, nc ? D.twc_scan + nc : nullptr, ni ? D.W + ni : nullptr, h3))) return rc; }
   const int64_t btwc = h3[0];
   ctx->counts[TRC_B_TWC] = btwc; ctx->counts[TRC_TOKENS] = h3[1];
   ALLOC(D.twc, uint8_t, btwc);
-  LAUNCH(k_chunk_header, nc, 64, D);
   // C5: item text (layout per item, then a flat copy per piece)
-  ALLOC(D.pdst, int64_t, nk); ALLOC(D.pflag, uint8_t, nk);
+  ALLOC(D.pdst, int64_t, nk);
   CK(cudaMemsetAsync(D.pdst, 0xff, 8 * (size_t)(nk > 0 ? nk : 1), st));
+#ifdef TRC_HOSTSIM
+  ALLOC(D.pflag, uint8_t, nk);
+  LAUNCH(k_chunk_header, nc, 64, D);
   LAUNCH(k_item_layout, ni, 128, D);
   LAUNCH(k_emit_pieces_flat, nk * 8, 256, D);
+#else
+  {
+    TrcItemLay* lay;
+    ALLOC(lay, TrcItemLay, ni);
+    const int hb = (int)((nc * 32 + 255) / 256), ib = (int)((ni + 255) / 256);
+    if (hb + ib > 0) {
+      prof_begin(ctx, st, "k_headers_items");
+      k_headers_items<<<hb + ib, 256, 0, st>>>(D, lay, hb);
+      prof_end(ctx, st);
+      ctx->launches++;
+      CK(cudaGetLastError());
+    }
+    LAUNCH(k_emit_pieces_flat, nk * 8, 256, D, lay);
+  }
+#endif
   if (nraw > 0) { if ((rc = sentence_stage_emit(ctx, st))) return rc; }
   CK(cudaEventRecord(ctx->ev[3], st));
   ctx->ev_chunk = true;

@@ -54,3 +54,37 @@ def test_long_segments(gpu_engine, mean_len):
     segs.insert(7, {"start": 0.0, "end": 1.0, "text": " \t ", "speaker": "A"})
     segs.insert(9, {"start": 0.0, "end": 1.0, "text": "", "speaker": "A"})
     _run(gpu_engine, segs)
+
+
+def _tail_batch(seed, n, giant_every=0):
+    """Mostly short segments with a heavy tail up to ~4 KB (no fixed tile size fits everywhere), optionally an oversized
+    segment every `giant_every` segments."""
+    rng = random.Random(seed)
+    segs = []
+    for i in range(n):
+        u = rng.random()
+        L = rng.randint(0, 25) if u < 0.9 else (rng.randint(200, 1300) if u < 0.995 else rng.randint(1300, 1360))
+        if giant_every and i % giant_every == giant_every // 2:
+            L = rng.randint(1500, 9000)
+        segs.append({"start": float(i), "end": float(i + 1), "text": "".join(rng.choice(ALPHA) for _ in range(L)), "speaker": "A"})
+    return segs
+
+
+@pytest.mark.parametrize("giant_every", [0, 97])
+def test_tiles_of_varying_size(gpu_engine, giant_every):
+    """Heavy-tailed lengths, and oversized segments between short ones: the pre-pass finds no fixed tile size that fits
+    everywhere (or sees an oversized segment) and the fused kernel runs on tiles cut by byte windows (k_tile_flags)."""
+    _run(gpu_engine, _tail_batch(11 + giant_every, 6000, giant_every))
+
+
+@pytest.mark.parametrize("tsegs", ["128", "40", "3"])
+def test_forced_tile_sizes_take_the_slow_lane(tsegs, monkeypatch):
+    """TRCHUNK_TSEGS pins the tile size: with 128 segments per tile most tiles of this batch exceed the tile buffer and go
+    through the slow lane (thread-per-segment routines), which the automatic choice avoids."""
+    monkeypatch.setenv("TRCHUNK_TSEGS", tsegs)
+    eng = E.Engine(0)
+    try:
+        _run(eng, _tail_batch(5, 3000, 0))
+        _run(eng, _tail_batch(6, 1500, 200))
+    finally:
+        eng.close()

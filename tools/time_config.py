@@ -8,9 +8,10 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--config", type=int, default=4)
 ap.add_argument("--scale", type=float, default=1.0)
 ap.add_argument("--steps", type=int, default=3)
+ap.add_argument("--lexicon", type=int, default=0)
 a = ap.parse_args()
 eng = E.Engine(0)
-t = time.time(); b, mt, desc = synth.config(a.config, a.scale); print(desc, "generated in %.1fs" % (time.time() - t), b.n_seg, len(b.text))
+t = time.time(); b, mt, desc = synth.config(a.config, a.scale, lexicon=a.lexicon) if a.lexicon else synth.config(a.config, a.scale); print(desc, "generated in %.1fs" % (time.time() - t), b.n_seg, len(b.text))
 dev = torch.device("cuda", 0)
 dt = {k: torch.from_numpy(getattr(b, k)).to(dev) for k in ("text", "seg_off", "start", "end", "speaker", "doc_off", "spk_bytes", "spk_off")}
 ptrs = {k: v.data_ptr() for k, v in dt.items()}
