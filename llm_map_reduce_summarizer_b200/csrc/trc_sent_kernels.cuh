@@ -485,7 +485,46 @@ __global__ void k_sent_greedy_write(TrcDev D, TrcSentState S) {
 }
 #endif
 
-// K6 for sentence/clause records: "[ts] text" (+ joining space) into the item text; warp per record
+// K6 for sentence/clause records: "[ts] text" (+ joining space) into the item text; warp per record (test build), eight
+// lanes per record (CUDA build: a sentence is ~35 bytes; a warp each left three quarters of the lanes without a byte)
+#ifndef TRC_HOSTSIM
+__global__ void k_emit_sent_recs(TrcDev D, TrcSentState S) {
+  for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; (q >> 3) < S.n_recs; q += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = q >> 3;
+    const int lane = (int)(q & 7);
+    const TrcSent* Rp = S.recs + r;
+    const int32_t sub = Rp->sub;
+    if (sub < 0) continue;
+    const int64_t off = Rp->off, len = Rp->len, ois = Rp->off_in_sub;
+    const double st = Rp->start;
+    const int32_t last = Rp->last_in_sub;
+    const int32_t grp = D.subs[sub].group;
+    const int64_t t = D.item_off[grp] + (sub - D.sub_off[grp]);
+    uint8_t* base = D.twc + D.it_dst[t];
+    if (ois == 0 && lane == 0 && t > D.chunks[D.cscanf[t + 1] - 1].item0) { base[-2] = '\n'; base[-1] = '\n'; }
+    uint8_t* dst = base + ois;
+    int64_t h; int m, sec;
+    trc_ts_split(st, &h, &m, &sec);
+    int o;
+    if (h <= 0) {                          // "[MM:SS] ": one byte per lane
+      const unsigned long long pre = (unsigned long long)'[' | ((unsigned long long)('0' + m / 10) << 8) | ((unsigned long long)('0' + m % 10) << 16) |
+                                     ((unsigned long long)':' << 24) | ((unsigned long long)('0' + sec / 10) << 32) |
+                                     ((unsigned long long)('0' + sec % 10) << 40) | ((unsigned long long)']' << 48) | ((unsigned long long)' ' << 56);
+      dst[lane] = (uint8_t)(pre >> (8 * lane));
+      o = 8;
+    } else {
+      uint8_t buf[TRC_TS_MAX + 4];
+      const int tl = trc_fmt_ts(st, buf + 1);
+      buf[0] = '['; buf[tl + 1] = ']'; buf[tl + 2] = ' ';
+      for (int k = lane; k < tl + 3; k += 8) dst[k] = buf[k];
+      o = tl + 3;
+    }
+    const uint8_t* src = D.C + off;
+    for (int64_t k = lane; k < len; k += 8) dst[o + k] = src[k];
+    if (!last && lane == 7) dst[o + len] = ' ';
+  }
+}
+#else
 __global__ void k_emit_sent_recs(TrcDev D, TrcSentState S) {
   WSTRIDE(r, S.n_recs) {
     const TrcSent R = S.recs[r];
@@ -505,6 +544,7 @@ __global__ void k_emit_sent_recs(TrcDev D, TrcSentState S) {
     if (!R.last_in_sub && lane == 0) dst[tl + 3 + R.len] = ' ';
   }
 }
+#endif
 
 // ---- host staging -----------------------------------------------------------------------------------------
 static int count_units(trc_ctx* ctx, cudaStream_t st, const uint8_t* bytes, const int64_t* ustart, const int64_t* uend,
@@ -606,6 +646,10 @@ static int sentence_stage_write(trc_ctx* ctx, cudaStream_t st, const int32_t*) {
   return TRC_OK;
 }
 static int sentence_stage_emit(trc_ctx* ctx, cudaStream_t st) {
+#ifdef TRC_HOSTSIM
   LAUNCH_W(k_emit_sent_recs, ctx->SS.n_recs, ctx->D, ctx->SS);
+#else
+  LAUNCH(k_emit_sent_recs, ctx->SS.n_recs * 8, 256, ctx->D, ctx->SS);
+#endif
   return TRC_OK;
 }

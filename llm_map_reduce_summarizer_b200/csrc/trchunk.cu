@@ -716,20 +716,62 @@ __global__ void k_orbit(const int64_t* __restrict__ range_off, const int32_t* __
   GSTRIDE(x, n_doc) trc_orbit_walk(range_off, nxt, flag, x);
 }
 #ifndef TRC_HOSTSIM
-// Orbit of ONE long chain (a single huge document: config 4 walks 10 k chunk starts one after the other).  The hops are a
-// dependent chain whatever is done, so the link array is staged in shared memory first (coalesced, by the whole block)
-// and one thread walks it there: ~30 cycles per hop instead of an L2 round trip.  Ranges of up to ORBIT_SMEM links.
+// Orbit of ONE long chain (a single huge document: config 4 walks 2 k merged-segment starts over 1 M pieces, then 10 k chunk
+// starts over 10 k items).  The hops are a dependent chain, so the links are staged in shared memory by the whole block:
+//  * up to ORBIT_DBL links: pointer doubling.  reach = {f^k(first) : k < 2^r} and J = f^(2^r) after r rounds; a round marks
+//    J(reach) and squares J, all threads at once; it ends when J(first) has left the range.  10 k hops take 14 rounds of a
+//    few hundred cycles instead of 10 k shared-memory round trips by one thread (308 us -> ~10 us);
+//  * longer ranges: the links only point forward, so the range is staged window by window and one thread walks each window
+//    in shared memory (~30 cycles per hop instead of an L2 round trip).
 #define ORBIT_SMEM 49152
+#define ORBIT_DBL 20480
 __global__ void __launch_bounds__(1024) k_orbit_staged(const int64_t* __restrict__ range_off, const int32_t* __restrict__ nxt, int32_t* flag, int64_t n_doc) {
   extern __shared__ int32_t s_nxt[];
+  __shared__ int64_t s_pos;
   for (int64_t x = blockIdx.x; x < n_doc; x += gridDim.x) {
     const int64_t a = range_off[x], b = range_off[x + 1];
     const int64_t n = b - a;
     if (n <= 0) continue;
-    if (n > ORBIT_SMEM) { if (threadIdx.x == 0) trc_orbit_walk(range_off, nxt, flag, x); continue; }
-    for (int64_t k = threadIdx.x; k < n; k += blockDim.x) s_nxt[k] = (int32_t)(nxt[a + k] - a);
+    if (n <= ORBIT_DBL) {
+      const int32_t nn = (int32_t)n;
+      int32_t* Jc = s_nxt; int32_t* Jn = s_nxt + nn;
+      uint8_t* reach = reinterpret_cast<uint8_t*>(s_nxt + 2 * nn);
+      for (int32_t k = threadIdx.x; k < nn; k += blockDim.x) {
+        const int64_t t = (int64_t)nxt[a + k] - a;
+        Jc[k] = t < nn ? (int32_t)t : nn;
+        reach[k] = k == 0;
+      }
+      __syncthreads();
+      for (;;) {
+        for (int32_t k = threadIdx.x; k < nn; k += blockDim.x) {
+          const int32_t t = Jc[k];
+          if (t < nn) { if (reach[k]) reach[t] = 1; Jn[k] = Jc[t]; } else Jn[k] = nn;
+        }
+        __syncthreads();
+        int32_t* tmp = Jc; Jc = Jn; Jn = tmp;
+        if (Jc[0] >= nn) break;
+        __syncthreads();
+      }
+      __syncthreads();
+      for (int32_t k = threadIdx.x; k < nn; k += blockDim.x) if (reach[k]) flag[a + k] = 1;
+      __syncthreads();
+      continue;
+    }
+    if (threadIdx.x == 0) s_pos = 0;
     __syncthreads();
-    if (threadIdx.x == 0) { int32_t p = 0; while (p < n) { flag[a + p] = 1; p = s_nxt[p]; } }
+    for (;;) {
+      const int64_t w0 = s_pos;
+      if (w0 >= n) break;
+      const int64_t cnt = (n - w0) < ORBIT_SMEM ? (n - w0) : ORBIT_SMEM;
+      for (int64_t k = threadIdx.x; k < cnt; k += blockDim.x) s_nxt[k] = (int32_t)(nxt[a + w0 + k] - a - w0);   // relative to the window
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        int64_t p = 0;
+        while (p < cnt) { flag[a + w0 + p] = 1; p = s_nxt[p]; }
+        s_pos = w0 + p;
+      }
+      __syncthreads();
+    }
     __syncthreads();
   }
 }

@@ -26,5 +26,5 @@ prof = eng.profile()
 c = eng.counts()
 print(c)
 print("wall ms/step %.3f  tokens/s %.3e" % (wall * 1e3, c["tokens"] / wall))
-for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0])[:12]:
+for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0])[:int(os.environ.get("TOP", "12"))]:
     print("  %-24s %.3f ms/step (%d launches)" % (k, v[0] / a.steps, v[1] // a.steps))
