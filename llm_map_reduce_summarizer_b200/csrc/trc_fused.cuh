@@ -69,6 +69,9 @@ struct FuseArgs {
   unsigned long long* grp_cnt; unsigned long long* grp_bytes; unsigned long long* grp_kept;
   unsigned long long* wstat;        // [0] words through the word-level counter, [1] first sightings, [2] words left to the generic matcher
   const int32_t* tile_start;        // k_clean_tok_c32: first segment of every tile (+ n at the end), or null: tile t = segments [t * tsegs, ...)
+  // cut mode of k_clean_tok_c32 (oversized segments cut into parts, trc_giant.cuh): per segment of the launch the caller's
+  // segment it belongs to, and whether it continues one; per kept record the first special-token hit (position << 4 | k)
+  const int32_t* vorig; const uint8_t* vcont; unsigned long long* special_pos;
 };
 #define FUSE_PH(i) do { if (A.phase && tid == 0) { long long now_ = clock64(); atomicAdd(&A.phase[i], (unsigned long long)(now_ - ph_t)); ph_t = now_; } } while (0)
 

@@ -29,7 +29,8 @@
 #define F5_OUT_CAP (F5_IN_CAP + F5_IN_CAP / 2)
 #define F5_WORD_CAP (F5_T * 11)
 #define F5_SLOW_CAP (F5_T * 2)
-#define F5_NM 14
+#define F5_NM 15
+#define F5_NOLEAD 14                            // mask row: starts of segments that continue a cut oversized segment
 #define F5_MATCH_T (F5_T / 4)                   // threads that run the packed-word matcher when only a few words are queued
 #define F5_HOT (F5_T * 4)                       // entries of the CTA's word cache
 
@@ -51,7 +52,8 @@ struct F5Smem {
   int32_t spmin[F5_SEGS];
   uint16_t loff[F5_SEGS + 1];
   uint16_t wfirst[F5_SEGS + 1];
-  uint16_t koff[F5_SEGS];
+  uint8_t cont[F5_SEGS];                        // cut mode: the segment continues an oversized segment
+  int16_t koff[F5_SEGS];                        // kept record of the segment relative to the tile's first (-1: a record of an earlier tile)
   uint16_t kr[F5_SEGS + 4];                     // by rank among the non-empty raw segments: kept segments up to it
   uint32_t wsa[F5_NW], wsb[F5_NW];              // warp totals of the block scans
   int32_t wsum[3][F5_NW];
@@ -183,6 +185,11 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
   W32 M;
   M.sp = S.u.m[F4_SP] + 1; M.w = S.u.m[F4_W] + 1; M.ct = S.u.m[F4_CT] + 1; M.bd = S.u.m[F4_BD] + 1; M.ep = S.u.m[F4_EP] + 1;
   M.lt = S.u.m[F4_LT] + 1; M.drop = S.u.m[F4_DROP] + 1; M.ds = S.u.m[F4_DS] + 1;
+  // Cut mode (A.vcont): oversized segments arrive cut into parts in front of whitespace runs (k_cut_find); a part that
+  // continues a segment keeps its leading whitespace (one space), opens no kept record and adds its bytes, tokens and
+  // code points to the record of the part that started the segment - the most recent record before it.
+  const bool cutmode = A.vcont != nullptr;
+  if (cutmode) M.nolead = S.u.m[F5_NOLEAD] + 1;
   uint32_t* const c_cp = S.u.m[F4_COPY] + 1; uint32_t* const c_se = S.u.m[F4_SPACE] + 1; uint32_t* const c_in = S.u.m[F4_INS] + 1;
   uint32_t* const p_os = S.u.m[F4_PRE_OS] + 1; uint32_t* const p_tb = S.u.m[F4_PRE_TB] + 1; uint32_t* const m_ns = S.u.m[F4_NS] + 1;
   uint32_t parity = 0;
@@ -228,11 +235,12 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
       }
     }
     if (wid == F5_NW - 1) {                   // document of the first segment: one 32-ary search per tile, under the tile load
+      const int64_t s0o = A.vorig ? (int64_t)A.vorig[s0] : s0;       // (doc_off counts the caller's segments)
       int64_t lo = 0, hi = D.n_doc;
       while (hi - lo > 1) {
         const int64_t step = (hi - lo + 31) >> 5;
         const int64_t pv = lo + step * (lane + 1);
-        const bool le = pv < hi && D.doc_off[pv] <= s0;
+        const bool le = pv < hi && D.doc_off[pv] <= s0o;
         const int cnt = __popc(__ballot_sync(0xffffffffu, le));
         const int64_t nhi = lo + step * (cnt + 1);
         lo += step * cnt;
@@ -242,6 +250,7 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
     }
     for (int k = tid; k <= ns; k += F5_T) S.rel[k] = (int32_t)((D.seg_off[s0 + k] - base) < (1 << 30) ? (D.seg_off[s0 + k] - base) : (1 << 30));
     int32_t mylen = 0, mynw = 0, mykeep = 0, mychars = 0, loff = 0, woff = 0, koff = 0, mytok = 0, mysp = -1;
+    const int mycont = (cutmode && tid < ns) ? (int)A.vcont[s0 + tid] : 0;
     int32_t tot_out = 0, tot_words = 0, tot_kept = 0;
     long long gbase = 0, kbase = 0;
     bool fast_out = false;
@@ -252,6 +261,7 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
       // rows built with atomic ORs, "nothing there" on both sides of the tile
       S.u.m[F4_BD][tid] = 0u; S.u.m[F4_DROP][tid] = 0u; S.u.m[F4_DS][tid] = 0u;
       if (tid < 2) { S.u.m[F4_BD][F5_NCH + tid] = 0u; S.u.m[F4_DROP][F5_NCH + tid] = 0u; S.u.m[F4_DS][F5_NCH + tid] = 0u; }
+      if (cutmode) { S.u.m[F5_NOLEAD][tid] = 0u; if (tid < 2) S.u.m[F5_NOLEAD][F5_NCH + tid] = 0u; }
       if (tid < F5_NM) { S.u.m[tid][0] = 0u; S.u.m[tid][nch + 1] = 0u; }
       if (tid < F5_SEGS) { S.xtok[tid] = 0; S.spmin[tid] = 0x7fffffff; }
       if (tid == 0) S.sfflag = 0;
@@ -259,7 +269,7 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
       for (int32_t k = (int32_t)n16 + tid; k < span; k += F5_T) S.y.in[k] = D.text[base + k];
       __syncthreads();
       FUSE_PH(0);
-      if (tid < ns) { const int32_t a = S.rel[tid], b = S.rel[tid + 1]; if (b > a) w32_or_bit(M.bd, a); }
+      if (tid < ns) { const int32_t a = S.rel[tid], b = S.rel[tid + 1]; if (b > a) { w32_or_bit(M.bd, a); if (mycont) w32_or_bit(S.u.m[F5_NOLEAD] + 1, a); } }
       // ---- P1: classes of this thread's chunk (lead bytes of multi-byte characters are parked in the COPY row)
       uint32_t lead = 0, sf = 0;
       const uint32_t valid = w32_valid(c, al, span);
@@ -348,8 +358,8 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
             if (e == 0) br = (int32_t)(tb >> 16) + __popc(M.bd[cc] & below);
           }
         }
-        loff = pv[0][0]; mylen = pv[1][0] - pv[0][0]; mykeep = mylen > 0;
-        mynw = mykeep ? pv[1][1] - pv[0][1] + 1 : 0;
+        loff = pv[0][0]; mylen = pv[1][0] - pv[0][0]; mykeep = mylen > 0 && !mycont;       // a record, and a first word with a virtual space
+        mynw = mylen > 0 ? pv[1][1] - pv[0][1] + (mycont ? 0 : 1) : 0;
         mychars = mylen - (pv[1][2] - pv[0][2]);
         nonempty = S.rel[tid + 1] > S.rel[tid];
       }
@@ -358,7 +368,7 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
       tot_kept = S.tot[0]; tot_words = S.tot[1];
       if (tid == 0) { fuse_publish(A.desc_bytes, tile, tot_out); fuse_publish(A.desc_kept, tile, tot_kept); }
       fast_out = tot_words <= F5_WORD_CAP;
-      if (tid < ns) { S.loff[tid] = (uint16_t)loff; S.wfirst[tid] = (uint16_t)woff; S.koff[tid] = (uint16_t)koff; }
+      if (tid < ns) { S.loff[tid] = (uint16_t)loff; S.wfirst[tid] = (uint16_t)woff; S.koff[tid] = (int16_t)(koff - mycont); S.cont[tid] = (uint8_t)mycont; }
       if (tid == 0) { S.loff[ns] = (uint16_t)tot_out; S.wfirst[ns] = (uint16_t)tot_words; }
       if (nonempty) S.kr[br] = (uint16_t)(koff + (mykeep ? 1 : 0));
       FUSE_PH(4);
@@ -570,7 +580,11 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
             const uint32_t cc = trc_count_unit(T, F, byte_id, S.out + st, n, vs, [&](int64_t ls, int64_t len) -> uint32_t {
               const unsigned long long slot = atomicAdd(&A.wl_cnt[0], 1ULL);
               const unsigned long long off = atomicAdd(&A.wl_cnt[1], (unsigned long long)len);
-              if ((int64_t)slot < A.wl_cap) { LongEntry le; le.unit = j; le.lstart = ls + (vs ? 0 : (st - sl + 1)); le.len = len; le.scratch_off = (int64_t)off; A.wl[slot] = le; }
+              if ((int64_t)slot < A.wl_cap) {
+                LongEntry le; le.unit = j; le.len = len; le.scratch_off = (int64_t)off;
+                le.lstart = S.cont[seg] ? -1 - (gbase + st + ls) : ls + (vs ? 0 : (st - sl + 1));     // (a part: absolute position in the cleaned text)
+                A.wl[slot] = le;
+              }
               return 0u;
             });
             cnt[w] = 0;
@@ -578,7 +592,7 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
           }
         }
         __syncthreads();
-        if (tid < ns && mykeep) {                      // per segment: sum of its words
+        if (tid < ns && mylen > 0) {                   // per segment: sum of its words
           int32_t t = S.xtok[tid];
           const int32_t w1 = woff + mynw;
           for (int32_t w = woff; w < w1; ++w) t += cnt[w];
@@ -598,13 +612,13 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
         gbase = S.gbase; kbase = S.kbase;
         f3_copy_out(D.C + gbase, S.out, tot_out, tid, F5_T);
         if (tid < ns && mylen > 0) {
-          const int64_t j = kbase + koff;
+          const int64_t j = kbase + koff - mycont;
           const uint8_t* p = S.out + loff;
           const int32_t len0 = mylen;
-          const uint32_t cc = trc_count_unit(T, F, byte_id, p, len0, 1, [&](int64_t ls, int64_t len) -> uint32_t {
+          const uint32_t cc = trc_count_unit(T, F, byte_id, p, len0, mycont ? 0 : 1, [&](int64_t ls, int64_t len) -> uint32_t {
             const unsigned long long slot = atomicAdd(&A.wl_cnt[0], 1ULL);
             const unsigned long long off = atomicAdd(&A.wl_cnt[1], (unsigned long long)len);
-            if ((int64_t)slot < A.wl_cap) { LongEntry le; le.unit = j; le.lstart = ls; le.len = len; le.scratch_off = (int64_t)off; A.wl[slot] = le; }
+            if ((int64_t)slot < A.wl_cap) { LongEntry le; le.unit = j; le.lstart = mycont ? -1 - (gbase + loff + ls) : ls; le.len = len; le.scratch_off = (int64_t)off; A.wl[slot] = le; }
             return 0u;
           });
           mytok = (int32_t)cc;
@@ -613,6 +627,8 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
       }
     } else {
       // ================= slow lane: sequential per-segment routines on global memory; giants come pre-cleaned =====
+      // (never in cut mode: its tiles always fit and no oversized segment is left; the host checks this counter)
+      if (cutmode && tid == 0) atomicAdd(&A.wstat[3], 1ULL);
       const uint8_t* src = D.text + base;
       int64_t a = 0, b = 0;
       if (tid < ns) {
@@ -668,12 +684,22 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
     }
     FUSE_PH(7);
     // ---- outputs
+    if (tid < ns && cutmode) {                 // counts are sums over the parts of a segment: everything was zeroed before the launch
+      const int64_t io = A.vorig[s0 + tid];
+      if (mychars) atomicAdd(&D.cchars[io], mychars);
+      if (mylen > 0) {
+        const int64_t jo = kbase + koff - mycont;
+        if (mytok) atomicAdd(&D.ctok[jo], (uint32_t)mytok);
+        if (mysp >= 0) atomicMin(&A.special_pos[jo], (unsigned long long)(((gbase + loff) << 4) | mysp));
+      }
+    }
     if (tid < ns) {
-      D.cchars[s0 + tid] = mychars;
+      if (!cutmode) D.cchars[s0 + tid] = mychars;
       if (mykeep) {
         const int64_t j = kbase + koff;
-        const int64_t i = s0 + tid;
-        D.k2r[j] = (int32_t)i; D.coff[j] = gbase + loff; D.ctok[j] = (uint32_t)mytok; A.seg_special[j] = mysp;
+        const int64_t i = A.vorig ? (int64_t)A.vorig[s0 + tid] : s0 + tid;
+        D.k2r[j] = (int32_t)i; D.coff[j] = gbase + loff;
+        if (!cutmode) { D.ctok[j] = (uint32_t)mytok; A.seg_special[j] = mysp; }
         int64_t lo = S.doc0;                  // documents are rarely shorter than a few segments: walk, then search
         for (int q = 0; q < 4 && D.doc_off[lo + 1] <= i; ++q) ++lo;
         if (D.doc_off[lo + 1] <= i) {

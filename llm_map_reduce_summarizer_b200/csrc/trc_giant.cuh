@@ -26,12 +26,13 @@ struct GiantState {
 
 // cnt[0]: warps that saw an oversized segment.  cnt[1 + q]: tiles of cand.v[q] segments whose raw bytes would not fit a
 // tile of the fused kernel (`cap` bytes from the 16-byte aligned start) - the host picks the tile size from these.
-struct TileCand { int v[4]; };
+struct TileCand { int v[4]; int all8; };   // all8: every candidate is a multiple of 8 (only every eighth segment can start a tile)
 __global__ void k_giant_any(TrcDev D, unsigned long long* cnt, TileCand cand, int64_t cap) {
   int found = 0;
   GSTRIDE(i, D.n) {
     const int64_t a = D.seg_off[i];
     found |= (D.seg_off[i + 1] - a) > TRC_GIANT_MIN;
+    if (cand.all8 && (i & 7)) continue;
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const int ts = cand.v[q];
@@ -64,6 +65,81 @@ __global__ void k_giant_list(TrcDev D, const int32_t* __restrict__ flag, const i
     else of_seg[i] = -1;
   }
 }
+// ---- cutting oversized segments into parts (generation 5) ----------------------------------------------------------------
+// An oversized segment is handed to the fused kernel as PARTS of at most TRC_CUT_STEP + TRC_CUT_SEARCH bytes.  A cut sits
+// in front of a whitespace run that follows an ASCII non-whitespace byte, so the part before it ends in text and the
+// part after it starts with the run; the kernel lets a continuing part keep that run (one space), and the cleaned parts
+// back to back ARE the cleaned segment, provided no rule of clean_text looks across the cut:
+//  * whitespace collapse and strip (preprocessor.py:72): the run lies inside one part;
+//  * duplicate words (:76): only fires if the word before the run equals the word after it - a cut is taken only where
+//    they differ in their last byte, where one of them is no \w-run at all, or where nothing follows the run;
+//  * space after . ! ? (:80): needs a letter right after the mark, and a whitespace byte follows the part's last byte.
+// One thread per cut target (every TRC_CUT_STEP bytes) looks for the first such place within TRC_CUT_SEARCH bytes.  A
+// target without one is skipped; when that leaves a part too long for a tile (kilobytes of one repeated word, non-ASCII
+// text without ASCII whitespace) *bad is set and the batch takes the byte-parallel pre-pass below instead.
+#define TRC_CUT_STEP 2048
+#define TRC_CUT_SEARCH 1024
+__global__ void k_cut_counts(const int64_t* __restrict__ len, int64_t ng, int32_t* tcnt) { GSTRIDE(q, ng) tcnt[q] = (int32_t)((len[q] - 1) / TRC_CUT_STEP); }
+__global__ void k_cut_find(TrcDev D, TrcTables T, const int32_t* __restrict__ list, const int64_t* __restrict__ len, const int64_t* __restrict__ tpre,
+                           int64_t ng, int64_t nt, int64_t* cutpos) {
+  GSTRIDE(t, nt) {
+    int64_t lo = 0, hi = ng;
+    while (hi - lo > 1) { const int64_t mid = (lo + hi) >> 1; if (tpre[mid] <= t) lo = mid; else hi = mid; }
+    const int64_t c = t - tpre[lo] + 1;                       // the c-th target of this segment
+    const int64_t s = D.seg_off[list[lo]], L = len[lo];
+    const uint8_t* p = D.text + s;
+    int64_t k = c * TRC_CUT_STEP;
+    const int64_t lim = k + TRC_CUT_SEARCH < L ? k + TRC_CUT_SEARCH : L;
+    int64_t found = -1;
+    while (k < lim) {
+      const uint8_t b = p[k], a = p[k - 1];
+      if (!(b < 0x80 && (T.props[b] & TRC_P_SPACE) && a < 0x80 && !(T.props[a] & TRC_P_SPACE))) { ++k; continue; }
+      int64_t r = k + 1;                                      // the whitespace run [k, r)
+      bool ascii = true;
+      while (r < L) { const uint8_t x = p[r]; if (x >= 0x80) { ascii = false; break; } if (!(T.props[x] & TRC_P_SPACE)) break; ++r; }
+      if (!ascii) { k = r + 1; continue; }                    // the run may go on with a multi-byte character: not decided here
+      if (r == L) { found = k; break; }                       // nothing but whitespace follows
+      int64_t e = r;                                          // the \w-run [r, e) after it
+      while (e < L) { const uint8_t x = p[e]; if (x >= 0x80) { ascii = false; break; } if (!(T.props[x] & TRC_P_WORD)) break; ++e; }
+      if (!ascii) { k = e + 1; continue; }
+      if (e == r || !(T.props[a] & TRC_P_WORD) || p[e - 1] != a) { found = k; break; }
+      k = e;                                                  // same last byte: the words may be equal
+    }
+    cutpos[t] = found < 0 ? -1 : s + found;                   // -1: no cut at this target (k_vseg_build makes the part before it longer)
+  }
+}
+// The segment list the fused kernel sees: the caller's segments with every oversized one replaced by its parts.
+// A target without a cut leaves an EMPTY part behind (its start is the next part's start), so the part in front of it grows
+// by a step; it still has to fit a tile of the fused kernel on its own (max_part), else *bad is set.
+__global__ void k_vseg_build(TrcDev D, const int32_t* __restrict__ gflag, const int64_t* __restrict__ gscan, const int64_t* __restrict__ tpre,
+                             const int64_t* __restrict__ cutpos, int64_t nt, int64_t* vseg_off, int32_t* vorig, uint8_t* vcont,
+                             int64_t max_part, unsigned long long* bad) {
+  GSTRIDE(i, D.n) {
+    const int64_t q = gscan[i];                               // oversized segments before i
+    const int64_t v = i + tpre[q];
+    vseg_off[v] = D.seg_off[i]; vorig[v] = (int32_t)i; vcont[v] = 0;
+    if (gflag[i]) {
+      const int64_t t0 = tpre[q], t1 = tpre[q + 1];
+      int64_t nxt = D.seg_off[i + 1];                         // start of the part after the one being laid down
+      bool too_long = false;
+      for (int64_t t = t1 - 1; t >= t0; --t) {
+        const int64_t u = v + 1 + (t - t0);
+        const int64_t cpos = cutpos[t] < 0 ? nxt : cutpos[t];
+        too_long |= nxt - cpos > max_part;
+        vseg_off[u] = cpos; vorig[u] = (int32_t)i; vcont[u] = 1;
+        nxt = cpos;
+      }
+      too_long |= nxt - D.seg_off[i] > max_part;
+      if (too_long) atomicAdd(bad, 1ULL);
+    }
+    if (i == D.n - 1) vseg_off[D.n + nt] = D.seg_off[D.n];
+  }
+}
+__global__ void k_special_from_pos(const unsigned long long* __restrict__ pos, int64_t nk, int32_t* seg_special) {
+  GSTRIDE(j, nk) seg_special[j] = pos[j] == ~0ULL ? -1 : (int32_t)(pos[j] & 15ULL);
+}
+struct CutView { int64_t nv; const int64_t* vseg_off; const int32_t* vorig; const uint8_t* vcont; unsigned long long* bad; };
+
 __device__ __forceinline__ int64_t giant_of_byte(const GiantState& G, int64_t p) {
   int64_t lo = 0, hi = G.ng;
   while (hi - lo > 1) { int64_t mid = (lo + hi) >> 1; if (G.boff[mid] <= p) lo = mid; else hi = mid; }

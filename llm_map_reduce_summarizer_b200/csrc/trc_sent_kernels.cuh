@@ -548,7 +548,7 @@ __global__ void k_emit_sent_recs(TrcDev D, TrcSentState S) {
 
 // ---- host staging -----------------------------------------------------------------------------------------
 static int count_units(trc_ctx* ctx, cudaStream_t st, const uint8_t* bytes, const int64_t* ustart, const int64_t* uend,
-                       int64_t n, int64_t total_bytes, int vs, uint32_t* counts, int32_t* special, bool allow_sync_free);
+                       int64_t n, int64_t total_bytes, int vs, uint32_t* counts, int32_t* special, bool allow_sync_free, int64_t coop_min);
 
 static int sentence_stage_count(trc_ctx* ctx, cudaStream_t st, int32_t* nsub_g, int32_t nraw) {
   TrcDev& D = ctx->D;
@@ -592,8 +592,8 @@ static int sentence_stage_count(trc_ctx* ctx, cudaStream_t st, int32_t* nsub_g, 
   int64_t* wsum; int64_t* tst; int64_t* ten; uint32_t* tcnt;
   ALLOC(wsum, int64_t, S.n_sent); ALLOC(tst, int64_t, S.n_sent); ALLOC(ten, int64_t, S.n_sent); ALLOC(tcnt, uint32_t, S.n_sent);
   LAUNCH(k_sent_wordsum, S.n_sent, 128, D, S, ctx->WS, (int64_t)0, S.n_sent, ustart, uend, tst, ten, wsum);
-  if ((rc = count_units(ctx, st, D.C, ustart, uend, S.n_sent, total, 1, cnt, nullptr, false))) return rc;
-  if (ctx->WS.of_seg) { if ((rc = count_units(ctx, st, D.C, tst, ten, S.n_sent, total, 0, tcnt, nullptr, false))) return rc; }
+  if ((rc = count_units(ctx, st, D.C, ustart, uend, S.n_sent, total, 1, cnt, nullptr, false, 512))) return rc;
+  if (ctx->WS.of_seg) { if ((rc = count_units(ctx, st, D.C, tst, ten, S.n_sent, total, 0, tcnt, nullptr, false, 512))) return rc; }
 #ifdef TRC_HOSTSIM
   LAUNCH(k_sent_tok, S.n_sent, 128, D, ctx->T, S, ustart, uend, tst, ten, wsum, cnt, tcnt, ncl, (int64_t*)nullptr, (unsigned long long*)nullptr);
 #else
@@ -633,8 +633,8 @@ static int sentence_stage_count(trc_ctx* ctx, cudaStream_t st, int32_t* nsub_g, 
     int64_t* cwsum; int64_t* cts; int64_t* cte; uint32_t* ctc;
     ALLOC(cwsum, int64_t, ncls); ALLOC(cts, int64_t, ncls); ALLOC(cte, int64_t, ncls); ALLOC(ctc, uint32_t, ncls);
     LAUNCH(k_sent_wordsum, ncls, 128, D, S, ctx->WS, S.n_sent, ncls, cus, cue, cts, cte, cwsum);
-    if ((rc = count_units(ctx, st, D.C, cus, cue, ncls, total, 1, ccnt, nullptr, false))) return rc;
-    if (ctx->WS.of_seg) { if ((rc = count_units(ctx, st, D.C, cts, cte, ncls, total, 0, ctc, nullptr, false))) return rc; }
+    if ((rc = count_units(ctx, st, D.C, cus, cue, ncls, total, 1, ccnt, nullptr, false, 512))) return rc;
+    if (ctx->WS.of_seg) { if ((rc = count_units(ctx, st, D.C, cts, cte, ncls, total, 0, ctc, nullptr, false, 512))) return rc; }
     LAUNCH(k_clause_tok, ncls, 128, ctx->T, S, cus, cue, cts, cte, cwsum, ccnt, ctc, ncls);
   }
   LAUNCH_W(k_sent_greedy_count, (int64_t)nraw, D, S, nsub_g);

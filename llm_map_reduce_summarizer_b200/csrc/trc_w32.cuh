@@ -14,6 +14,8 @@
 struct W32 {
   uint32_t* sp; uint32_t* w; uint32_t* ct; uint32_t* bd; uint32_t* ep; uint32_t* lt; uint32_t* drop; uint32_t* ds;
   int32_t nch;
+  const uint32_t* nolead = nullptr;   // optional: segment starts whose leading whitespace is NOT stripped (the segment
+                                      // continues an oversized segment that was cut in front of a whitespace run)
 };
 
 TRC_HD uint32_t w32_bit(const uint32_t* a, int32_t k) { return (a[k >> 5] >> (k & 31)) & 1u; }     // k >= -32
@@ -278,11 +280,11 @@ TRC_HD W32Codes w32_chunk_codes(const uint8_t* in, const W32& M, int32_t c, int3
     }
   }
   // leading whitespace: runs that start at a segment start
-  uint32_t seeds = sp & bd;
+  uint32_t seeds = sp & bd & ~(M.nolead ? M.nolead[c] : 0u);
   if ((sp & 1u) && (spp >> 31) && !(bd & 1u)) {              // a run enters from the previous chunk: is it leading?
     int32_t p = k0;
     while (p > lo && w32_bit(M.sp, p - 1) && !w32_bit(M.bd, p)) --p;
-    if (w32_bit(M.sp, p) && w32_bit(M.bd, p)) seeds |= 1u;
+    if (w32_bit(M.sp, p) && w32_bit(M.bd, p) && !(M.nolead && w32_bit(M.nolead, p))) seeds |= 1u;
   }
   uint32_t lead_ws = 0;
   while (seeds) {                                            // one flood per seed: adjacent seeds must not cancel

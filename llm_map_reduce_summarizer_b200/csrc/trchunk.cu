@@ -473,10 +473,19 @@ static uint32_t hostsim_bpe_long(const TrcTables& T, const uint32_t* byte_id, co
 __global__ void k_count_units(TrcTables T, const uint32_t* __restrict__ byte_id, const uint8_t* __restrict__ bytes,
                               const int64_t* __restrict__ ustart, const int64_t* __restrict__ uend, int64_t n, int vs,
                               uint32_t* __restrict__ counts, int32_t* __restrict__ special, LongEntry* wl,
-                              unsigned long long* wl_cnt, int64_t wl_cap) {
+                              unsigned long long* wl_cnt, int64_t wl_cap, int64_t coop_min, unsigned long long* coop_cnt,
+                              int32_t* coop_owner, int64_t* coop_base) {
   GSTRIDE(j, n) {
     const uint8_t* p = bytes + ustart[j];
     int64_t nb = uend[j] - ustart[j];
+    if (coop_min > 0 && nb >= coop_min) {                  // a long unit of cleaned text: its 32-byte chunks go to k_count_units_coop
+      const int64_t nch = (nb + 31) >> 5;
+      const int64_t off = (int64_t)atomicAdd(coop_cnt, (unsigned long long)nch);
+      coop_base[j] = off;
+      for (int64_t k = 0; k < nch; ++k) coop_owner[off + k] = (int32_t)j;
+      counts[j] = 0;
+      continue;
+    }
     uint32_t c = trc_count_unit(T, trc_fast_default(T), byte_id, p, nb, vs, [&](int64_t ls, int64_t len) -> uint32_t {
 #ifdef TRC_HOSTSIM
       TrcStr S; S.p = p; S.n = nb + vs; S.vs = vs;
@@ -494,6 +503,38 @@ __global__ void k_count_units(TrcTables T, const uint32_t* __restrict__ byte_id,
 }
 
 #ifndef TRC_HOSTSIM
+// Long units of CLEANED text (a sentence of several KB in an over-budget monologue): a thread walked them byte by byte, a
+// load latency each.  Cleaned text has single U+0020 between words and the pre-tokeniser never joins across one
+// (DESIGN.md §3), so the count of a unit is the sum over its words: k_count_units lists the 32-byte chunks of every unit
+// of coop_min bytes or more, and here a thread per chunk counts the words that START in its chunk.
+__global__ void k_count_units_coop(TrcTables T, const uint32_t* __restrict__ byte_id, const uint8_t* __restrict__ bytes,
+                                   const int64_t* __restrict__ ustart, const int64_t* __restrict__ uend, int vs,
+                                   uint32_t* __restrict__ counts, LongEntry* wl, unsigned long long* wl_cnt, int64_t wl_cap,
+                                   const unsigned long long* __restrict__ coop_cnt, const int32_t* __restrict__ coop_owner,
+                                   const int64_t* __restrict__ coop_base) {
+  const TrcFast F = trc_fast_default(T);
+  const int64_t nchunks = (int64_t)*coop_cnt;
+  GSTRIDE(g, nchunks) {
+    const int64_t j = coop_owner[g];
+    const int64_t a = ustart[j], b = uend[j];
+    const int64_t c0 = a + ((g - coop_base[j]) << 5), c1 = c0 + 32 < b ? c0 + 32 : b;
+    uint32_t total = 0;
+    for (int64_t i = c0; i < c1; ++i) {
+      if (i != a && bytes[i] != ' ') continue;
+      int64_t e = i + 1;
+      while (e < b && bytes[e] != ' ') ++e;
+      const int wvs = i == a ? vs : 0;
+      const int64_t shift = i == a ? 0 : (i - a) + vs;     // logical index of the word's first byte inside the unit
+      total += trc_count_unit(T, F, byte_id, bytes + i, e - i, wvs, [&](int64_t ls, int64_t len) -> uint32_t {
+        unsigned long long slot = atomicAdd(&wl_cnt[0], 1ULL);
+        unsigned long long off = atomicAdd(&wl_cnt[1], (unsigned long long)len);
+        if ((int64_t)slot < wl_cap) { LongEntry le; le.unit = j; le.lstart = shift + ls; le.len = len; le.scratch_off = (int64_t)off; wl[slot] = le; }
+        return 0u;
+      });
+    }
+    if (total) atomicAdd(&counts[j], total);
+  }
+}
 // Byte-pair merge of one long span per block; the four work arrays live in global scratch.
 #define LONG_T 256
 #define LONGB_T 1024                     // threads of the long-span block = most chunks a span is cut into
@@ -512,8 +553,10 @@ __global__ void __launch_bounds__(LONGB_T) k_bpe_long(TrcTables T, const uint32_
   const int tid = threadIdx.x;
   for (int64_t w = blockIdx.x; w < n_entries; w += gridDim.x) {
     const LongEntry e = wl[w];
-    TrcStr S; S.p = bytes + ustart[e.unit]; S.vs = vs; S.n = uend[e.unit] - ustart[e.unit] + vs;
     const int64_t len = e.len;
+    TrcStr S; S.p = bytes + ustart[e.unit]; S.vs = vs; S.n = uend[e.unit] - ustart[e.unit] + vs;
+    int64_t l0 = e.lstart;
+    if (l0 < 0) { S.p = bytes + (-1 - l0); S.vs = 0; S.n = len; l0 = 0; }      // absolute position (parts of a cut segment, trc_fused5.cuh)
     uint32_t* id = scratch + e.scratch_off;
     uint32_t* rk = scratch + scratch_total + e.scratch_off;
     int32_t* nx = (int32_t*)(scratch + 2 * scratch_total + e.scratch_off);
@@ -537,7 +580,7 @@ __global__ void __launch_bounds__(LONGB_T) k_bpe_long(TrcTables T, const uint32_
     bool batched = true;
     int64_t m = len;
     for (;;) {
-      for (int64_t i = tid; i < len; i += LONGB_T) { id[i] = byte_id[S.at(e.lstart + i)]; nx[i] = (int32_t)(i + 1); pv[i] = (int32_t)(i - 1); }
+      for (int64_t i = tid; i < len; i += LONGB_T) { id[i] = byte_id[S.at(l0 + i)]; nx[i] = (int32_t)(i + 1); pv[i] = (int32_t)(i - 1); }
       __syncthreads();
       for (int64_t i = tid; i < len; i += LONGB_T) rk[i] = i + 1 < len ? trc_pair_rank(T, id[i], id[i + 1]) : TRC_NO_RANK;
       __syncthreads();
@@ -1217,15 +1260,28 @@ static int to_device(trc_ctx* ctx, cudaStream_t st, const Tp* src, int64_t count
 
 // Token counts of n units (device pointers).  Long spans are finished by k_bpe_long after one sync.
 static int count_units(trc_ctx* ctx, cudaStream_t st, const uint8_t* bytes, const int64_t* ustart, const int64_t* uend,
-                       int64_t n, int64_t total_bytes, int vs, uint32_t* counts, int32_t* special, bool allow_sync_free) {
+                       int64_t n, int64_t total_bytes, int vs, uint32_t* counts, int32_t* special, bool allow_sync_free, int64_t coop_min = 0) {
   if (n <= 0) return TRC_OK;
+  if (special) coop_min = 0;                   // (the cooperative counter does not look for special-token literals)
+#ifdef TRC_HOSTSIM
+  coop_min = 0;
+#endif
   // a long span has more than TRC_SHORT_SPAN LOGICAL bytes, and with vs every unit is one byte longer than it is stored
   const int64_t cap = (total_bytes + (vs ? n : 0)) / (TRC_SHORT_SPAN + 1) + 1;
   LongEntry* wl; unsigned long long* wl_cnt;
   ALLOC(wl, LongEntry, cap);
   ALLOC(wl_cnt, unsigned long long, 2);
   CK(cudaMemsetAsync(wl_cnt, 0, 16, st));
-  LAUNCH(k_count_units, n, 128, ctx->T, ctx->d_byte_id, bytes, ustart, uend, n, vs, counts, special, wl, wl_cnt, cap);
+  unsigned long long* coop_cnt = nullptr; int32_t* coop_owner = nullptr; int64_t* coop_base = nullptr;
+  const int64_t coop_bound = total_bytes / 32 + n + 1;      // most 32-byte chunks the long units can have
+  if (coop_min > 0) {
+    ALLOC(coop_cnt, unsigned long long, 1); ALLOC(coop_owner, int32_t, coop_bound); ALLOC(coop_base, int64_t, n);
+    CK(cudaMemsetAsync(coop_cnt, 0, 8, st));
+  }
+  LAUNCH(k_count_units, n, 128, ctx->T, ctx->d_byte_id, bytes, ustart, uend, n, vs, counts, special, wl, wl_cnt, cap, coop_min, coop_cnt, coop_owner, coop_base);
+#ifndef TRC_HOSTSIM
+  if (coop_min > 0) LAUNCH(k_count_units_coop, coop_bound, 128, ctx->T, ctx->d_byte_id, bytes, ustart, uend, vs, counts, wl, wl_cnt, cap, coop_cnt, coop_owner, coop_base);
+#endif
   unsigned long long h[2];
   int rc = read_back(ctx, st, wl_cnt, 16, h);
   if (rc) return rc;
@@ -1255,7 +1311,7 @@ static int count_units(trc_ctx* ctx, cudaStream_t st, const uint8_t* bytes, cons
 
 #ifndef TRC_HOSTSIM
 // Pre-pass for segments larger than a fused tile (trc_giant.cuh).  Leaves *V empty when there are none.
-static int giant_stage(trc_ctx* ctx, cudaStream_t st, int64_t braw, GiantView* V, TileCand cand, int64_t tile_cap, int64_t* stats) {
+static int giant_stage(trc_ctx* ctx, cudaStream_t st, int64_t braw, GiantView* V, TileCand cand, int64_t tile_cap, int64_t* stats, CutView* cut) {
   TrcDev& D = ctx->D;
   const int64_t n = D.n;
   int rc;
@@ -1282,6 +1338,24 @@ static int giant_stage(trc_ctx* ctx, cudaStream_t st, int64_t braw, GiantView* V
   int64_t gb = 0;
   if ((rc = read_back(ctx, st, boff + ng, 8, &gb))) return rc;
   if (gb >= (1LL << 31)) { ctx->err = "more than 2 GiB of oversized segments in one batch"; return TRC_EUNSUPPORTED; }
+  ctx->counts[TRC_N_GIANTS] = ng;
+  if (cut) {                                   // generation 5: parts for the fused kernel instead of the byte-parallel pre-pass
+    int32_t* tcnt; int64_t* tpre; int64_t* cutpos; int64_t nt = 0;
+    ALLOC(tcnt, int32_t, ng); ALLOC(tpre, int64_t, ng + 1);
+    LAUNCH(k_cut_counts, ng, 128, len, ng, tcnt);
+    if ((rc = scan_excl(ctx, st, tcnt, tpre, ng))) return rc;
+    if ((rc = read_back(ctx, st, tpre + ng, 8, &nt))) return rc;
+    if (n + nt < (1LL << 31)) {
+      int64_t* vseg_off; int32_t* vorig; uint8_t* vcont;
+      ALLOC(cutpos, int64_t, nt); ALLOC(cut->bad, unsigned long long, 1);
+      CK(cudaMemsetAsync(cut->bad, 0, 8, st));
+      LAUNCH(k_cut_find, nt, 128, D, ctx->T, list, len, tpre, ng, nt, cutpos);
+      ALLOC(vseg_off, int64_t, n + nt + 1); ALLOC(vorig, int32_t, n + nt); ALLOC(vcont, uint8_t, n + nt);
+      LAUNCH(k_vseg_build, n, 256, D, gflag, gscan, tpre, cutpos, nt, vseg_off, vorig, vcont, tile_cap - 64, cut->bad);
+      cut->nv = n + nt; cut->vseg_off = vseg_off; cut->vorig = vorig; cut->vcont = vcont;
+      return TRC_OK;
+    }
+  }
   G.list = list; G.boff = boff; G.ng = ng; G.gb = gb; G.of_seg = of_seg;
   ALLOC(G.cls, uint8_t, gb); ALLOC(G.code, uint8_t, gb); ALLOC(G.fns, int32_t, ng); ALLOC(G.pk, int64_t, gb); ALLOC(G.opk, int64_t, gb + 1);
   ALLOC(G.toff, int64_t, ng + 1); ALLOC(G.chars, int32_t, ng); ALLOC(G.tok, uint32_t, ng); ALLOC(G.spw, long long, ng);
@@ -1320,7 +1394,6 @@ static int giant_stage(trc_ctx* ctx, cudaStream_t st, int64_t braw, GiantView* V
   LAUNCH(k_giant_totals, ng, 64, G, wscan, wpre);
   ctx->WS.of_seg = of_seg; ctx->WS.toff = G.toff; ctx->WS.wscan = wscan; ctx->WS.wpre = wpre;
   V->of_seg = of_seg; V->toff = G.toff; V->text = G.text; V->chars = G.chars; V->tok = G.tok; V->spw = G.spw;
-  ctx->counts[TRC_N_GIANTS] = ng;
   return TRC_OK;
 }
 #endif
@@ -1601,29 +1674,62 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       // segments, heavy-tailed lengths - tiles of varying size (k_tile_flags).
       FuseArgs A;
       A.G = GiantView{};
-      A.tile_start = nullptr;
+      A.tile_start = nullptr; A.vorig = nullptr; A.vcont = nullptr; A.special_pos = nullptr;
+      TrcDev Dk = D;                         // the batch as the fused kernel sees it (cut mode: parts in place of oversized segments)
       int64_t ntiles_var = -1;
       if (gen >= 3) {
-        TileCand cand{{0, 0, 0, 0}};
+        TileCand cand{{0, 0, 0, 0}, 0};
         int64_t stats[5] = {0, 0, 0, 0, 0};
         const char* forced = gen >= 5 ? getenv("TRCHUNK_TSEGS") : nullptr;          // experiments: a fixed tile size
         if (forced) { const int v = atoi(forced); if (v >= 1 && v <= F5_SEGS) tsegs4 = v; else forced = nullptr; }
-        if (gen >= 5 && !forced) for (int q = 0; q < 4; ++q) { cand.v[q] = tsegs4 * (8 - q) / 8; if (cand.v[q] < 1) cand.v[q] = 1; }
-        if ((rc = giant_stage(ctx, st, braw, &A.G, cand, F5_IN_CAP, stats))) return rc;
+        if (gen >= 5 && !forced) {
+          for (int q = 0; q < 4; ++q) { cand.v[q] = tsegs4 * (8 - q) / 8; if (cand.v[q] < 1) cand.v[q] = 1; }
+          if (tsegs4 >= 16) { cand.all8 = 1; for (int q = 0; q < 4; ++q) cand.v[q] &= ~7; }
+        }
+        const char* cut_env = getenv("TRCHUNK_GIANT_CUT");                           // "0": keep the byte-parallel pre-pass (tests)
+        const bool want_cut = gen >= 5 && !forced && !(cut_env && atoi(cut_env) == 0);
+        CutView CV{};
+        if ((rc = giant_stage(ctx, st, braw, &A.G, cand, F5_IN_CAP, stats, want_cut ? &CV : nullptr))) return rc;
         if (gen >= 5 && !forced) {
           int pick = -1;
           if (stats[0] == 0) for (int q = 0; q < 4 && pick < 0; ++q) if (stats[1 + q] == 0) pick = q;
           if (pick >= 0) tsegs4 = cand.v[pick];
           else {
             static_assert(F5_IN_CAP > TRC_GIANT_MIN + 16, "a window of the varying tiles");
-            int32_t* tflag; int64_t* tscan; int32_t* tstart;
-            ALLOC(tflag, int32_t, n); ALLOC(tscan, int64_t, n + 1);
-            LAUNCH(k_tile_flags, n, 256, D, tflag, (int64_t)(F5_IN_CAP - TRC_GIANT_MIN - 16), (int)F5_SEGS);
-            if ((rc = scan_excl(ctx, st, tflag, tscan, n))) return rc;
-            if ((rc = read_back(ctx, st, tscan + n, 8, &ntiles_var))) return rc;
-            ALLOC(tstart, int32_t, ntiles_var + 1);
-            LAUNCH(k_scatter_starts, n, 256, tflag, tscan, tstart, n);
-            A.tile_start = tstart;
+            auto var_tiles = [&](const TrcDev& Dx, const unsigned long long* word, int64_t* word_out) -> int {
+              int32_t* tflag; int64_t* tscan; int32_t* tstart;
+              ALLOC(tflag, int32_t, Dx.n); ALLOC(tscan, int64_t, Dx.n + 1);
+              LAUNCH(k_tile_flags, Dx.n, 256, Dx, tflag, (int64_t)(F5_IN_CAP - TRC_GIANT_MIN - 16), (int)F5_SEGS);
+              int r2;
+              if ((r2 = scan_excl(ctx, st, tflag, tscan, Dx.n))) return r2;
+              int64_t h2[2] = {0, 0};
+              if ((r2 = read_back2(ctx, st, tscan + Dx.n, word, h2))) return r2;
+              ntiles_var = h2[0];
+              if (word_out) *word_out = h2[1];
+              ALLOC(tstart, int32_t, ntiles_var + 1);
+              LAUNCH(k_scatter_starts, Dx.n, 256, tflag, tscan, tstart, Dx.n);
+              A.tile_start = tstart;
+              return TRC_OK;
+            };
+            bool cut_done = false;
+            if (CV.nv > 0) {
+              Dk.seg_off = CV.vseg_off; Dk.n = CV.nv;
+              int64_t bad = 0;
+              if ((rc = var_tiles(Dk, CV.bad, &bad))) return rc;
+              if (getenv("TRCHUNK_CUT_DEBUG")) fprintf(stderr, "[trchunk] cut: %lld segments -> %lld, targets without a cut: %lld, tiles %lld\n", (long long)n, (long long)CV.nv, (long long)bad, (long long)ntiles_var);
+              if (bad == 0) {
+                cut_done = true;
+                A.vorig = CV.vorig; A.vcont = CV.vcont;
+                ALLOC(A.special_pos, unsigned long long, n);
+                CK(cudaMemsetAsync(A.special_pos, 0xff, 8 * (size_t)n, st));
+                CK(cudaMemsetAsync(D.ctok, 0, 4 * (size_t)n, st));
+                CK(cudaMemsetAsync(D.cchars, 0, 4 * (size_t)n, st));
+              } else {                       // a segment that cannot be cut: the byte-parallel pre-pass for this batch
+                Dk = D;
+                if ((rc = giant_stage(ctx, st, braw, &A.G, TileCand{{0, 0, 0, 0}, 0}, F5_IN_CAP, stats, nullptr))) return rc;
+              }
+            }
+            if (!cut_done) { if ((rc = var_tiles(D, nullptr, nullptr))) return rc; }
           }
         }
       }
@@ -1665,7 +1771,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       if (gen >= 5) {
         blocks = (int)(ntiles < 148 * F5_CTAS ? ntiles : 148 * F5_CTAS);
         prof_begin(ctx, st, "k_clean_tok_c32");
-        k_clean_tok_c32<<<blocks, F5_T, sizeof(F5Smem), st>>>(D, ctx->T, ctx->d_byte_id, A, ntiles, tsegs4);
+        k_clean_tok_c32<<<blocks, F5_T, sizeof(F5Smem), st>>>(Dk, ctx->T, ctx->d_byte_id, A, ntiles, tsegs4);
       } else if (gen >= 4) {
         const int64_t want = (ntiles + F4_WARPS - 1) / F4_WARPS;
         blocks = (int)(want < 148 ? want : 148);
@@ -1681,11 +1787,15 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       prof_end(ctx, st);
       ctx->launches++;
       CK(cudaGetLastError());
-      unsigned long long h[25];
-      if ((rc = read_back(ctx, st, fz + 2, 200, h))) return rc;     // wl count, wl scratch, n_kept, bclean, -, slow words, ..., word statistics
+      unsigned long long h[26];
+      if ((rc = read_back(ctx, st, fz + 2, 208, h))) return rc;     // wl count, wl scratch, n_kept, bclean, -, slow words, ..., word statistics
       ctx->counts[TRC_N_WORDS] = (int64_t)h[22]; ctx->counts[TRC_N_WORD_FIRST] = (int64_t)h[23]; ctx->counts[TRC_N_WORD_SLOW] = (int64_t)h[24];
       nk = (int64_t)h[2]; bclean = (int64_t)h[3];
       D.n_kept = nk;
+      if (A.vcont) {
+        if (h[25]) { ctx->err = "internal: a tile of a batch with cut segments took the slow lane"; return TRC_EINVAL; }
+        LAUNCH(k_special_from_pos, nk, 256, A.special_pos, nk, seg_special);
+      }
       {
         int64_t nslow = (int64_t)h[5] < A.sl_cap ? (int64_t)h[5] : A.sl_cap;   // entries past the capacity were counted in the kernel
         if (nslow > 0) {       // on the side stream: nothing before the per-group token totals needs these counts

@@ -88,3 +88,24 @@ def test_forced_tile_sizes_take_the_slow_lane(tsegs, monkeypatch):
         _run(eng, _tail_batch(6, 1500, 200))
     finally:
         eng.close()
+
+
+def test_oversized_segments_cut_and_uncut(monkeypatch):
+    """Oversized segments reach the fused kernel as parts cut in front of whitespace runs (default), or pre-cleaned by the
+    byte-parallel pre-pass (TRCHUNK_GIANT_CUT=0, and any batch with a segment that cannot be cut: here 9 KB of one repeated
+    word, and 6 KB without ASCII whitespace)."""
+    rng = random.Random(77)
+    base = _tail_batch(21, 1200, 150)
+    words = ["alpha", "beta", "beta", "Gamma.", "x", "the", "the", "end.Next", "café", "你好", "3.5", "don't"]
+    for k in range(6):
+        base.insert(100 + 150 * k, {"start": 0.0, "end": 1.0, "speaker": "A",
+                                    "text": " ".join(rng.choice(words) for _ in range(rng.randint(1500, 9000)))})
+    uncuttable = [dict(base[0], text="same " * 1800), dict(base[0], text="你好　" * 900 + "tail")]
+    for env, extra in (("1", []), ("0", []), ("1", uncuttable)):
+        monkeypatch.setenv("TRCHUNK_GIANT_CUT", env)
+        eng = E.Engine(0)
+        try:
+            _run(eng, base[:400] + extra + base[400:])
+            assert eng.counts()["n_giants"] >= 6
+        finally:
+            eng.close()
