@@ -376,8 +376,14 @@ struct SubAcc {
 // The greedy below is sequential per segment, but a thread that walks 80-byte records one by one waits a memory
 // round trip per record.  On the device a WARP runs it: the lanes load 32 consecutive records at once and hand
 // them around with shuffles while every lane executes the same (uniform) loop; lane 0 does the writes.
-struct SentLite { int64_t len, cl0; double start, end; int32_t tok, ncl; };
-TRC_HD SentLite sent_lite(const TrcSent& R) { SentLite o; o.len = R.len; o.cl0 = R.cl0; o.start = R.start; o.end = R.end; o.tok = R.tok; o.ncl = R.ncl; return o; }
+// (`piece`, the byte length of "[ts] text", is worked out here - by every lane for its own record when a warp loads a
+// window - and not inside the sequential loop, where all lanes would format the same timestamp.)
+struct SentLite { int64_t len, cl0, piece; double start, end; int32_t tok, ncl; };
+TRC_HD SentLite sent_lite(const TrcSent& R) {
+  SentLite o; o.len = R.len; o.cl0 = R.cl0; o.start = R.start; o.end = R.end; o.tok = R.tok; o.ncl = R.ncl;
+  o.piece = 1 + trc_ts_len(R.start) + 2 + R.len;
+  return o;
+}
 struct SentFetchDirect {
   const TrcSent* recs;
   TRC_HD SentLite operator()(int64_t r) { return sent_lite(recs[r]); }
@@ -396,6 +402,7 @@ struct SentFetchWarp {
     o.len = __shfl_sync(0xffffffffu, mine.len, src); o.cl0 = __shfl_sync(0xffffffffu, mine.cl0, src);
     o.start = __shfl_sync(0xffffffffu, mine.start, src); o.end = __shfl_sync(0xffffffffu, mine.end, src);
     o.tok = __shfl_sync(0xffffffffu, mine.tok, src); o.ncl = __shfl_sync(0xffffffffu, mine.ncl, src);
+    o.piece = __shfl_sync(0xffffffffu, mine.piece, src);
     return o;
   }
 };
@@ -415,7 +422,7 @@ TRC_HD void sg_flush(TrcSentState& S, TrcSub* out, int32_t& ns, int32_t g, int32
 // flushed between a sub-chunk's first append and its own flush).
 template <bool WRITE>
 TRC_HD void sg_append(TrcSentState& S, SubAcc& a, int32_t r, const SentLite& R, int64_t sub_index, bool wr) {
-  int64_t piece = 1 + trc_ts_len(R.start) + 2 + R.len;
+  const int64_t piece = R.piece;
   if (a.n == 0) { a.r0 = r; a.text_len = 0; }
   if (WRITE && wr) { S.recs[r].sub = (int32_t)sub_index; S.recs[r].off_in_sub = a.n ? a.text_len + 1 : 0; }
   a.text_len += piece + (a.n ? 1 : 0);
@@ -429,7 +436,8 @@ TRC_HD int32_t trc_split_sentences(const TrcDev& D, TrcSentState S, int64_t q, T
   int64_t E = D.doc_E[D.sdoc[j]];
   int32_t ns = 0;
   SubAcc cur; cur.tok = 0; cur.text_len = 0; cur.n = 0; cur.r0 = cur.r1 = -1; cur.start = D.start[D.k2r[j]]; cur.end = 0; cur.start_src = j;
-  for (int64_t r = S.sent_off[q]; r < S.sent_off[q + 1]; ++r) {
+  const int64_t r_end = S.sent_off[q + 1];
+  for (int64_t r = S.sent_off[q]; r < r_end; ++r) {
     const SentLite R = fetch(r);
     if (R.len == 0) continue;
     if (R.tok > E) {
