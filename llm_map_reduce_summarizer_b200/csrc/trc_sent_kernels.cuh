@@ -19,6 +19,29 @@ TRC_HD int64_t rl_find(const int64_t* boff, int64_t n, int64_t pos) {   // last 
   return lo;
 }
 
+// The same for the threads of a warp that ask for ascending positions (consecutive cells or records): one of them
+// searches, the others step forward from its answer - ten dependent loads per thread became one or two.
+TRC_HD int64_t rl_find_near(const int64_t* boff, int64_t n, int64_t pos) {
+#if defined(__CUDA_ARCH__)
+  const unsigned m = __activemask();
+  const int leader = __ffs(m) - 1;
+  int64_t q = 0;
+  if ((int)(threadIdx.x & 31) == leader) q = rl_find(boff, n, pos);
+  q = __shfl_sync(m, q, leader);
+  if (boff[q] > pos) return rl_find(boff, n, pos);
+  while (q + 1 < n && boff[q + 1] <= pos) ++q;
+  return q;
+#else
+  return rl_find(boff, n, pos);
+#endif
+}
+// Breaks before byte x of the concatenated texts: the scan runs over 8-byte cells (cellscan), the rest is counted.
+TRC_HD int64_t pk_breaks_before(const uint8_t* brk, const int64_t* cellscan, int64_t x) {
+  int64_t v = cellscan[x >> 3];
+  for (int64_t p = x & ~(int64_t)7; p < x; ++p) v += brk[p] != 0;
+  return v;
+}
+
 // Punkt break decision for every text byte of the over-budget raw segments, a thread per 8 bytes.  Ordinary
 // cells (inside one segment, ASCII, no control bytes) are handled on bit masks: only the '.', '?' and '!' bytes
 // go through the context test; the domain check of the sentence path (single U+0020 between words, no leading /
@@ -34,7 +57,7 @@ TRC_HD void pk_break_byte(const TrcDev& D, const TrcTables& T, const uint8_t* s,
 }
 TRC_HD void pk_break_cell(const TrcDev& D, const TrcTables& T, const TrcSentState& S, int64_t total, int64_t cell, uint8_t* brk) {
   const int64_t p0 = cell * 8;
-  int64_t q = rl_find(S.rl_boff, S.n_rl, p0);
+  int64_t q = rl_find_near(S.rl_boff, S.n_rl, p0);
   if (p0 + 16 <= S.rl_boff[q + 1]) {                        // (two aligned words are read: both inside the segment)
     const int32_t j = D.gstart[S.rl_groups[q]];
     const int64_t c0 = D.coff[j], n = D.coff[j + 1] - c0, i = p0 - S.rl_boff[q];
@@ -81,25 +104,38 @@ TRC_HD void pk_break_cell(const TrcDev& D, const TrcTables& T, const TrcSentStat
 __global__ void k_punkt_breaks(TrcDev D, TrcTables T, TrcSentState S, int64_t total, uint8_t* brk) {
   GSTRIDE(cell, (total + 7) / 8) pk_break_cell(D, T, S, total, cell, brk);
 }
-__global__ void k_brk_pos(const uint8_t* __restrict__ brk, const int64_t* __restrict__ bscan, int64_t total, int64_t* pos) {
-  GSTRIDE(p, total) if (brk[p]) pos[bscan[p]] = p;
+__global__ void k_cell_counts(const uint8_t* __restrict__ brk, int64_t total, uint8_t* cellcnt) {
+  GSTRIDE(cell, (total + 7) / 8) {
+    const int64_t p0 = cell * 8, p1 = p0 + 8 < total ? p0 + 8 : total;
+    int c = 0;
+    for (int64_t p = p0; p < p1; ++p) c += brk[p] != 0;
+    cellcnt[cell] = (uint8_t)c;
+  }
 }
-__global__ void k_sent_counts(TrcSentState S, const int64_t* __restrict__ bscan, int32_t* ns) {
-  GSTRIDE(q, S.n_rl) ns[q] = (int32_t)(bscan[S.rl_boff[q + 1]] - bscan[S.rl_boff[q]]) + 1;
+__global__ void k_brk_pos(const uint8_t* __restrict__ brk, const int64_t* __restrict__ cellscan, int64_t total, int64_t* pos) {
+  GSTRIDE(cell, (total + 7) / 8) {
+    const int64_t p0 = cell * 8, p1 = p0 + 8 < total ? p0 + 8 : total;
+    int64_t o = cellscan[cell];
+    if (cellscan[cell + 1] == o) continue;
+    for (int64_t p = p0; p < p1; ++p) if (brk[p]) pos[o++] = p;
+  }
+}
+__global__ void k_sent_counts(TrcSentState S, const uint8_t* __restrict__ brk, const int64_t* __restrict__ cellscan, int32_t* ns) {
+  GSTRIDE(q, S.n_rl) ns[q] = (int32_t)(pk_breaks_before(brk, cellscan, S.rl_boff[q + 1]) - pk_breaks_before(brk, cellscan, S.rl_boff[q])) + 1;
 }
 
 // one thread per sentence slice: slice bounds, realignment with its neighbours, strip, code points
-__global__ void k_sent_build(TrcDev D, TrcSentState S, const int64_t* __restrict__ bscan, const int64_t* __restrict__ brk_pos,
-                             int64_t* chars64) {
+__global__ void k_sent_build(TrcDev D, TrcSentState S, const uint8_t* __restrict__ brk, const int64_t* __restrict__ cellscan,
+                             const int64_t* __restrict__ brk_pos, int64_t* chars64) {
   GSTRIDE(r, S.n_sent) {
-    int64_t q = rl_find(S.sent_off, S.n_rl, r);
+    int64_t q = rl_find_near(S.sent_off, S.n_rl, r);
     int32_t g = S.rl_groups[q];
     int32_t j = D.gstart[g];
     const uint8_t* s = D.C + D.coff[j];
     int64_t n = D.coff[j + 1] - D.coff[j];
     int64_t i = r - S.sent_off[q];
     int64_t nb = S.sent_off[q + 1] - S.sent_off[q] - 1;     // breaks of this segment
-    int64_t b0 = bscan[S.rl_boff[q]];
+    int64_t b0 = pk_breaks_before(brk, cellscan, S.rl_boff[q]);
     auto slice = [&](int64_t k, int64_t* a, int64_t* b) {   // _slices_from_text
       if (k == 0) *a = 0;
       else { int64_t c = brk_pos[b0 + k - 1] - S.rl_boff[q]; *a = pk_nonword(s[c + 1]) ? c + 1 : c + 2; }
@@ -124,7 +160,7 @@ __global__ void k_sent_build(TrcDev D, TrcSentState S, const int64_t* __restrict
 __global__ void k_sent_times(TrcDev D, TrcSentState S, const int64_t* __restrict__ cscan, int64_t* ustart, int64_t* uend) {
   GSTRIDE(r, S.n_sent) {
     TrcSent& R = S.recs[r];
-    int64_t q = rl_find(S.sent_off, S.n_rl, r);
+    int64_t q = rl_find_near(S.sent_off, S.n_rl, r);
     int32_t j = D.gstart[R.group];
     int32_t raw = D.k2r[j];
     double st = D.start[raw], en = D.end[raw];
@@ -575,16 +611,19 @@ static int sentence_stage_count(trc_ctx* ctx, cudaStream_t st, int32_t* nsub_g, 
   if ((rc = read_back(ctx, st, rl_boff + nraw, 8, &total))) return rc;
   S.rl_groups = rl_groups; S.n_rl = nraw; S.rl_boff = rl_boff;
   // Punkt breaks
-  uint8_t* brk; int64_t* bscan;
-  ALLOC(brk, uint8_t, total + 8); ALLOC(bscan, int64_t, total + 1);
-  LAUNCH(k_punkt_breaks, (total + 7) / 8, 128, D, ctx->T, S, total, brk);
-  if ((rc = scan_excl(ctx, st, brk, bscan, total))) return rc;
+  // (the break flags are scanned per 8-byte cell: an eighth of the scan over bytes, positions inside a cell are counted)
+  uint8_t* brk; uint8_t* cellcnt; int64_t* cellscan;
+  const int64_t ncell = (total + 7) / 8;
+  ALLOC(brk, uint8_t, total + 8); ALLOC(cellcnt, uint8_t, ncell); ALLOC(cellscan, int64_t, ncell + 1);
+  LAUNCH(k_punkt_breaks, ncell, 128, D, ctx->T, S, total, brk);
+  LAUNCH(k_cell_counts, ncell, 256, brk, total, cellcnt);
+  if ((rc = scan_excl(ctx, st, cellcnt, cellscan, ncell))) return rc;
   int64_t nbrk = 0;
-  if ((rc = read_back(ctx, st, bscan + total, 8, &nbrk))) return rc;
+  if ((rc = read_back(ctx, st, cellscan + ncell, 8, &nbrk))) return rc;
   int64_t* brk_pos; int32_t* ns; int64_t* sent_off;
   ALLOC(brk_pos, int64_t, nbrk); ALLOC(ns, int32_t, nraw); ALLOC(sent_off, int64_t, nraw + 1);
-  LAUNCH(k_brk_pos, total, 256, brk, bscan, total, brk_pos);
-  LAUNCH(k_sent_counts, (int64_t)nraw, 128, S, bscan, ns);
+  LAUNCH(k_brk_pos, ncell, 256, brk, cellscan, total, brk_pos);
+  LAUNCH(k_sent_counts, (int64_t)nraw, 128, S, brk, cellscan, ns);
   if ((rc = scan_excl(ctx, st, ns, sent_off, (int64_t)nraw))) return rc;
   S.sent_off = sent_off;
   S.n_sent = nbrk + nraw;
@@ -594,7 +633,7 @@ static int sentence_stage_count(trc_ctx* ctx, cudaStream_t st, int32_t* nsub_g, 
   ALLOC(ustart, int64_t, S.n_sent); ALLOC(uend, int64_t, S.n_sent); ALLOC(cnt, uint32_t, S.n_sent); ALLOC(ncl, int32_t, S.n_sent);
   ALLOC(clscan, int64_t, S.n_sent + 1);
   S.recs = recs0; S.n_recs = S.n_sent;
-  LAUNCH(k_sent_build, S.n_sent, 128, D, S, bscan, brk_pos, chars64);
+  LAUNCH(k_sent_build, S.n_sent, 128, D, S, brk, cellscan, brk_pos, chars64);
   if ((rc = scan_excl(ctx, st, chars64, cscan, S.n_sent))) return rc;
   LAUNCH(k_sent_times, S.n_sent, 128, D, S, cscan, ustart, uend);
   int64_t* wsum; int64_t* tst; int64_t* ten; uint32_t* tcnt;
