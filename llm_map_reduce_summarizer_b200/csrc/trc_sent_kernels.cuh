@@ -55,7 +55,11 @@ TRC_HD void pk_break_byte(const TrcDev& D, const TrcTables& T, const uint8_t* s,
   else if (c >= 0xC0) { int l; uint32_t cp = trc_decode(s, i, n, &l); bad = (T.props[cp] & TRC_P_SPACE) != 0; }
   if (bad) D.doc_err[D.sdoc[j]] = -1;
 }
-TRC_HD void pk_break_cell(const TrcDev& D, const TrcTables& T, const TrcSentState& S, int64_t total, int64_t cell, uint8_t* brk) {
+// `cand(q, i, p)` decides the '.', '?' or '!' at byte i of over-budget segment q (byte p of the concatenated texts): the test
+// build evaluates it on the spot; the CUDA kernel queues it, because the context test is ~2 000 instructions and ran with
+// five of 32 lanes when every thread evaluated the candidates of its own cell.
+template <class Cand>
+TRC_HD void pk_break_cell(const TrcDev& D, const TrcTables& T, const TrcSentState& S, int64_t total, int64_t cell, uint8_t* brk, Cand&& cand) {
   const int64_t p0 = cell * 8;
   int64_t q = rl_find_near(S.rl_boff, S.n_rl, p0);
   if (p0 + 16 <= S.rl_boff[q + 1]) {                        // (two aligned words are read: both inside the segment)
@@ -81,11 +85,10 @@ TRC_HD void pk_break_cell(const TrcDev& D, const TrcTables& T, const TrcSentStat
       if (bad) D.doc_err[D.sdoc[j]] = -1;
       uint32_t se = sw_pack(pk_eq8(x, '.') | pk_eq8(x, '?') | pk_eq8(x, '!'));
       uint64_t flags = 0;
-      const uint8_t* s = D.C + c0;
       while (se) {
         const int k = (int)trc_ctz32(se);
         se &= se - 1;
-        if (pk_is_break(T, s, n, i + k)) flags |= 1ULL << (8 * k);
+        if (cand(q, i + k, p0 + k)) flags |= 1ULL << (8 * k);
       }
 #if defined(__CUDA_ARCH__)
       *reinterpret_cast<unsigned long long*>(brk + p0) = flags;
@@ -101,9 +104,40 @@ TRC_HD void pk_break_cell(const TrcDev& D, const TrcTables& T, const TrcSentStat
     pk_break_byte(D, T, D.C + D.coff[j], D.coff[j + 1] - D.coff[j], p - S.rl_boff[q], j, brk + p);
   }
 }
+#ifdef TRC_HOSTSIM
 __global__ void k_punkt_breaks(TrcDev D, TrcTables T, TrcSentState S, int64_t total, uint8_t* brk) {
-  GSTRIDE(cell, (total + 7) / 8) pk_break_cell(D, T, S, total, cell, brk);
+  GSTRIDE(cell, (total + 7) / 8) pk_break_cell(D, T, S, total, cell, brk, [&](int64_t q, int64_t i, int64_t) {
+    const int32_t j = D.gstart[S.rl_groups[q]];
+    return pk_is_break(T, D.C + D.coff[j], D.coff[j + 1] - D.coff[j], i);
+  });
 }
+#else
+#define PK_T 128
+__global__ void __launch_bounds__(PK_T) k_punkt_breaks(TrcDev D, TrcTables T, TrcSentState S, int64_t total, uint8_t* brk) {
+  __shared__ int64_t s_p[PK_T * 8];
+  __shared__ int64_t s_i[PK_T * 8];
+  __shared__ int32_t s_q[PK_T * 8];
+  __shared__ int s_n;
+  const int64_t ncell = (total + 7) / 8;
+  for (int64_t base = (int64_t)blockIdx.x * PK_T; base < ncell; base += (int64_t)gridDim.x * PK_T) {
+    if (threadIdx.x == 0) s_n = 0;
+    __syncthreads();
+    const int64_t cell = base + threadIdx.x;
+    if (cell < ncell) pk_break_cell(D, T, S, total, cell, brk, [&](int64_t q, int64_t i, int64_t p) {
+      const int slot = atomicAdd(&s_n, 1);
+      s_p[slot] = p; s_i[slot] = i; s_q[slot] = (int32_t)q;
+      return false;
+    });
+    __syncthreads();                            // the cells' flag words are written (zero where a candidate is queued)
+    const int nc = s_n;
+    for (int k = threadIdx.x; k < nc; k += PK_T) {
+      const int32_t j = D.gstart[S.rl_groups[s_q[k]]];
+      if (pk_is_break(T, D.C + D.coff[j], D.coff[j + 1] - D.coff[j], s_i[k])) brk[s_p[k]] = 1;
+    }
+    __syncthreads();
+  }
+}
+#endif
 __global__ void k_cell_counts(const uint8_t* __restrict__ brk, int64_t total, uint8_t* cellcnt) {
   GSTRIDE(cell, (total + 7) / 8) {
     const int64_t p0 = cell * 8, p1 = p0 + 8 < total ? p0 + 8 : total;
@@ -532,7 +566,19 @@ __global__ void k_sent_greedy_write(TrcDev D, TrcSentState S) {
 // K6 for sentence/clause records: "[ts] text" (+ joining space) into the item text; warp per record (test build), eight
 // lanes per record (CUDA build: a sentence is ~35 bytes; a warp each left three quarters of the lanes without a byte)
 #ifndef TRC_HOSTSIM
-__global__ void k_emit_sent_recs(TrcDev D, TrcSentState S) {
+// Where the text of every sentence / clause sub-chunk goes (one lookup chain per sub-chunk instead of one per record), and
+// the "\n\n" in front of it when it is not the first item of its chunk.
+__global__ void k_sub_dst(TrcDev D, int64_t* sub_dst) {
+  GSTRIDE(sub, D.n_subs) {
+    if (D.subs[sub].kind == 0) { sub_dst[sub] = -1; continue; }
+    const int32_t grp = D.subs[sub].group;
+    const int64_t t = D.item_off[grp] + (sub - D.sub_off[grp]);
+    const int64_t d = D.it_dst[t];
+    sub_dst[sub] = d;
+    if (t > D.chunks[D.cscanf[t + 1] - 1].item0) { D.twc[d - 2] = '\n'; D.twc[d - 1] = '\n'; }
+  }
+}
+__global__ void k_emit_sent_recs(TrcDev D, TrcSentState S, const int64_t* __restrict__ sub_dst) {
   for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; (q >> 3) < S.n_recs; q += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = q >> 3;
     const int lane = (int)(q & 7);
@@ -542,11 +588,7 @@ __global__ void k_emit_sent_recs(TrcDev D, TrcSentState S) {
     const int64_t off = Rp->off, len = Rp->len, ois = Rp->off_in_sub;
     const double st = Rp->start;
     const int32_t last = Rp->last_in_sub;
-    const int32_t grp = D.subs[sub].group;
-    const int64_t t = D.item_off[grp] + (sub - D.sub_off[grp]);
-    uint8_t* base = D.twc + D.it_dst[t];
-    if (ois == 0 && lane == 0 && t > D.chunks[D.cscanf[t + 1] - 1].item0) { base[-2] = '\n'; base[-1] = '\n'; }
-    uint8_t* dst = base + ois;
+    uint8_t* dst = D.twc + sub_dst[sub] + ois;
     int64_t h; int m, sec;
     trc_ts_split(st, &h, &m, &sec);
     int o;
@@ -696,7 +738,10 @@ static int sentence_stage_emit(trc_ctx* ctx, cudaStream_t st) {
 #ifdef TRC_HOSTSIM
   LAUNCH_W(k_emit_sent_recs, ctx->SS.n_recs, ctx->D, ctx->SS);
 #else
-  LAUNCH(k_emit_sent_recs, ctx->SS.n_recs * 8, 256, ctx->D, ctx->SS);
+  int64_t* sub_dst;
+  ALLOC(sub_dst, int64_t, ctx->D.n_subs);
+  LAUNCH(k_sub_dst, ctx->D.n_subs, 128, ctx->D, sub_dst);
+  LAUNCH(k_emit_sent_recs, ctx->SS.n_recs * 8, 256, ctx->D, ctx->SS, sub_dst);
 #endif
   return TRC_OK;
 }
