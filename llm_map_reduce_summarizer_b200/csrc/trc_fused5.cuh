@@ -168,6 +168,7 @@ __device__ __forceinline__ int f5_seg_of_word(const F5Smem& S, int ns, int32_t w
   return lo;
 }
 
+template <bool CUT>
 __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTables T, const uint32_t* __restrict__ byte_id, FuseArgs A,
                                                            int64_t ntiles, int tsegs) {
   extern __shared__ __align__(16) unsigned char fuse_raw[];
@@ -188,7 +189,7 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
   // Cut mode (A.vcont): oversized segments arrive cut into parts in front of whitespace runs (k_cut_find); a part that
   // continues a segment keeps its leading whitespace (one space), opens no kept record and adds its bytes, tokens and
   // code points to the record of the part that started the segment - the most recent record before it.
-  const bool cutmode = A.vcont != nullptr;
+  constexpr bool cutmode = CUT;                  // (two instantiations: the bench workloads pay nothing for the cut-mode branches)
   if (cutmode) M.nolead = S.u.m[F5_NOLEAD] + 1;
   uint32_t* const c_cp = S.u.m[F4_COPY] + 1; uint32_t* const c_se = S.u.m[F4_SPACE] + 1; uint32_t* const c_in = S.u.m[F4_INS] + 1;
   uint32_t* const p_os = S.u.m[F4_PRE_OS] + 1; uint32_t* const p_tb = S.u.m[F4_PRE_TB] + 1; uint32_t* const m_ns = S.u.m[F4_NS] + 1;
@@ -235,7 +236,7 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
       }
     }
     if (wid == F5_NW - 1) {                   // document of the first segment: one 32-ary search per tile, under the tile load
-      const int64_t s0o = A.vorig ? (int64_t)A.vorig[s0] : s0;       // (doc_off counts the caller's segments)
+      const int64_t s0o = cutmode ? (int64_t)A.vorig[s0] : s0;       // (doc_off counts the caller's segments)
       int64_t lo = 0, hi = D.n_doc;
       while (hi - lo > 1) {
         const int64_t step = (hi - lo + 31) >> 5;
@@ -368,7 +369,7 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
       tot_kept = S.tot[0]; tot_words = S.tot[1];
       if (tid == 0) { fuse_publish(A.desc_bytes, tile, tot_out); fuse_publish(A.desc_kept, tile, tot_kept); }
       fast_out = tot_words <= F5_WORD_CAP;
-      if (tid < ns) { S.loff[tid] = (uint16_t)loff; S.wfirst[tid] = (uint16_t)woff; S.koff[tid] = (int16_t)(koff - mycont); S.cont[tid] = (uint8_t)mycont; }
+      if (tid < ns) { S.loff[tid] = (uint16_t)loff; S.wfirst[tid] = (uint16_t)woff; S.koff[tid] = (int16_t)(koff - mycont); if (cutmode) S.cont[tid] = (uint8_t)mycont; }
       if (tid == 0) { S.loff[ns] = (uint16_t)tot_out; S.wfirst[ns] = (uint16_t)tot_words; }
       if (nonempty) S.kr[br] = (uint16_t)(koff + (mykeep ? 1 : 0));
       FUSE_PH(4);
@@ -582,7 +583,7 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
               const unsigned long long off = atomicAdd(&A.wl_cnt[1], (unsigned long long)len);
               if ((int64_t)slot < A.wl_cap) {
                 LongEntry le; le.unit = j; le.len = len; le.scratch_off = (int64_t)off;
-                le.lstart = S.cont[seg] ? -1 - (gbase + st + ls) : ls + (vs ? 0 : (st - sl + 1));     // (a part: absolute position in the cleaned text)
+                le.lstart = (cutmode && S.cont[seg]) ? -1 - (gbase + st + ls) : ls + (vs ? 0 : (st - sl + 1));     // (a part: absolute position in the cleaned text)
                 A.wl[slot] = le;
               }
               return 0u;
@@ -697,7 +698,7 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
       if (!cutmode) D.cchars[s0 + tid] = mychars;
       if (mykeep) {
         const int64_t j = kbase + koff;
-        const int64_t i = A.vorig ? (int64_t)A.vorig[s0 + tid] : s0 + tid;
+        const int64_t i = cutmode ? (int64_t)A.vorig[s0 + tid] : s0 + tid;
         D.k2r[j] = (int32_t)i; D.coff[j] = gbase + loff;
         if (!cutmode) { D.ctok[j] = (uint32_t)mytok; A.seg_special[j] = mysp; }
         int64_t lo = S.doc0;                  // documents are rarely shorter than a few segments: walk, then search

@@ -1764,14 +1764,16 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
         CK(cudaFuncSetAttribute(k_clean_tok_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FuseSmem)));
         CK(cudaFuncSetAttribute(k_clean_tok_fused3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(F3Smem)));
         CK(cudaFuncSetAttribute(k_clean_tok_w32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(F4Smem)));
-        CK(cudaFuncSetAttribute(k_clean_tok_c32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(F5Smem)));
+        CK(cudaFuncSetAttribute(k_clean_tok_c32<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(F5Smem)));
+        CK(cudaFuncSetAttribute(k_clean_tok_c32<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(F5Smem)));
         attr_done[ctx->device & 63] = true;
       }
       int blocks = (int)(ntiles < 148 * 2 ? ntiles : 148 * 2);
       if (gen >= 5) {
         blocks = (int)(ntiles < 148 * F5_CTAS ? ntiles : 148 * F5_CTAS);
         prof_begin(ctx, st, "k_clean_tok_c32");
-        k_clean_tok_c32<<<blocks, F5_T, sizeof(F5Smem), st>>>(Dk, ctx->T, ctx->d_byte_id, A, ntiles, tsegs4);
+        if (A.vcont) k_clean_tok_c32<true><<<blocks, F5_T, sizeof(F5Smem), st>>>(Dk, ctx->T, ctx->d_byte_id, A, ntiles, tsegs4);
+        else k_clean_tok_c32<false><<<blocks, F5_T, sizeof(F5Smem), st>>>(Dk, ctx->T, ctx->d_byte_id, A, ntiles, tsegs4);
       } else if (gen >= 4) {
         const int64_t want = (ntiles + F4_WARPS - 1) / F4_WARPS;
         blocks = (int)(want < 148 ? want : 148);
