@@ -219,10 +219,33 @@ TRC_HD PkBuf pk_buf(const uint8_t* s) { PkBuf o; o.mis = (int64_t)((uintptr_t)s 
 TRC_HD int32_t pk_count_chars(const uint8_t* s, int64_t a, int64_t b) {
   if (b <= a) return 0;
   if (b - a < 16) { int32_t c = 0; for (int64_t i = a; i < b; ++i) c += (s[i] & 0xC0) != 0x80; return c; }
+  // continuation bytes (10xxxxxx) of the aligned 8-byte words that cover [a, b); the first and the last word are masked
   const PkBuf B = pk_buf(s);
-  const int64_t a2 = a + B.mis, b2 = b + B.mis;
-  int32_t cont = 0;
-  for (int64_t W = a2 >> 3; W <= (b2 - 1) >> 3; ++W) cont += (int32_t)trc_popc32(pk_word(B.sb, W, a2, b2).cont);
+  const int64_t a2 = a + B.mis, b2 = b + B.mis, W0 = a2 >> 3, W1 = (b2 - 1) >> 3;
+  auto cm = [&](int64_t W) -> uint64_t {
+    uint64_t x;
+#if defined(__CUDA_ARCH__)
+    x = *reinterpret_cast<const unsigned long long*>(B.sb + 8 * W);
+#else
+    memcpy(&x, B.sb + 8 * W, 8);
+#endif
+    return (x & SW_H) & ~((x << 1) & SW_H);
+  };
+  auto pc = [](uint64_t m) -> int32_t {
+#if defined(__CUDA_ARCH__)
+    return (int32_t)__popcll(m);
+#else
+    return (int32_t)__builtin_popcountll(m);
+#endif
+  };
+  const unsigned e = (unsigned)(b2 - 8 * W1);                            // bytes of the last word that belong to [a, b): 1..8
+  const uint64_t head = ~0ULL << (8 * (unsigned)(a2 & 7)), tail = e < 8u ? (1ULL << (8 * e)) - 1ULL : ~0ULL;
+  int32_t cont;
+  if (W0 == W1) cont = pc(cm(W0) & head & tail);
+  else {
+    cont = pc(cm(W0) & head) + pc(cm(W1) & tail);
+    for (int64_t W = W0 + 1; W < W1; ++W) cont += pc(cm(W));
+  }
   return (int32_t)(b - a) - cont;
 }
 

@@ -113,23 +113,31 @@ __global__ void k_punkt_breaks(TrcDev D, TrcTables T, TrcSentState S, int64_t to
 }
 #else
 #define PK_T 128
+#define PK_CELLS 4                             // cells per thread and tile: ~120 candidates per tile, a candidate for every thread
+#define PK_LIST (PK_T * 8)
 __global__ void __launch_bounds__(PK_T) k_punkt_breaks(TrcDev D, TrcTables T, TrcSentState S, int64_t total, uint8_t* brk) {
-  __shared__ int64_t s_p[PK_T * 8];
-  __shared__ int64_t s_i[PK_T * 8];
-  __shared__ int32_t s_q[PK_T * 8];
+  __shared__ int64_t s_p[PK_LIST];
+  __shared__ int64_t s_i[PK_LIST];
+  __shared__ int32_t s_q[PK_LIST];
   __shared__ int s_n;
   const int64_t ncell = (total + 7) / 8;
-  for (int64_t base = (int64_t)blockIdx.x * PK_T; base < ncell; base += (int64_t)gridDim.x * PK_T) {
+  for (int64_t base = (int64_t)blockIdx.x * (PK_T * PK_CELLS); base < ncell; base += (int64_t)gridDim.x * (PK_T * PK_CELLS)) {
     if (threadIdx.x == 0) s_n = 0;
     __syncthreads();
-    const int64_t cell = base + threadIdx.x;
-    if (cell < ncell) pk_break_cell(D, T, S, total, cell, brk, [&](int64_t q, int64_t i, int64_t p) {
-      const int slot = atomicAdd(&s_n, 1);
-      s_p[slot] = p; s_i[slot] = i; s_q[slot] = (int32_t)q;
-      return false;
-    });
+    for (int c = 0; c < PK_CELLS; ++c) {
+      const int64_t cell = base + c * PK_T + threadIdx.x;
+      if (cell < ncell) pk_break_cell(D, T, S, total, cell, brk, [&](int64_t q, int64_t i, int64_t p) {
+        const int slot = atomicAdd(&s_n, 1);
+        if (slot >= PK_LIST) {                  // (text that is mostly '.', '?' and '!': decided on the spot)
+          const int32_t j = D.gstart[S.rl_groups[q]];
+          return pk_is_break(T, D.C + D.coff[j], D.coff[j + 1] - D.coff[j], i);
+        }
+        s_p[slot] = p; s_i[slot] = i; s_q[slot] = (int32_t)q;
+        return false;
+      });
+    }
     __syncthreads();                            // the cells' flag words are written (zero where a candidate is queued)
-    const int nc = s_n;
+    const int nc = s_n < PK_LIST ? s_n : PK_LIST;
     for (int k = threadIdx.x; k < nc; k += PK_T) {
       const int32_t j = D.gstart[S.rl_groups[s_q[k]]];
       if (pk_is_break(T, D.C + D.coff[j], D.coff[j + 1] - D.coff[j], s_i[k])) brk[s_p[k]] = 1;
@@ -657,7 +665,11 @@ static int sentence_stage_count(trc_ctx* ctx, cudaStream_t st, int32_t* nsub_g, 
   uint8_t* brk; uint8_t* cellcnt; int64_t* cellscan;
   const int64_t ncell = (total + 7) / 8;
   ALLOC(brk, uint8_t, total + 8); ALLOC(cellcnt, uint8_t, ncell); ALLOC(cellscan, int64_t, ncell + 1);
+#ifdef TRC_HOSTSIM
   LAUNCH(k_punkt_breaks, ncell, 128, D, ctx->T, S, total, brk);
+#else
+  LAUNCH(k_punkt_breaks, (ncell + PK_CELLS - 1) / PK_CELLS, PK_T, D, ctx->T, S, total, brk);
+#endif
   LAUNCH(k_cell_counts, ncell, 256, brk, total, cellcnt);
   if ((rc = scan_excl(ctx, st, cellcnt, cellscan, ncell))) return rc;
   int64_t nbrk = 0;

@@ -22,7 +22,11 @@ for l in sass[start + 1:]:
     m = re.match(r"\s+/\*([0-9a-f]{4,})\*/\s+(\S.*);", l)
     if m and cur:
         line_of[int(m.group(1), 16)] = cur
-out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+m0 = re.match(r"_Z(\d+)", kern)                         # reports with several kernels: only the rows of this one
+base_name = kern[len(m0.group(0)):len(m0.group(0)) + int(m0.group(1))] if m0 else kern
+out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "-k", "regex:^" + base_name + "($|<|\\()"], capture_output=True, text=True).stdout
+if os.environ.get("KERNEL_ID"):                          # several launches of the kernel in the report: pick one by its ID
+    out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-id", ":::" + os.environ["KERNEL_ID"]], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
 hdr = rows[1]
 ix = {h: i for i, h in enumerate(hdr)}
