@@ -72,6 +72,7 @@ struct FuseArgs {
   // cut mode of k_clean_tok_c32 (oversized segments cut into parts, trc_giant.cuh): per segment of the launch the caller's
   // segment it belongs to, and whether it continues one; per kept record the first special-token hit (position << 4 | k)
   const int32_t* vorig; const uint8_t* vcont; unsigned long long* special_pos;
+  uint8_t* wtok;                    // cut mode: per byte of the cleaned text, tokens of the word that starts there (TrcWordSums::wtok)
 };
 #define FUSE_PH(i) do { if (A.phase && tid == 0) { long long now_ = clock64(); atomicAdd(&A.phase[i], (unsigned long long)(now_ - ph_t)); ph_t = now_; } } while (0)
 

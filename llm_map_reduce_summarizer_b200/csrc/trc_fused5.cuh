@@ -568,6 +568,10 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
             A.sl[slbase + q] = sw;
           } else cnt[w] = 255;
         }
+        if (cutmode && A.wtok) {                       // per-word counts for the sentence stage (words on the slow list: their kernels)
+          __syncthreads();
+          for (int32_t w = tid; w < tot_words; w += F5_T) if (cnt[w] != 255) A.wtok[gbase + (int32_t)(S.y.wstart[w] & 0x7fffu)] = cnt[w];
+        }
         if (S.flag) {                                  // rare: words that fit neither list are counted here
           __syncthreads();
           for (int32_t w = tid; w < tot_words; w += F5_T) {
@@ -578,7 +582,9 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
             const int seg = f5_seg_of_word(S, ns, w);
             const int32_t sl = (int32_t)S.loff[seg];
             const int64_t j = kbase + S.koff[seg];
+            bool deferred = false;
             const uint32_t cc = trc_count_unit(T, F, byte_id, S.out + st, n, vs, [&](int64_t ls, int64_t len) -> uint32_t {
+              deferred = true;
               const unsigned long long slot = atomicAdd(&A.wl_cnt[0], 1ULL);
               const unsigned long long off = atomicAdd(&A.wl_cnt[1], (unsigned long long)len);
               if ((int64_t)slot < A.wl_cap) {
@@ -589,6 +595,7 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
               return 0u;
             });
             cnt[w] = 0;
+            if (cutmode && A.wtok) A.wtok[gbase + st] = (uint8_t)((deferred || cc >= 255u) ? 255u : cc);
             atomicAdd(&S.xtok[seg], (int32_t)cc);
           }
         }
@@ -604,6 +611,7 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
         FUSE_PH(10);
       } else {
         // too many words for the list: write the tile out and count per segment
+        if (cutmode && tid == 0) atomicAdd(&A.wstat[4], 1ULL);          // (no per-word counts from this tile: the sentence stage counts itself)
         if (wid == 0) {
           long long gb, kb;
           f5_resolve2(A.desc_bytes, A.desc_kept, tile, tot_out, tot_kept, lane, &gb, &kb);
@@ -728,12 +736,13 @@ __global__ void __launch_bounds__(F5_T, F5_CTAS) k_clean_tok_c32(TrcDev D, TrcTa
 // words; on an open vocabulary of 500 k forms 1.47 M occurrences are ~0.35 M.  Words that are not in the memo (longer
 // than 15 bytes, or crowded out of their two slots) are counted per occurrence as before.
 __device__ __forceinline__ uint32_t f5_count_slow_word(const TrcDev& D, const TrcTables& T, const TrcFast& F, const uint32_t* byte_id, const SlowWord& w,
-                                                       LongEntry* wl, unsigned long long* wl_cnt, int64_t wl_cap) {
+                                                       LongEntry* wl, unsigned long long* wl_cnt, int64_t wl_cap, bool* deferred = nullptr) {
   const int vs = (int)((uint32_t)w.len_vs >> 31);
   const int64_t len = w.len_vs & 0x7fffffff;
   const int64_t j = w.unit;
   const int64_t rel = w.pos - D.coff[j];
   return trc_count_unit(T, F, byte_id, D.C + w.pos, len, vs, [&](int64_t ls, int64_t slen) -> uint32_t {
+    if (deferred) *deferred = true;
     unsigned long long slot = atomicAdd(&wl_cnt[0], 1ULL);
     unsigned long long off = atomicAdd(&wl_cnt[1], (unsigned long long)slen);
     if ((int64_t)slot < wl_cap) { LongEntry e; e.unit = j; e.lstart = ls + (vs ? 0 : rel + 1); e.len = slen; e.scratch_off = (int64_t)off; wl[slot] = e; }
@@ -785,8 +794,10 @@ __global__ void k_slow_words_count(TrcDev D, TrcTables T, const uint32_t* __rest
     const int64_t q = (int64_t)(d & ((1ULL << 40) - 1));
     const unsigned long long slot = d >> 40;
     const SlowWord w = sl[q];
-    const uint32_t c = f5_count_slow_word(D, T, F, byte_id, w, A.wl, A.wl_cnt, A.wl_cap);
+    bool deferred = false;
+    const uint32_t c = f5_count_slow_word(D, T, F, byte_id, w, A.wl, A.wl_cnt, A.wl_cap, &deferred);
     atomicAdd(&D.ctok[w.unit], c);
+    if (A.wtok) A.wtok[w.pos] = (uint8_t)((deferred || c >= 255u) ? 255u : c);
     if (slot != F5_NOSLOT) {
       const bool whole = c > 0 && c < 250u;             // (words of <= 15 bytes have no span for the long-span kernel)
       if (whole) {
@@ -807,7 +818,10 @@ __global__ void k_slow_words_follow(TrcDev D, TrcTables T, const uint32_t* __res
     const int64_t q = (int64_t)(d & ((1ULL << 40) - 1));
     const size_t slot = (size_t)(d >> 40);
     const SlowWord w = sl[q];
-    if (A.memo_lock[slot] == 3u) atomicAdd(&D.ctok[w.unit], (uint32_t)(A.memo[2 * slot + 1] >> 56) - 1u);
-    else atomicAdd(&D.ctok[w.unit], f5_count_slow_word(D, T, F, byte_id, w, A.wl, A.wl_cnt, A.wl_cap));
+    bool deferred = false;
+    const uint32_t c = A.memo_lock[slot] == 3u ? (uint32_t)(A.memo[2 * slot + 1] >> 56) - 1u
+                                               : f5_count_slow_word(D, T, F, byte_id, w, A.wl, A.wl_cnt, A.wl_cap, &deferred);
+    atomicAdd(&D.ctok[w.unit], c);
+    if (A.wtok) A.wtok[w.pos] = (uint8_t)((deferred || c >= 255u) ? 255u : c);
   }
 }

@@ -43,6 +43,8 @@ struct TrcWordSums {
   const int64_t* toff;        // cleaned offset of every giant inside the giants' text buffer
   const int64_t* wscan;       // words that start before byte x of that buffer
   const int64_t* wpre;        // tokens of the words before word w
+  const uint8_t* wtok;        // cut mode instead of the four above: per byte of the cleaned text, the token count of the word that
+                              // starts there (0: no word starts there, 255: not known); nullptr: none
 };
 
 TRC_HD bool pk_nonword(uint8_t c) {

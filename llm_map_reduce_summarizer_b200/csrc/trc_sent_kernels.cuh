@@ -248,6 +248,42 @@ __global__ void k_sent_wordsum(TrcDev D, TrcSentState S, TrcWordSums W, int64_t 
         }
       }
     }
+    else if (W.wtok && R.len > 0) {
+      // cut mode: the fused kernel left the token count of every word at the word's first byte (its space, or the first
+      // byte of the segment); zero elsewhere, 255 = not known there.  Same head / middle / tail split as above.
+      const int32_t j = D.gstart[R.group];
+      const int64_t c0 = D.coff[j], c1 = D.coff[j + 1];
+      const bool left = a == c0 || D.C[a - 1] == ' ', right = b == c1 || D.C[b] == ' ';
+      int64_t m0 = a, m1 = b;
+      bool whole = false;
+      if (!left) { while (m0 < b && D.C[m0] != ' ') ++m0; if (m0 >= b) whole = true; }
+      if (!whole && !right) { m1 = b - 1; while (m1 >= m0 && D.C[m1] != ' ') --m1; if (m1 < m0) whole = true; }
+      if (!whole) {
+        const int64_t x0 = left ? (a == c0 ? a : a - 1) : m0, x1 = m1;      // words that start in [x0, x1)
+        int64_t sum = 0;
+        bool unknown = x1 - x0 > 512;        // (a long record is counted directly, a thread per 32 bytes: k_count_units_coop)
+        int64_t x = unknown ? x1 : x0;
+        for (; x < x1 && (x & 7); ++x) { const uint8_t t = W.wtok[x]; sum += t; unknown |= t == 255; }
+        for (; x + 8 <= x1; x += 8) {
+          uint64_t q;
+#if defined(__CUDA_ARCH__)
+          q = *reinterpret_cast<const unsigned long long*>(W.wtok + x);
+#else
+          memcpy(&q, W.wtok + x, 8);
+#endif
+          if (!q) continue;
+          unknown |= pk_eq8(q, 0xFF) != 0;
+          const uint64_t pair = (q & 0x00FF00FF00FF00FFULL) + ((q >> 8) & 0x00FF00FF00FF00FFULL);
+          sum += (int64_t)((pair * 0x0001000100010001ULL) >> 48);
+        }
+        for (; x < x1; ++x) { const uint8_t t = W.wtok[x]; sum += t; unknown |= t == 255; }
+        if (!unknown) {
+          h1 = left ? a : m0;
+          if (!right) t0 = m1;
+          v = sum;
+        }
+      }
+    }
     hs[r] = h0; he[r] = h1; ts[r] = t0; te[r] = t1; wsum[r] = v;
   }
 }
@@ -693,8 +729,8 @@ static int sentence_stage_count(trc_ctx* ctx, cudaStream_t st, int32_t* nsub_g, 
   int64_t* wsum; int64_t* tst; int64_t* ten; uint32_t* tcnt;
   ALLOC(wsum, int64_t, S.n_sent); ALLOC(tst, int64_t, S.n_sent); ALLOC(ten, int64_t, S.n_sent); ALLOC(tcnt, uint32_t, S.n_sent);
   LAUNCH(k_sent_wordsum, S.n_sent, 128, D, S, ctx->WS, (int64_t)0, S.n_sent, ustart, uend, tst, ten, wsum);
-  if ((rc = count_units(ctx, st, D.C, ustart, uend, S.n_sent, total, 1, cnt, nullptr, false, 512))) return rc;
-  if (ctx->WS.of_seg) { if ((rc = count_units(ctx, st, D.C, tst, ten, S.n_sent, total, 0, tcnt, nullptr, false, 512))) return rc; }
+  if ((rc = count_units(ctx, st, D.C, ustart, uend, S.n_sent, total, 1, cnt, nullptr, false, 128))) return rc;
+  if (ctx->WS.of_seg || ctx->WS.wtok) { if ((rc = count_units(ctx, st, D.C, tst, ten, S.n_sent, total, 0, tcnt, nullptr, false, 128))) return rc; }
 #ifdef TRC_HOSTSIM
   LAUNCH(k_sent_tok, S.n_sent, 128, D, ctx->T, S, ustart, uend, tst, ten, wsum, cnt, tcnt, ncl, (int64_t*)nullptr, (unsigned long long*)nullptr);
 #else
@@ -734,8 +770,8 @@ static int sentence_stage_count(trc_ctx* ctx, cudaStream_t st, int32_t* nsub_g, 
     int64_t* cwsum; int64_t* cts; int64_t* cte; uint32_t* ctc;
     ALLOC(cwsum, int64_t, ncls); ALLOC(cts, int64_t, ncls); ALLOC(cte, int64_t, ncls); ALLOC(ctc, uint32_t, ncls);
     LAUNCH(k_sent_wordsum, ncls, 128, D, S, ctx->WS, S.n_sent, ncls, cus, cue, cts, cte, cwsum);
-    if ((rc = count_units(ctx, st, D.C, cus, cue, ncls, total, 1, ccnt, nullptr, false, 512))) return rc;
-    if (ctx->WS.of_seg) { if ((rc = count_units(ctx, st, D.C, cts, cte, ncls, total, 0, ctc, nullptr, false, 512))) return rc; }
+    if ((rc = count_units(ctx, st, D.C, cus, cue, ncls, total, 1, ccnt, nullptr, false, 128))) return rc;
+    if (ctx->WS.of_seg || ctx->WS.wtok) { if ((rc = count_units(ctx, st, D.C, cts, cte, ncls, total, 0, ctc, nullptr, false, 128))) return rc; }
     LAUNCH(k_clause_tok, ncls, 128, ctx->T, S, cus, cue, cts, cte, cwsum, ccnt, ctc, ncls);
   }
   LAUNCH_W(k_sent_greedy_count, (int64_t)nraw, D, S, nsub_g);

@@ -1263,6 +1263,7 @@ static int count_units(trc_ctx* ctx, cudaStream_t st, const uint8_t* bytes, cons
                        int64_t n, int64_t total_bytes, int vs, uint32_t* counts, int32_t* special, bool allow_sync_free, int64_t coop_min = 0) {
   if (n <= 0) return TRC_OK;
   if (special) coop_min = 0;                   // (the cooperative counter does not look for special-token literals)
+  if (coop_min > 0) { if (const char* e = getenv("TRCHUNK_COOP_MIN")) { const long v = atol(e); if (v > 0) coop_min = v; } }   // experiments
 #ifdef TRC_HOSTSIM
   coop_min = 0;
 #endif
@@ -1674,7 +1675,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       // segments, heavy-tailed lengths - tiles of varying size (k_tile_flags).
       FuseArgs A;
       A.G = GiantView{};
-      A.tile_start = nullptr; A.vorig = nullptr; A.vcont = nullptr; A.special_pos = nullptr;
+      A.tile_start = nullptr; A.vorig = nullptr; A.vcont = nullptr; A.special_pos = nullptr; A.wtok = nullptr;
       TrcDev Dk = D;                         // the batch as the fused kernel sees it (cut mode: parts in place of oversized segments)
       int64_t ntiles_var = -1;
       if (gen >= 3) {
@@ -1724,6 +1725,10 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
                 CK(cudaMemsetAsync(A.special_pos, 0xff, 8 * (size_t)n, st));
                 CK(cudaMemsetAsync(D.ctok, 0, 4 * (size_t)n, st));
                 CK(cudaMemsetAsync(D.cchars, 0, 4 * (size_t)n, st));
+                if (ctx->use_memo) {         // per-word token counts for the sentence stage (the slow words' kernels fill theirs in)
+                  ALLOC(A.wtok, uint8_t, ccap + 8);
+                  CK(cudaMemsetAsync(A.wtok, 0, (size_t)ccap + 8, st));
+                }
               } else {                       // a segment that cannot be cut: the byte-parallel pre-pass for this batch
                 Dk = D;
                 if ((rc = giant_stage(ctx, st, braw, &A.G, TileCand{{0, 0, 0, 0}, 0}, F5_IN_CAP, stats, nullptr))) return rc;
@@ -1789,14 +1794,15 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       prof_end(ctx, st);
       ctx->launches++;
       CK(cudaGetLastError());
-      unsigned long long h[26];
-      if ((rc = read_back(ctx, st, fz + 2, 208, h))) return rc;     // wl count, wl scratch, n_kept, bclean, -, slow words, ..., word statistics
+      unsigned long long h[27];
+      if ((rc = read_back(ctx, st, fz + 2, 216, h))) return rc;     // wl count, wl scratch, n_kept, bclean, -, slow words, ..., word statistics
       ctx->counts[TRC_N_WORDS] = (int64_t)h[22]; ctx->counts[TRC_N_WORD_FIRST] = (int64_t)h[23]; ctx->counts[TRC_N_WORD_SLOW] = (int64_t)h[24];
       nk = (int64_t)h[2]; bclean = (int64_t)h[3];
       D.n_kept = nk;
       if (A.vcont) {
         if (h[25]) { ctx->err = "internal: a tile of a batch with cut segments took the slow lane"; return TRC_EINVAL; }
         LAUNCH(k_special_from_pos, nk, 256, A.special_pos, nk, seg_special);
+        if (A.wtok && h[26] == 0) ctx->WS.wtok = A.wtok;          // (h[26]: tiles that counted per segment and left no per-word counts)
       }
       {
         int64_t nslow = (int64_t)h[5] < A.sl_cap ? (int64_t)h[5] : A.sl_cap;   // entries past the capacity were counted in the kernel
