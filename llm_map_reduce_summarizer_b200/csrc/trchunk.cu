@@ -1227,6 +1227,23 @@ static int read_back2(trc_ctx* ctx, cudaStream_t st, const void* a, const void* 
   return TRC_OK;
 }
 
+// Two 8-byte values and a pair of them in one round trip (the group / merged-text totals and the side stream's counters).
+#ifndef TRC_HOSTSIM
+__global__ void k_read_back4(const unsigned long long* a, const unsigned long long* b, const unsigned long long* c2, unsigned long long* dst) {
+  if (threadIdx.x == 0) dst[0] = a ? *a : 0ULL;
+  if (threadIdx.x == 1) dst[1] = b ? *b : 0ULL;
+  if (threadIdx.x == 2) dst[2] = c2 ? c2[0] : 0ULL;
+  if (threadIdx.x == 3) dst[3] = c2 ? c2[1] : 0ULL;
+}
+static int read_back4(trc_ctx* ctx, cudaStream_t st, const void* a, const void* b, const void* c2, int64_t out[4]) {
+  k_read_back4<<<1, 32, 0, st>>>((const unsigned long long*)a, (const unsigned long long*)b, (const unsigned long long*)c2, (unsigned long long*)ctx->d_pin);
+  ctx->launches++;
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(st));
+  for (int k = 0; k < 4; ++k) out[k] = ctx->h_pin[k];
+  return TRC_OK;
+}
+#endif
 // Three counters in one round trip: a 4-byte and two 8-byte values (any pointer may be null: 0).
 #ifndef TRC_HOSTSIM
 __global__ void k_read_back3(const int32_t* a, const unsigned long long* b, const unsigned long long* c, unsigned long long* dst) {
@@ -1934,6 +1951,16 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   if ((rc = scan_excl(ctx, st, D.plen, D.poff, nk))) return rc;
   if (!D.preserve) { if ((rc = scan_excl(ctx, st, plen_sub, D.poffs, nk))) return rc; }
   int64_t m = 0, bm = 0;
+#ifndef TRC_HOSTSIM
+  if (nk && slow_pending) {                    // the join with the side stream rides on the same round trip (see below)
+    CK(cudaEventRecord(ctx->ev_aux[1], ctx->aux_stream));
+    CK(cudaStreamWaitEvent(st, ctx->ev_aux[1], 0));
+    int64_t t4[4];
+    if ((rc = read_back4(ctx, st, D.gscan + nk, D.poff + nk, j_fz + 2, t4))) return rc;
+    m = t4[0]; bm = t4[1]; j_h0 = (unsigned long long)t4[2]; j_h1 = (unsigned long long)t4[3];
+    slow_pending = false;
+  } else
+#endif
   if (nk) { int64_t t2[2]; if ((rc = read_back2(ctx, st, D.gscan + nk, D.poff + nk, t2))) return rc; m = t2[0]; bm = t2[1]; }
   D.m = m; ctx->counts[TRC_N_GROUPS] = m;
   ctx->counts[TRC_B_MERGED] = bm;
