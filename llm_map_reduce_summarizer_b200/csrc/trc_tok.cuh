@@ -189,6 +189,18 @@ TRC_HD int trc_bpe_short(const TrcTables& T, const uint32_t* byte_id, const TrcS
 // Index of a special-token literal contained in the unit's real bytes, or -1.
 TRC_HD int trc_find_special(const TrcTables& T, const uint8_t* p, int64_t n) {
   for (int64_t i = 0; i < n; ++i) {
+    if (T.sp_single < 0x100u && i + 8 <= n && (((uintptr_t)(p + i)) & 7) == 0) {
+      // every literal starts with the same ASCII byte: eight bytes without it are skipped at once (a 64 KB unit was a load
+      // latency per byte for the one thread that walks it)
+      uint64_t x;
+#if defined(__CUDA_ARCH__)
+      x = *reinterpret_cast<const unsigned long long*>(p + i);
+#else
+      memcpy(&x, p + i, 8);
+#endif
+      const uint64_t t = x ^ (0x0101010101010101ULL * (uint64_t)T.sp_single);
+      if (!((t - 0x0101010101010101ULL) & ~t & 0x8080808080808080ULL)) { i += 7; continue; }
+    }
     uint8_t b = p[i];
     if (!((T.sp_first[b >> 6] >> (b & 63)) & 1ULL)) continue;
     for (uint32_t k = 0; k < T.n_sp; ++k) {
