@@ -498,26 +498,40 @@ TRC_HD SentLite sent_lite(const TrcSent& R) {
   o.piece = 1 + trc_ts_len(R.start) + 2 + R.len;
   return o;
 }
+// A record as the greedy sees it: accessors, so that the warp version moves a field between lanes only where the loop
+// reads it (the counting pass reads nothing but the token count: one shuffle per record instead of twelve).
+struct SentViewDirect {
+  SentLite v;
+  TRC_HD int32_t tok() const { return v.tok; }
+  TRC_HD int64_t piece() const { return v.piece; }
+  TRC_HD double start() const { return v.start; }
+  TRC_HD double end() const { return v.end; }
+  TRC_HD int64_t cl0() const { return v.cl0; }
+  TRC_HD int32_t ncl() const { return v.ncl; }
+};
 struct SentFetchDirect {
   const TrcSent* recs;
-  TRC_HD SentLite operator()(int64_t r) { return sent_lite(recs[r]); }
+  TRC_HD SentViewDirect operator()(int64_t r) { return SentViewDirect{sent_lite(recs[r])}; }
 };
 #ifndef TRC_HOSTSIM
+struct SentViewWarp {
+  const SentLite* mine; int src;
+  __device__ int32_t tok() const { return __shfl_sync(0xffffffffu, mine->tok, src); }
+  __device__ int64_t piece() const { return __shfl_sync(0xffffffffu, mine->piece, src); }
+  __device__ double start() const { return __shfl_sync(0xffffffffu, mine->start, src); }
+  __device__ double end() const { return __shfl_sync(0xffffffffu, mine->end, src); }
+  __device__ int64_t cl0() const { return __shfl_sync(0xffffffffu, mine->cl0, src); }
+  __device__ int32_t ncl() const { return __shfl_sync(0xffffffffu, mine->ncl, src); }
+};
 struct SentFetchWarp {
   const TrcSent* recs; int64_t hi; int lane; int64_t win0; SentLite mine;
-  __device__ SentLite operator()(int64_t r) {
+  __device__ SentViewWarp operator()(int64_t r) {
     if (r < win0 || r >= win0 + 32) {
       win0 = r;
       const int64_t x = r + lane;
       if (x < hi) mine = sent_lite(recs[x]);
     }
-    const int src = (int)(r - win0);
-    SentLite o;
-    o.len = __shfl_sync(0xffffffffu, mine.len, src); o.cl0 = __shfl_sync(0xffffffffu, mine.cl0, src);
-    o.start = __shfl_sync(0xffffffffu, mine.start, src); o.end = __shfl_sync(0xffffffffu, mine.end, src);
-    o.tok = __shfl_sync(0xffffffffu, mine.tok, src); o.ncl = __shfl_sync(0xffffffffu, mine.ncl, src);
-    o.piece = __shfl_sync(0xffffffffu, mine.piece, src);
-    return o;
+    return SentViewWarp{&mine, (int)(r - win0)};
   }
 };
 #endif
@@ -532,17 +546,22 @@ TRC_HD void sg_flush(TrcSentState& S, TrcSub* out, int32_t& ns, int32_t g, int32
   }
   ++ns;
 }
-// Appends record r to the sub-chunk under construction, which will be flushed as number ns (nothing else is
-// flushed between a sub-chunk's first append and its own flush).
-template <bool WRITE>
-TRC_HD void sg_append(TrcSentState& S, SubAcc& a, int32_t r, const SentLite& R, int64_t sub_index, bool wr) {
-  const int64_t piece = R.piece;
+// Appends record r (tok tokens) to the sub-chunk under construction, which will be flushed as number ns (nothing else is
+// flushed between a sub-chunk's first append and its own flush).  Only the writing pass needs the record's text length
+// and end time.
+template <bool WRITE, class View>
+TRC_HD void sg_append(TrcSentState& S, SubAcc& a, int32_t r, const View& R, int32_t tok, int64_t sub_index, bool wr) {
   if (a.n == 0) { a.r0 = r; a.text_len = 0; }
-  if (WRITE && wr) { S.recs[r].sub = (int32_t)sub_index; S.recs[r].off_in_sub = a.n ? a.text_len + 1 : 0; }
-  a.text_len += piece + (a.n ? 1 : 0);
-  a.tok += R.tok; a.r1 = r; a.n += 1; a.end = R.end;
+  if (WRITE) {
+    const int64_t piece = R.piece();
+    if (wr) { S.recs[r].sub = (int32_t)sub_index; S.recs[r].off_in_sub = a.n ? a.text_len + 1 : 0; }
+    a.text_len += piece + (a.n ? 1 : 0);
+    a.end = R.end();
+  }
+  a.tok += tok; a.r1 = r; a.n += 1;
 }
 
+// (a record is empty exactly when its token count is 0: k_sent_tok / k_clause_tok give every non-empty record 2 + ...)
 template <bool WRITE, class Fetch>
 TRC_HD int32_t trc_split_sentences(const TrcDev& D, TrcSentState S, int64_t q, TrcSub* out, int64_t sub_base, Fetch&& fetch, bool wr) {
   int32_t g = S.rl_groups[q];
@@ -552,31 +571,35 @@ TRC_HD int32_t trc_split_sentences(const TrcDev& D, TrcSentState S, int64_t q, T
   SubAcc cur; cur.tok = 0; cur.text_len = 0; cur.n = 0; cur.r0 = cur.r1 = -1; cur.start = D.start[D.k2r[j]]; cur.end = 0; cur.start_src = j;
   const int64_t r_end = S.sent_off[q + 1];
   for (int64_t r = S.sent_off[q]; r < r_end; ++r) {
-    const SentLite R = fetch(r);
-    if (R.len == 0) continue;
-    if (R.tok > E) {
+    const auto R = fetch(r);
+    const int32_t tok = R.tok();
+    if (tok == 0) continue;
+    if (tok > E) {
       // clause sub-chunks of this sentence (:437-542)
-      SubAcc cl; cl.tok = 0; cl.text_len = 0; cl.n = 0; cl.r0 = cl.r1 = -1; cl.start = R.start; cl.end = 0; cl.start_src = -1;
+      const double r_start = R.start(), r_endt = R.end();
+      const int64_t cl0 = R.cl0(), ncl = R.ncl();
+      SubAcc cl; cl.tok = 0; cl.text_len = 0; cl.n = 0; cl.r0 = cl.r1 = -1; cl.start = r_start; cl.end = 0; cl.start_src = -1;
       // an existing sub-chunk is closed first (:378-381), but it is appended BEFORE the clause chunks
-      if (cur.tok > 0) { cur.end = R.start; sg_flush<WRITE>(S, out, ns, g, 1, cur, wr); }
-      for (int64_t c = R.cl0; c < R.cl0 + R.ncl; ++c) {
-        const SentLite C = sent_lite(S.recs[c]);
-        if (C.len == 0) continue;
-        if (cl.tok + C.tok > E && cl.tok > 0) {
+      if (cur.tok > 0) { cur.end = r_start; sg_flush<WRITE>(S, out, ns, g, 1, cur, wr); }
+      for (int64_t c = cl0; c < cl0 + ncl; ++c) {
+        const SentViewDirect C{sent_lite(S.recs[c])};
+        if (C.v.len == 0) continue;
+        if (cl.tok + C.v.tok > E && cl.tok > 0) {
           sg_flush<WRITE>(S, out, ns, g, 2, cl, wr);
-          cl.tok = 0; cl.text_len = 0; cl.n = 0; cl.start = C.start; cl.start_src = -1;
+          cl.tok = 0; cl.text_len = 0; cl.n = 0; cl.start = C.v.start; cl.start_src = -1;
         }
-        sg_append<WRITE>(S, cl, (int32_t)c, C, sub_base + ns, wr);
+        sg_append<WRITE>(S, cl, (int32_t)c, C, C.v.tok, sub_base + ns, wr);
       }
       if (cl.tok > 0) sg_flush<WRITE>(S, out, ns, g, 2, cl, wr);
-      cur.tok = 0; cur.text_len = 0; cur.n = 0; cur.start = R.end; cur.start_src = -1;     // :387-399
-    } else if (cur.tok + R.tok > E && cur.tok > 0) {
-      cur.end = R.start;                                                                   // :404
+      cur.tok = 0; cur.text_len = 0; cur.n = 0; cur.start = r_endt; cur.start_src = -1;    // :387-399
+    } else if (cur.tok + tok > E && cur.tok > 0) {
+      if (WRITE) cur.end = R.start();                                                      // :404
       sg_flush<WRITE>(S, out, ns, g, 1, cur, wr);
-      cur.tok = 0; cur.text_len = 0; cur.n = 0; cur.start = R.start; cur.start_src = -1;   // :409-421
-      sg_append<WRITE>(S, cur, (int32_t)r, R, sub_base + ns, wr);
+      cur.tok = 0; cur.text_len = 0; cur.n = 0; cur.start_src = -1;                        // :409-421
+      if (WRITE) cur.start = cur.end;
+      sg_append<WRITE>(S, cur, (int32_t)r, R, tok, sub_base + ns, wr);
     } else {
-      sg_append<WRITE>(S, cur, (int32_t)r, R, sub_base + ns, wr);                          // :423-429
+      sg_append<WRITE>(S, cur, (int32_t)r, R, tok, sub_base + ns, wr);                     // :423-429
     }
   }
   if (cur.tok > 0) sg_flush<WRITE>(S, out, ns, g, 1, cur, wr);
