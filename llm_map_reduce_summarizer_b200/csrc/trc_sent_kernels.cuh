@@ -614,18 +614,90 @@ __global__ void k_sent_greedy_write(TrcDev D, TrcSentState S) {
   GSTRIDE(q, S.n_rl) { int64_t base = D.sub_off[S.rl_groups[q]]; trc_split_sentences<true>(D, S, q, D.subs + base, base, SentFetchDirect{S.recs}, true); }
 }
 #else
+// The same greedy for a warp, written for the loop it is: ~1 400 dependent iterations per segment in a warp that has the
+// SM quadrant almost to itself, so every instruction of an iteration is paid in full (profiles: 73 instructions per
+// sentence through the generic code, most of them 64-bit index arithmetic and struct traffic).  Lanes load 32 records'
+// token counts (and, when writing, text lengths and start times) at once; the uniform inner loop moves one or two values
+// per record between lanes and keeps 32-bit indices; what a record gets (sub-chunk, offset) is parked in the lane that
+// loaded it and stored 32 records at a time.  Over-budget sentences (rare) go through the generic clause code.
+template <bool WRITE>
+__device__ int32_t sg_warp(const TrcDev& D, TrcSentState S, int64_t q, TrcSub* out, int64_t sub_base, int lane) {
+  const int32_t g = S.rl_groups[q];
+  const int32_t j = D.gstart[g];
+  const int64_t E = D.doc_E[D.sdoc[j]];
+  const int64_t rbase = S.sent_off[q];
+  const int32_t n = (int32_t)(S.sent_off[q + 1] - rbase);
+  TrcSent* const recs = S.recs + rbase;
+  const bool wr = lane == 0;
+  int32_t ns = 0;
+  SubAcc cur; cur.tok = 0; cur.text_len = 0; cur.n = 0; cur.r0 = cur.r1 = -1; cur.start = D.start[D.k2r[j]]; cur.end = 0; cur.start_src = j;
+  // (the next window's records are requested before the current window is walked: their latency hides under the walk)
+  int32_t ntok = 0; double nstart = 0.0; int64_t nlen = 0;
+  if (lane < n) { ntok = recs[lane].tok; if (WRITE) { nstart = recs[lane].start; nlen = recs[lane].len; } }
+  for (int32_t base = 0; base < n; base += 32) {
+    const int32_t k = base + lane;
+    const int32_t mytok = ntok; const double mystart = nstart;
+    int32_t mypiece = 0;
+    if (WRITE && k < n) mypiece = (int32_t)(1 + trc_ts_len(mystart) + 2 + nlen);
+    ntok = 0;
+    if (k + 32 < n) { ntok = recs[k + 32].tok; if (WRITE) { nstart = recs[k + 32].start; nlen = recs[k + 32].len; } }
+    int32_t mysub = -1; int64_t myoff = 0;
+    const int cnt = n - base < 32 ? n - base : 32;
+    for (int t = 0; t < cnt; ++t) {
+      const int32_t tok = __shfl_sync(0xffffffffu, mytok, t);
+      if (tok == 0) continue;                                   // an empty record (see trc_split_sentences)
+      const int32_t r = (int32_t)(rbase + base + t);            // record index as the sub-chunks store it
+      if (tok > E) {
+        const TrcSent& R = S.recs[r];
+        const double r_start = R.start, r_endt = R.end;
+        const int64_t cl0 = R.cl0, ncl = R.ncl;
+        SubAcc cl; cl.tok = 0; cl.text_len = 0; cl.n = 0; cl.r0 = cl.r1 = -1; cl.start = r_start; cl.end = 0; cl.start_src = -1;
+        if (cur.tok > 0) { cur.end = r_start; sg_flush<WRITE>(S, out, ns, g, 1, cur, wr); }
+        for (int64_t c = cl0; c < cl0 + ncl; ++c) {
+          const SentViewDirect C{sent_lite(S.recs[c])};
+          if (C.v.len == 0) continue;
+          if (cl.tok + C.v.tok > E && cl.tok > 0) {
+            sg_flush<WRITE>(S, out, ns, g, 2, cl, wr);
+            cl.tok = 0; cl.text_len = 0; cl.n = 0; cl.start = C.v.start; cl.start_src = -1;
+          }
+          sg_append<WRITE>(S, cl, (int32_t)c, C, C.v.tok, sub_base + ns, wr);
+        }
+        if (cl.tok > 0) sg_flush<WRITE>(S, out, ns, g, 2, cl, wr);
+        cur.tok = 0; cur.text_len = 0; cur.n = 0; cur.start = r_endt; cur.start_src = -1;
+        continue;
+      }
+      if (cur.tok + tok > E && cur.tok > 0) {
+        if (WRITE) cur.end = __shfl_sync(0xffffffffu, mystart, t);
+        sg_flush<WRITE>(S, out, ns, g, 1, cur, wr);
+        cur.tok = 0; cur.text_len = 0; cur.n = 0; cur.start_src = -1;
+        if (WRITE) cur.start = cur.end;
+      }
+      if (cur.n == 0) { cur.r0 = r; cur.text_len = 0; }
+      if (WRITE) {
+        const int32_t piece = __shfl_sync(0xffffffffu, mypiece, t);
+        if (lane == t) { mysub = (int32_t)(sub_base + ns); myoff = cur.n ? cur.text_len + 1 : 0; }
+        cur.text_len += piece + (cur.n ? 1 : 0);
+      }
+      cur.tok += tok; cur.r1 = r; cur.n += 1;
+    }
+    if (WRITE && mysub >= 0) { recs[k].sub = mysub; recs[k].off_in_sub = myoff; }
+  }
+  if (cur.tok > 0) {
+    if (WRITE) cur.end = S.recs[cur.r1].end;                    // the end of the last record appended
+    sg_flush<WRITE>(S, out, ns, g, 1, cur, wr);
+  }
+  return ns;
+}
 __global__ void k_sent_greedy_count(TrcDev D, TrcSentState S, int32_t* nsub_g) {
   WSTRIDE(q, S.n_rl) {
-    SentFetchWarp f; f.recs = S.recs; f.hi = S.sent_off[q + 1]; f.lane = TRC_LANE; f.win0 = -64;
-    const int32_t n = trc_split_sentences<false>(D, S, q, nullptr, 0, f, TRC_LANE == 0);
+    const int32_t n = sg_warp<false>(D, S, q, nullptr, 0, TRC_LANE);
     if (TRC_LANE == 0) nsub_g[S.rl_groups[q]] = n;
   }
 }
 __global__ void k_sent_greedy_write(TrcDev D, TrcSentState S) {
   WSTRIDE(q, S.n_rl) {
-    SentFetchWarp f; f.recs = S.recs; f.hi = S.sent_off[q + 1]; f.lane = TRC_LANE; f.win0 = -64;
-    int64_t base = D.sub_off[S.rl_groups[q]];
-    trc_split_sentences<true>(D, S, q, D.subs + base, base, f, TRC_LANE == 0);
+    const int64_t base = D.sub_off[S.rl_groups[q]];
+    sg_warp<true>(D, S, q, D.subs + base, base, TRC_LANE);
   }
 }
 #endif
