@@ -23,7 +23,7 @@
 #endif
 #define F5_CTAS (1024 / F5_T)                   // CTAs per SM
 #define F5_NW (F5_T / 32)
-#define F5_SEGS (F5_T / 2)
+#define F5_SEGS F5_T                            // a thread per segment in the per-segment phases
 #define F5_IN_CAP (F5_T * 32)
 #define F5_NCH (F5_IN_CAP / 32)                 // one chunk per thread
 #define F5_OUT_CAP (F5_IN_CAP + F5_IN_CAP / 2)

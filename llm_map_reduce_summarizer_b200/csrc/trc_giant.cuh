@@ -46,13 +46,13 @@ __global__ void k_giant_any(TrcDev D, unsigned long long* cnt, TileCand cand, in
 }
 // Tiles of varying size for batches whose segments do not fit tiles of a fixed segment count (oversized segments, heavy
 // tails): a tile is a run of segments that start inside the same window of `win` bytes, at most `max_segs` of them, and an
-// oversized segment is a tile of its own.  Its raw bytes then span less than win + TRC_GIANT_MIN + 16.
-__global__ void k_tile_flags(TrcDev D, int32_t* flag, int64_t win, int max_segs) {
+// segment of more than `iso` bytes is a tile of its own.  The raw bytes of any other tile span less than win + iso + 16.
+__global__ void k_tile_flags(TrcDev D, int32_t* flag, int64_t win, int max_segs, int64_t iso) {
   GSTRIDE(i, D.n) {
     int f = (uint32_t)i % (uint32_t)max_segs == 0u;
     if (!f) {
       const int64_t a = D.seg_off[i], p = D.seg_off[i - 1], b = D.seg_off[i + 1];
-      f = (a / win != p / win) || (b - a > TRC_GIANT_MIN) || (a - p > TRC_GIANT_MIN);
+      f = (a / win != p / win) || (b - a > iso) || (a - p > iso);
     }
     flag[i] = f;
   }
@@ -66,7 +66,7 @@ __global__ void k_giant_list(TrcDev D, const int32_t* __restrict__ flag, const i
   }
 }
 // ---- cutting oversized segments into parts (generation 5) ----------------------------------------------------------------
-// An oversized segment is handed to the fused kernel as PARTS of at most TRC_CUT_STEP + TRC_CUT_SEARCH bytes.  A cut sits
+// An oversized segment is handed to the fused kernel as PARTS of (normally) at most TRC_CUT_STEP + TRC_CUT_SEARCH bytes.  A cut sits
 // in front of a whitespace run that follows an ASCII non-whitespace byte, so the part before it ends in text and the
 // part after it starts with the run; the kernel lets a continuing part keep that run (one space), and the cleaned parts
 // back to back ARE the cleaned segment, provided no rule of clean_text looks across the cut:
@@ -77,8 +77,9 @@ __global__ void k_giant_list(TrcDev D, const int32_t* __restrict__ flag, const i
 // One thread per cut target (every TRC_CUT_STEP bytes) looks for the first such place within TRC_CUT_SEARCH bytes.  A
 // target without one is skipped; when that leaves a part too long for a tile (kilobytes of one repeated word, non-ASCII
 // text without ASCII whitespace) *bad is set and the batch takes the byte-parallel pre-pass below instead.
-#define TRC_CUT_STEP 2048
-#define TRC_CUT_SEARCH 1024
+#define TRC_CUT_STEP 1024
+#define TRC_CUT_SEARCH 512
+#define TRC_CUT_ISO 2048             // parts are at most STEP + SEARCH bytes unless a target had no cut: longer ones get a tile each
 __global__ void k_cut_counts(const int64_t* __restrict__ len, int64_t ng, int32_t* tcnt) { GSTRIDE(q, ng) tcnt[q] = (int32_t)((len[q] - 1) / TRC_CUT_STEP); }
 __global__ void k_cut_find(TrcDev D, TrcTables T, const int32_t* __restrict__ list, const int64_t* __restrict__ len, const int64_t* __restrict__ tpre,
                            int64_t ng, int64_t nt, int64_t* cutpos) {

@@ -1714,10 +1714,10 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
           if (pick >= 0) tsegs4 = cand.v[pick];
           else {
             static_assert(F5_IN_CAP > TRC_GIANT_MIN + 16, "a window of the varying tiles");
-            auto var_tiles = [&](const TrcDev& Dx, const unsigned long long* word, int64_t* word_out) -> int {
+            auto var_tiles = [&](const TrcDev& Dx, int64_t iso, const unsigned long long* word, int64_t* word_out) -> int {
               int32_t* tflag; int64_t* tscan; int32_t* tstart;
               ALLOC(tflag, int32_t, Dx.n); ALLOC(tscan, int64_t, Dx.n + 1);
-              LAUNCH(k_tile_flags, Dx.n, 256, Dx, tflag, (int64_t)(F5_IN_CAP - TRC_GIANT_MIN - 16), (int)F5_SEGS);
+              LAUNCH(k_tile_flags, Dx.n, 256, Dx, tflag, (int64_t)F5_IN_CAP - iso - 16, (int)F5_SEGS, iso);
               int r2;
               if ((r2 = scan_excl(ctx, st, tflag, tscan, Dx.n))) return r2;
               int64_t h2[2] = {0, 0};
@@ -1733,7 +1733,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
             if (CV.nv > 0) {
               Dk.seg_off = CV.vseg_off; Dk.n = CV.nv;
               int64_t bad = 0;
-              if ((rc = var_tiles(Dk, CV.bad, &bad))) return rc;
+              if ((rc = var_tiles(Dk, TRC_CUT_ISO, CV.bad, &bad))) return rc;
               if (getenv("TRCHUNK_CUT_DEBUG")) fprintf(stderr, "[trchunk] cut: %lld segments -> %lld, targets without a cut: %lld, tiles %lld\n", (long long)n, (long long)CV.nv, (long long)bad, (long long)ntiles_var);
               if (bad == 0) {
                 cut_done = true;
@@ -1751,7 +1751,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
                 if ((rc = giant_stage(ctx, st, braw, &A.G, TileCand{{0, 0, 0, 0}, 0}, F5_IN_CAP, stats, nullptr))) return rc;
               }
             }
-            if (!cut_done) { if ((rc = var_tiles(D, nullptr, nullptr))) return rc; }
+            if (!cut_done) { if ((rc = var_tiles(D, TRC_GIANT_MIN, nullptr, nullptr))) return rc; }
           }
         }
       }
