@@ -745,8 +745,23 @@ __global__ void k_emit_sent_recs(TrcDev D, TrcSentState S, const int64_t* __rest
       o = tl + 3;
     }
     const uint8_t* src = D.C + off;
-    for (int64_t k = lane; k < len; k += 8) dst[o + k] = src[k];
-    if (!last && lane == 7) dst[o + len] = ' ';
+    uint8_t* db = dst + o;
+    if (!last && lane == 7) db[len] = ' ';
+    if (len < 24) { for (int64_t k = lane; k < len; k += 8) db[k] = src[k]; continue; }
+    // 4-byte words aligned to the destination (two aligned source words + a funnel shift each), as in k_emit_pieces_flat
+    const int head = (int)((4 - ((uintptr_t)db & 3)) & 3);
+    if (lane < head) db[lane] = src[lane];
+    const int64_t nw = (len - head) >> 2;
+    const uint8_t* s0 = src + head;
+    const unsigned sh = (unsigned)((uintptr_t)s0 & 3) * 8u;
+    const uint32_t* sw = reinterpret_cast<const uint32_t*>((uintptr_t)s0 & ~(uintptr_t)3);
+    uint32_t* dw = reinterpret_cast<uint32_t*>(db + head);
+    for (int64_t k = lane; k < nw; k += 8) {
+      const uint32_t a = sw[k], b = sh ? sw[k + 1] : 0u;
+      dw[k] = __funnelshift_r(a, b, sh);
+    }
+    const int64_t done = head + (nw << 2);
+    if (lane < len - done) db[done + lane] = src[done + lane];
   }
 }
 #else

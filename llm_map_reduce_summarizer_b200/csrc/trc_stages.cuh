@@ -81,15 +81,19 @@ TRC_HD void trc_merge_next(const TrcDev& D, int64_t j) {
   int64_t hi = D.kdoc_off[x + 1];
   int64_t k = j + 1;
   if (D.merge && D.kspk) {                   // the same scan on the per-piece copies (contiguous loads, no indirection)
-    const int32_t sp = D.kspk[j];
-    double cur = D.kdur[j];
-    while (k < hi) {
-      if (D.kspk[k] != sp) break;
-      const double d = D.kdur[k];
-      if (D.has_cap && cur + d > D.cap) break;
-      cur += d;
-      ++k;
+    const int32_t* const ps = D.kspk; const double* const pd = D.kdur;
+    const double cap = D.cap; const bool has_cap = D.has_cap != 0;
+    const int32_t sp = ps[j];
+    double cur = pd[j];
+    int32_t kk = (int32_t)k; const int32_t hh = (int32_t)hi;      // (piece indices fit 31 bits: k2r, mnxt are int32)
+    while (kk < hh) {
+      if (ps[kk] != sp) break;
+      const double t = cur + pd[kk];           // the running sum the reference would have after taking this piece
+      if (has_cap && t > cap) break;
+      cur = t;
+      ++kk;
     }
+    k = kk;
   } else if (D.merge) {
     int32_t r = D.k2r[j];
     int32_t sp = D.spk[r];
