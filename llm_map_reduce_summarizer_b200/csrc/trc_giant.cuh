@@ -24,14 +24,14 @@ struct GiantState {
   const int32_t* of_seg;            // per raw segment: giant index or -1 (n entries)
 };
 
-// cnt[0]: warps that saw an oversized segment.  cnt[1 + q]: tiles of cand.v[q] segments whose raw bytes would not fit a
+// cnt[0]: oversized segments.  cnt[1 + q]: tiles of cand.v[q] segments whose raw bytes would not fit a
 // tile of the fused kernel (`cap` bytes from the 16-byte aligned start) - the host picks the tile size from these.
 struct TileCand { int v[4]; int all8; };   // all8: every candidate is a multiple of 8 (only every eighth segment can start a tile)
 __global__ void k_giant_any(TrcDev D, unsigned long long* cnt, TileCand cand, int64_t cap) {
   int found = 0;
   GSTRIDE(i, D.n) {
     const int64_t a = D.seg_off[i];
-    found |= (D.seg_off[i + 1] - a) > TRC_GIANT_MIN;
+    found += (D.seg_off[i + 1] - a) > TRC_GIANT_MIN;
     if (cand.all8 && (i & 7)) continue;
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
@@ -42,7 +42,7 @@ __global__ void k_giant_any(TrcDev D, unsigned long long* cnt, TileCand cand, in
       }
     }
   }
-  if (__any_sync(0xffffffffu, found) && (threadIdx.x & 31) == 0) atomicAdd(cnt, 1ULL);
+  if (found) atomicAdd(cnt, (unsigned long long)found);       // (rare: most batches have none)
 }
 // Tiles of varying size for batches whose segments do not fit tiles of a fixed segment count (oversized segments, heavy
 // tails): a tile is a run of segments that start inside the same window of `win` bytes, at most `max_segs` of them, and an

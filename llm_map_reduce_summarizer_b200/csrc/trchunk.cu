@@ -1345,24 +1345,26 @@ static int giant_stage(trc_ctx* ctx, cudaStream_t st, int64_t braw, GiantView* V
   ALLOC(gflag, int32_t, n); ALLOC(gscan, int64_t, n + 1);
   LAUNCH(k_giant_flag, n, 256, D, gflag);
   if ((rc = scan_excl(ctx, st, gflag, gscan, n))) return rc;
-  int64_t ng = 0;
-  if ((rc = read_back(ctx, st, gscan + n, 8, &ng))) return rc;
-  if (ng == 0) return TRC_OK;
+  const int64_t ng = stats[0];                  // (k_giant_any counted them: no second round trip)
   GiantState G{};
   int32_t* list; int64_t* len; int32_t* of_seg; int64_t* boff;
   ALLOC(list, int32_t, ng); ALLOC(len, int64_t, ng); ALLOC(of_seg, int32_t, n); ALLOC(boff, int64_t, ng + 1);
   LAUNCH(k_giant_list, n, 256, D, gflag, gscan, list, len, of_seg);
   if ((rc = scan_excl(ctx, st, len, boff, ng))) return rc;
-  int64_t gb = 0;
-  if ((rc = read_back(ctx, st, boff + ng, 8, &gb))) return rc;
-  if (gb >= (1LL << 31)) { ctx->err = "more than 2 GiB of oversized segments in one batch"; return TRC_EUNSUPPORTED; }
-  ctx->counts[TRC_N_GIANTS] = ng;
-  if (cut) {                                   // generation 5: parts for the fused kernel instead of the byte-parallel pre-pass
-    int32_t* tcnt; int64_t* tpre; int64_t* cutpos; int64_t nt = 0;
+  int64_t gb = 0, nt = 0;
+  int32_t* tcnt = nullptr; int64_t* tpre = nullptr;
+  if (cut) {                                   // (their bytes and the number of cut targets come back together)
     ALLOC(tcnt, int32_t, ng); ALLOC(tpre, int64_t, ng + 1);
     LAUNCH(k_cut_counts, ng, 128, len, ng, tcnt);
     if ((rc = scan_excl(ctx, st, tcnt, tpre, ng))) return rc;
-    if ((rc = read_back(ctx, st, tpre + ng, 8, &nt))) return rc;
+    int64_t h2[2];
+    if ((rc = read_back2(ctx, st, boff + ng, tpre + ng, h2))) return rc;
+    gb = h2[0]; nt = h2[1];
+  } else if ((rc = read_back(ctx, st, boff + ng, 8, &gb))) return rc;
+  if (gb >= (1LL << 31)) { ctx->err = "more than 2 GiB of oversized segments in one batch"; return TRC_EUNSUPPORTED; }
+  ctx->counts[TRC_N_GIANTS] = ng;
+  if (cut) {                                   // generation 5: parts for the fused kernel instead of the byte-parallel pre-pass
+    int64_t* cutpos;
     if (n + nt < (1LL << 31)) {
       int64_t* vseg_off; int32_t* vorig; uint8_t* vcont;
       ALLOC(cutpos, int64_t, nt); ALLOC(cut->bad, unsigned long long, 1);
