@@ -109,3 +109,38 @@ def test_oversized_segments_cut_and_uncut(monkeypatch):
             assert eng.counts()["n_giants"] >= 6
         finally:
             eng.close()
+
+
+def test_special_token_inside_cut_segment(monkeypatch):
+    """A special-token literal inside an oversized segment: the parts of a cut segment report their first hit with its
+    position, the record keeps the earliest (tiktoken raises for the first literal in the text).  Two documents with the
+    two literals in opposite order, cut and uncut: DOC_ERR = 1 + index of the literal that comes first."""
+    from llm_map_reduce_summarizer_b200 import vocab
+    filler = " ".join(["word", "other", "thing."] * 700)                     # ~13 KB: several parts
+    a, b = vocab.SPECIALS[0], vocab.SPECIALS[1]
+    docs = [[{"start": 0.0, "end": 9.0, "speaker": "A", "text": filler + " " + x + " " + filler + " " + y + " " + filler}]
+            for x, y in ((a, b), (b, a))]
+    docs.append([{"start": 0.0, "end": 9.0, "speaker": "A", "text": filler}])
+    for env in ("1", "0"):
+        monkeypatch.setenv("TRCHUNK_GIANT_CUT", env)
+        eng = E.Engine(0)
+        try:
+            eng.preprocess(E.pack_documents(docs), want_merged_text=False)
+            assert eng.counts()["n_giants"] == 3
+            assert eng.array("DOC_ERR", "<i4").tolist() == [1, 2, 0], env
+        finally:
+            eng.close()
+
+
+def test_cut_segment_through_the_word_cap_fallback(gpu_engine):
+    """Oversized segments of one-letter words: a tile holds more words than the fused kernel's word list, so it counts per
+    segment (continuing parts without the virtual space, added to the record of the part that started the segment), and
+    a 200-letter span inside such a part reaches the long-span kernel by its absolute position."""
+    rng = random.Random(5)
+    one = " ".join(rng.choice("abcdefgh") for _ in range(4000))
+    segs = [{"start": 0.0, "end": 1.0, "speaker": "A", "text": "short one"},
+            {"start": 1.0, "end": 2.0, "speaker": "A", "text": one + " " + "qzx" * 70 + " " + one},
+            {"start": 2.0, "end": 3.0, "speaker": "B", "text": "x " * 3000 + "end"},
+            {"start": 3.0, "end": 4.0, "speaker": "B", "text": "tail segment"}]
+    _run(gpu_engine, segs)
+    assert gpu_engine.counts()["n_giants"] == 2 and gpu_engine.counts()["n_long_spans"] >= 1

@@ -157,3 +157,28 @@ def test_long_spans_batched_merge(gpu_engine):
     dt = time.perf_counter() - t0
     assert int(c1[0]) == len(enc.encode_ordinary(one[0]))
     assert dt < 0.1, dt
+
+
+def test_sentence_counts_over_a_cut_segment(gpu_engine):
+    """An over-budget monologue of 30 KB goes through the sentence stage with token counts taken from the per-word token
+    bytes of the cut-mode fused kernel; a 300-letter span (its count is finished later by the long-span kernel, so its byte
+    says "not known") and sentences of several KB (counted directly) sit in the middle.  Chunks against the oracle."""
+    import parity_common as pc
+    from oracle import chunker as OC, preprocess as OP
+    rng = random.Random(12)
+    words = ["alpha", "beta", "Gamma", "delta", "x", "the", "Mr.", "3.5", "café", "don't", "end"]
+    sents = []
+    for i in range(900):
+        n = rng.randint(3, 14) if i % 97 else 900                       # every 97th sentence is several KB long
+        sents.append(" ".join(rng.choice(words) for _ in range(n)).capitalize() + rng.choice([".", "!", "?"]))
+    sents.insert(400, "Before " + "qzxv" * 75 + " after.")
+    text = " ".join(sents)
+    assert len(text.encode()) > 20000
+    segs = [{"start": 0.0, "end": 30.0, "text": "Intro words here.", "speaker": "B"},
+            {"start": 30.0, "end": 3000.0, "text": text, "speaker": "A"},
+            {"start": 3000.0, "end": 3010.0, "text": "Closing words.", "speaker": "B"}]
+    for mx in (400, 1000):
+        proc, chunks = pc.run_dropin(gpu_engine, segs, mx)
+        want = OC.ChunkerOracle(mx).chunk(OP.preprocess(segs))
+        assert pc.same(chunks, want), mx
+    assert gpu_engine.counts()["n_giants"] == 1 and gpu_engine.counts()["n_sent"] > 800
