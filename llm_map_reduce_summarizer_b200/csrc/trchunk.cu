@@ -939,6 +939,28 @@ __global__ void k_build_items(TrcDev D) {
     }
   }
 }
+#ifndef TRC_HOSTSIM
+// the same with a warp per merged segment (few segments of hundreds of pieces: config 4): the lanes fill pc_item
+__global__ void k_build_items_w(TrcDev D) {
+  const int lane = threadIdx.x & 31;
+  WSTRIDE(g, D.m) {
+    if (lane == 0) trc_build_items(D, g);
+    __syncwarp();
+    const int64_t t0 = D.item_off[g];
+    const int32_t a = D.gstart[g], b = D.gstart[g + 1];
+    if (D.it_sub[t0] < 0) { for (int32_t j = a + lane; j < b; j += 32) D.pc_item[j] = (int32_t)t0; }
+    else {
+      const int32_t cnt = D.nitems_g[g];
+      for (int32_t j = a + lane; j < b; j += 32) D.pc_item[j] = -1;
+      __syncwarp();
+      for (int32_t k = 0; k < cnt; ++k) {
+        const TrcSub& sb = D.subs[D.it_sub[t0 + k]];
+        if (sb.kind == 0) for (int32_t j = sb.r0 + lane; j <= sb.r1; j += 32) D.pc_item[j] = (int32_t)(t0 + k);
+      }
+    }
+  }
+}
+#endif
 __global__ void k_forced_list(TrcDev D, const int32_t* __restrict__ large_flag, const int64_t* __restrict__ large_scan, int64_t* forced_pos) {
   GSTRIDE(g, D.m) if (large_flag[g]) forced_pos[large_scan[g]] = D.item_off[g];
 }
@@ -2152,7 +2174,11 @@ extern "C" int trc_chunk(trc_ctx* ctx, const int32_t* doc_max_tokens, int32_t co
   ALLOC(D.it_group, int32_t, ni); ALLOC(D.it_sub, int32_t, ni); ALLOC(D.it_tok, int32_t, ni); ALLOC(D.it_len, int64_t, ni);
   ALLOC(D.it_forced, uint8_t, ni); ALLOC(D.pc_item, int32_t, nk);
   ALLOC(D.W, int64_t, ni + 1); ALLOC(D.L, int64_t, ni + 1); ALLOC(D.idoc_off, int64_t, nd + 1);
+#ifdef TRC_HOSTSIM
   LAUNCH(k_build_items, m, 128, D);
+#else
+  if (nk >= 64 * m) LAUNCH_W(k_build_items_w, m, D); else LAUNCH(k_build_items, m, 128, D);
+#endif
   if ((rc = scan_excl(ctx, st, D.it_tok, D.W, ni))) return rc;
   if ((rc = scan_excl(ctx, st, D.it_len, D.L, ni, 2))) return rc;
   if (m) LAUNCH(k_map_off, nd + 1, 256, D.gdoc_off, D.item_off, D.idoc_off, nd + 1);
