@@ -787,8 +787,7 @@ __global__ void k_emit_sent_recs(TrcDev D, TrcSentState S) {
 #endif
 
 // ---- host staging -----------------------------------------------------------------------------------------
-static int count_units(trc_ctx* ctx, cudaStream_t st, const uint8_t* bytes, const int64_t* ustart, const int64_t* uend,
-                       int64_t n, int64_t total_bytes, int vs, uint32_t* counts, int32_t* special, bool allow_sync_free, int64_t coop_min);
+// (count_units is defined in trchunk.cu before this file is included)
 
 static int sentence_stage_count(trc_ctx* ctx, cudaStream_t st, int32_t* nsub_g, int32_t nraw) {
   TrcDev& D = ctx->D;

@@ -1297,9 +1297,17 @@ static int to_device(trc_ctx* ctx, cudaStream_t st, const Tp* src, int64_t count
   return TRC_OK;
 }
 
-// Token counts of n units (device pointers).  Long spans are finished by k_bpe_long after one sync.
+// Token counts of n units (device pointers).  Long spans are finished by k_bpe_long after one sync - or, with `defer`, by
+// finish_long() once the caller has read the two counters (defer->ext_cnt, zeroed by the caller) with a round trip of its own.
+struct DeferLong {
+  unsigned long long* ext_cnt = nullptr; bool pending = false;
+  LongEntry* wl = nullptr; int64_t cap = 0; const uint8_t* bytes = nullptr; const int64_t* ustart = nullptr; const int64_t* uend = nullptr;
+  int vs = 0; uint32_t* counts = nullptr;
+};
+static int finish_long(trc_ctx* ctx, cudaStream_t st, DeferLong& dl, unsigned long long h0, unsigned long long h1);
 static int count_units(trc_ctx* ctx, cudaStream_t st, const uint8_t* bytes, const int64_t* ustart, const int64_t* uend,
-                       int64_t n, int64_t total_bytes, int vs, uint32_t* counts, int32_t* special, bool allow_sync_free, int64_t coop_min = 0) {
+                       int64_t n, int64_t total_bytes, int vs, uint32_t* counts, int32_t* special, bool allow_sync_free, int64_t coop_min = 0,
+                       DeferLong* defer = nullptr) {
   if (n <= 0) return TRC_OK;
   if (special) coop_min = 0;                   // (the cooperative counter does not look for special-token literals)
   if (coop_min > 0) { if (const char* e = getenv("TRCHUNK_COOP_MIN")) { const long v = atol(e); if (v > 0) coop_min = v; } }   // experiments
@@ -1310,8 +1318,15 @@ static int count_units(trc_ctx* ctx, cudaStream_t st, const uint8_t* bytes, cons
   const int64_t cap = (total_bytes + (vs ? n : 0)) / (TRC_SHORT_SPAN + 1) + 1;
   LongEntry* wl; unsigned long long* wl_cnt;
   ALLOC(wl, LongEntry, cap);
-  ALLOC(wl_cnt, unsigned long long, 2);
-  CK(cudaMemsetAsync(wl_cnt, 0, 16, st));
+#ifndef TRC_HOSTSIM
+  if (defer && defer->ext_cnt) wl_cnt = defer->ext_cnt;
+  else
+#endif
+  {
+    defer = nullptr;
+    ALLOC(wl_cnt, unsigned long long, 2);
+    CK(cudaMemsetAsync(wl_cnt, 0, 16, st));
+  }
   unsigned long long* coop_cnt = nullptr; int32_t* coop_owner = nullptr; int64_t* coop_base = nullptr;
   const int64_t coop_bound = total_bytes / 32 + n + 1;      // most 32-byte chunks the long units can have
   if (coop_min > 0) {
@@ -1322,6 +1337,11 @@ static int count_units(trc_ctx* ctx, cudaStream_t st, const uint8_t* bytes, cons
 #ifndef TRC_HOSTSIM
   if (coop_min > 0) LAUNCH(k_count_units_coop, coop_bound, 128, ctx->T, ctx->d_byte_id, bytes, ustart, uend, vs, counts, wl, wl_cnt, cap, coop_cnt, coop_owner, coop_base);
 #endif
+  if (defer) {
+    defer->pending = true; defer->wl = wl; defer->cap = cap; defer->bytes = bytes; defer->ustart = ustart; defer->uend = uend;
+    defer->vs = vs; defer->counts = counts;
+    return TRC_OK;
+  }
   unsigned long long h[2];
   int rc = read_back(ctx, st, wl_cnt, 16, h);
   if (rc) return rc;
@@ -1346,21 +1366,43 @@ static int count_units(trc_ctx* ctx, cudaStream_t st, const uint8_t* bytes, cons
   }
   return TRC_OK;
 }
+static int finish_long(trc_ctx* ctx, cudaStream_t st, DeferLong& dl, unsigned long long h0, unsigned long long h1) {
+  dl.pending = false;
+#ifndef TRC_HOSTSIM
+  if ((int64_t)h0 > dl.cap) { ctx->err = "long-span work list overflow"; return TRC_EINVAL; }   // cannot happen: cap is the bound
+  if (h0 > 0) {
+    uint32_t* scratch;
+    ALLOC(scratch, uint32_t, 4 * (int64_t)h1);
+    const int blocks = (int)(h0 < 148 * 8 ? h0 : 148 * 8);
+    prof_begin(ctx, st, "k_bpe_long");
+    k_bpe_long<<<blocks, LONGB_T, 0, st>>>(ctx->T, ctx->d_byte_id, dl.bytes, dl.ustart, dl.uend, dl.vs, dl.counts, dl.wl, (int64_t)h0, scratch, (int64_t)h1);
+    prof_end(ctx, st);
+    ctx->launches++;
+    CK(cudaGetLastError());
+    ctx->counts[TRC_N_LONG_SPANS] += (int64_t)h0;
+  }
+#else
+  (void)ctx; (void)st; (void)h0; (void)h1;
+#endif
+  return TRC_OK;
+}
 
 #include "trc_sent_kernels.cuh"
 
 #ifndef TRC_HOSTSIM
 // Pre-pass for segments larger than a fused tile (trc_giant.cuh).  Leaves *V empty when there are none.
-static int giant_stage(trc_ctx* ctx, cudaStream_t st, int64_t braw, GiantView* V, TileCand cand, int64_t tile_cap, int64_t* stats, CutView* cut) {
+static int giant_stage(trc_ctx* ctx, cudaStream_t st, int64_t braw, GiantView* V, TileCand cand, int64_t tile_cap, int64_t* stats, CutView* cut,
+                       unsigned long long* cblock = nullptr) {
   TrcDev& D = ctx->D;
   const int64_t n = D.n;
   int rc;
   {                                            // most batches have none: one counting pass decides
-    unsigned long long* gcnt;
-    ALLOC(gcnt, unsigned long long, 5);
-    CK(cudaMemsetAsync(gcnt, 0, 40, st));
+    // (cblock: seven words of the caller, [5..6] = the long-span counters of the speaker strings, read in the same round trip)
+    unsigned long long* gcnt = cblock;
+    if (!gcnt) ALLOC(gcnt, unsigned long long, 7);
+    CK(cudaMemsetAsync(gcnt, 0, cblock ? 40 : 56, st));
     LAUNCH(k_giant_any, n, 256, D, gcnt, cand, tile_cap);
-    if ((rc = read_back(ctx, st, gcnt, 40, stats))) return rc;      // [0] oversized segments seen, [1..4] tiles that would not fit, per candidate
+    if ((rc = read_back(ctx, st, gcnt, 56, stats))) return rc;      // [0] oversized segments, [1..4] tiles that would not fit, per candidate
     if (stats[0] == 0) return TRC_OK;
   }
   int32_t* gflag; int64_t* gscan;
@@ -1663,7 +1705,15 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   ALLOC(spk_ub, uint8_t, bspk + B->n_spk); ALLOC(spk_uo, int64_t, B->n_spk + 1);
   ALLOC(spk_tok, uint32_t, B->n_spk); ALLOC(spk_special, int32_t, B->n_spk);
   LAUNCH(k_build_spk_units, (int64_t)B->n_spk, 128, D.spk_bytes, D.spk_off, B->n_spk, spk_ub, spk_uo);
-  if ((rc = count_units(ctx, st, spk_ub, spk_uo, spk_uo + 1, B->n_spk, bspk + B->n_spk, 1, spk_tok, spk_special, false))) return rc;
+  // (the check for long spans in speaker strings waits for the next host round trip: the pre-pass of the fused kernel)
+  DeferLong spk_long;
+  unsigned long long* cblock = nullptr;
+#ifndef TRC_HOSTSIM
+  ALLOC(cblock, unsigned long long, 7);
+  CK(cudaMemsetAsync(cblock, 0, 56, st));
+  spk_long.ext_cnt = cblock + 5;
+#endif
+  if ((rc = count_units(ctx, st, spk_ub, spk_uo, spk_uo + 1, B->n_spk, bspk + B->n_spk, 1, spk_tok, spk_special, false, 0, &spk_long))) return rc;
   D.spk_tok = spk_tok;
 
   int64_t nk = 0, bclean = 0;
@@ -1721,7 +1771,7 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
       int64_t ntiles_var = -1;
       if (gen >= 3) {
         TileCand cand{{0, 0, 0, 0}, 0};
-        int64_t stats[5] = {0, 0, 0, 0, 0};
+        int64_t stats[7] = {0, 0, 0, 0, 0, 0, 0};
         const char* forced = gen >= 5 ? getenv("TRCHUNK_TSEGS") : nullptr;          // experiments: a fixed tile size
         if (forced) { const int v = atoi(forced); if (v >= 1 && v <= F5_SEGS) tsegs4 = v; else forced = nullptr; }
         if (gen >= 5 && !forced) {
@@ -1731,7 +1781,8 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
         const char* cut_env = getenv("TRCHUNK_GIANT_CUT");                           // "0": keep the byte-parallel pre-pass (tests)
         const bool want_cut = gen >= 5 && !forced && !(cut_env && atoi(cut_env) == 0);
         CutView CV{};
-        if ((rc = giant_stage(ctx, st, braw, &A.G, cand, F5_IN_CAP, stats, want_cut ? &CV : nullptr))) return rc;
+        if ((rc = giant_stage(ctx, st, braw, &A.G, cand, F5_IN_CAP, stats, want_cut ? &CV : nullptr, cblock))) return rc;
+        if (spk_long.pending) { if ((rc = finish_long(ctx, st, spk_long, (unsigned long long)stats[5], (unsigned long long)stats[6]))) return rc; }
         if (gen >= 5 && !forced) {
           int pick = -1;
           if (stats[0] == 0) for (int q = 0; q < 4 && pick < 0; ++q) if (stats[1 + q] == 0) pick = q;
@@ -1940,6 +1991,11 @@ extern "C" int trc_preprocess(trc_ctx* ctx, const trc_batch* B, void* stream) {
   // P2: tokens of " " + cleaned text, special-token scan
   ALLOC(D.ctok, uint32_t, nk); ALLOC(seg_special, int32_t, nk);
   if ((rc = count_units(ctx, st, D.C, D.coff, D.coff + 1, nk, bclean, 1, D.ctok, seg_special, true))) return rc;
+  }
+  if (spk_long.pending) {                      // (paths without the fused kernel's pre-pass: a round trip of its own)
+    unsigned long long h[2];
+    if ((rc = read_back(ctx, st, spk_long.ext_cnt, 16, h))) return rc;
+    if ((rc = finish_long(ctx, st, spk_long, h[0], h[1]))) return rc;
   }
   D.kspk = nullptr; D.kdur = nullptr;
   if (D.merge && D.has_cap && !(modeB && B->group_off)) { ALLOC(D.kspk, int32_t, nk); ALLOC(D.kdur, double, nk); }

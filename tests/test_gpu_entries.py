@@ -182,3 +182,17 @@ def test_sentence_counts_over_a_cut_segment(gpu_engine):
         want = OC.ChunkerOracle(mx).chunk(OP.preprocess(segs))
         assert pc.same(chunks, want), mx
     assert gpu_engine.counts()["n_giants"] == 1 and gpu_engine.counts()["n_sent"] > 800
+
+
+def test_long_span_in_a_speaker_name(gpu_engine):
+    """The long-span check of the speaker strings rides on the fused kernel's pre-pass round trip: a 70-letter speaker name
+    (one pre-tokeniser span beyond the thread-local limit) must still be counted by the long-span kernel."""
+    import parity_common as pc
+    from oracle import chunker as OC, preprocess as OP
+    name = "qxzjvkw" * 10
+    segs = [{"start": float(i), "end": float(i + 1), "text": "some words to count here %d" % i, "speaker": name if i % 2 else "B"}
+            for i in range(40)]
+    proc, chunks = pc.run_dropin(gpu_engine, segs, 400)
+    want = OC.ChunkerOracle(400).chunk(OP.preprocess(segs))
+    assert pc.same(chunks, want)
+    assert gpu_engine.counts()["n_long_spans"] >= 1
