@@ -487,19 +487,15 @@ struct SubAcc {
   int64_t tok, text_len; int32_t r0, r1, n; double start, end; int32_t start_src;
 };
 
-// The greedy below is sequential per segment, but a thread that walks 80-byte records one by one waits a memory
-// round trip per record.  On the device a WARP runs it: the lanes load 32 consecutive records at once and hand
-// them around with shuffles while every lane executes the same (uniform) loop; lane 0 does the writes.
-// (`piece`, the byte length of "[ts] text", is worked out here - by every lane for its own record when a warp loads a
-// window - and not inside the sequential loop, where all lanes would format the same timestamp.)
+// The greedy below is sequential per segment; it is the form the test build runs (a thread per segment).  The CUDA build
+// runs the same decisions in sg_warp (further down): a warp per segment, 32 records per load.
 struct SentLite { int64_t len, cl0, piece; double start, end; int32_t tok, ncl; };
 TRC_HD SentLite sent_lite(const TrcSent& R) {
   SentLite o; o.len = R.len; o.cl0 = R.cl0; o.start = R.start; o.end = R.end; o.tok = R.tok; o.ncl = R.ncl;
   o.piece = 1 + trc_ts_len(R.start) + 2 + R.len;
   return o;
 }
-// A record as the greedy sees it: accessors, so that the warp version moves a field between lanes only where the loop
-// reads it (the counting pass reads nothing but the token count: one shuffle per record instead of twelve).
+// A record as the greedy sees it.
 struct SentViewDirect {
   SentLite v;
   TRC_HD int32_t tok() const { return v.tok; }
@@ -513,28 +509,6 @@ struct SentFetchDirect {
   const TrcSent* recs;
   TRC_HD SentViewDirect operator()(int64_t r) { return SentViewDirect{sent_lite(recs[r])}; }
 };
-#ifndef TRC_HOSTSIM
-struct SentViewWarp {
-  const SentLite* mine; int src;
-  __device__ int32_t tok() const { return __shfl_sync(0xffffffffu, mine->tok, src); }
-  __device__ int64_t piece() const { return __shfl_sync(0xffffffffu, mine->piece, src); }
-  __device__ double start() const { return __shfl_sync(0xffffffffu, mine->start, src); }
-  __device__ double end() const { return __shfl_sync(0xffffffffu, mine->end, src); }
-  __device__ int64_t cl0() const { return __shfl_sync(0xffffffffu, mine->cl0, src); }
-  __device__ int32_t ncl() const { return __shfl_sync(0xffffffffu, mine->ncl, src); }
-};
-struct SentFetchWarp {
-  const TrcSent* recs; int64_t hi; int lane; int64_t win0; SentLite mine;
-  __device__ SentViewWarp operator()(int64_t r) {
-    if (r < win0 || r >= win0 + 32) {
-      win0 = r;
-      const int64_t x = r + lane;
-      if (x < hi) mine = sent_lite(recs[x]);
-    }
-    return SentViewWarp{&mine, (int)(r - win0)};
-  }
-};
-#endif
 
 template <bool WRITE>
 TRC_HD void sg_flush(TrcSentState& S, TrcSub* out, int32_t& ns, int32_t g, int32_t kind, SubAcc& a, bool wr) {
