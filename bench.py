@@ -280,6 +280,32 @@ def workload_config(args, b, mt, desc, table):
             "parallelism": "documents sharded by rank, no collective"}
 
 
+def pin_near_gpu(index):
+    """Keep this process (and the threads and pinned buffers it creates from here on) on the host cores next to its GPU:
+    with one rank per GPU on a two-socket box, a rank on the far socket pays the socket link for every pinned copy and
+    every mapped counter read.  A box with one NUMA node lists all cores and nothing changes.  Returns a note for the line."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(index)).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        dom, rest = bus.lower().split(":", 1)
+        path = "/sys/bus/pci/devices/%s:%s/local_cpulist" % (dom[-4:], rest)
+        cpus = set()
+        for part in open(path).read().strip().split(","):
+            if part:
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+        have = os.sched_getaffinity(0)
+        want = cpus & have
+        if want and want != have:
+            os.sched_setaffinity(0, want)
+            return "%d cores next to the GPU (of %d)" % (len(want), len(have))
+        return "unchanged (%d cores, all local)" % len(have)
+    except Exception as e:       # no NVML, no sysfs entry: run where the launcher put us
+        return "unchanged (%s)" % type(e).__name__
+
+
 def table_name():
     from llm_map_reduce_summarizer_b200 import vocab
     return vocab.resolve_table_name()
@@ -403,6 +429,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a B200: the path has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
+    affinity = pin_near_gpu(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     build.build()
@@ -623,6 +650,7 @@ def main():
             line["cpu_baseline"] = cpu
         if extra:
             line["configs"] = extra
+        line["cpu_affinity"] = affinity
         line["counts"].update({"words": counts["n_words"], "words_first_sighting": counts["n_word_first"],
                                "words_generic_matcher": counts["n_word_slow"]})
         print(json.dumps(line))
