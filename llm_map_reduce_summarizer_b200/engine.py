@@ -198,6 +198,7 @@ class Engine:
         """rank_table: optional (name, tokens: list[bytes], ranks: list[int]) instead of the table
         `tokenizer_name` resolves to (any byte-pair table whose ranks are its merge priorities)."""
         self.lib = N.load_library(lib_path)
+        self._lib_path = lib_path
         h = C.c_void_p()
         rc = self.lib.trc_create(int(device), C.byref(h))
         if rc != 0:
@@ -576,6 +577,19 @@ def default_engine(tokenizer_name="cl100k_base"):
     key = (dev, tokenizer_name)
     if key not in _ENGINES:
         _ENGINES[key] = Engine(dev, None, tokenizer_name)
+    return _ENGINES[key]
+
+
+def scratch_engine(tokenizer_name="cl100k_base"):
+    """A second context on the same device for stand-alone helpers (`clean_text`): what they run does not replace the
+    batch that `preprocess_transcript` left resident on the default engine, so a following `chunk_transcript` or
+    `aggregate_by_time_interval` does not have to run stage P again."""
+    dev = int(os.environ.get("TRCHUNK_DEVICE", "0"))
+    key = (dev, tokenizer_name, "scratch")
+    main = default_engine(tokenizer_name)
+    if key not in _ENGINES or getattr(_ENGINES[key], "_lib_path", None) != getattr(main, "_lib_path", None):
+        # (the library of the default engine: the CPU test-suite installs an engine on the g++ test build)
+        _ENGINES[key] = Engine(main.device, getattr(main, "_lib_path", None), tokenizer_name)
     return _ENGINES[key]
 
 

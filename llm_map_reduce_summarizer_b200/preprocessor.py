@@ -61,8 +61,9 @@ def preprocess_transcript(segments: List[Dict[Any, Any]], merge_same_speaker: bo
 
 
 def clean_text(text: str) -> str:
-    """preprocessor.py:69-89 (one segment through the same kernel)."""
-    eng = _eng.default_engine()
+    """preprocessor.py:69-89 (one segment through the same kernel, on a scratch context: the batch that
+    preprocess_transcript left resident on the default engine stays where it is)."""
+    eng = _eng.scratch_engine()
     batch = _eng.pack_documents([[{"start": 0, "end": 0, "text": text, "speaker": ""}]])
     eng.preprocess(batch, merge_same_speaker=False, want_merged_text=False)
     P_clean = eng.array("CLEAN", "u1")

@@ -84,7 +84,8 @@ def test_save_chunks_records_and_timestamps_cuda(gpu_engine, tmp_path):
         serial = gpu_engine.batch_serial
         c = BC.BigChunkeroosky(max_tokens_per_chunk=2000)
         assert [c._format_time(x) for x in (0, 59.999, 3600, -1, 360000)] == ["00:00", "00:59", "01:00:00", "59:59", "100:00:00"]
-        assert gpu_engine.batch_serial == serial                      # the helper did not evict the batch
+        assert PP.clean_text("  so  so it   is.Then ") == "so it is. Then"
+        assert gpu_engine.batch_serial == serial                      # the helpers did not evict the batch
         chunks = c.postprocess_chunks(c.chunk_transcript(proc))
     want = OC.ChunkerOracle(2000).chunk(OP.preprocess(segs))
     a, b = tmp_path / "a.json", tmp_path / "b.json"
